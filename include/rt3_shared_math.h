@@ -1,0 +1,710 @@
+/*
+ * rt3_shared_math.h — the reference's Slang shader math restated as plain C++ that compiles both
+ * as host code (g++, used by oracle/) and as device code (nvcc, used by the CUDA kernels).
+ *
+ * Determinism contract.  Every function below uses only IEEE-754 binary32 operations that are
+ * correctly rounded on x86-64 and on sm_100a ( + - * / sqrt fma, int<->float conversion ) in a
+ * fixed order.  Transcendentals (sin, cos, atan2, asin, exp2, log2) are replaced by fixed
+ * polynomial kernels built from those operations.  Build flags that make this hold:
+ *     nvcc:  -fmad=false   (no implicit contraction; explicit fmaf() still maps to FFMA)
+ *            default -prec-div=true -prec-sqrt=true -ftz=false, never --use_fast_math
+ *     g++ :  -ffp-contract=off -mfma  (fmaf inlines to vfmadd), never -ffast-math
+ * Under that contract the CPU oracle and the GPU kernels produce BIT-IDENTICAL results for every
+ * function in this file; rt3m::contract_probe() is a runtime check of the flags.
+ *
+ * Each function cites the reference file:line it follows (paths under /root/reference).
+ */
+#ifndef RT3_SHARED_MATH_H
+#define RT3_SHARED_MATH_H
+
+#include <stdint.h>
+#include <string.h>
+#include <math.h>
+#include "rt3.h"
+
+#if defined(__FAST_MATH__)
+#error "rt3_shared_math.h must not be compiled with -ffast-math"
+#endif
+
+#ifdef __CUDACC__
+#define RT3_HD __host__ __device__ __forceinline__
+#else
+#define RT3_HD inline
+#endif
+
+namespace rt3m {
+
+/* ---------------------------------------------------------------- scalar helpers ------------- */
+RT3_HD float as_float(uint32_t u) {
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+RT3_HD uint32_t as_uint(float f) {
+#ifdef __CUDA_ARCH__
+    return __float_as_uint(f);
+#else
+    uint32_t u; memcpy(&u, &f, 4); return u;
+#endif
+}
+RT3_HD float fma_(float a, float b, float c) {
+#ifdef __CUDA_ARCH__
+    return __fmaf_rn(a, b, c);
+#else
+    return __builtin_fmaf(a, b, c);
+#endif
+}
+RT3_HD float sqrt_(float a) {
+#ifdef __CUDA_ARCH__
+    return __fsqrt_rn(a);
+#else
+    return __builtin_sqrtf(a);
+#endif
+}
+RT3_HD float min_(float a, float b) { return a < b ? a : b; }
+RT3_HD float max_(float a, float b) { return a > b ? a : b; }
+RT3_HD float clamp_(float v, float lo, float hi) { return min_(max_(v, lo), hi); }
+RT3_HD float floor_(float a) {
+#ifdef __CUDA_ARCH__
+    return floorf(a);
+#else
+    return __builtin_floorf(a);
+#endif
+}
+RT3_HD float abs_(float a) { return as_float(as_uint(a) & 0x7FFFFFFFu); }
+/* a*b+c evaluated with two roundings; used to detect accidental contraction. */
+RT3_HD float contract_probe(float a, float b, float c) { return a * b + c; }
+
+/* ---------------------------------------------------------------- vectors -------------------- */
+struct vec2 { float x, y; };
+struct vec3 { float x, y, z; };
+struct vec4 { float x, y, z, w; };
+
+RT3_HD vec3 v3(float x, float y, float z) { vec3 r; r.x = x; r.y = y; r.z = z; return r; }
+RT3_HD vec3 v3(const float* p) { return v3(p[0], p[1], p[2]); }
+RT3_HD vec3 operator+(vec3 a, vec3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+RT3_HD vec3 operator-(vec3 a, vec3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+RT3_HD vec3 operator*(vec3 a, vec3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+RT3_HD vec3 operator*(vec3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+RT3_HD float dot(vec3 a, vec3 b) { return fma_(a.z, b.z, fma_(a.y, b.y, a.x * b.x)); }
+RT3_HD vec3 cross(vec3 a, vec3 b) {
+    return v3(fma_(a.y, b.z, -(a.z * b.y)), fma_(a.z, b.x, -(a.x * b.z)), fma_(a.x, b.y, -(a.y * b.x)));
+}
+/* Slang normalize(v) = v * rsqrt(dot(v,v)); restated with a correctly rounded 1/sqrt. */
+RT3_HD vec3 normalize(vec3 a) { float s = 1.0f / sqrt_(dot(a, a)); return a * s; }
+/* a + t*d */
+RT3_HD vec3 madd(vec3 a, float t, vec3 d) { return v3(fma_(t, d.x, a.x), fma_(t, d.y, a.y), fma_(t, d.z, a.z)); }
+
+/* column-major 4x4 (glam::Mat4, `column_major float4x4`) times (x,y,z,w): HLSL mul(M, v). */
+RT3_HD vec4 mat4_mul(const float* m, float x, float y, float z, float w) {
+    vec4 r;
+    r.x = fma_(m[12], w, fma_(m[8], z, fma_(m[4], y, m[0] * x)));
+    r.y = fma_(m[13], w, fma_(m[9], z, fma_(m[5], y, m[1] * x)));
+    r.z = fma_(m[14], w, fma_(m[10], z, fma_(m[6], y, m[2] * x)));
+    r.w = fma_(m[15], w, fma_(m[11], z, fma_(m[7], y, m[3] * x)));
+    return r;
+}
+/* row-major 3x4 affine transform of a point / of a direction (w = 0). */
+RT3_HD vec3 xform_point(const float* m, vec3 p) {
+    return v3(fma_(m[2], p.z, fma_(m[1], p.y, fma_(m[0], p.x, m[3]))),
+              fma_(m[6], p.z, fma_(m[5], p.y, fma_(m[4], p.x, m[7]))),
+              fma_(m[10], p.z, fma_(m[9], p.y, fma_(m[8], p.x, m[11]))));
+}
+RT3_HD vec3 xform_dir(const float* m, vec3 d) {
+    return v3(fma_(m[2], d.z, fma_(m[1], d.y, m[0] * d.x)),
+              fma_(m[6], d.z, fma_(m[5], d.y, m[4] * d.x)),
+              fma_(m[10], d.z, fma_(m[9], d.y, m[8] * d.x)));
+}
+RT3_HD bool xform_is_identity(const float* m) {
+    return m[0] == 1.f && m[1] == 0.f && m[2] == 0.f && m[3] == 0.f && m[4] == 0.f && m[5] == 1.f && m[6] == 0.f &&
+           m[7] == 0.f && m[8] == 0.f && m[9] == 0.f && m[10] == 1.f && m[11] == 0.f;
+}
+
+/* ---------------------------------------------------------------- RNG ------------------------ */
+/* shaders/include/random.slang:5-15 (Bob Jenkins' integer hash). */
+RT3_HD uint32_t hash_jenkins(uint32_t a) {
+    a = (a + 0x7ed55d16u) + (a << 12);
+    a = (a ^ 0xc761c23cu) ^ (a >> 19);
+    a = (a + 0x165667b1u) + (a << 5);
+    a = (a + 0xd3a2646cu) ^ (a << 9);
+    a = (a + 0xfd7046c5u) + (a << 3);
+    a = (a ^ 0xb55a4f09u) ^ (a >> 16);
+    return a;
+}
+/* shaders/include/math.slang:105-112 */
+RT3_HD uint32_t integer_explode(uint32_t x) {
+    x = (x | (x << 8)) & 0x00FF00FFu;
+    x = (x | (x << 4)) & 0x0F0F0F0Fu;
+    x = (x | (x << 2)) & 0x33333333u;
+    x = (x | (x << 1)) & 0x55555555u;
+    return x;
+}
+/* shaders/include/math.slang:114-117 */
+RT3_HD uint32_t zcurve_to_linear_index(uint32_t x, uint32_t y) { return integer_explode(x) | (integer_explode(y) << 1); }
+
+/* shaders/include/random.slang:18-24 */
+RT3_HD float radical_inverse_vdc(uint32_t bits) {
+    bits = (bits << 16) | (bits >> 16);
+    bits = ((bits & 0x55555555u) << 1) | ((bits & 0xAAAAAAAAu) >> 1);
+    bits = ((bits & 0x33333333u) << 2) | ((bits & 0xCCCCCCCCu) >> 2);
+    bits = ((bits & 0x0F0F0F0Fu) << 4) | ((bits & 0xF0F0F0F0u) >> 4);
+    bits = ((bits & 0x00FF00FFu) << 8) | ((bits & 0xFF00FF00u) >> 8);
+    return float(bits) * 2.3283064365386963e-10f;
+}
+RT3_HD float frac_(float x) { return x - floor_(x); }
+/* shaders/include/random.slang:30-35 (R2 / plastic-number sequence). */
+RT3_HD vec2 r2_sequence(uint32_t i) {
+    const float a1 = (float)(1.0 / 1.32471795724474602596);
+    const float a2 = (float)(1.0 / (1.32471795724474602596 * 1.32471795724474602596));
+    vec2 r;
+    r.x = frac_(a1 * float(i) + 0.5f);
+    r.y = frac_(a2 * float(i) + 0.5f);
+    return r;
+}
+
+/* The same sequence evaluated in 0.32 fixed point (exact for every i): frac(a*i + 0.5) with
+ * a1 = 0xC13FA9A9 / 2^32, a2 = 0x91E10DA5 / 2^32, reduced to 24 bits.  Used by the blue-noise sampler,
+ * where the float form above loses its fraction bits as i grows. */
+RT3_HD vec2 r2_sequence_fixed(uint32_t i) {
+    vec2 r;
+    r.x = float((i * 0xC13FA9A9u + 0x80000000u) >> 8) * 5.9604644775390625e-08f;
+    r.y = float((i * 0x91E10DA5u + 0x80000000u) >> 8) * 5.9604644775390625e-08f;
+    return r;
+}
+
+/* shaders/include/random.slang:37-90 */
+struct RandomSamplerState {
+    uint32_t seed, index;
+};
+RT3_HD RandomSamplerState rng_init(uint32_t px, uint32_t py, uint32_t frame_index) {
+    RandomSamplerState s;
+    s.index = 0;
+    s.seed = hash_jenkins(zcurve_to_linear_index(px, py)) + frame_index;
+    return s;
+}
+RT3_HD uint32_t rotl32(uint32_t x, uint32_t r) { return (x << r) | (x >> (32 - r)); }
+RT3_HD uint32_t murmur3_at(uint32_t seed, uint32_t index) {
+    uint32_t k = index;
+    k *= 0xcc9e2d51u;
+    k = rotl32(k, 15);
+    k *= 0x1b873593u;
+    uint32_t h = seed ^ k;
+    h = rotl32(h, 13) * 5u + 0xe6546b64u;
+    h ^= 4u;
+    h ^= h >> 16;
+    h *= 0x85ebca6bu;
+    h ^= h >> 13;
+    h *= 0xc2b2ae35u;
+    h ^= h >> 16;
+    return h;
+}
+RT3_HD uint32_t rng_murmur3(RandomSamplerState& s) { return murmur3_at(s.seed, s.index++); }
+RT3_HD float u32_to_unit_float(uint32_t v) { return as_float((v & 0x007FFFFFu) | 0x3F800000u) - 1.0f; }
+RT3_HD float rng_uniform_float(RandomSamplerState& s) { return u32_to_unit_float(rng_murmur3(s)); }
+
+/* ---------------------------------------------------------------- deterministic trig --------- */
+/* sin and cos of 2*pi*u for u in [0,1): exact quadrant reduction (x4 is exact, x - round(x) is
+ * exact), then the Cephes sinf/cosf minimax kernels on [-pi/4, pi/4].  Replaces sin(phi)/cos(phi)
+ * with phi = u*TAU (shaders/include/brdf.slang:57-62); differs from a correctly rounded sin(phi)
+ * by a few 1e-7, i.e. by less than the rounding of phi itself. */
+RT3_HD void sincos_2pi(float u, float& s, float& c) {
+    float x = u * 4.0f;
+    int q = (int)(x + 0.5f);
+    float r = x - (float)q;
+    float a = r * 1.57079632679489661923f;
+    float a2 = a * a;
+    float sp = fma_(fma_(fma_(-1.9515295891e-4f, a2, 8.3321608736e-3f), a2, -1.6666654611e-1f), a2 * a, a);
+    float cp = fma_(fma_(fma_(2.443315711809948e-5f, a2, -1.388731625493765e-3f), a2, 4.166664568298827e-2f), a2 * a2,
+                    fma_(-0.5f, a2, 1.0f));
+    switch (q & 3) {
+        case 0: s = sp; c = cp; break;
+        case 1: s = cp; c = -sp; break;
+        case 2: s = -sp; c = -cp; break;
+        default: s = -cp; c = sp; break;
+    }
+}
+/* atan(x) for x in [0,1]: odd minimax polynomial (max error ~1e-6 rad). */
+RT3_HD float atan01(float x) {
+    float x2 = x * x;
+    float p = fma_(fma_(fma_(fma_(fma_(-0.0117212f, x2, 0.05265332f), x2, -0.11643287f), x2, 0.19354346f), x2, -0.33262347f), x2,
+                   0.99997726f);
+    return p * x;
+}
+RT3_HD float atan2_(float y, float x) {
+    float ax = abs_(x), ay = abs_(y);
+    float mx = max_(ax, ay), mn = min_(ax, ay);
+    float a = (mx == 0.0f) ? 0.0f : atan01(mn / mx);
+    if (ay > ax) a = 1.57079632679489661923f - a;
+    if (x < 0.0f) a = 3.14159265358979323846f - a;
+    return (y < 0.0f) ? -a : a;
+}
+RT3_HD float asin_(float y) {
+    float yc = clamp_(y, -1.0f, 1.0f);
+    return atan2_(yc, sqrt_(max_(0.0f, fma_(-yc, yc, 1.0f))));
+}
+/* 2^e for integer e in [-126,127], exact. */
+RT3_HD float exp2i(int e) { return as_float((uint32_t)(e + 127) << 23); }
+/* log2(x), x > 0 normal: exponent + ln(m) by the atanh series in s = (m-1)/(m+1), |s| <= 0.1716
+ * (truncation error < 4e-10), then scaled by 1/ln 2. */
+RT3_HD float log2_(float x) {
+    uint32_t b = as_uint(x);
+    int e = (int)((b >> 23) & 0xFF) - 127;
+    float m = as_float((b & 0x007FFFFFu) | 0x3F800000u); /* [1,2) */
+    if (m > 1.41421356f) { m = m * 0.5f; e += 1; }
+    float s = (m - 1.0f) / (m + 1.0f);
+    float s2 = s * s;
+    float p = fma_(fma_(fma_(fma_(0.11111111111f, s2, 0.14285714286f), s2, 0.2f), s2, 0.33333333333f), s2, 1.0f);
+    float ln = 2.0f * s * p;
+    return fma_(ln, 1.44269504088896340736f, (float)e);
+}
+/* 2^x for x in [-126, 126]: integer / fraction split, degree-7 Taylor polynomial of 2^f on [-0.5,0.5]
+ * (truncation error < 2e-9 relative). */
+RT3_HD float exp2_(float x) {
+    float xc = clamp_(x, -126.0f, 126.0f);
+    float fl = floor_(xc + 0.5f);
+    float f = xc - fl;
+    float p = fma_(fma_(fma_(fma_(fma_(fma_(1.52527338e-5f, f, 1.54035304e-4f), f, 1.33335581e-3f), f, 9.61812911e-3f), f,
+                             5.55041087e-2f), f, 2.40226507e-1f), f, 6.93147181e-1f);
+    p = fma_(p, f, 1.0f);
+    return p * exp2i((int)fl);
+}
+RT3_HD float pow_(float x, float y) { return (x <= 0.0f) ? 0.0f : exp2_(y * log2_(x)); }
+
+/* ---------------------------------------------------------------- math.slang ----------------- */
+/* shaders/include/math.slang:6-12 */
+RT3_HD vec2 direction_to_equirect_uv(vec3 d) {
+    vec2 r;
+    r.x = 0.5f + atan2_(d.z, d.x) * 0.15915494309189533577f;
+    r.y = 0.5f - asin_(d.y) * 0.31830988618379067154f;
+    return r;
+}
+/* shaders/include/math.slang:29-50 (Duff et al. 2017); columns (b1, b2, n). */
+struct onb { vec3 b1, b2, n; };
+RT3_HD onb build_orthonormal_basis(vec3 n) {
+    onb r;
+    if (n.z < 0.0f) {
+        const float a = 1.0f / (1.0f - n.z);
+        const float b = n.x * n.y * a;
+        r.b1 = v3(1.0f - n.x * n.x * a, -b, n.x);
+        r.b2 = v3(b, n.y * n.y * a - 1.0f, -n.y);
+    } else {
+        const float a = 1.0f / (1.0f + n.z);
+        const float b = -n.x * n.y * a;
+        r.b1 = v3(1.0f - n.x * n.x * a, b, -n.x);
+        r.b2 = v3(b, 1.0f - n.y * n.y * a, -n.y);
+    }
+    r.n = n;
+    return r;
+}
+/* mul(tangent_to_world, wi) with the float3x3 of math.slang:45-49: row i = (b1[i], b2[i], n[i]). */
+RT3_HD vec3 onb_to_world(const onb& t, vec3 wi) {
+    return v3(fma_(t.n.x, wi.z, fma_(t.b2.x, wi.y, t.b1.x * wi.x)), fma_(t.n.y, wi.z, fma_(t.b2.y, wi.y, t.b1.y * wi.x)),
+              fma_(t.n.z, wi.z, fma_(t.b2.z, wi.y, t.b1.z * wi.x)));
+}
+/* shaders/include/math.slang:120-123 */
+RT3_HD float luminance(vec3 c) { return fma_(c.z, 0.114f, fma_(c.y, 0.587f, c.x * 0.299f)); }
+
+/* shaders/include/brdf.slang:56-73 — DiffuseBrdf::sample: wi in tangent space; value_over_pdf = albedo. */
+RT3_HD vec3 diffuse_sample_wi(float ux, float uy) {
+    float cos_theta = sqrt_(max_(0.0f, 1.0f - uy));
+    float sin_theta = sqrt_(max_(0.0f, 1.0f - cos_theta * cos_theta));
+    float sp, cp;
+    sincos_2pi(ux, sp, cp);
+    return v3(cp * sin_theta, sp * sin_theta, cos_theta);
+}
+
+/* ---------------------------------------------------------------- packing.slang -------------- */
+/* shaders/include/packing.slang:2-10 */
+RT3_HD float unpack_unorm(uint32_t pckd, uint32_t bits) {
+    uint32_t maxv = (1u << bits) - 1u;
+    return float(pckd & maxv) / float(maxv);
+}
+RT3_HD uint32_t pack_unorm(float val, uint32_t bits) {
+    uint32_t maxv = (1u << bits) - 1u;
+    return (uint32_t)(clamp_(val, 0.0f, 1.0f) * float(maxv) + 0.5f);
+}
+/* shaders/include/packing.slang:12-27 */
+RT3_HD uint32_t pack_normal_11_10_11(vec3 n) {
+    uint32_t p = 0;
+    p += pack_unorm(n.x * 0.5f + 0.5f, 11);
+    p += pack_unorm(n.y * 0.5f + 0.5f, 10) << 11;
+    p += pack_unorm(n.z * 0.5f + 0.5f, 11) << 21;
+    return p;
+}
+RT3_HD vec3 unpack_normal_11_10_11(uint32_t p) {
+    vec3 v = v3(unpack_unorm(p, 11) * 2.0f - 1.0f, unpack_unorm(p >> 11, 10) * 2.0f - 1.0f, unpack_unorm(p >> 21, 11) * 2.0f - 1.0f);
+    return normalize(v);
+}
+/* shaders/include/packing.slang:46-62 */
+RT3_HD uint32_t pack_color_888(vec3 c) {
+    uint32_t p = 0;
+    p += pack_unorm(sqrt_(c.x), 8);
+    p += pack_unorm(sqrt_(c.y), 8) << 8;
+    p += pack_unorm(sqrt_(c.z), 8) << 16;
+    return p;
+}
+RT3_HD vec3 unpack_color_888(uint32_t p) {
+    vec3 c = v3(unpack_unorm(p, 8), unpack_unorm(p >> 8, 8), unpack_unorm(p >> 16, 8));
+    return c * c;
+}
+/* f32tof16 / f16tof32 (packing.slang:88-97 uses the HLSL intrinsics): software IEEE round-to-nearest-even. */
+RT3_HD uint32_t f32_to_f16(float f) {
+    uint32_t x = as_uint(f);
+    uint32_t sign = (x >> 16) & 0x8000u;
+    uint32_t absx = x & 0x7FFFFFFFu;
+    if (absx >= 0x7F800000u) return sign | (absx > 0x7F800000u ? 0x7E00u : 0x7C00u);
+    if (absx >= 0x477FF000u) return sign | 0x7C00u; /* rounds to >= 65520 -> inf */
+    if (absx < 0x33000001u) return sign;            /* <= 2^-25 -> 0 */
+    int e = (int)(absx >> 23) - 127;
+    uint32_t m = (absx & 0x007FFFFFu) | 0x00800000u;
+    if (e < -14) { /* subnormal half */
+        int shift = (-14 - e) + 13;
+        uint32_t q = m >> shift;
+        uint32_t rem = m & ((1u << shift) - 1u);
+        uint32_t half = 1u << (shift - 1);
+        if (rem > half || (rem == half && (q & 1u))) q++;
+        return sign | q;
+    }
+    uint32_t q = ((uint32_t)(e + 15) << 10) | ((m >> 13) & 0x3FFu);
+    uint32_t rem = m & 0x1FFFu;
+    if (rem > 0x1000u || (rem == 0x1000u && (q & 1u))) q++;
+    return sign | q;
+}
+RT3_HD float f16_to_f32(uint32_t h) {
+    uint32_t sign = (h & 0x8000u) << 16;
+    uint32_t e = (h >> 10) & 0x1Fu;
+    uint32_t m = h & 0x3FFu;
+    if (e == 0) {
+        if (m == 0) return as_float(sign);
+        float v = float(m) * 5.9604644775390625e-08f; /* 2^-24 */
+        return as_float(as_uint(v) | sign);
+    }
+    if (e == 31) return as_float(sign | 0x7F800000u | (m << 13));
+    return as_float(sign | ((e + 112u) << 23) | (m << 13));
+}
+RT3_HD uint32_t pack_2x16f_uint(float a, float b) { return f32_to_f16(a) | (f32_to_f16(b) << 16); }
+
+/* shaders/include/packing.slang:99-162 (EXT_texture_shared_exponent). */
+RT3_HD int floor_log2(float x) { return (int)((as_uint(x) & 0x7F800000u) >> 23) - 127; }
+RT3_HD uint32_t float3_to_rgb9e5(vec3 rgb) {
+    const float MAX_RGB9E5 = (511.0f / 512.0f) * 65536.0f;
+    float rc = clamp_(rgb.x, 0.0f, MAX_RGB9E5);
+    float gc = clamp_(rgb.y, 0.0f, MAX_RGB9E5);
+    float bc = clamp_(rgb.z, 0.0f, MAX_RGB9E5);
+    float maxrgb = max_(rc, max_(gc, bc));
+    int fl = floor_log2(maxrgb);
+    int exp_shared = (fl > -16 ? fl : -16) + 1 + 15;
+    float denom = exp2i(exp_shared - 15 - 9);
+    int maxm = (int)floor_(maxrgb / denom + 0.5f);
+    if (maxm == 512) { denom *= 2.0f; exp_shared += 1; }
+    int rm = (int)floor_(rc / denom + 0.5f);
+    int gm = (int)floor_(gc / denom + 0.5f);
+    int bm = (int)floor_(bc / denom + 0.5f);
+    return ((uint32_t)rm << 23) | ((uint32_t)gm << 14) | ((uint32_t)bm << 5) | (uint32_t)exp_shared;
+}
+RT3_HD vec3 rgb9e5_to_float3(uint32_t v) {
+    int exponent = (int)(v & 31u) - 15 - 9;
+    float scale = exp2i(exponent);
+    return v3(float((v >> 23) & 511u) * scale, float((v >> 14) & 511u) * scale, float((v >> 5) & 511u) * scale);
+}
+
+/* ---------------------------------------------------------------- gbuffer_helpers.slang ------ */
+struct GbufferData {
+    vec3 albedo, emissive, normal;
+    float roughness, metalness;
+};
+struct uint4_ { uint32_t x, y, z, w; };
+/* shaders/include/gbuffer_helpers.slang:22-34 */
+RT3_HD uint4_ gbuffer_pack(const GbufferData& g) {
+    uint4_ r;
+    r.x = pack_color_888(g.albedo);
+    r.y = pack_normal_11_10_11(g.normal);
+    r.z = pack_2x16f_uint(sqrt_(g.roughness), g.metalness);
+    r.w = float3_to_rgb9e5(g.emissive);
+    return r;
+}
+/* shaders/include/gbuffer_helpers.slang:59-70 */
+RT3_HD GbufferData gbuffer_unpack(uint4_ d) {
+    GbufferData r;
+    r.albedo = unpack_color_888(d.x);
+    r.normal = unpack_normal_11_10_11(d.y);
+    float pr = f16_to_f32(d.z & 0xFFFFu);
+    r.roughness = pr * pr;
+    r.metalness = f16_to_f32((d.z >> 16) & 0xFFFFu);
+    r.emissive = rgb9e5_to_float3(d.w);
+    return r;
+}
+
+/* shaders/include/gbuffer_helpers.slang:85-103 with PlanarViewConstants mapped onto GConst:
+ * matClipToView = proj_inverse, matViewToWorld = view_inverse, viewportSize = window_size,
+ * cameraDirectionOrPosition = translation column of view_inverse. */
+RT3_HD vec3 view_dir(uint32_t px, uint32_t py, const rt3_params& p) {
+    float ux = (float(px) + 0.5f) / p.window_size[0];
+    float uy = (float(py) + 0.5f) / p.window_size[1];
+    float dx = ux * 2.0f - 1.0f, dy = uy * 2.0f - 1.0f;
+    vec4 target = mat4_mul(p.proj_inv, dx, dy, 1.0f, 1.0f);
+    vec3 nt = normalize(v3(target.x, target.y, target.z));
+    vec4 d = mat4_mul(p.view_inv, nt.x, nt.y, nt.z, 0.0f);
+    return v3(d.x, d.y, d.z);
+}
+RT3_HD vec3 camera_position(const rt3_params& p) { return v3(p.view_inv[12], p.view_inv[13], p.view_inv[14]); }
+RT3_HD rt3_ray setup_primary_ray(uint32_t px, uint32_t py, const rt3_params& p) {
+    rt3_ray r;
+    vec3 o = camera_position(p), d = view_dir(px, py, p);
+    r.o[0] = o.x; r.o[1] = o.y; r.o[2] = o.z;
+    r.d[0] = d.x; r.d[1] = d.y; r.d[2] = d.z;
+    r.tmin = 0.0f;
+    r.tmax = RT3_BACKGROUND_DEPTH;
+    return r;
+}
+
+/* ---------------------------------------------------------------- ray / triangle -------------- */
+/* The reference delegates this to the Vulkan driver (TraceRay; src/renderer/pipeline_cache/mod.rs:64-73),
+ * so the arithmetic is DEFINED here: Moeller-Trumbore on (v0, e1 = v1-v0, e2 = v2-v0), no culling,
+ * barycentrics (u,v) weight v1 and v2 (BuiltInTriangleIntersectionAttributes), hit iff
+ * u >= 0, v >= 0, u+v <= 1 and tmin < t < tmax.  Closest hit = smallest t; equal t resolves to the
+ * smaller global triangle id (a traversal-order-independent rule). */
+RT3_HD bool ray_triangle(vec3 o, vec3 d, vec3 v0, vec3 e1, vec3 e2, float& t, float& u, float& v) {
+    vec3 pvec = cross(d, e2);
+    float det = dot(e1, pvec);
+    if (det == 0.0f) return false;
+    float inv = 1.0f / det;
+    vec3 tvec = o - v0;
+    u = dot(tvec, pvec) * inv;
+    vec3 qvec = cross(tvec, e1);
+    v = dot(d, qvec) * inv;
+    t = dot(e2, qvec) * inv;
+    return (u >= 0.0f) & (v >= 0.0f) & (u + v <= 1.0f);
+}
+RT3_HD bool closer_hit(float t, uint32_t prim, float best_t, uint32_t best_prim) {
+    return t < best_t || (t == best_t && prim < best_prim);
+}
+
+/* ---------------------------------------------------------------- scene views ---------------- */
+struct SceneView {
+    const rt3_vertex* vertices;
+    const uint32_t* indices;
+    const rt3_geometry_info* geometries;
+    /* segment table: one entry per (instance, geometry) in flattening order */
+    const uint32_t* seg_first_prim; /* n_segments + 1 (prefix of triangle counts) */
+    const uint32_t* seg_geometry;   /* n_segments */
+    const uint32_t* seg_instance;   /* n_segments */
+    const float* inst_xform;        /* n_instances x 12 (row-major 3x4) */
+    uint32_t n_segments;
+    /* textures: slot table */
+    const uint8_t* const* tex_data; /* RGBA8 */
+    const uint32_t* tex_dim;        /* 2 per slot */
+    uint32_t n_textures;
+    const float* srgb_lut;          /* 256 floats: sRGB byte -> linear */
+    /* environment */
+    const float* env; uint32_t env_w, env_h;
+    /* blue noise */
+    const uint8_t* bn; uint32_t bn_w, bn_h;
+};
+
+RT3_HD uint32_t find_segment(const SceneView& s, uint32_t prim) {
+    uint32_t lo = 0, hi = s.n_segments; /* seg_first_prim[lo] <= prim < seg_first_prim[hi] */
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (s.seg_first_prim[mid] <= prim) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+/* World-space triangle of (segment, primitive): geometry transform then instance transform. */
+RT3_HD void world_triangle(const SceneView& s, uint32_t seg, uint32_t prim_in_geo, vec3& a, vec3& b, vec3& c) {
+    const rt3_geometry_info& g = s.geometries[s.seg_geometry[seg]];
+    uint32_t io = g.index_offset + 3u * prim_in_geo;
+    uint32_t i0 = g.vertex_offset + s.indices[io], i1 = g.vertex_offset + s.indices[io + 1], i2 = g.vertex_offset + s.indices[io + 2];
+    a = v3(s.vertices[i0].p); b = v3(s.vertices[i1].p); c = v3(s.vertices[i2].p);
+    if (!xform_is_identity(g.xform)) { a = xform_point(g.xform, a); b = xform_point(g.xform, b); c = xform_point(g.xform, c); }
+    const float* ix = s.inst_xform + 12u * s.seg_instance[seg];
+    if (!xform_is_identity(ix)) { a = xform_point(ix, a); b = xform_point(ix, b); c = xform_point(ix, c); }
+}
+
+/* Textures[i].SampleLevel(uv, 0) as DEFINED for the missing bindless_descriptor.slang: RGBA8 sRGB,
+ * bilinear, repeat addressing, texel centres at (i + 0.5) / size. */
+RT3_HD vec3 sample_texture(const SceneView& s, int slot, float u, float v) {
+    if (slot < 0 || (uint32_t)slot >= s.n_textures || s.tex_data[slot] == nullptr) return v3(1.f, 1.f, 1.f);
+    uint32_t w = s.tex_dim[2 * slot], h = s.tex_dim[2 * slot + 1];
+    const uint8_t* t = s.tex_data[slot];
+    float fx = frac_(u) * float(w) - 0.5f, fy = frac_(v) * float(h) - 0.5f;
+    float flx = floor_(fx), fly = floor_(fy);
+    float ax = fx - flx, ay = fy - fly;
+    int x0 = (int)flx, y0 = (int)fly;
+    int x1 = x0 + 1, y1 = y0 + 1;
+    x0 = (x0 % (int)w + (int)w) % (int)w; x1 = (x1 % (int)w + (int)w) % (int)w;
+    y0 = (y0 % (int)h + (int)h) % (int)h; y1 = (y1 % (int)h + (int)h) % (int)h;
+    const uint8_t* p00 = t + 4u * ((uint32_t)y0 * w + (uint32_t)x0);
+    const uint8_t* p10 = t + 4u * ((uint32_t)y0 * w + (uint32_t)x1);
+    const uint8_t* p01 = t + 4u * ((uint32_t)y1 * w + (uint32_t)x0);
+    const uint8_t* p11 = t + 4u * ((uint32_t)y1 * w + (uint32_t)x1);
+    float w00 = (1.0f - ax) * (1.0f - ay), w10 = ax * (1.0f - ay), w01 = (1.0f - ax) * ay, w11 = ax * ay;
+    vec3 r;
+    r.x = fma_(s.srgb_lut[p11[0]], w11, fma_(s.srgb_lut[p01[0]], w01, fma_(s.srgb_lut[p10[0]], w10, s.srgb_lut[p00[0]] * w00)));
+    r.y = fma_(s.srgb_lut[p11[1]], w11, fma_(s.srgb_lut[p01[1]], w01, fma_(s.srgb_lut[p10[1]], w10, s.srgb_lut[p00[1]] * w00)));
+    r.z = fma_(s.srgb_lut[p11[2]], w11, fma_(s.srgb_lut[p01[2]], w01, fma_(s.srgb_lut[p10[2]], w10, s.srgb_lut[p00[2]] * w00)));
+    return r;
+}
+
+/* Skybox.SampleLevel(direction_to_equirect_uv(d), 0) — shaders/old/refrence_mode.slang:38 (commented
+ * out there), shaders/old/postprocess.slang:101-105.  RGB float equirect image, bilinear, repeat-u, clamp-v. */
+RT3_HD vec3 sample_environment(const SceneView& s, vec3 dir) {
+    if (s.env == nullptr) return v3(0.f, 0.f, 0.f);
+    vec2 uv = direction_to_equirect_uv(dir);
+    float fx = uv.x * float(s.env_w) - 0.5f, fy = uv.y * float(s.env_h) - 0.5f;
+    float flx = floor_(fx), fly = floor_(fy);
+    float ax = fx - flx, ay = fy - fly;
+    int x0 = (int)flx, y0 = (int)fly, x1 = x0 + 1, y1 = y0 + 1;
+    int w = (int)s.env_w, h = (int)s.env_h;
+    x0 = (x0 % w + w) % w; x1 = (x1 % w + w) % w;
+    y0 = y0 < 0 ? 0 : (y0 > h - 1 ? h - 1 : y0);
+    y1 = y1 < 0 ? 0 : (y1 > h - 1 ? h - 1 : y1);
+    const float* p00 = s.env + 3u * ((uint32_t)y0 * s.env_w + (uint32_t)x0);
+    const float* p10 = s.env + 3u * ((uint32_t)y0 * s.env_w + (uint32_t)x1);
+    const float* p01 = s.env + 3u * ((uint32_t)y1 * s.env_w + (uint32_t)x0);
+    const float* p11 = s.env + 3u * ((uint32_t)y1 * s.env_w + (uint32_t)x1);
+    float w00 = (1.0f - ax) * (1.0f - ay), w10 = ax * (1.0f - ay), w01 = (1.0f - ax) * ay, w11 = ax * ay;
+    vec3 r;
+    r.x = fma_(p11[0], w11, fma_(p01[0], w01, fma_(p10[0], w10, p00[0] * w00)));
+    r.y = fma_(p11[1], w11, fma_(p01[1], w01, fma_(p10[1], w10, p00[1] * w00)));
+    r.z = fma_(p11[2], w11, fma_(p01[2], w01, fma_(p10[2], w10, p00[2] * w00)));
+    return r;
+}
+
+/* shaders/include/hit_logic.slang:5-40.  `prim` is the global triangle id (the payload's
+ * geometryIndex/primitiveId pair, default_hit.slang:7-8, is recovered through the segment table).
+ * The per-vertex colour the old shader reads (hit_logic.slang:27) does not exist in the 32-byte
+ * Vertex (assets/mod.rs:127-133) and is taken as (1,1,1). */
+RT3_HD GbufferData hit_info(const SceneView& s, uint32_t prim, float bu, float bv, uint32_t* out_geometry = nullptr) {
+    uint32_t seg = find_segment(s, prim);
+    uint32_t gi = s.seg_geometry[seg];
+    if (out_geometry) *out_geometry = gi;
+    const rt3_geometry_info& g = s.geometries[gi];
+    uint32_t io = g.index_offset + 3u * (prim - s.seg_first_prim[seg]);
+    uint32_t i0 = g.vertex_offset + s.indices[io], i1 = g.vertex_offset + s.indices[io + 1], i2 = g.vertex_offset + s.indices[io + 2];
+    const rt3_vertex& a = s.vertices[i0];
+    const rt3_vertex& b = s.vertices[i1];
+    const rt3_vertex& c = s.vertices[i2];
+    float w0 = 1.0f - bu - bv, w1 = bu, w2 = bv;
+    vec3 n = v3(fma_(c.n[0], w2, fma_(b.n[0], w1, a.n[0] * w0)), fma_(c.n[1], w2, fma_(b.n[1], w1, a.n[1] * w0)),
+                fma_(c.n[2], w2, fma_(b.n[2], w1, a.n[2] * w0)));
+    n = normalize(n);
+    n = normalize(xform_dir(g.xform, n));
+    const float* ix = s.inst_xform + 12u * s.seg_instance[seg];
+    if (!xform_is_identity(ix)) n = normalize(xform_dir(ix, n));
+    float tu = fma_(c.t[0], w2, fma_(b.t[0], w1, a.t[0] * w0));
+    float tv = fma_(c.t[1], w2, fma_(b.t[1], w1, a.t[1] * w0));
+    vec3 color = v3(g.base_color[0], g.base_color[1], g.base_color[2]);
+    if (g.base_color_tex > -1) color = color * sample_texture(s, g.base_color_tex, tu, tv);
+    GbufferData o;
+    o.metalness = g.metallic;
+    o.roughness = g.roughness;
+    o.emissive = v3(g.emission[0] * 12.0f, g.emission[1] * 12.0f, g.emission[2] * 12.0f);
+    o.normal = n;
+    o.albedo = color;
+    return o;
+}
+
+/* ---------------------------------------------------------------- samplers ------------------- */
+/* The 2 random numbers of bounce `dim_pair` (refrence_mode.slang:43: x drawn first).  Faithful mode:
+ * the murmur3 counter stream.  RT3_FLAG_BLUENOISE (no reference counterpart; resources/bluenoise.png
+ * ships unused): blue-noise tile value of the pixel (channel pair by dimension) Cranley-Patterson
+ * rotated by the R2 sequence (random.slang:30-35) indexed by the running draw counter and frame. */
+RT3_HD vec2 sample_2d(const SceneView& s, uint32_t flags, uint32_t px, uint32_t py, uint32_t frame, RandomSamplerState& rng) {
+    vec2 u;
+    if ((flags & RT3_FLAG_BLUENOISE) && s.bn != nullptr) {
+        uint32_t k = rng.index >> 1; /* 2-D draw number within the pixel's stream */
+        rng.index += 2;
+        /* decorrelate successive dimensions by shifting the tile with a per-dimension Jenkins hash */
+        uint32_t h = hash_jenkins(k * 0x9E3779B9u + 0x85EBCA6Bu);
+        uint32_t tx = (px + (h & 0xFFFFu)) & (s.bn_w - 1u), ty = (py + (h >> 16)) & (s.bn_h - 1u);
+        const uint8_t* t = s.bn + 4u * (ty * s.bn_w + tx);
+        uint32_t ch = (k & 1u) * 2u;
+        vec2 r = r2_sequence_fixed(frame * 64u + k);
+        u.x = frac_((float(t[ch]) + 0.5f) * (1.0f / 256.0f) + r.x);
+        u.y = frac_((float(t[ch + 1]) + 0.5f) * (1.0f / 256.0f) + r.y);
+        /* keep strictly below 1 */
+        u.x = min_(u.x, 0.99999994f); u.y = min_(u.y, 0.99999994f);
+    } else {
+        u.x = rng_uniform_float(rng);
+        u.y = rng_uniform_float(rng);
+    }
+    return u;
+}
+
+/* ---------------------------------------------------------------- path tracing step ---------- */
+/* One bounce of shaders/old/refrence_mode.slang:42-51: sample the diffuse lobe at `surface`,
+ * advance the ray to the hit point, gather emission, update throughput. */
+struct PathVertexOut { vec3 origin, dir; };
+RT3_HD PathVertexOut bounce_step(const GbufferData& surface, vec3 ray_o, vec3 ray_d, float depth, vec2 urand, vec3& radiance,
+                                 vec3& ray_color) {
+    onb t = build_orthonormal_basis(surface.normal);
+    vec3 wi = diffuse_sample_wi(urand.x, urand.y);
+    PathVertexOut o;
+    o.origin = v3(ray_o.x + depth * ray_d.x, ray_o.y + depth * ray_d.y, ray_o.z + depth * ray_d.z);
+    o.dir = onb_to_world(t, wi);
+    radiance = radiance + ray_color * surface.emissive;
+    ray_color = ray_color * surface.albedo;
+    return o;
+}
+/* shaders/old/refrence_mode.slang:59-65 */
+RT3_HD vec3 temporal_blend(vec3 prev, vec3 radiance, float blendfactor) {
+    if (blendfactor >= 1.0f) return radiance;
+    return v3(prev.x + (radiance.x - prev.x) * blendfactor, prev.y + (radiance.y - prev.y) * blendfactor,
+              prev.z + (radiance.z - prev.z) * blendfactor);
+}
+
+/* ---------------------------------------------------------------- postprocess.slang ---------- */
+/* shaders/old/postprocess.slang:13-24 */
+RT3_HD float agx_contrast(float x) {
+    float x2 = x * x, x4 = x2 * x2;
+    return 15.5f * x4 * x2 - 40.14f * x4 * x + 31.96f * x4 - 6.868f * x2 * x + 0.4298f * x2 + 0.1191f * x - 0.00232f;
+}
+/* shaders/old/postprocess.slang:26-46: HLSL mul(v, M) with the row-major literal = row vector times matrix. */
+RT3_HD vec3 agx(vec3 val) {
+    const float m[9] = {0.842479062253094f, 0.0423282422610123f, 0.0423756549057051f, 0.0784335999999992f, 0.878468636469772f,
+                        0.0784336f,         0.0792237451477643f, 0.0791661274605434f, 0.879142973793104f};
+    const float min_ev = -12.47393f, max_ev = 4.026069f;
+    vec3 r = v3(fma_(val.z, m[6], fma_(val.y, m[3], val.x * m[0])), fma_(val.z, m[7], fma_(val.y, m[4], val.x * m[1])),
+                fma_(val.z, m[8], fma_(val.y, m[5], val.x * m[2])));
+    float range = max_ev - min_ev;
+    r.x = (clamp_(r.x > 0.f ? log2_(r.x) : min_ev, min_ev, max_ev) - min_ev) / range;
+    r.y = (clamp_(r.y > 0.f ? log2_(r.y) : min_ev, min_ev, max_ev) - min_ev) / range;
+    r.z = (clamp_(r.z > 0.f ? log2_(r.z) : min_ev, min_ev, max_ev) - min_ev) / range;
+    return v3(agx_contrast(r.x), agx_contrast(r.y), agx_contrast(r.z));
+}
+/* shaders/old/postprocess.slang:63-88 with AGX_LOOK == 2 ("punchy"). */
+RT3_HD vec3 agx_look(vec3 val) {
+    float luma = fma_(val.z, 0.0722f, fma_(val.y, 0.7152f, val.x * 0.2126f));
+    vec3 p = v3(pow_(val.x, 1.1f), pow_(val.y, 1.1f), pow_(val.z, 1.1f));
+    const float sat = 1.1f;
+    return v3(luma + sat * (p.x - luma), luma + sat * (p.y - luma), luma + sat * (p.z - luma));
+}
+/* shaders/old/postprocess.slang:48-61 (the 2.2 power is commented out there). */
+RT3_HD vec3 agx_eotf(vec3 val) {
+    const float m[9] = {1.19687900512017f,  -0.0528968517574562f, -0.0529716355144438f, -0.0980208811401368f, 1.15190312990417f,
+                        -0.0980434501171241f, -0.0990297440797205f, -0.0989611768448433f, 1.15107367264116f};
+    return v3(fma_(val.z, m[6], fma_(val.y, m[3], val.x * m[0])), fma_(val.z, m[7], fma_(val.y, m[4], val.x * m[1])),
+              fma_(val.z, m[8], fma_(val.y, m[5], val.x * m[2])));
+}
+RT3_HD vec3 postprocess_pixel(const SceneView& s, const rt3_params& p, uint32_t px, uint32_t py, float depth, vec3 in_color) {
+    vec3 color = in_color;
+    if (depth == RT3_BACKGROUND_DEPTH) color = sample_environment(s, view_dir(px, py, p));
+    return agx_eotf(agx_look(agx(color)));
+}
+
+#ifndef __CUDA_ARCH__
+/* Host-side table: sRGB byte -> linear float (IEC 61966-2-1), evaluated in double and rounded once. */
+inline void build_srgb_lut(float* lut256) {
+    for (int i = 0; i < 256; ++i) {
+        double c = i / 255.0;
+        lut256[i] = (float)(c <= 0.04045 ? c / 12.92 : pow((c + 0.055) / 1.055, 2.4));
+    }
+}
+#endif
+
+} /* namespace rt3m */
+#endif

@@ -1,0 +1,499 @@
+/*
+ * oracle.cpp — CPU oracle for the ray-traced G-buffer + reference-mode path tracer.
+ *
+ * TEST INFRASTRUCTURE ONLY (see oracle.h).  PARITY UNPINNED at the driver boundary (see oracle.h).
+ *
+ * Structure
+ *   - per-pixel passes follow the reference's raygen shaders statement by statement
+ *       orc_pass_gbuffer    <- shaders/old/gbuffer.slang:8-20
+ *       orc_pass_reference  <- shaders/old/refrence_mode.slang:14-66
+ *       orc_pass_postprocess<- shaders/old/postprocess.slang:90-112
+ *     with the shader math taken from include/rt3_shared_math.h (each function there cites its source);
+ *   - trace() (the missing bindless_descriptor.slang wrapper over TraceRay) is a closest-hit query
+ *     over world-space triangles, implemented twice: brute force over every triangle (the definition)
+ *     and a binned-SAH BVH2 written for this oracle (the fast path; proven equal to brute force in tests).
+ *   - deliberately single-ray, one-pixel-at-a-time recursion-free loops: nothing here is shared with
+ *     the CUDA implementation except the math header.
+ */
+#include "oracle.h"
+#include "rt3_shared_math.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstdlib>
+#include <thread>
+#include <vector>
+
+using namespace rt3m;
+
+namespace {
+
+struct WorldTri { vec3 v0, e1, e2; };
+struct Box {
+    vec3 lo, hi;
+    void reset() { lo = v3(3.4e38f, 3.4e38f, 3.4e38f); hi = v3(-3.4e38f, -3.4e38f, -3.4e38f); }
+    void grow(vec3 p) {
+        lo = v3(min_(lo.x, p.x), min_(lo.y, p.y), min_(lo.z, p.z));
+        hi = v3(max_(hi.x, p.x), max_(hi.y, p.y), max_(hi.z, p.z));
+    }
+    void grow(const Box& b) { grow(b.lo); grow(b.hi); }
+    float area() const { vec3 e = hi - lo; return 2.0f * (e.x * e.y + e.y * e.z + e.z * e.x); }
+};
+struct Node2 { Box box; uint32_t left, count; /* count>0: leaf, tris [left,left+count); else children left,left+1 */ };
+
+}  // namespace
+
+struct orc_scene {
+    std::vector<rt3_vertex> vertices;
+    std::vector<uint32_t> indices;
+    std::vector<rt3_geometry_info> geometries;
+    std::vector<uint32_t> inst_first, inst_count;
+    std::vector<float> inst_xform;
+    std::vector<uint32_t> seg_first_prim, seg_geometry, seg_instance;
+    std::vector<std::vector<uint8_t>> textures;
+    std::vector<const uint8_t*> tex_ptr;
+    std::vector<uint32_t> tex_dim;
+    std::vector<float> env;
+    uint32_t env_w = 0, env_h = 0;
+    std::vector<uint8_t> bn;
+    uint32_t bn_w = 0, bn_h = 0;
+    float srgb_lut[256];
+    /* built */
+    std::vector<WorldTri> tris;      /* global id order */
+    std::vector<uint32_t> order;     /* BVH leaf order -> global id */
+    std::vector<Node2> nodes;
+    Box bounds;
+    float pad = 0.f;
+    SceneView view() const {
+        SceneView s;
+        s.vertices = vertices.data(); s.indices = indices.data(); s.geometries = geometries.data();
+        s.seg_first_prim = seg_first_prim.data(); s.seg_geometry = seg_geometry.data(); s.seg_instance = seg_instance.data();
+        s.inst_xform = inst_xform.data(); s.n_segments = (uint32_t)seg_geometry.size();
+        s.tex_data = tex_ptr.data(); s.tex_dim = tex_dim.data(); s.n_textures = (uint32_t)tex_ptr.size();
+        s.srgb_lut = srgb_lut;
+        s.env = env.empty() ? nullptr : env.data(); s.env_w = env_w; s.env_h = env_h;
+        s.bn = bn.empty() ? nullptr : bn.data(); s.bn_w = bn_w; s.bn_h = bn_h;
+        return s;
+    }
+};
+
+namespace {
+
+template <class F>
+void parallel_for(uint64_t n, int threads, uint64_t grain, F f) {
+    if (threads <= 1 || n <= grain) { f(0, n); return; }
+    std::atomic<uint64_t> next(0);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+        pool.emplace_back([&]() {
+            for (;;) {
+                uint64_t b = next.fetch_add(grain);
+                if (b >= n) break;
+                f(b, std::min(n, b + grain));
+            }
+        });
+    for (auto& th : pool) th.join();
+}
+
+/* ---- BVH2: binned SAH (16 bins), leaves of <= 4 triangles --------------------------------- */
+struct Builder {
+    orc_scene& s;
+    std::vector<Box> tbox;
+    std::vector<vec3> cen;
+    explicit Builder(orc_scene& sc) : s(sc) {}
+    static float axis(vec3 v, int a) { return a == 0 ? v.x : (a == 1 ? v.y : v.z); }
+    void build() {
+        uint32_t n = (uint32_t)s.tris.size();
+        tbox.resize(n); cen.resize(n); s.order.resize(n);
+        for (uint32_t i = 0; i < n; ++i) {
+            const WorldTri& t = s.tris[i];
+            Box b; b.reset(); b.grow(t.v0); b.grow(t.v0 + t.e1); b.grow(t.v0 + t.e2);
+            b.lo = b.lo - v3(s.pad, s.pad, s.pad); b.hi = b.hi + v3(s.pad, s.pad, s.pad);
+            tbox[i] = b; cen[i] = (b.lo + b.hi) * 0.5f; s.order[i] = i;
+        }
+        s.nodes.clear(); s.nodes.reserve(2 * (size_t)n + 2);
+        if (n == 0) return;
+        s.nodes.push_back(Node2());
+        struct Job { uint32_t node, first, count; };
+        std::vector<Job> stack; stack.push_back({0, 0, n});
+        while (!stack.empty()) {
+            Job j = stack.back(); stack.pop_back();
+            Box nb, cb; nb.reset(); cb.reset();
+            for (uint32_t i = j.first; i < j.first + j.count; ++i) { nb.grow(tbox[s.order[i]]); cb.grow(cen[s.order[i]]); }
+            Node2& nd = s.nodes[j.node]; nd.box = nb;
+            if (j.count <= 2) { nd.left = j.first; nd.count = j.count; continue; }
+            const int NB = 16;
+            float best = 3.4e38f; int baxis = -1, bsplit = -1;
+            for (int a = 0; a < 3; ++a) {
+                float lo = axis(cb.lo, a), hi = axis(cb.hi, a);
+                if (!(hi > lo)) continue;
+                Box bb[NB]; uint32_t bc[NB];
+                for (int k = 0; k < NB; ++k) { bb[k].reset(); bc[k] = 0; }
+                float scale = NB / (hi - lo);
+                for (uint32_t i = j.first; i < j.first + j.count; ++i) {
+                    uint32_t id = s.order[i];
+                    int k = std::min(NB - 1, (int)((axis(cen[id], a) - lo) * scale));
+                    bb[k].grow(tbox[id]); bc[k]++;
+                }
+                float la[NB], ra[NB]; uint32_t lc[NB], rc[NB];
+                Box acc; acc.reset(); uint32_t c = 0;
+                for (int k = 0; k < NB - 1; ++k) { if (bc[k]) acc.grow(bb[k]); c += bc[k]; la[k] = c ? acc.area() : 0.f; lc[k] = c; }
+                acc.reset(); c = 0;
+                for (int k = NB - 1; k > 0; --k) { if (bc[k]) acc.grow(bb[k]); c += bc[k]; ra[k - 1] = c ? acc.area() : 0.f; rc[k - 1] = c; }
+                for (int k = 0; k < NB - 1; ++k) {
+                    if (!lc[k] || !rc[k]) continue;
+                    float cost = la[k] * lc[k] + ra[k] * rc[k];
+                    if (cost < best) { best = cost; baxis = a; bsplit = k; }
+                }
+            }
+            float leaf_cost = nb.area() * j.count;
+            if (j.count <= 4 && (baxis < 0 || best >= leaf_cost)) { nd.left = j.first; nd.count = j.count; continue; }
+            uint32_t mid;
+            if (baxis >= 0) {
+                float lo = axis(cb.lo, baxis), hi = axis(cb.hi, baxis);
+                float scale = NB / (hi - lo);
+                auto it = std::partition(s.order.begin() + j.first, s.order.begin() + j.first + j.count, [&](uint32_t id) {
+                    int k = std::min(NB - 1, (int)((axis(cen[id], baxis) - lo) * scale));
+                    return k <= bsplit;
+                });
+                mid = (uint32_t)(it - s.order.begin());
+            } else {
+                mid = j.first + j.count / 2; /* all centroids coincide: median split */
+            }
+            if (mid == j.first || mid == j.first + j.count) mid = j.first + j.count / 2;
+            uint32_t l = (uint32_t)s.nodes.size();
+            s.nodes.push_back(Node2()); s.nodes.push_back(Node2());
+            s.nodes[j.node].left = l; s.nodes[j.node].count = 0;
+            stack.push_back({l, j.first, mid - j.first});
+            stack.push_back({l + 1, mid, j.first + j.count - mid});
+        }
+    }
+};
+
+inline float safe_inv(float d) {
+    const float tiny = 1e-20f;
+    if (abs_(d) < tiny) d = (as_uint(d) >> 31) ? -tiny : tiny;
+    return 1.0f / d;
+}
+inline bool slab(const Box& b, vec3 o, vec3 id, float tmin, float tmax) {
+    float x1 = (b.lo.x - o.x) * id.x, x2 = (b.hi.x - o.x) * id.x;
+    float y1 = (b.lo.y - o.y) * id.y, y2 = (b.hi.y - o.y) * id.y;
+    float z1 = (b.lo.z - o.z) * id.z, z2 = (b.hi.z - o.z) * id.z;
+    float tn = max_(max_(min_(x1, x2), min_(y1, y2)), max_(min_(z1, z2), tmin));
+    float tf = min_(min_(max_(x1, x2), max_(y1, y2)), min_(max_(z1, z2), tmax));
+    return tn <= tf * 1.0000005f;
+}
+
+/* trace(): closest hit.  The payload semantics follow default_hit.slang:4-8 / default_miss.slang:4-7. */
+rt3_hit closest_brute(const orc_scene& s, const rt3_ray& r) {
+    rt3_hit h; h.t = r.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+    vec3 o = v3(r.o), d = v3(r.d);
+    uint32_t n = (uint32_t)s.tris.size();
+    for (uint32_t i = 0; i < n; ++i) {
+        float t, u, v;
+        const WorldTri& tr = s.tris[i];
+        if (ray_triangle(o, d, tr.v0, tr.e1, tr.e2, t, u, v) && t > r.tmin && t < r.tmax && closer_hit(t, i, h.t, h.prim)) {
+            h.t = t; h.u = u; h.v = v; h.prim = i;
+        }
+    }
+    if (h.prim == RT3_MISS) h.t = r.tmax;
+    return h;
+}
+rt3_hit closest_bvh(const orc_scene& s, const rt3_ray& r) {
+    rt3_hit h; h.t = r.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+    if (s.nodes.empty()) return h;
+    vec3 o = v3(r.o), d = v3(r.d);
+    vec3 id = v3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
+    uint32_t stack[128]; int sp = 0; stack[sp++] = 0;
+    while (sp) {
+        const Node2& nd = s.nodes[stack[--sp]];
+        if (!slab(nd.box, o, id, r.tmin, h.t)) continue;
+        if (nd.count) {
+            for (uint32_t k = nd.left; k < nd.left + nd.count; ++k) {
+                uint32_t i = s.order[k];
+                float t, u, v;
+                const WorldTri& tr = s.tris[i];
+                if (ray_triangle(o, d, tr.v0, tr.e1, tr.e2, t, u, v) && t > r.tmin && t < r.tmax && closer_hit(t, i, h.t, h.prim)) {
+                    h.t = t; h.u = u; h.v = v; h.prim = i;
+                }
+            }
+        } else {
+            if (sp + 2 > 128) abort();
+            stack[sp++] = nd.left; stack[sp++] = nd.left + 1;
+        }
+    }
+    return h;
+}
+bool any_brute(const orc_scene& s, const rt3_ray& r) {
+    vec3 o = v3(r.o), d = v3(r.d);
+    for (const WorldTri& tr : s.tris) {
+        float t, u, v;
+        if (ray_triangle(o, d, tr.v0, tr.e1, tr.e2, t, u, v) && t > r.tmin && t < r.tmax) return true;
+    }
+    return false;
+}
+bool any_bvh(const orc_scene& s, const rt3_ray& r) {
+    if (s.nodes.empty()) return false;
+    vec3 o = v3(r.o), d = v3(r.d);
+    vec3 id = v3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
+    uint32_t stack[128]; int sp = 0; stack[sp++] = 0;
+    while (sp) {
+        const Node2& nd = s.nodes[stack[--sp]];
+        if (!slab(nd.box, o, id, r.tmin, r.tmax)) continue;
+        if (nd.count) {
+            for (uint32_t k = nd.left; k < nd.left + nd.count; ++k) {
+                float t, u, v;
+                const WorldTri& tr = s.tris[s.order[k]];
+                if (ray_triangle(o, d, tr.v0, tr.e1, tr.e2, t, u, v) && t > r.tmin && t < r.tmax) return true;
+            }
+        } else { stack[sp++] = nd.left; stack[sp++] = nd.left + 1; }
+    }
+    return false;
+}
+
+inline rt3_ray make_ray(vec3 o, vec3 d, float tmin, float tmax) {
+    rt3_ray r; r.o[0] = o.x; r.o[1] = o.y; r.o[2] = o.z; r.d[0] = d.x; r.d[1] = d.y; r.d[2] = d.z; r.tmin = tmin; r.tmax = tmax; return r;
+}
+
+}  // namespace
+
+extern "C" {
+
+orc_scene* orc_scene_create(const rt3_vertex* v, uint32_t nv, const uint32_t* idx, uint32_t ni, const rt3_geometry_info* g, uint32_t ng,
+                            const uint32_t* inst_first_geo, const uint32_t* inst_geo_count, const float* inst_xform, uint32_t n_inst) {
+    orc_scene* s = new orc_scene();
+    s->vertices.assign(v, v + nv); s->indices.assign(idx, idx + ni); s->geometries.assign(g, g + ng);
+    if (n_inst == 0) {
+        s->inst_first = {0}; s->inst_count = {ng};
+        s->inst_xform = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    } else {
+        s->inst_first.assign(inst_first_geo, inst_first_geo + n_inst);
+        s->inst_count.assign(inst_geo_count, inst_geo_count + n_inst);
+        s->inst_xform.assign(inst_xform, inst_xform + 12 * (size_t)n_inst);
+    }
+    build_srgb_lut(s->srgb_lut);
+    return s;
+}
+void orc_scene_destroy(orc_scene* s) { delete s; }
+void orc_scene_set_texture(orc_scene* s, uint32_t slot, uint32_t w, uint32_t h, const uint8_t* rgba8) {
+    if (s->textures.size() <= slot) { s->textures.resize(slot + 1); s->tex_dim.resize(2 * (slot + 1), 0); }
+    s->textures[slot].assign(rgba8, rgba8 + 4 * (size_t)w * h);
+    s->tex_dim[2 * slot] = w; s->tex_dim[2 * slot + 1] = h;
+    s->tex_ptr.resize(s->textures.size());
+    for (size_t i = 0; i < s->textures.size(); ++i) s->tex_ptr[i] = s->textures[i].empty() ? nullptr : s->textures[i].data();
+}
+void orc_scene_set_environment(orc_scene* s, uint32_t w, uint32_t h, const float* rgb) { s->env.assign(rgb, rgb + 3 * (size_t)w * h); s->env_w = w; s->env_h = h; }
+void orc_scene_set_bluenoise(orc_scene* s, uint32_t w, uint32_t h, const uint8_t* rgba8) { s->bn.assign(rgba8, rgba8 + 4 * (size_t)w * h); s->bn_w = w; s->bn_h = h; }
+
+double orc_scene_build(orc_scene* s) {
+    auto t0 = std::chrono::steady_clock::now();
+    /* segment table: instances in push order, geometries in range order */
+    s->seg_first_prim.clear(); s->seg_geometry.clear(); s->seg_instance.clear();
+    uint32_t total = 0;
+    for (uint32_t i = 0; i < s->inst_first.size(); ++i)
+        for (uint32_t g = s->inst_first[i]; g < s->inst_first[i] + s->inst_count[i]; ++g) {
+            s->seg_first_prim.push_back(total); s->seg_geometry.push_back(g); s->seg_instance.push_back(i);
+            total += s->geometries[g].index_count / 3;
+        }
+    s->seg_first_prim.push_back(total);
+    SceneView sv = s->view();
+    s->tris.resize(total);
+    s->bounds.reset();
+    for (uint32_t seg = 0; seg < s->seg_geometry.size(); ++seg)
+        for (uint32_t p = s->seg_first_prim[seg]; p < s->seg_first_prim[seg + 1]; ++p) {
+            vec3 a, b, c;
+            world_triangle(sv, seg, p - s->seg_first_prim[seg], a, b, c);
+            WorldTri t; t.v0 = a; t.e1 = b - a; t.e2 = c - a;
+            s->tris[p] = t;
+            s->bounds.grow(a); s->bounds.grow(b); s->bounds.grow(c);
+        }
+    vec3 e = s->bounds.hi - s->bounds.lo;
+    s->pad = total ? max_(e.x, max_(e.y, e.z)) * (1.0f / 65536.0f) : 0.f;
+    Builder b(*s); b.build();
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+uint32_t orc_num_triangles(const orc_scene* s) { return (uint32_t)s->tris.size(); }
+void orc_scene_bounds(const orc_scene* s, float lo[3], float hi[3]) {
+    lo[0] = s->bounds.lo.x; lo[1] = s->bounds.lo.y; lo[2] = s->bounds.lo.z;
+    hi[0] = s->bounds.hi.x; hi[1] = s->bounds.hi.y; hi[2] = s->bounds.hi.z;
+}
+void orc_resolve_prim(const orc_scene* s, uint32_t prim, uint32_t* instance, uint32_t* geometry, uint32_t* primitive) {
+    SceneView sv = s->view();
+    uint32_t seg = find_segment(sv, prim);
+    *instance = s->seg_instance[seg]; *geometry = s->seg_geometry[seg]; *primitive = prim - s->seg_first_prim[seg];
+}
+void orc_world_triangles(const orc_scene* s, float* out9) {
+    for (size_t i = 0; i < s->tris.size(); ++i) {
+        const WorldTri& t = s->tris[i];
+        vec3 b = t.v0 + t.e1, c = t.v0 + t.e2;
+        float* o = out9 + 9 * i;
+        o[0] = t.v0.x; o[1] = t.v0.y; o[2] = t.v0.z; o[3] = b.x; o[4] = b.y; o[5] = b.z; o[6] = c.x; o[7] = c.y; o[8] = c.z;
+    }
+}
+
+void orc_trace_closest(const orc_scene* s, const rt3_ray* rays, uint64_t n, rt3_hit* out, int mode, int threads) {
+    parallel_for(n, threads, mode ? 4096 : 64, [&](uint64_t b, uint64_t e) {
+        for (uint64_t i = b; i < e; ++i) out[i] = mode ? closest_bvh(*s, rays[i]) : closest_brute(*s, rays[i]);
+    });
+}
+void orc_trace_any(const orc_scene* s, const rt3_ray* rays, uint64_t n, uint32_t* out_bits, int mode, int threads) {
+    uint64_t words = (n + 31) / 32;
+    parallel_for(words, threads, mode ? 128 : 2, [&](uint64_t b, uint64_t e) {
+        for (uint64_t w = b; w < e; ++w) {
+            uint32_t bits = 0;
+            for (uint64_t i = w * 32; i < std::min(n, w * 32 + 32); ++i)
+                if (mode ? any_bvh(*s, rays[i]) : any_brute(*s, rays[i])) bits |= 1u << (i & 31);
+            out_bits[w] = bits;
+        }
+    });
+}
+
+/* shaders/old/gbuffer.slang:8-20 */
+void orc_pass_gbuffer(const orc_scene* s, const rt3_params* p, rt3_rect rc, uint32_t* gbuffer, float* depth, uint32_t* opt_ids, float* opt_bary,
+                      int threads) {
+    SceneView sv = s->view();
+    uint32_t pitch = (uint32_t)p->window_size[0];
+    parallel_for(rc.h, threads, 4, [&](uint64_t y0, uint64_t y1) {
+        for (uint32_t y = rc.y0 + (uint32_t)y0; y < rc.y0 + (uint32_t)y1; ++y)
+            for (uint32_t x = rc.x0; x < rc.x0 + rc.w; ++x) {
+                size_t px = (size_t)y * pitch + x;
+                rt3_ray ray = setup_primary_ray(x, y, *p);     /* gbuffer.slang:10 */
+                rt3_hit h = closest_bvh(*s, ray);               /* gbuffer.slang:12 */
+                if (h.prim == RT3_MISS) {                       /* gbuffer.slang:14-16: gbuffer colour left untouched */
+                    depth[px] = RT3_BACKGROUND_DEPTH;
+                    if (opt_ids) { opt_ids[2 * px] = RT3_MISS; opt_ids[2 * px + 1] = RT3_MISS; }
+                    if (opt_bary) { opt_bary[2 * px] = 0.f; opt_bary[2 * px + 1] = 0.f; }
+                } else {                                        /* gbuffer.slang:17-19 */
+                    uint32_t geo;
+                    uint4_ g = gbuffer_pack(hit_info(sv, h.prim, h.u, h.v, &geo));
+                    gbuffer[4 * px] = g.x; gbuffer[4 * px + 1] = g.y; gbuffer[4 * px + 2] = g.z; gbuffer[4 * px + 3] = g.w;
+                    depth[px] = h.t;
+                    if (opt_ids) { opt_ids[2 * px] = h.prim; opt_ids[2 * px + 1] = geo; }
+                    if (opt_bary) { opt_bary[2 * px] = h.u; opt_bary[2 * px + 1] = h.v; }
+                }
+            }
+    });
+}
+
+/* shaders/old/refrence_mode.slang:14-66 */
+void orc_pass_reference(const orc_scene* s, const rt3_params* p, rt3_rect rc, const uint32_t* gbuffer, const float* depth, const float* prev_light,
+                        float* light, int threads, rt3_counters* opt_counters) {
+    SceneView sv = s->view();
+    uint32_t pitch = (uint32_t)p->window_size[0];
+    std::atomic<uint64_t> n_secondary(0), n_started(0), n_escaped(0);
+    parallel_for(rc.h, threads, 4, [&](uint64_t y0, uint64_t y1) {
+        uint64_t secondary = 0, started = 0, escaped = 0;
+        for (uint32_t y = rc.y0 + (uint32_t)y0; y < rc.y0 + (uint32_t)y1; ++y)
+            for (uint32_t x = rc.x0; x < rc.x0 + rc.w; ++x) {
+                size_t px = (size_t)y * pitch + x;
+                float gdepth = depth[px];
+                if (gdepth == RT3_BACKGROUND_DEPTH) continue;                          /* :18-21 */
+                uint4_ packed = {gbuffer[4 * px], gbuffer[4 * px + 1], gbuffer[4 * px + 2], gbuffer[4 * px + 3]};
+                GbufferData gdata = gbuffer_unpack(packed);                             /* :23 */
+                RandomSamplerState rng = rng_init(x, y, p->frame);                      /* :25 */
+                vec3 radiance = v3(0.f, 0.f, 0.f);
+                for (uint32_t i = 0; i < p->samples; ++i) {                             /* :28 */
+                    vec3 ray_color = v3(1.f, 1.f, 1.f);
+                    rt3_ray pr = setup_primary_ray(x, y, *p);                           /* :30 */
+                    vec3 ro = v3(pr.o), rd = v3(pr.d);
+                    const float tmin = 0.001f, tmax = pr.tmax;                          /* :31 */
+                    GbufferData surface = gdata;
+                    float hit_t = gdepth;
+                    bool missed = false;                                                /* payload.geometryIndex = 0, :34 */
+                    started++;
+                    for (uint32_t b = 0; b < p->bounces; ++b) {                         /* :36 */
+                        if (missed) {                                                   /* :37-40 */
+                            if (p->flags & RT3_FLAG_ENV) radiance = radiance + ray_color * sample_environment(sv, rd);
+                            break;
+                        }
+                        vec2 urand = sample_2d(sv, p->flags, x, y, p->frame, rng);     /* :43 */
+                        PathVertexOut nv = bounce_step(surface, ro, rd, hit_t, urand, radiance, ray_color); /* :44-51 */
+                        ro = nv.origin; rd = nv.dir;
+                        if (b != p->bounces - 1) {                                      /* :53-56 */
+                            rt3_hit h = closest_bvh(*s, make_ray(ro, rd, tmin, tmax));
+                            secondary++;
+                            if (h.prim == RT3_MISS) { missed = true; escaped++; }
+                            else { surface = hit_info(sv, h.prim, h.u, h.v); hit_t = h.t; }
+                        }
+                    }
+                }
+                float ns = float(p->samples);                                           /* :59 (radiance /= samples) */
+                radiance = v3(radiance.x / ns, radiance.y / ns, radiance.z / ns);
+                vec3 prev = v3(0.f, 0.f, 0.f);
+                if (p->blendfactor < 1.0f && prev_light) prev = v3(prev_light[4 * px], prev_light[4 * px + 1], prev_light[4 * px + 2]);
+                vec3 o = temporal_blend(prev, radiance, p->blendfactor);                /* :61-65 */
+                light[4 * px] = o.x; light[4 * px + 1] = o.y; light[4 * px + 2] = o.z; light[4 * px + 3] = 0.f;
+            }
+        n_secondary += secondary; n_started += started; n_escaped += escaped;
+    });
+    if (opt_counters) {
+        opt_counters->rays_secondary += n_secondary; opt_counters->paths_started += n_started; opt_counters->paths_escaped += n_escaped;
+    }
+}
+
+/* shaders/old/postprocess.slang:90-112 */
+void orc_pass_postprocess(const orc_scene* s, const rt3_params* p, rt3_rect rc, const float* depth, const float* in, float* out, int threads) {
+    SceneView sv = s->view();
+    uint32_t pitch = (uint32_t)p->window_size[0];
+    parallel_for(rc.h, threads, 8, [&](uint64_t y0, uint64_t y1) {
+        for (uint32_t y = rc.y0 + (uint32_t)y0; y < rc.y0 + (uint32_t)y1; ++y)
+            for (uint32_t x = rc.x0; x < rc.x0 + rc.w; ++x) {
+                size_t px = (size_t)y * pitch + x;
+                vec3 c = postprocess_pixel(sv, *p, x, y, depth[px], v3(in[4 * px], in[4 * px + 1], in[4 * px + 2]));
+                out[4 * px] = c.x; out[4 * px + 1] = c.y; out[4 * px + 2] = c.z; out[4 * px + 3] = 1.0f;
+            }
+    });
+}
+
+/* ---- known-answer hooks -------------------------------------------------------------------- */
+uint32_t orc_hash_jenkins(uint32_t a) { return hash_jenkins(a); }
+uint32_t orc_zcurve(uint32_t x, uint32_t y) { return zcurve_to_linear_index(x, y); }
+uint32_t orc_murmur3(uint32_t seed, uint32_t index) { return murmur3_at(seed, index); }
+float orc_uniform_float(uint32_t seed, uint32_t index) { return u32_to_unit_float(murmur3_at(seed, index)); }
+uint32_t orc_rng_seed(uint32_t px, uint32_t py, uint32_t frame) { return rng_init(px, py, frame).seed; }
+void orc_onb(const float n[3], float out9[9]) {
+    onb t = build_orthonormal_basis(v3(n));
+    out9[0] = t.b1.x; out9[1] = t.b1.y; out9[2] = t.b1.z; out9[3] = t.b2.x; out9[4] = t.b2.y; out9[5] = t.b2.z; out9[6] = t.n.x; out9[7] = t.n.y; out9[8] = t.n.z;
+}
+void orc_diffuse_sample(float ux, float uy, float out3[3]) { vec3 w = diffuse_sample_wi(ux, uy); out3[0] = w.x; out3[1] = w.y; out3[2] = w.z; }
+void orc_sincos_2pi(float u, float out2[2]) { sincos_2pi(u, out2[0], out2[1]); }
+float orc_atan2(float y, float x) { return atan2_(y, x); }
+float orc_asin(float y) { return asin_(y); }
+float orc_log2(float x) { return log2_(x); }
+float orc_exp2(float x) { return exp2_(x); }
+void orc_equirect_uv(const float d[3], float out2[2]) { vec2 r = direction_to_equirect_uv(v3(d)); out2[0] = r.x; out2[1] = r.y; }
+uint32_t orc_f32_to_f16(float f) { return f32_to_f16(f); }
+float orc_f16_to_f32(uint32_t h) { return f16_to_f32(h); }
+uint32_t orc_rgb9e5_pack(const float rgb[3]) { return float3_to_rgb9e5(v3(rgb)); }
+void orc_rgb9e5_unpack(uint32_t v, float out3[3]) { vec3 r = rgb9e5_to_float3(v); out3[0] = r.x; out3[1] = r.y; out3[2] = r.z; }
+uint32_t orc_pack_normal(const float n[3]) { return pack_normal_11_10_11(v3(n)); }
+void orc_unpack_normal(uint32_t p, float out3[3]) { vec3 r = unpack_normal_11_10_11(p); out3[0] = r.x; out3[1] = r.y; out3[2] = r.z; }
+uint32_t orc_pack_color(const float c[3]) { return pack_color_888(v3(c)); }
+void orc_unpack_color(uint32_t p, float out3[3]) { vec3 r = unpack_color_888(p); out3[0] = r.x; out3[1] = r.y; out3[2] = r.z; }
+void orc_gbuffer_pack(const float albedo[3], const float emissive[3], const float normal[3], float roughness, float metalness, uint32_t out4[4]) {
+    GbufferData g; g.albedo = v3(albedo); g.emissive = v3(emissive); g.normal = v3(normal); g.roughness = roughness; g.metalness = metalness;
+    uint4_ r = gbuffer_pack(g); out4[0] = r.x; out4[1] = r.y; out4[2] = r.z; out4[3] = r.w;
+}
+void orc_gbuffer_unpack(const uint32_t in4[4], float out11[11]) {
+    uint4_ d = {in4[0], in4[1], in4[2], in4[3]};
+    GbufferData g = gbuffer_unpack(d);
+    out11[0] = g.albedo.x; out11[1] = g.albedo.y; out11[2] = g.albedo.z; out11[3] = g.emissive.x; out11[4] = g.emissive.y; out11[5] = g.emissive.z;
+    out11[6] = g.normal.x; out11[7] = g.normal.y; out11[8] = g.normal.z; out11[9] = g.roughness; out11[10] = g.metalness;
+}
+void orc_primary_ray(const rt3_params* p, uint32_t px, uint32_t py, rt3_ray* out) { *out = setup_primary_ray(px, py, *p); }
+int orc_ray_triangle(const float o[3], const float d[3], const float v0[3], const float v1[3], const float v2[3], float out_tuv[3]) {
+    vec3 a = v3(v0);
+    return ray_triangle(v3(o), v3(d), a, v3(v1) - a, v3(v2) - a, out_tuv[0], out_tuv[1], out_tuv[2]) ? 1 : 0;
+}
+void orc_r2(uint32_t i, float out2[2]) { vec2 r = r2_sequence(i); out2[0] = r.x; out2[1] = r.y; }
+float orc_vdc(uint32_t bits) { return radical_inverse_vdc(bits); }
+void orc_sample_2d(const orc_scene* s, uint32_t flags, uint32_t px, uint32_t py, uint32_t frame, uint32_t index, float out2[2]) {
+    SceneView sv = s->view();
+    RandomSamplerState r = rng_init(px, py, frame); r.index = index;
+    vec2 u = sample_2d(sv, flags, px, py, frame, r); out2[0] = u.x; out2[1] = u.y;
+}
+void orc_agx(const float in3[3], float out3[3]) { vec3 c = agx_eotf(agx_look(agx(v3(in3)))); out3[0] = c.x; out3[1] = c.y; out3[2] = c.z; }
+float orc_contract_probe(float a, float b, float c) { return contract_probe(a, b, c); }
+
+}  // extern "C"
