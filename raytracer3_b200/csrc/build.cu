@@ -1,0 +1,341 @@
+/*
+ * build.cu — GPU acceleration-structure build (replaces the driver's vkCmdBuildAccelerationStructuresKHR
+ * behind RayTracingContext::create_acceleration_structure, /root/reference/src/renderer/vulkan/raytracing.rs:88-148).
+ *
+ * Stages (all on the device; the host only reads back 4-byte counters between collapse levels):
+ *   k_flatten        scene buffers + instances -> world-space (v0,e1,e2,id) records, scene AABB
+ *   k_morton         63-bit Morton code of each triangle's box centre
+ *   radix sort       8 passes x 8 bits, stable: k_radix_hist -> k_radix_scan -> k_radix_scatter
+ *   k_gather_sorted  triangles into Morton order
+ *   k_lbvh_hierarchy Karras 2012, one thread per internal node
+ *   k_refit          bottom-up AABBs + subtree counts with one atomic flag per internal node
+ *   k_collapse       BVH2 -> 8-wide quantised nodes, one thread per wide node, level by level
+ */
+#include "common.cuh"
+
+using namespace rt3b;
+
+namespace {
+
+__device__ __forceinline__ int float_to_ordered(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7FFFFFFF; }
+__host__ __device__ __forceinline__ float ordered_to_float(int i) {
+    int j = i >= 0 ? i : i ^ 0x7FFFFFFF;
+#ifdef __CUDA_ARCH__
+    return __int_as_float(j);
+#else
+    float f; memcpy(&f, &j, 4); return f;
+#endif
+}
+
+__global__ void k_init_bounds(int* b) {
+    if (threadIdx.x < 3) b[threadIdx.x] = 0x7F7FFFFF;            /* +FLT_MAX ordered */
+    else if (threadIdx.x < 6) b[threadIdx.x] = (int)0x80800000;  /* ordered(-FLT_MAX) = 0xFF7FFFFF ^ 0x7FFFFFFF */
+}
+
+__global__ void __launch_bounds__(256) k_flatten(rt3m::SceneView s, uint32_t n, Tri48* tris, int* bounds) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+    if (i < n) {
+        uint32_t seg = rt3m::find_segment(s, i);
+        rt3m::vec3 a, b, c;
+        rt3m::world_triangle(s, seg, i - s.seg_first_prim[seg], a, b, c);
+        Tri48 t;
+        t.v0[0] = a.x; t.v0[1] = a.y; t.v0[2] = a.z; t.prim = i;
+        t.e1[0] = b.x - a.x; t.e1[1] = b.y - a.y; t.e1[2] = b.z - a.z; t.pad0 = 0;
+        t.e2[0] = c.x - a.x; t.e2[1] = c.y - a.y; t.e2[2] = c.z - a.z; t.pad1 = 0;
+        float4* o = (float4*)(tris + i);
+        o[0] = make_float4(t.v0[0], t.v0[1], t.v0[2], __uint_as_float(i));
+        o[1] = make_float4(t.e1[0], t.e1[1], t.e1[2], 0.f);
+        o[2] = make_float4(t.e2[0], t.e2[1], t.e2[2], 0.f);
+        lo[0] = fminf(a.x, fminf(b.x, c.x)); hi[0] = fmaxf(a.x, fmaxf(b.x, c.x));
+        lo[1] = fminf(a.y, fminf(b.y, c.y)); hi[1] = fmaxf(a.y, fmaxf(b.y, c.y));
+        lo[2] = fminf(a.z, fminf(b.z, c.z)); hi[2] = fmaxf(a.z, fmaxf(b.z, c.z));
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        for (int off = 16; off; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xFFFFFFFFu, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xFFFFFFFFu, hi[k], off));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(bounds + k, float_to_ordered(lo[k]));
+            atomicMax(bounds + 3 + k, float_to_ordered(hi[k]));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_morton(const Tri48* tris, uint32_t n, float3 lo, float3 inv_ext, uint64_t* keys, uint32_t* vals) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float l[3], h[3];
+    tri_bounds(tris[i], 0.f, l, h);
+    float cx = (0.5f * (l[0] + h[0]) - lo.x) * inv_ext.x, cy = (0.5f * (l[1] + h[1]) - lo.y) * inv_ext.y, cz = (0.5f * (l[2] + h[2]) - lo.z) * inv_ext.z;
+    keys[i] = morton63(cx, cy, cz);
+    vals[i] = i;
+}
+
+/* ---- radix sort: 8-bit digits, tile of RADIX_TILE keys per block, stable --------------------------- */
+constexpr int RADIX_THREADS = 256;
+constexpr int RADIX_ROUNDS = 16;
+constexpr int RADIX_TILE = RADIX_THREADS * RADIX_ROUNDS;
+
+__global__ void __launch_bounds__(RADIX_THREADS) k_radix_hist(const uint64_t* keys, uint32_t n, int shift, uint32_t* hist, uint32_t nblocks) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t base = blockIdx.x * RADIX_TILE;
+    for (int r = 0; r < RADIX_ROUNDS; ++r) {
+        uint32_t i = base + r * RADIX_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(uint32_t)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+/* exclusive scan of `m` counters by one block of 1024 threads (m = 256 * nblocks) */
+__global__ void __launch_bounds__(1024) k_radix_scan(uint32_t* data, uint32_t m) {
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t base = 0; base < m; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t v = i < m ? data[i] : 0u;
+        uint32_t x = v;
+        for (int off = 1; off < 32; off <<= 1) { uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, off); if (lane >= off) x += y; }
+        if (lane == 31) warp_sums[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = warp_sums[lane];
+            for (int off = 1; off < 32; off <<= 1) { uint32_t y = __shfl_up_sync(0xFFFFFFFFu, w, off); if (lane >= off) w += y; }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        uint32_t excl = x - v + (warp ? warp_sums[warp - 1] : 0u) + carry;
+        if (i < m) data[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                                                                 uint32_t n, int shift, const uint32_t* hist, uint32_t nblocks) {
+    __shared__ uint32_t base[256];
+    __shared__ uint32_t wcnt[RADIX_THREADS / 32][256];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    base[threadIdx.x] = hist[threadIdx.x * nblocks + blockIdx.x];
+    const uint32_t tile = blockIdx.x * RADIX_TILE;
+    for (int r = 0; r < RADIX_ROUNDS; ++r) {
+        for (int w = 0; w < RADIX_THREADS / 32; ++w) wcnt[w][threadIdx.x] = 0;
+        __syncthreads();
+        uint32_t i = tile + r * RADIX_THREADS + threadIdx.x;
+        bool valid = i < n;
+        uint64_t key = valid ? keys_in[i] : 0ull;
+        uint32_t val = valid ? vals_in[i] : 0u;
+        uint32_t d = valid ? ((uint32_t)(key >> shift) & 255u) : (256u + lane);
+        uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
+        uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+        if (valid && rank == 0) wcnt[warp][d] = __popc(peers);
+        __syncthreads();
+        {   /* thread = digit: exclusive prefix over warps, advance the running base */
+            uint32_t run = base[threadIdx.x];
+            for (int w = 0; w < RADIX_THREADS / 32; ++w) { uint32_t t = wcnt[w][threadIdx.x]; wcnt[w][threadIdx.x] = run; run += t; }
+            base[threadIdx.x] = run;
+        }
+        __syncthreads();
+        if (valid) {
+            uint32_t pos = wcnt[warp][d] + rank;
+            keys_out[pos] = key; vals_out[pos] = val;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_gather_sorted(const Tri48* tris, const uint32_t* order, uint32_t n, Tri48* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4* s = (const float4*)(tris + order[i]);
+    float4* d = (float4*)(out + i);
+    d[0] = s[0]; d[1] = s[1]; d[2] = s[2];
+}
+
+__global__ void __launch_bounds__(256) k_lbvh_hierarchy(const uint64_t* keys, int n, Bvh2Node* nodes, uint32_t* parent) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n - 1) lbvh_build_node(keys, n, i, nodes, parent);
+}
+
+__global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_t n, float pad, Bvh2Node* nodes, const uint32_t* parent, uint32_t* flags,
+                                               uint32_t* counts) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    Bvh2Node leaf;
+    tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi);
+    leaf.left = leaf.right = 0;
+    nodes[n - 1 + k] = leaf;
+    uint32_t cur = parent[n - 1 + k];
+    while (cur != 0xFFFFFFFFu) {
+        __threadfence();
+        if (atomicAdd(flags + cur, 1u) == 0u) return;   /* first arrival: the sibling subtree is not ready yet */
+        volatile Bvh2Node* nd = nodes + cur;
+        uint32_t l = nd->left, r = nd->right;
+        uint32_t li = (l & LEAF_FLAG) ? n - 1 + (l & ~LEAF_FLAG) : l, ri = (r & LEAF_FLAG) ? n - 1 + (r & ~LEAF_FLAG) : r;
+        volatile Bvh2Node* a = nodes + li;
+        volatile Bvh2Node* b = nodes + ri;
+        for (int ax = 0; ax < 3; ++ax) { nd->lo[ax] = fminf(a->lo[ax], b->lo[ax]); nd->hi[ax] = fmaxf(a->hi[ax], b->hi[ax]); }
+        volatile uint32_t* vc = counts;
+        vc[cur] = ((l & LEAF_FLAG) ? 1u : vc[l]) + ((r & LEAF_FLAG) ? 1u : vc[r]);
+        cur = parent[cur];
+    }
+}
+
+__global__ void __launch_bounds__(128) k_collapse(CollapseCtx c, const uint32_t* items, uint32_t count) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) collapse_one(c, items[2 * i], items[2 * i + 1]);
+}
+
+__global__ void k_empty_root(WideNode* nodes) {
+    if (threadIdx.x < 20) nodes[0].w[threadIdx.x] = 0;
+}
+
+struct StageTimer {
+    rt3_context* c; cudaStream_t st; cudaEvent_t a, b;
+    StageTimer(rt3_context* c_, cudaStream_t s) : c(c_), st(s) { a = c->ev[0]; b = c->ev[1]; }
+    void begin() { cudaEventRecord(a, st); }
+    double end() { cudaEventRecord(b, st); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
+};
+
+}  // namespace
+
+void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out) {
+    (void)flags;
+    rt3_build_stats bs;
+    memset(&bs, 0, sizeof(bs));
+    const uint32_t n = c->n_triangles;
+    bs.triangles = n;
+    StageTimer tm(c, st);
+    cudaEvent_t total_a = c->ev[2], total_b = c->ev[3];
+    cudaEventRecord(total_a, st);
+
+    Tri48* out_tris = ensure<Tri48>(c, c->bvh_tris, n ? n : 1);
+    if (n == 0) {
+        WideNode* nodes = ensure<WideNode>(c, c->bvh_nodes, 1);
+        RT3_LAUNCH(c, k_empty_root, 1, 32, 0, st, nodes);
+        RT3_CUDA(c, cudaStreamSynchronize(st));
+        c->n_wide_nodes = 1; bs.wide_nodes = 1; bs.node_bytes = sizeof(WideNode);
+        c->accel_valid = true; c->last_build = bs;
+        if (out) *out = bs;
+        return;
+    }
+    Scratch s_tris, s_sorted, s_keys[2], s_vals[2], s_hist, s_nodes2, s_parent, s_flags, s_counts, s_items[2], s_misc;
+    auto cleanup = [&]() {
+        s_tris.release(); s_sorted.release(); s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release();
+        s_nodes2.release(); s_parent.release(); s_flags.release(); s_counts.release(); s_items[0].release(); s_items[1].release(); s_misc.release();
+    };
+    try {
+        /* flatten */
+        Tri48* tris = ensure<Tri48>(c, s_tris, n);
+        int* d_bounds = (int*)ensure<uint32_t>(c, s_misc, 16);   /* [0..5] bounds, [8] node ctr, [9] tri ctr, [10] queue ctr, [12],[13] sah */
+        tm.begin();
+        RT3_LAUNCH(c, k_init_bounds, 1, 32, 0, st, d_bounds);
+        RT3_LAUNCH(c, k_flatten, div_up(n, 256), 256, 0, st, c->view, n, tris, d_bounds);
+        int hb[6];
+        RT3_CUDA(c, cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, st));
+        bs.ms_flatten = tm.end();
+        float lo[3], hi[3];
+        for (int k = 0; k < 3; ++k) { lo[k] = ordered_to_float(hb[k]); hi[k] = ordered_to_float(hb[3 + k]); bs.scene_lo[k] = lo[k]; bs.scene_hi[k] = hi[k]; }
+        float ext = fmaxf(hi[0] - lo[0], fmaxf(hi[1] - lo[1], hi[2] - lo[2]));
+        const float pad = ext * (1.0f / 65536.0f);
+        /* morton */
+        uint64_t* keys0 = ensure<uint64_t>(c, s_keys[0], n);
+        uint64_t* keys1 = ensure<uint64_t>(c, s_keys[1], n);
+        uint32_t* vals0 = ensure<uint32_t>(c, s_vals[0], n);
+        uint32_t* vals1 = ensure<uint32_t>(c, s_vals[1], n);
+        tm.begin();
+        float3 flo = make_float3(lo[0], lo[1], lo[2]);
+        float3 inv = make_float3(hi[0] > lo[0] ? 1.0f / (hi[0] - lo[0]) : 0.f, hi[1] > lo[1] ? 1.0f / (hi[1] - lo[1]) : 0.f,
+                                 hi[2] > lo[2] ? 1.0f / (hi[2] - lo[2]) : 0.f);
+        RT3_LAUNCH(c, k_morton, div_up(n, 256), 256, 0, st, tris, n, flo, inv, keys0, vals0);
+        bs.ms_morton = tm.end();
+        /* sort */
+        const uint32_t nblocks = div_up(n, RADIX_TILE);
+        uint32_t* hist = ensure<uint32_t>(c, s_hist, 256 * (size_t)nblocks);
+        tm.begin();
+        for (int pass = 0; pass < 8; ++pass) {
+            const uint64_t* ki = (pass & 1) ? keys1 : keys0; uint64_t* ko = (pass & 1) ? keys0 : keys1;
+            const uint32_t* vi = (pass & 1) ? vals1 : vals0; uint32_t* vo = (pass & 1) ? vals0 : vals1;
+            RT3_LAUNCH(c, k_radix_hist, nblocks, RADIX_THREADS, 0, st, ki, n, pass * 8, hist, nblocks);
+            RT3_LAUNCH(c, k_radix_scan, 1, 1024, 0, st, hist, 256u * nblocks);
+            RT3_LAUNCH(c, k_radix_scatter, nblocks, RADIX_THREADS, 0, st, ki, vi, ko, vo, n, pass * 8, hist, nblocks);
+        }
+        Tri48* sorted = ensure<Tri48>(c, s_sorted, n);
+        RT3_LAUNCH(c, k_gather_sorted, div_up(n, 256), 256, 0, st, tris, vals0, n, sorted);
+        bs.ms_sort = tm.end();
+        s_tris.release();
+        /* hierarchy */
+        Bvh2Node* nodes2 = ensure<Bvh2Node>(c, s_nodes2, 2 * (size_t)n);
+        uint32_t* parent = ensure<uint32_t>(c, s_parent, 2 * (size_t)n);
+        uint32_t* nflags = ensure<uint32_t>(c, s_flags, n);
+        uint32_t* counts = ensure<uint32_t>(c, s_counts, n);
+        tm.begin();
+        RT3_CUDA(c, cudaMemsetAsync(parent, 0xFF, sizeof(uint32_t) * 2 * (size_t)n, st));
+        RT3_CUDA(c, cudaMemsetAsync(nflags, 0, sizeof(uint32_t) * n, st));
+        RT3_CUDA(c, cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n, st));
+        if (n > 1) RT3_LAUNCH(c, k_lbvh_hierarchy, div_up(n - 1, 256), 256, 0, st, keys0, (int)n, nodes2, parent);
+        bs.ms_hierarchy = tm.end();
+        tm.begin();
+        RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, pad, nodes2, parent, nflags, counts);
+        bs.ms_refit = tm.end();
+        s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release(); s_parent.release(); s_flags.release();
+        /* collapse */
+        WideNode* wide = ensure<WideNode>(c, c->bvh_nodes, n);
+        uint32_t* items0 = ensure<uint32_t>(c, s_items[0], 2 * (size_t)n + 2);
+        uint32_t* items1 = ensure<uint32_t>(c, s_items[1], 2 * (size_t)n + 2);
+        uint32_t* ctr = (uint32_t*)d_bounds + 8;
+        tm.begin();
+        uint32_t init_ctr[8] = {1u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        RT3_CUDA(c, cudaMemcpyAsync(ctr, init_ctr, sizeof(init_ctr), cudaMemcpyHostToDevice, st));
+        uint32_t first_item[2] = {n == 1 ? (LEAF_FLAG | 0u) : 0u, 0u};
+        RT3_CUDA(c, cudaMemcpyAsync(items0, first_item, sizeof(first_item), cudaMemcpyHostToDevice, st));
+        CollapseCtx cc;
+        cc.nodes = nodes2; cc.counts = counts; cc.tris_sorted = sorted; cc.n_leaves = n; cc.out_nodes = wide; cc.out_tris = out_tris;
+        cc.node_counter = ctr; cc.tri_counter = ctr + 1; cc.next_count = ctr + 2; cc.sah_accum = (float*)(ctr + 4);
+        uint32_t count = 1, levels = 0;
+        uint32_t* cur = items0; uint32_t* nxt = items1;
+        while (count) {
+            RT3_CUDA(c, cudaMemsetAsync(ctr + 2, 0, 4, st));
+            cc.next_items = nxt;
+            RT3_LAUNCH(c, k_collapse, div_up(count, 128), 128, 0, st, cc, cur, count);
+            RT3_CUDA(c, cudaMemcpyAsync(&count, ctr + 2, 4, cudaMemcpyDeviceToHost, st));
+            RT3_CUDA(c, cudaStreamSynchronize(st));
+            std::swap(cur, nxt);
+            levels++;
+            if (levels > 4 * RT3_MAX_STACK) RT3_FAIL(c, RT3_ERR_STATE, "BVH collapse did not terminate");
+        }
+        uint32_t fin[8];
+        RT3_CUDA(c, cudaMemcpyAsync(fin, ctr, sizeof(fin), cudaMemcpyDeviceToHost, st));
+        bs.ms_collapse = tm.end();
+        if (levels >= RT3_MAX_STACK) RT3_FAIL(c, RT3_ERR_STATE, "wide BVH deeper than the traversal stack");
+        if (fin[1] != n) RT3_FAIL(c, RT3_ERR_STATE, "BVH collapse lost triangles");
+        c->n_wide_nodes = fin[0];
+        bs.wide_nodes = fin[0]; bs.bvh2_nodes = 2 * n - 1; bs.levels = levels;
+        bs.node_bytes = (uint64_t)fin[0] * sizeof(WideNode); bs.tri_bytes = (uint64_t)n * sizeof(Tri48);
+        float sah_nodes, sah_tris;
+        memcpy(&sah_nodes, &fin[4], 4); memcpy(&sah_tris, &fin[5], 4);
+        float ex = hi[0] - lo[0] + 2 * pad, ey = hi[1] - lo[1] + 2 * pad, ez = hi[2] - lo[2] + 2 * pad;
+        float root_area = 2.0f * (ex * ey + ey * ez + ez * ex);
+        bs.sah_cost = root_area > 0 ? (sah_nodes + sah_tris) / root_area : 0.f;
+    } catch (...) {
+        cleanup();
+        throw;
+    }
+    cleanup();
+    cudaEventRecord(total_b, st); cudaEventSynchronize(total_b);
+    float ms = 0; cudaEventElapsedTime(&ms, total_a, total_b); bs.ms_total = ms;
+    c->accel_valid = true; c->last_build = bs;
+    if (out) *out = bs;
+}

@@ -1,0 +1,432 @@
+/*
+ * bvh_logic.h — per-thread logic of the GPU BVH builder and of the wide-BVH traversal.
+ *
+ * Replaces what the reference delegates to the Vulkan driver / RT cores:
+ *   vkCmdBuildAccelerationStructuresKHR   /root/reference/src/renderer/vulkan/raytracing.rs:106-141
+ *   TraceRay inside vkCmdTraceRaysKHR     /root/reference/src/renderer/pipeline_cache/mod.rs:64-73
+ *
+ * Everything here is `RT3_HD` (host + device): the CUDA kernels in build.cu / trace.cu call these
+ * functions one thread at a time, and tests/emu compiles the very same functions with g++ to check the
+ * algorithmic logic (Karras ranges, wide collapse, node encoding, traversal order) on a machine
+ * without a GPU.  The emulation is test infrastructure; librt3.so contains device code only.
+ *
+ * Design (B200 has no RT cores, so traversal is SM software):
+ *   LBVH   : 63-bit Morton codes -> radix sort -> Karras 2012 hierarchy -> atomic bottom-up refit
+ *   wide   : BVH2 collapsed top-down into an 8-wide node with child boxes quantised to 8 bits on a
+ *            per-node power-of-two grid (80 bytes per node = five 16-byte loads), children placed in
+ *            octant slots so that near-to-far order is a bit trick on the ray's sign octant
+ *            (after Ylitie, Karras, Laine 2017), triangles stored next to the leaves as 48-byte
+ *            (v0, e1, e2, id) records = three 16-byte loads.
+ */
+#ifndef RT3_BVH_LOGIC_H
+#define RT3_BVH_LOGIC_H
+
+#include "rt3_shared_math.h"
+
+namespace rt3b {
+
+using rt3m::vec3;
+
+/* ------------------------------------------------------------------------------------------------ */
+struct Bvh2Node {            /* 32 B */
+    float lo[3]; uint32_t left;
+    float hi[3]; uint32_t right;
+};
+struct Tri48 {               /* 48 B: three float4 */
+    float v0[3]; uint32_t prim;
+    float e1[3]; uint32_t pad0;
+    float e2[3]; uint32_t pad1;
+};
+struct WideNode { uint32_t w[20]; };   /* 80 B: see encode_wide_node() */
+
+static const uint32_t LEAF_FLAG = 0x80000000u;
+#define RT3_MAX_STACK 64
+
+struct u32x4 { uint32_t x, y, z, w; };
+
+#ifdef __CUDA_ARCH__
+#define RT3_ATOMIC_ADD_U32(p, v) atomicAdd((p), (v))
+#define RT3_ATOMIC_ADD_F32(p, v) atomicAdd((p), (v))
+RT3_HD u32x4 ld_u32x4(const void* p) { uint4 v = __ldg((const uint4*)p); u32x4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r; }
+RT3_HD int clz32(uint32_t x) { return __clz((int)x); }
+RT3_HD int clz64(uint64_t x) { return __clzll((long long)x); }
+RT3_HD int popc32(uint32_t x) { return __popc(x); }
+RT3_HD int bfind32(uint32_t x) { return 31 - __clz((int)x); }
+/* per-byte sign fill: 0x80 -> 0xFF, else 0x00 */
+RT3_HD uint32_t sign_extend_s8x4(uint32_t x) { return __byte_perm(x, 0, 0xBA98); }
+#else
+inline uint32_t host_atomic_add(uint32_t* p, uint32_t v) { uint32_t o = *p; *p += v; return o; }
+inline float host_atomic_add(float* p, float v) { float o = *p; *p += v; return o; }
+#define RT3_ATOMIC_ADD_U32(p, v) rt3b::host_atomic_add((p), (v))
+#define RT3_ATOMIC_ADD_F32(p, v) rt3b::host_atomic_add((p), (v))
+RT3_HD u32x4 ld_u32x4(const void* p) { u32x4 r; memcpy(&r, p, 16); return r; }
+RT3_HD int clz32(uint32_t x) { return x ? __builtin_clz(x) : 32; }
+RT3_HD int clz64(uint64_t x) { return x ? __builtin_clzll(x) : 64; }
+RT3_HD int popc32(uint32_t x) { return __builtin_popcount(x); }
+RT3_HD int bfind32(uint32_t x) { return 31 - __builtin_clz(x); }
+RT3_HD uint32_t sign_extend_s8x4(uint32_t x) {
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) if (x & (0x80u << (8 * i))) r |= 0xFFu << (8 * i);
+    return r;
+}
+#endif
+
+/* ---------------------------------------------------------------- Morton codes ----------------- */
+RT3_HD uint64_t expand_bits_21(uint64_t v) {
+    v &= 0x1FFFFFull;
+    v = (v | (v << 32)) & 0x001F00000000FFFFull;
+    v = (v | (v << 16)) & 0x001F0000FF0000FFull;
+    v = (v | (v << 8)) & 0x100F00F00F00F00Full;
+    v = (v | (v << 4)) & 0x10C30C30C30C30C3ull;
+    v = (v | (v << 2)) & 0x1249249249249249ull;
+    return v;
+}
+/* x, y, z in [0,1] */
+RT3_HD uint64_t morton63(float x, float y, float z) {
+    const float S = 2097152.0f; /* 2^21 */
+    float fx = rt3m::min_(rt3m::max_(x * S, 0.0f), S - 1.0f);
+    float fy = rt3m::min_(rt3m::max_(y * S, 0.0f), S - 1.0f);
+    float fz = rt3m::min_(rt3m::max_(z * S, 0.0f), S - 1.0f);
+    return (expand_bits_21((uint64_t)fx) << 2) | (expand_bits_21((uint64_t)fy) << 1) | expand_bits_21((uint64_t)fz);
+}
+
+/* ---------------------------------------------------------------- Karras 2012 hierarchy -------- */
+/* Common-prefix length of keys i and j, with the index as tie-breaker for duplicate keys. */
+RT3_HD int lbvh_delta(const uint64_t* keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + clz32((uint32_t)i ^ (uint32_t)j);
+    return clz64(a ^ b);
+}
+/* Internal node i of n-1; leaves are referenced as LEAF_FLAG | sorted index.  parent[] has 2n-1
+ * entries: internal nodes first, then leaves at n-1+k. */
+RT3_HD void lbvh_build_node(const uint64_t* keys, int n, int i, Bvh2Node* nodes, uint32_t* parent) {
+    int d = (lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = lbvh_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (lbvh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = lbvh_delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (lbvh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + (d < 0 ? -1 : 0);
+    int lo = i < j ? i : j, hi = i < j ? j : i;
+    uint32_t left = (lo == gamma) ? (LEAF_FLAG | (uint32_t)gamma) : (uint32_t)gamma;
+    uint32_t right = (hi == gamma + 1) ? (LEAF_FLAG | (uint32_t)(gamma + 1)) : (uint32_t)(gamma + 1);
+    nodes[i].left = left;
+    nodes[i].right = right;
+    parent[(left & LEAF_FLAG) ? (uint32_t)(n - 1) + (left & ~LEAF_FLAG) : left] = (uint32_t)i;
+    parent[(right & LEAF_FLAG) ? (uint32_t)(n - 1) + (right & ~LEAF_FLAG) : right] = (uint32_t)i;
+    if (i == 0) parent[0] = 0xFFFFFFFFu;
+}
+
+RT3_HD void tri_bounds(const Tri48& t, float pad, float lo[3], float hi[3]) {
+    for (int a = 0; a < 3; ++a) {
+        float p0 = t.v0[a], p1 = t.v0[a] + t.e1[a], p2 = t.v0[a] + t.e2[a];
+        lo[a] = rt3m::min_(p0, rt3m::min_(p1, p2)) - pad;
+        hi[a] = rt3m::max_(p0, rt3m::max_(p1, p2)) + pad;
+    }
+}
+RT3_HD float box_area(const float lo[3], const float hi[3]) {
+    float ex = hi[0] - lo[0], ey = hi[1] - lo[1], ez = hi[2] - lo[2];
+    return 2.0f * (ex * ey + ey * ez + ez * ex);
+}
+
+/* ---------------------------------------------------------------- BVH2 -> 8-wide collapse ------ */
+/* BVH2 storage for the collapse: nodes[0 .. n-2] internal, nodes[n-1 .. 2n-2] leaves (box only);
+ * counts[i] = triangles below internal node i. */
+struct CollapseCtx {
+    const Bvh2Node* nodes;
+    const uint32_t* counts;
+    const Tri48* tris_sorted;     /* leaf k -> triangle */
+    uint32_t n_leaves;
+    WideNode* out_nodes;
+    Tri48* out_tris;
+    uint32_t* node_counter;       /* next free wide node  */
+    uint32_t* tri_counter;        /* next free triangle   */
+    uint32_t* next_items;         /* pairs (bvh2 ref, wide index) for the next level */
+    uint32_t* next_count;
+    float* sah_accum;             /* [0] node term, [1] triangle term (area-weighted)   */
+};
+
+RT3_HD uint32_t bvh2_slot(const CollapseCtx& c, uint32_t ref) {
+    return (ref & LEAF_FLAG) ? (c.n_leaves - 1u) + (ref & ~LEAF_FLAG) : ref;
+}
+RT3_HD uint32_t bvh2_count(const CollapseCtx& c, uint32_t ref) { return (ref & LEAF_FLAG) ? 1u : c.counts[ref]; }
+
+/* Smallest e with extent * 2^-e <= 255 (then widened by the caller if rounding pushes a child past 255). */
+RT3_HD int quant_exponent(float extent) {
+    if (!(extent > 0.0f)) return -100;
+    float q = extent / 255.0f;
+    int e = (int)((rt3m::as_uint(q) >> 23) & 0xFF) - 127;   /* floor(log2 q) for normal q */
+    if (rt3m::exp2i(e < -126 ? -126 : e) < q) e += 1;
+    if (e < -100) e = -100;
+    if (e > 100) e = 100;
+    return e;
+}
+
+/*
+ * Node layout (20 words):
+ *   w0..w2  p = node box min (float)            w3  ex | ey<<8 | ez<<16 | imask<<24   (e biased by 127)
+ *   w4      child_base (first inner child)      w5  tri_base
+ *   w6,w7   meta[8]: 0 = empty; inner: 0x20 | (24 + slot); leaf: unary(count 1..3) << 5 | tri offset (0..23)
+ *   w8,w9   qlo.x[8]   w10,w11 qlo.y[8]   w12,w13 qlo.z[8]
+ *   w14,w15 qhi.x[8]   w16,w17 qhi.y[8]   w18,w19 qhi.z[8]
+ * child box = p + q * 2^e, conservative (floor / ceil).
+ */
+RT3_HD void collapse_one(const CollapseCtx& c, uint32_t ref, uint32_t wide_index) {
+    uint32_t ch[8];
+    int nc;
+    uint32_t self = bvh2_slot(c, ref);
+    if (ref & LEAF_FLAG) { ch[0] = ref; nc = 1; }
+    else { ch[0] = c.nodes[ref].left; ch[1] = c.nodes[ref].right; nc = 2; }
+    /* greedy: open the inner child of largest surface area until 8 slots are used */
+    while (nc < 8) {
+        int best = -1; float best_a = -1.0f;
+        for (int k = 0; k < nc; ++k) {
+            if (ch[k] & LEAF_FLAG) continue;
+            const Bvh2Node& nd = c.nodes[ch[k]];
+            float a = box_area(nd.lo, nd.hi);
+            if (a > best_a) { best_a = a; best = k; }
+        }
+        if (best < 0) break;
+        uint32_t r = ch[best];
+        ch[best] = c.nodes[r].left;
+        ch[nc++] = c.nodes[r].right;
+    }
+    const Bvh2Node& me = c.nodes[self];
+    float cx = 0.5f * (me.lo[0] + me.hi[0]), cy = 0.5f * (me.lo[1] + me.hi[1]), cz = 0.5f * (me.lo[2] + me.hi[2]);
+    /* octant slot assignment: greedy maximisation of sum dot(child centre - node centre, corner direction) */
+    float cost[8][8];
+    for (int k = 0; k < nc; ++k) {
+        const Bvh2Node& nd = c.nodes[bvh2_slot(c, ch[k])];
+        float dx = 0.5f * (nd.lo[0] + nd.hi[0]) - cx, dy = 0.5f * (nd.lo[1] + nd.hi[1]) - cy, dz = 0.5f * (nd.lo[2] + nd.hi[2]) - cz;
+        for (int s = 0; s < 8; ++s) cost[k][s] = ((s & 1) ? dx : -dx) + ((s & 2) ? dy : -dy) + ((s & 4) ? dz : -dz);
+    }
+    int slot_child[8];
+    for (int s = 0; s < 8; ++s) slot_child[s] = -1;
+    uint32_t child_done = 0;
+    for (int it = 0; it < nc; ++it) {
+        int bk = -1, bs = -1; float bc = -3.4e38f;
+        for (int k = 0; k < nc; ++k) {
+            if (child_done & (1u << k)) continue;
+            for (int s = 0; s < 8; ++s) {
+                if (slot_child[s] >= 0) continue;
+                if (cost[k][s] > bc) { bc = cost[k][s]; bk = k; bs = s; }
+            }
+        }
+        slot_child[bs] = bk; child_done |= 1u << bk;
+    }
+    /* classify, count */
+    uint32_t n_inner = 0, n_tris = 0, imask = 0;
+    for (int s = 0; s < 8; ++s) {
+        int k = slot_child[s];
+        if (k < 0) continue;
+        uint32_t cnt = bvh2_count(c, ch[k]);
+        if (cnt <= 3u) n_tris += cnt; else { n_inner++; imask |= 1u << s; }
+    }
+    uint32_t child_base = n_inner ? RT3_ATOMIC_ADD_U32(c.node_counter, n_inner) : 0u;
+    uint32_t tri_base = n_tris ? RT3_ATOMIC_ADD_U32(c.tri_counter, n_tris) : 0u;
+    /* quantisation grid */
+    int e[3];
+    for (int a = 0; a < 3; ++a) e[a] = quant_exponent(me.hi[a] - me.lo[a]);
+    uint32_t qlo[3][8], qhi[3][8];
+    for (int a = 0; a < 3; ++a) {
+        for (;;) {
+            float inv = rt3m::exp2i(-e[a]);
+            bool ok = true;
+            for (int s = 0; s < 8; ++s) {
+                int k = slot_child[s];
+                if (k < 0) { qlo[a][s] = 255; qhi[a][s] = 0; continue; }
+                const Bvh2Node& nd = c.nodes[bvh2_slot(c, ch[k])];
+                float fl = rt3m::floor_((nd.lo[a] - me.lo[a]) * inv);
+                float fh = -rt3m::floor_(-((nd.hi[a] - me.lo[a]) * inv));
+                if (fl < 0.0f) fl = 0.0f;
+                if (fh > 255.0f) { ok = false; break; }
+                if (fh < fl) fh = fl;
+                /* make sure the decoded planes really enclose the child (guards the rounding of the subtraction) */
+                float scale = rt3m::exp2i(e[a]);
+                if (rt3m::fma_(fl, scale, me.lo[a]) > nd.lo[a] && fl > 0.0f) fl -= 1.0f;
+                if (rt3m::fma_(fh, scale, me.lo[a]) < nd.hi[a]) { fh += 1.0f; if (fh > 255.0f) { ok = false; break; } }
+                qlo[a][s] = (uint32_t)fl; qhi[a][s] = (uint32_t)fh;
+            }
+            if (ok) break;
+            e[a] += 1;
+        }
+    }
+    WideNode out;
+    out.w[0] = rt3m::as_uint(me.lo[0]); out.w[1] = rt3m::as_uint(me.lo[1]); out.w[2] = rt3m::as_uint(me.lo[2]);
+    out.w[3] = (uint32_t)(e[0] + 127) | ((uint32_t)(e[1] + 127) << 8) | ((uint32_t)(e[2] + 127) << 16) | (imask << 24);
+    out.w[4] = child_base; out.w[5] = tri_base;
+    uint32_t meta[8];
+    uint32_t tri_off = 0, inner_rank = 0;
+    float my_area = box_area(me.lo, me.hi);
+    float tri_term = 0.0f;
+    for (int s = 0; s < 8; ++s) {
+        int k = slot_child[s];
+        if (k < 0) { meta[s] = 0; continue; }
+        uint32_t cnt = bvh2_count(c, ch[k]);
+        if (cnt > 3u) {
+            meta[s] = 0x20u | (24u + (uint32_t)s);
+            uint32_t q = RT3_ATOMIC_ADD_U32(c.next_count, 1u);
+            c.next_items[2 * q] = ch[k];
+            c.next_items[2 * q + 1] = child_base + inner_rank;
+            inner_rank++;
+        } else {
+            meta[s] = ((cnt == 1u ? 1u : (cnt == 2u ? 3u : 7u)) << 5) | tri_off;
+            /* gather the (<= 3) triangles below ch[k] */
+            uint32_t st[4]; int sp = 0; st[sp++] = ch[k];
+            while (sp) {
+                uint32_t r = st[--sp];
+                if (r & LEAF_FLAG) { c.out_tris[tri_base + tri_off] = c.tris_sorted[r & ~LEAF_FLAG]; tri_off++; }
+                else { st[sp++] = c.nodes[r].right; st[sp++] = c.nodes[r].left; }
+            }
+            const Bvh2Node& nd = c.nodes[bvh2_slot(c, ch[k])];
+            tri_term += box_area(nd.lo, nd.hi) * (float)cnt;
+        }
+    }
+    out.w[6] = meta[0] | (meta[1] << 8) | (meta[2] << 16) | (meta[3] << 24);
+    out.w[7] = meta[4] | (meta[5] << 8) | (meta[6] << 16) | (meta[7] << 24);
+    for (int a = 0; a < 3; ++a) {
+        out.w[8 + 2 * a] = qlo[a][0] | (qlo[a][1] << 8) | (qlo[a][2] << 16) | (qlo[a][3] << 24);
+        out.w[9 + 2 * a] = qlo[a][4] | (qlo[a][5] << 8) | (qlo[a][6] << 16) | (qlo[a][7] << 24);
+        out.w[14 + 2 * a] = qhi[a][0] | (qhi[a][1] << 8) | (qhi[a][2] << 16) | (qhi[a][3] << 24);
+        out.w[15 + 2 * a] = qhi[a][4] | (qhi[a][5] << 8) | (qhi[a][6] << 16) | (qhi[a][7] << 24);
+    }
+    c.out_nodes[wide_index] = out;
+    if (c.sah_accum) {
+        RT3_ATOMIC_ADD_F32(c.sah_accum, my_area);
+        RT3_ATOMIC_ADD_F32(c.sah_accum + 1, tri_term);
+    }
+}
+
+/* ---------------------------------------------------------------- traversal -------------------- */
+struct RayPrep {
+    float ox, oy, oz, dx, dy, dz;     /* origin, direction                        */
+    float idx, idy, idz;               /* safe reciprocal direction                */
+    uint32_t octinv4;                  /* (7 - octant) replicated in 4 bytes       */
+    float tmin;
+};
+RT3_HD float safe_rcp_dir(float d) {
+    const float tiny = 1e-20f;
+    if (rt3m::abs_(d) < tiny) d = (rt3m::as_uint(d) >> 31) ? -tiny : tiny;
+    return 1.0f / d;
+}
+RT3_HD RayPrep prepare_ray(const rt3_ray& r) {
+    RayPrep p;
+    p.ox = r.o[0]; p.oy = r.o[1]; p.oz = r.o[2];
+    p.dx = r.d[0]; p.dy = r.d[1]; p.dz = r.d[2];
+    p.idx = safe_rcp_dir(p.dx); p.idy = safe_rcp_dir(p.dy); p.idz = safe_rcp_dir(p.dz);
+    uint32_t oct = (p.idx < 0.0f ? 1u : 0u) | (p.idy < 0.0f ? 2u : 0u) | (p.idz < 0.0f ? 4u : 0u);
+    p.octinv4 = (7u - oct) * 0x01010101u;
+    p.tmin = r.tmin;
+    return p;
+}
+
+RT3_HD uint32_t byte_of(uint32_t w, int j) { return (w >> (8 * j)) & 0xFFu; }
+
+/* Intersect the 8 quantised child boxes of one node.  Returns the hit mask: bits 24..31 = inner
+ * children in near-to-far priority order for this ray's octant, bits 0..23 = triangles of hit leaves. */
+RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n0, const u32x4& n1, const u32x4& n2,
+                                    const u32x4& n3, const u32x4& n4) {
+    const uint32_t e = n0.w;
+    const float sx = rt3m::as_float((e & 0xFFu) << 23) * r.idx;
+    const float sy = rt3m::as_float(((e >> 8) & 0xFFu) << 23) * r.idy;
+    const float sz = rt3m::as_float(((e >> 16) & 0xFFu) << 23) * r.idz;
+    const float bx = (rt3m::as_float(n0.x) - r.ox) * r.idx;
+    const float by = (rt3m::as_float(n0.y) - r.oy) * r.idy;
+    const float bz = (rt3m::as_float(n0.z) - r.oz) * r.idz;
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        const uint32_t meta4 = half ? n1.w : n1.z;
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+        const uint32_t bit_index4 = (meta4 ^ (r.octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t qlx = half ? n2.y : n2.x, qly = half ? n2.w : n2.z, qlz = half ? n3.y : n3.x;
+        const uint32_t qhx = half ? n3.w : n3.z, qhy = half ? n4.y : n4.x, qhz = half ? n4.w : n4.z;
+        const uint32_t nx = r.idx < 0.0f ? qhx : qlx, fx = r.idx < 0.0f ? qlx : qhx;
+        const uint32_t ny = r.idy < 0.0f ? qhy : qly, fy = r.idy < 0.0f ? qly : qhy;
+        const uint32_t nz = r.idz < 0.0f ? qhz : qlz, fz = r.idz < 0.0f ? qlz : qhz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float t0x = rt3m::fma_((float)byte_of(nx, j), sx, bx), t1x = rt3m::fma_((float)byte_of(fx, j), sx, bx);
+            float t0y = rt3m::fma_((float)byte_of(ny, j), sy, by), t1y = rt3m::fma_((float)byte_of(fy, j), sy, by);
+            float t0z = rt3m::fma_((float)byte_of(nz, j), sz, bz), t1z = rt3m::fma_((float)byte_of(fz, j), sz, bz);
+            float tn = rt3m::max_(rt3m::max_(t0x, t0y), rt3m::max_(t0z, r.tmin));
+            float tf = rt3m::min_(rt3m::min_(t1x, t1y), rt3m::min_(t1z, tmax));
+            if (tn <= tf) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
+        }
+    }
+    return hitmask;
+}
+
+struct TraverseStats { uint32_t nodes, tris; };
+
+/* Closest hit (ANY = false) or first hit found (ANY = true).  `hit.t` must come in as the ray's tmax and
+ * hit.prim as RT3_MISS.  Returns true if something was hit. */
+template <bool ANY>
+RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ray& ray, rt3_hit& hit, TraverseStats* stats) {
+    RayPrep r = prepare_ray(ray);
+    const vec3 o = rt3m::v3(r.ox, r.oy, r.oz), d = rt3m::v3(r.dx, r.dy, r.dz);
+    uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
+    int sp = 0;
+    uint32_t ng_base = 0, ng_hits = 0x80000000u;   /* node group: root */
+    uint32_t tg_base = 0, tg_hits = 0;             /* triangle group   */
+    for (;;) {
+        if (ng_hits > 0x00FFFFFFu) {
+            const int bit = bfind32(ng_hits);
+            const uint32_t imask = ng_hits & 0xFFu;
+            ng_hits &= ~(1u << bit);
+            if (ng_hits > 0x00FFFFFFu) {
+                if (sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
+            }
+            const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
+            const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
+            const WideNode* n = nodes + (ng_base + rel);
+            const u32x4 n0 = ld_u32x4(n->w), n1 = ld_u32x4(n->w + 4), n2 = ld_u32x4(n->w + 8), n3 = ld_u32x4(n->w + 12), n4 = ld_u32x4(n->w + 16);
+            if (stats) stats->nodes++;
+            const uint32_t hm = intersect_wide_node(r, hit.t, n0, n1, n2, n3, n4);
+            ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
+            tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
+        } else {
+            tg_base = ng_base; tg_hits = ng_hits;
+            ng_hits = 0;
+        }
+        while (tg_hits) {
+            const int bit = bfind32(tg_hits);
+            tg_hits &= ~(1u << bit);
+            const Tri48* tp = tris + (tg_base + (uint32_t)bit);
+            const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
+            if (stats) stats->tris++;
+            float t, u, v;
+            const vec3 v0 = rt3m::v3(rt3m::as_float(a.x), rt3m::as_float(a.y), rt3m::as_float(a.z));
+            const vec3 e1 = rt3m::v3(rt3m::as_float(b.x), rt3m::as_float(b.y), rt3m::as_float(b.z));
+            const vec3 e2 = rt3m::v3(rt3m::as_float(c.x), rt3m::as_float(c.y), rt3m::as_float(c.z));
+            if (rt3m::ray_triangle(o, d, v0, e1, e2, t, u, v) && t > ray.tmin) {
+                if (ANY) {
+                    if (t < ray.tmax) { hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w; return true; }
+                } else if (t < ray.tmax && rt3m::closer_hit(t, a.w, hit.t, hit.prim)) {
+                    hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w;
+                }
+            }
+        }
+        if (ng_hits <= 0x00FFFFFFu) {
+            if (sp == 0) break;
+            sp--;
+            ng_base = stack_base[sp]; ng_hits = stack_hits[sp];
+        }
+    }
+    return hit.prim != RT3_MISS;
+}
+
+}  /* namespace rt3b */
+#endif

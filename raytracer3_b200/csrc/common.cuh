@@ -1,0 +1,157 @@
+/*
+ * common.cuh — context object, device buffers and launch helpers of librt3.so.
+ *
+ * The context plays the role of the reference's RenderWorld + RayTracingContext
+ * (/root/reference/src/renderer/world/mod.rs:103-117, src/renderer/vulkan/raytracing.rs:56-86): it owns
+ * the global append-only scene buffers, the acceleration structure and the scratch memory of the passes.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "rt3.h"
+#include "rt3_shared_math.h"
+#include "bvh_logic.h"
+
+#define RT3_ABI_VERSION 1u
+
+struct rt3_error_exit { rt3_status code; };
+
+#define RT3_CUDA(ctx, call)                                                                                   \
+    do {                                                                                                      \
+        cudaError_t e__ = (call);                                                                             \
+        if (e__ != cudaSuccess) {                                                                             \
+            (ctx)->set_error(std::string(#call) + ": " + cudaGetErrorString(e__) + " (" __FILE__ ":" + std::to_string(__LINE__) + ")"); \
+            throw rt3_error_exit{e__ == cudaErrorMemoryAllocation ? RT3_ERR_OOM : RT3_ERR_CUDA};             \
+        }                                                                                                     \
+    } while (0)
+
+#define RT3_FAIL(ctx, code, msg)            \
+    do {                                    \
+        (ctx)->set_error(msg);              \
+        throw rt3_error_exit{code};         \
+    } while (0)
+
+/* Growable device buffer: the analogue of DynamicBuffer (src/renderer/vulkan/buffer.rs:297-421):
+ * starts small, doubles on demand, append-only `push` from host memory. */
+struct DynBuf {
+    void* ptr = nullptr;
+    size_t size = 0, capacity = 0;   /* bytes */
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; size = capacity = 0; }
+};
+
+/* Plain owned device allocation, resized (not preserved) on demand. */
+struct Scratch {
+    void* ptr = nullptr;
+    size_t capacity = 0;
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; capacity = 0; }
+    template <class T> T* as() const { return (T*)ptr; }
+};
+
+struct InstanceRec { uint32_t first_geometry, geometry_count; float xform[12]; };
+struct TextureRec { uint8_t* data = nullptr; uint32_t w = 0, h = 0; };
+
+/* Pixel work list: one or many rects, frame-pitch or tile-slab addressing (see rt3.h). */
+struct PixelMap {
+    rt3_rect single;          /* used when n_tiles == 1          */
+    const rt3_rect* rects;    /* device array when n_tiles > 1   */
+    uint32_t n_tiles;
+    uint32_t tile_w, tile_h;  /* max rect size; slab stride      */
+    uint32_t bw, bh;          /* 8x4-pixel blocks per tile       */
+    uint32_t pitch;           /* frame width (frame addressing)  */
+    uint32_t slab;            /* 1 = tile-major slab addressing  */
+    uint32_t work;            /* n_tiles * bw * bh * 32          */
+};
+
+struct DeviceCounters {
+    unsigned long long rays_primary, rays_secondary, rays_shadow, paths_started, paths_escaped;
+};
+
+struct rt3_context {
+    int device = 0;
+    int sm_count = 148;
+    std::string error;
+    uint64_t launches = 0;
+    void set_error(const std::string& m) { error = m; }
+
+    /* scene (host mirrors of the small tables + device global buffers) */
+    DynBuf vertices, indices;
+    std::vector<rt3_geometry_info> h_geometries;
+    std::vector<InstanceRec> h_instances;
+    std::vector<TextureRec> textures;
+    float* d_env = nullptr; uint32_t env_w = 0, env_h = 0;
+    uint8_t* d_bn = nullptr; uint32_t bn_w = 0, bn_h = 0;
+    float* d_srgb_lut = nullptr;
+    bool scene_dirty = true;
+
+    /* tables rebuilt by rt3_accel_build */
+    Scratch d_geometries, d_seg_first, d_seg_geo, d_seg_inst, d_inst_xform, d_tex_ptr, d_tex_dim;
+    std::vector<uint32_t> h_seg_first, h_seg_geo, h_seg_inst;
+    uint32_t n_segments = 0, n_triangles = 0;
+    rt3m::SceneView view;           /* device pointers */
+
+    /* acceleration structure */
+    Scratch bvh_nodes, bvh_tris;
+    uint32_t n_wide_nodes = 0;
+    bool accel_valid = false;
+    rt3_build_stats last_build;
+
+    /* pass scratch */
+    Scratch q_rays[2], q_hits, q_thr[2], q_pix[2], px_radiance, px_rng, d_counts, d_rects, d_params;
+    Scratch f_gbuffer, f_depth, f_light, f_prev, f_rays, f_hits, f_bits, l2_buf;
+    DeviceCounters* d_counters = nullptr;
+    cudaEvent_t ev[8];
+};
+
+template <class T>
+static inline T* ensure(rt3_context* c, Scratch& s, size_t count) {
+    size_t bytes = count * sizeof(T);
+    if (bytes > s.capacity) {
+        if (s.ptr) cudaFree(s.ptr);
+        s.ptr = nullptr; s.capacity = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        RT3_CUDA(c, cudaMalloc(&s.ptr, want));
+        s.capacity = want;
+    }
+    return (T*)s.ptr;
+}
+
+static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+#define RT3_LAUNCH(ctx, kernel, grid, block, smem, stream, ...)                         \
+    do {                                                                                \
+        kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                     \
+        (ctx)->launches++;                                                              \
+        RT3_CUDA(ctx, cudaGetLastError());                                              \
+    } while (0)
+
+/* work index -> pixel.  Returns false for padding lanes. */
+__device__ __forceinline__ bool pixel_of(const PixelMap& m, uint32_t idx, uint32_t& x, uint32_t& y, size_t& out_index) {
+    const uint32_t per_tile = m.bw * m.bh * 32u;
+    const uint32_t k = idx / per_tile, rem = idx - k * per_tile;
+    const uint32_t blk = rem >> 5, lane = rem & 31u;
+    const uint32_t lx = (blk % m.bw) * 8u + (lane & 7u), ly = (blk / m.bw) * 4u + (lane >> 3);
+    rt3_rect r;
+    if (m.n_tiles == 1) r = m.single; else r = m.rects[k];
+    if (lx >= r.w || ly >= r.h) return false;
+    x = r.x0 + lx; y = r.y0 + ly;
+    out_index = m.slab ? ((size_t)k * m.tile_w * m.tile_h + (size_t)ly * m.tile_w + lx) : ((size_t)y * m.pitch + x);
+    return true;
+}
+
+/* implemented in build.cu / trace.cu / passes.cu */
+void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out);
+void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, cudaStream_t st);
+void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, uint64_t n, uint32_t* bits, cudaStream_t st);
+void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out);
+void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary,
+                        cudaStream_t st);
+void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m, const uint32_t* gbuffer, const float* depth, const float* prev,
+                          float* light, cudaStream_t st);
+void rt3_launch_postprocess(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, float* out, cudaStream_t st);
+void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h, const float* slab, float* frame,
+                       uint32_t frame_w, uint32_t frame_h, cudaStream_t st);
+double rt3_run_l2_sweep(rt3_context* c, size_t bytes, int iters);

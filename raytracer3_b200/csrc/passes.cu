@@ -1,0 +1,273 @@
+/*
+ * passes.cu — the ray passes as CUDA kernels.
+ *
+ *   k_gbuffer      <- /root/reference/shaders/old/gbuffer.slang:8-20        (primary visibility, one launch)
+ *   k_ref_init / k_ref_shade / k_ref_finish + k_trace
+ *                  <- /root/reference/shaders/old/refrence_mode.slang:14-66 (spp x bounce loop)
+ *   k_postprocess  <- /root/reference/shaders/old/postprocess.slang:90-112
+ *
+ * The reference runs one raygen thread per pixel that loops over samples and bounces around a
+ * black-box TraceRay.  Here the loop is turned inside out (wavefront): all live paths advance one
+ * bounce per kernel, terminated paths are compacted away with warp-aggregated atomics, and the
+ * traversal kernel sees a dense queue.  Per-pixel state that must survive between kernels is exactly
+ * what the raygen shader keeps in registers: the radiance sum, the RNG counter (random.slang:62: never
+ * reset between samples), the throughput and the current ray.  Each pixel has at most one path in
+ * flight, so the per-pixel sums are updated without atomics and in the reference's order, which keeps
+ * the result bit-identical to the per-pixel loop of the oracle.
+ */
+#include "common.cuh"
+
+using namespace rt3b;
+using namespace rt3m;
+
+namespace {
+
+constexpr int PASS_THREADS = 256;
+
+struct WarpCounters {
+    unsigned long long a = 0, b = 0;
+};
+__device__ __forceinline__ void flush_counter(unsigned long long v, unsigned long long* dst) {
+    for (int off = 16; off; off >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, off);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);
+}
+
+/* ---- pass 1 -------------------------------------------------------------------------------- */
+__global__ void __launch_bounds__(128) k_gbuffer(SceneView s, const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris, rt3_params p, PixelMap m,
+                                                 uint32_t* __restrict__ gbuffer, float* __restrict__ depth, uint32_t* __restrict__ ids,
+                                                 float* __restrict__ bary, DeviceCounters* counters) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x, y; size_t px;
+    const bool valid = idx < m.work && pixel_of(m, idx, x, y, px);
+    if (valid) {
+        rt3_ray ray = setup_primary_ray(x, y, p);                           /* gbuffer.slang:10 */
+        rt3_hit h; h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+        traverse_wide<false>(nodes, tris, ray, h, nullptr);                 /* gbuffer.slang:12 */
+        if (h.prim == RT3_MISS) {                                           /* gbuffer.slang:14-16 */
+            depth[px] = RT3_BACKGROUND_DEPTH;
+            if (ids) { ids[2 * px] = RT3_MISS; ids[2 * px + 1] = RT3_MISS; }
+            if (bary) { bary[2 * px] = 0.f; bary[2 * px + 1] = 0.f; }
+        } else {                                                            /* gbuffer.slang:17-19 */
+            uint32_t geo;
+            uint4_ g = gbuffer_pack(hit_info(s, h.prim, h.u, h.v, &geo));
+            ((uint4*)gbuffer)[px] = make_uint4(g.x, g.y, g.z, g.w);
+            depth[px] = h.t;
+            if (ids) { ids[2 * px] = h.prim; ids[2 * px + 1] = geo; }
+            if (bary) { bary[2 * px] = h.u; bary[2 * px + 1] = h.v; }
+        }
+    }
+    flush_counter(valid ? 1ull : 0ull, &counters->rays_primary);
+}
+
+/* ---- pass 2, wavefront --------------------------------------------------------------------- */
+__device__ __forceinline__ uint32_t warp_enqueue(bool alive, uint32_t* count) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);
+    uint32_t base = 0;
+    if (mask) {
+        const int leader = __ffs(mask) - 1;
+        if ((int)lane == leader) base = atomicAdd(count, (uint32_t)__popc(mask));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    }
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+__device__ __forceinline__ void store_ray(rt3_ray* q, uint32_t pos, vec3 o, vec3 d, float tmin, float tmax) {
+    float4* p = (float4*)(q + pos);
+    p[0] = make_float4(o.x, o.y, o.z, tmin);
+    p[1] = make_float4(d.x, d.y, d.z, tmax);
+}
+
+/* refrence_mode.slang:18-34 + bounce 0 of the loop at :36-51 (the surface comes from the G-buffer). */
+__global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_params p, PixelMap m, const uint32_t* __restrict__ gbuffer,
+                                                           const float* __restrict__ depth, float4* __restrict__ px_radiance, uint32_t* __restrict__ px_rng,
+                                                           int first_sample, rt3_ray* __restrict__ q_rays, float4* __restrict__ q_thr, uint32_t* q_count,
+                                                           DeviceCounters* counters) {
+    unsigned long long started = 0;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < m.work; base += stride) {   /* block-uniform trip count */
+        const uint32_t idx = base + threadIdx.x;
+        uint32_t x, y; size_t px;
+        bool alive = false;
+        vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0);
+        if (idx < m.work && pixel_of(m, idx, x, y, px)) {
+            const float gdepth = depth[px];
+            if (gdepth != RT3_BACKGROUND_DEPTH) {                                     /* :18-21 */
+                uint4 g4 = ((const uint4*)gbuffer)[px];
+                uint4_ packed = {g4.x, g4.y, g4.z, g4.w};
+                GbufferData surface = gbuffer_unpack(packed);                          /* :23 */
+                RandomSamplerState rng = rng_init(x, y, p.frame);                      /* :25 */
+                vec3 radiance = v3(0, 0, 0);
+                if (!first_sample) {
+                    rng.index = px_rng[idx];
+                    float4 r4 = px_radiance[idx];
+                    radiance = v3(r4.x, r4.y, r4.z);
+                }
+                started++;
+                if (p.bounces > 0) {
+                    rt3_ray pr = setup_primary_ray(x, y, p);                           /* :30 */
+                    vec3 ray_color = v3(1.f, 1.f, 1.f);
+                    vec2 urand = sample_2d(s, p.flags, x, y, p.frame, rng);            /* :43 */
+                    PathVertexOut nv = bounce_step(surface, v3(pr.o), v3(pr.d), gdepth, urand, radiance, ray_color);   /* :44-51 */
+                    o = nv.origin; d = nv.dir; thr = ray_color;
+                    alive = p.bounces > 1;                                             /* :53 */
+                }
+                px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);   /* w = 1: pixel is not background */
+                px_rng[idx] = rng.index;
+            } else if (first_sample) {
+                px_radiance[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        } else if (idx < m.work && first_sample) {
+            px_radiance[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const uint32_t pos = warp_enqueue(alive, q_count);
+        if (alive) {
+            store_ray(q_rays, pos, o, d, 0.001f, RT3_BACKGROUND_DEPTH);               /* :31, TMax of setupPrimaryRay */
+            q_thr[pos] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(idx));
+        }
+    }
+    flush_counter(started, &counters->paths_started);
+}
+
+/* Loop iteration b >= 1 of refrence_mode.slang:36-57 for every path whose ray was traced at b-1. */
+__global__ void __launch_bounds__(PASS_THREADS) k_ref_shade(SceneView s, rt3_params p, PixelMap m, uint32_t b, const rt3_ray* __restrict__ rays_in,
+                                                            const rt3_hit* __restrict__ hits, const float4* __restrict__ thr_in,
+                                                            const uint32_t* __restrict__ count_in, rt3_ray* __restrict__ rays_out,
+                                                            float4* __restrict__ thr_out, uint32_t* count_out, float4* __restrict__ px_radiance,
+                                                            uint32_t* __restrict__ px_rng, DeviceCounters* counters) {
+    const uint32_t n = *count_in;
+    unsigned long long traced = 0, escaped = 0;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {
+        const uint32_t i = base + threadIdx.x;
+        bool alive = false;
+        vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0);
+        uint32_t idx = 0;
+        if (i < n) {
+            traced++;
+            const float4 r0 = ((const float4*)(rays_in + i))[0], r1 = ((const float4*)(rays_in + i))[1];
+            const float4 h4 = ((const float4*)hits)[i];
+            const float4 t4 = thr_in[i];
+            idx = __float_as_uint(t4.w);
+            const uint32_t prim = __float_as_uint(h4.w);
+            vec3 ray_color = v3(t4.x, t4.y, t4.z);
+            float4 rad4 = px_radiance[idx];
+            vec3 radiance = v3(rad4.x, rad4.y, rad4.z);
+            const vec3 ro = v3(r0.x, r0.y, r0.z), rd = v3(r1.x, r1.y, r1.z);
+            if (prim == RT3_MISS) {                                                    /* :37-40 */
+                escaped++;
+                if (p.flags & RT3_FLAG_ENV) {
+                    radiance = radiance + ray_color * sample_environment(s, rd);       /* :38 (commented out in the reference) */
+                    px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
+                }
+            } else {
+                uint32_t x, y; size_t px;
+                pixel_of(m, idx, x, y, px);
+                GbufferData surface = hit_info(s, prim, h4.y, h4.z);                   /* :55 */
+                RandomSamplerState rng = rng_init(x, y, p.frame);
+                rng.index = px_rng[idx];
+                vec2 urand = sample_2d(s, p.flags, x, y, p.frame, rng);               /* :43 */
+                PathVertexOut nv = bounce_step(surface, ro, rd, h4.x, urand, radiance, ray_color);   /* :44-51 */
+                px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
+                px_rng[idx] = rng.index;
+                o = nv.origin; d = nv.dir; thr = ray_color;
+                alive = (b != p.bounces - 1);                                          /* :53 */
+            }
+        }
+        const uint32_t pos = warp_enqueue(alive, count_out);
+        if (alive) {
+            store_ray(rays_out, pos, o, d, 0.001f, RT3_BACKGROUND_DEPTH);
+            thr_out[pos] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(idx));
+        }
+    }
+    flush_counter(traced, &counters->rays_secondary);
+    flush_counter(escaped, &counters->paths_escaped);
+}
+
+/* refrence_mode.slang:59-65 */
+__global__ void __launch_bounds__(PASS_THREADS) k_ref_finish(rt3_params p, PixelMap m, const float4* __restrict__ px_radiance, const float* __restrict__ prev,
+                                                             float* __restrict__ light) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x, y; size_t px;
+    if (idx >= m.work || !pixel_of(m, idx, x, y, px)) return;
+    const float4 r4 = px_radiance[idx];
+    if (r4.w == 0.0f) return;                                   /* background: Light is not written (:18-21) */
+    const float ns = (float)p.samples;
+    vec3 radiance = v3(r4.x / ns, r4.y / ns, r4.z / ns);       /* :59 */
+    vec3 pv = v3(0, 0, 0);
+    if (p.blendfactor < 1.0f && prev) { float4 q = ((const float4*)prev)[px]; pv = v3(q.x, q.y, q.z); }
+    vec3 o = temporal_blend(pv, radiance, p.blendfactor);       /* :61-65 */
+    ((float4*)light)[px] = make_float4(o.x, o.y, o.z, 0.0f);
+}
+
+/* postprocess.slang:90-112 */
+__global__ void __launch_bounds__(PASS_THREADS) k_postprocess(SceneView s, rt3_params p, PixelMap m, const float* __restrict__ depth,
+                                                              const float* __restrict__ in, float* __restrict__ out) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x, y; size_t px;
+    if (idx >= m.work || !pixel_of(m, idx, x, y, px)) return;
+    float4 c = ((const float4*)in)[px];
+    vec3 r = postprocess_pixel(s, p, x, y, depth[px], v3(c.x, c.y, c.z));
+    ((float4*)out)[px] = make_float4(r.x, r.y, r.z, 1.0f);
+}
+
+__global__ void __launch_bounds__(PASS_THREADS) k_untile(const rt3_rect* __restrict__ rects, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h,
+                                                         const float4* __restrict__ slab, float4* __restrict__ frame, uint32_t frame_w, uint32_t frame_h) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t per = (size_t)tile_w * tile_h;
+    if (i >= per * n_tiles) return;
+    const uint32_t k = (uint32_t)(i / per), rem = (uint32_t)(i - (size_t)k * per);
+    const uint32_t ly = rem / tile_w, lx = rem - ly * tile_w;
+    const rt3_rect r = rects[k];
+    if (lx >= r.w || ly >= r.h) return;
+    const uint32_t x = r.x0 + lx, y = r.y0 + ly;
+    if (x < frame_w && y < frame_h) frame[(size_t)y * frame_w + x] = slab[i];
+}
+
+}  // namespace
+
+void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary,
+                        cudaStream_t st) {
+    if (!m.work) return;
+    RT3_LAUNCH(c, k_gbuffer, div_up(m.work, 128), 128, 0, st, c->view, c->bvh_nodes.as<WideNode>(), c->bvh_tris.as<Tri48>(), p, m, gbuffer, depth, ids, bary,
+               c->d_counters);
+}
+
+void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m, const uint32_t* gbuffer, const float* depth, const float* prev,
+                          float* light, cudaStream_t st) {
+    if (!m.work) return;
+    const size_t W = m.work;
+    rt3_ray* q_rays[2] = {ensure<rt3_ray>(c, c->q_rays[0], W), ensure<rt3_ray>(c, c->q_rays[1], W)};
+    float4* q_thr[2] = {ensure<float4>(c, c->q_thr[0], W), ensure<float4>(c, c->q_thr[1], W)};
+    rt3_hit* q_hits = ensure<rt3_hit>(c, c->q_hits, W);
+    float4* px_radiance = ensure<float4>(c, c->px_radiance, W);
+    uint32_t* px_rng = ensure<uint32_t>(c, c->px_rng, W);
+    uint32_t* counts = (uint32_t*)ensure<unsigned long long>(c, c->d_counts, 64);
+    const unsigned grid = std::min<unsigned>(div_up(W, PASS_THREADS), (unsigned)c->sm_count * 8u);
+    for (uint32_t sidx = 0; sidx < p.samples; ++sidx) {
+        RT3_CUDA(c, cudaMemsetAsync(counts, 0, 8, st));
+        RT3_LAUNCH(c, k_ref_init, grid, PASS_THREADS, 0, st, c->view, p, m, gbuffer, depth, px_radiance, px_rng, sidx == 0 ? 1 : 0, q_rays[0], q_thr[0], counts,
+                   c->d_counters);
+        int cur = 0;
+        for (uint32_t b = 1; b < p.bounces; ++b) {
+            rt3_launch_trace_closest(c, q_rays[cur], counts + cur, W, q_hits, st);
+            RT3_CUDA(c, cudaMemsetAsync(counts + (1 - cur), 0, 4, st));
+            RT3_LAUNCH(c, k_ref_shade, grid, PASS_THREADS, 0, st, c->view, p, m, b, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur], q_thr[1 - cur],
+                       counts + (1 - cur), px_radiance, px_rng, c->d_counters);
+            cur = 1 - cur;
+        }
+    }
+    RT3_LAUNCH(c, k_ref_finish, div_up(W, PASS_THREADS), PASS_THREADS, 0, st, p, m, px_radiance, prev, light);
+}
+
+void rt3_launch_postprocess(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, float* out, cudaStream_t st) {
+    if (!m.work) return;
+    RT3_LAUNCH(c, k_postprocess, div_up(m.work, PASS_THREADS), PASS_THREADS, 0, st, c->view, p, m, depth, in, out);
+}
+
+void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h, const float* slab, float* frame,
+                       uint32_t frame_w, uint32_t frame_h, cudaStream_t st) {
+    size_t total = (size_t)n_tiles * tile_w * tile_h;
+    if (!total) return;
+    RT3_LAUNCH(c, k_untile, div_up(total, PASS_THREADS), PASS_THREADS, 0, st, d_rects, n_tiles, tile_w, tile_h, (const float4*)slab, (float4*)frame, frame_w,
+               frame_h);
+}

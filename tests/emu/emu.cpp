@@ -1,0 +1,157 @@
+/*
+ * emu.cpp — TEST INFRASTRUCTURE: runs the per-thread device logic of raytracer3_b200/csrc/bvh_logic.h
+ * sequentially on the CPU (Karras hierarchy, refit, wide collapse + quantised encoding, wide traversal)
+ * and compares it with a brute-force loop over the same 48-byte triangle records.  It lets the
+ * `-m "not gpu"` suite debug the builder/traversal logic on a machine without a GPU.  It is not a
+ * fallback: librt3.so neither contains nor calls this code.
+ */
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+#include <vector>
+#include "../../raytracer3_b200/csrc/bvh_logic.h"
+
+using namespace rt3b;
+
+struct EmuBvh {
+    std::vector<Tri48> tris_in, tris_sorted, tris_out;
+    std::vector<WideNode> nodes;
+    uint32_t n_nodes = 0, n_tris = 0, levels = 0;
+    float sah[2] = {0, 0};
+    float pad = 0;
+    float lo[3], hi[3];
+};
+
+extern "C" {
+
+EmuBvh* emu_build(const float* tris9, uint32_t n) {
+    EmuBvh* b = new EmuBvh();
+    b->tris_in.resize(n);
+    for (int a = 0; a < 3; ++a) { b->lo[a] = 3.4e38f; b->hi[a] = -3.4e38f; }
+    for (uint32_t i = 0; i < n; ++i) {
+        const float* p = tris9 + 9 * (size_t)i;
+        Tri48& t = b->tris_in[i];
+        for (int a = 0; a < 3; ++a) {
+            t.v0[a] = p[a]; t.e1[a] = p[3 + a] - p[a]; t.e2[a] = p[6 + a] - p[a];
+            for (int k = 0; k < 3; ++k) { b->lo[a] = std::min(b->lo[a], p[3 * k + a]); b->hi[a] = std::max(b->hi[a], p[3 * k + a]); }
+        }
+        t.prim = i; t.pad0 = t.pad1 = 0;
+    }
+    float ext = n ? std::max(b->hi[0] - b->lo[0], std::max(b->hi[1] - b->lo[1], b->hi[2] - b->lo[2])) : 0.f;
+    b->pad = ext * (1.0f / 65536.0f);
+    if (n == 0) {
+        b->nodes.resize(1);
+        memset(&b->nodes[0], 0, sizeof(WideNode));
+        b->n_nodes = 1;
+        return b;
+    }
+    /* morton + sort */
+    std::vector<uint64_t> keys(n);
+    std::vector<uint32_t> order(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        float l[3], h[3];
+        tri_bounds(b->tris_in[i], 0.f, l, h);
+        float c[3];
+        for (int a = 0; a < 3; ++a) { float e = b->hi[a] - b->lo[a]; c[a] = e > 0 ? (0.5f * (l[a] + h[a]) - b->lo[a]) / e : 0.f; }
+        keys[i] = morton63(c[0], c[1], c[2]);
+    }
+    std::iota(order.begin(), order.end(), 0u);
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return keys[x] < keys[y]; });
+    std::vector<uint64_t> skeys(n);
+    b->tris_sorted.resize(n);
+    for (uint32_t i = 0; i < n; ++i) { skeys[i] = keys[order[i]]; b->tris_sorted[i] = b->tris_in[order[i]]; }
+    /* hierarchy */
+    std::vector<Bvh2Node> n2(2 * (size_t)n - 1);
+    std::vector<uint32_t> parent(2 * (size_t)n - 1, 0xFFFFFFFFu), counts(n > 1 ? n - 1 : 1, 0), flags(n > 1 ? n - 1 : 1, 0);
+    for (int i = 0; i + 1 < (int)n; ++i) lbvh_build_node(skeys.data(), (int)n, i, n2.data(), parent.data());
+    /* refit: the same walk the kernel does (second arrival computes the parent) */
+    for (uint32_t k = 0; k < n; ++k) {
+        Bvh2Node& leaf = n2[n - 1 + k];
+        tri_bounds(b->tris_sorted[k], b->pad, leaf.lo, leaf.hi);
+        leaf.left = leaf.right = 0;
+        uint32_t cur = parent[n - 1 + k];
+        while (cur != 0xFFFFFFFFu) {
+            if (flags[cur]++ == 0) break;
+            Bvh2Node& nd = n2[cur];
+            uint32_t l = (nd.left & LEAF_FLAG) ? n - 1 + (nd.left & ~LEAF_FLAG) : nd.left;
+            uint32_t r = (nd.right & LEAF_FLAG) ? n - 1 + (nd.right & ~LEAF_FLAG) : nd.right;
+            for (int a = 0; a < 3; ++a) { nd.lo[a] = std::min(n2[l].lo[a], n2[r].lo[a]); nd.hi[a] = std::max(n2[l].hi[a], n2[r].hi[a]); }
+            counts[cur] = ((nd.left & LEAF_FLAG) ? 1 : counts[nd.left]) + ((nd.right & LEAF_FLAG) ? 1 : counts[nd.right]);
+            cur = parent[cur];
+        }
+    }
+    /* collapse, level by level */
+    b->nodes.resize(n);  /* upper bound: every wide node has >= 2 children unless n == 1 */
+    b->tris_out.resize(n);
+    std::vector<uint32_t> q(2 * (size_t)n + 2), qn(2 * (size_t)n + 2);
+    uint32_t node_counter = 1, tri_counter = 0, q_count = 1, next_count = 0;
+    q[0] = (n == 1) ? (LEAF_FLAG | 0u) : 0u; q[1] = 0;
+    CollapseCtx c;
+    c.nodes = n2.data(); c.counts = counts.data(); c.tris_sorted = b->tris_sorted.data(); c.n_leaves = n;
+    c.out_nodes = b->nodes.data(); c.out_tris = b->tris_out.data(); c.node_counter = &node_counter; c.tri_counter = &tri_counter;
+    c.next_count = &next_count; c.sah_accum = b->sah;
+    while (q_count) {
+        next_count = 0; c.next_items = qn.data();
+        for (uint32_t i = 0; i < q_count; ++i) collapse_one(c, q[2 * i], q[2 * i + 1]);
+        q.swap(qn); q_count = next_count; b->levels++;
+    }
+    b->n_nodes = node_counter; b->n_tris = tri_counter;
+    return b;
+}
+void emu_destroy(EmuBvh* b) { delete b; }
+void emu_info(const EmuBvh* b, uint32_t* out4, float* sah2) {
+    out4[0] = b->n_nodes; out4[1] = b->n_tris; out4[2] = b->levels; out4[3] = (uint32_t)b->tris_in.size();
+    sah2[0] = b->sah[0]; sah2[1] = b->sah[1];
+}
+/* order-independent check that the collapse kept every triangle exactly once: returns number of mismatches */
+uint32_t emu_check_triangles(const EmuBvh* b) {
+    std::vector<uint32_t> seen(b->tris_in.size(), 0);
+    uint32_t bad = 0;
+    for (uint32_t i = 0; i < b->n_tris; ++i) {
+        const Tri48& t = b->tris_out[i];
+        if (t.prim >= seen.size()) { bad++; continue; }
+        seen[t.prim]++;
+        if (memcmp(&t, &b->tris_in[t.prim], sizeof(Tri48)) != 0) bad++;
+    }
+    for (uint32_t s : seen) if (s != 1) bad++;
+    return bad;
+}
+void emu_trace_closest(const EmuBvh* b, const rt3_ray* rays, uint64_t n, rt3_hit* out, int brute, double* stats2) {
+    uint64_t nodes = 0, tris = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        rt3_hit h; h.t = rays[i].tmax; h.u = h.v = 0.f; h.prim = RT3_MISS;
+        if (brute) {
+            rt3m::vec3 o = rt3m::v3(rays[i].o), d = rt3m::v3(rays[i].d);
+            for (const Tri48& t : b->tris_in) {
+                float tt, u, v;
+                if (rt3m::ray_triangle(o, d, rt3m::v3(t.v0), rt3m::v3(t.e1), rt3m::v3(t.e2), tt, u, v) && tt > rays[i].tmin && tt < rays[i].tmax &&
+                    rt3m::closer_hit(tt, t.prim, h.t, h.prim)) { h.t = tt; h.u = u; h.v = v; h.prim = t.prim; }
+            }
+        } else {
+            TraverseStats st = {0, 0};
+            traverse_wide<false>(b->nodes.data(), b->tris_out.data(), rays[i], h, &st);
+            nodes += st.nodes; tris += st.tris;
+        }
+        out[i] = h;
+    }
+    if (stats2 && n) { stats2[0] = (double)nodes / n; stats2[1] = (double)tris / n; }
+}
+void emu_trace_any(const EmuBvh* b, const rt3_ray* rays, uint64_t n, uint32_t* bits, int brute) {
+    for (uint64_t w = 0; w < (n + 31) / 32; ++w) bits[w] = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        bool hit = false;
+        if (brute) {
+            rt3m::vec3 o = rt3m::v3(rays[i].o), d = rt3m::v3(rays[i].d);
+            for (const Tri48& t : b->tris_in) {
+                float tt, u, v;
+                if (rt3m::ray_triangle(o, d, rt3m::v3(t.v0), rt3m::v3(t.e1), rt3m::v3(t.e2), tt, u, v) && tt > rays[i].tmin && tt < rays[i].tmax) { hit = true; break; }
+            }
+        } else {
+            rt3_hit h; h.t = rays[i].tmax; h.u = h.v = 0.f; h.prim = RT3_MISS;
+            hit = traverse_wide<true>(b->nodes.data(), b->tris_out.data(), rays[i], h, nullptr);
+        }
+        if (hit) bits[i >> 5] |= 1u << (i & 31);
+    }
+}
+}
