@@ -696,7 +696,6 @@ RT3_HD vec3 postprocess_pixel(const SceneView& s, const rt3_params& p, uint32_t 
     return agx_eotf(agx_look(agx(color)));
 }
 
-#ifndef __CUDA_ARCH__
 /* Host-side table: sRGB byte -> linear float (IEC 61966-2-1), evaluated in double and rounded once. */
 inline void build_srgb_lut(float* lut256) {
     for (int i = 0; i < 256; ++i) {
@@ -704,7 +703,6 @@ inline void build_srgb_lut(float* lut256) {
         lut256[i] = (float)(c <= 0.04045 ? c / 12.92 : pow((c + 0.055) / 1.055, 2.4));
     }
 }
-#endif
 
 } /* namespace rt3m */
 #endif

@@ -53,7 +53,13 @@ RT3_HD int clz64(uint64_t x) { return __clzll((long long)x); }
 RT3_HD int popc32(uint32_t x) { return __popc(x); }
 RT3_HD int bfind32(uint32_t x) { return 31 - __clz((int)x); }
 /* per-byte sign fill: 0x80 -> 0xFF, else 0x00 */
-RT3_HD uint32_t sign_extend_s8x4(uint32_t x) { return __byte_perm(x, 0, 0xBA98); }
+/* prmt generic mode: a selector nibble with its msb set replicates the sign bit of the selected byte
+ * (the __byte_perm intrinsic only honours 3 selector bits, so the PTX form is used directly). */
+RT3_HD uint32_t sign_extend_s8x4(uint32_t x) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(0u), "r"(0x0000BA98u));
+    return r;
+}
 #else
 inline uint32_t host_atomic_add(uint32_t* p, uint32_t v) { uint32_t o = *p; *p += v; return o; }
 inline float host_atomic_add(float* p, float v) { float o = *p; *p += v; return o; }

@@ -1,0 +1,371 @@
+"""Host-side mirror of the reference's renderer API for the ray-tracing path, over the C ABI.
+
+The reference is Rust; no Rust toolchain exists in this image, so the host side above librt3.so is
+this Python module (tests and bench are Python; INTEGRATION.md shows the Rust `extern "C"` binding).
+Names, argument meaning and error behaviour follow the reference (paths under /root/reference):
+
+  RenderContext       Context + RayTracingContext            src/renderer/vulkan/mod.rs:86-231, raytracing.rs:56-86
+  RenderWorld         global append-only scene buffers + AS  src/renderer/world/mod.rs:103-180
+  RenderGraph.image   named transient image resources        src/renderer/render_graph/mod.rs:440-483
+  RayTracingPass      builder .shader .constants .read .write .read_write .launch(WorkSize2D)
+                                                             src/renderer/render_graph/executions.rs:80-121, build.rs:66-193,371-384
+  ComputePass         .dispatch(WorkSize2D) (postprocess)    src/renderer/render_graph/executions.rs:21-55
+  WorkSize2D          FullScreen / FractionalFullScreen / X / XY   executions.rs:57-78
+
+Errors: the reference unwraps every Result (src/renderer/mod.rs:30), i.e. panics; here every non-zero
+rt3_status raises Rt3Error with rt3_last_error()'s message.  Device memory is torch CUDA tensors
+(plumbing only); passes are recorded on the current torch CUDA stream, the analogue of the reference's
+command buffer.
+"""
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib
+from .types import PARAMS, BuildStats, Counters, Rect, TraceStats, ptr
+
+
+def _torch():
+    import torch
+
+    return torch
+
+
+class RenderContext:
+    """One per CUDA device (rt3_context)."""
+
+    def __init__(self, device=0):
+        self.L = _lib.load()
+        h = C.c_void_p()
+        st = self.L.rt3_create(int(device), C.byref(h))
+        if st != 0:
+            raise _lib.Rt3Error(st, self.L.rt3_last_error(None).decode())
+        self.h = h
+        self.device = int(device)
+
+    def check(self, status):
+        if status != 0:
+            raise _lib.Rt3Error(status, self.L.rt3_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.rt3_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stream(self):
+        torch = _torch()
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def kernel_launches(self):
+        return int(self.L.rt3_kernel_launches(self.h))
+
+    def counters(self, reset=False):
+        c = Counters()
+        self.check(self.L.rt3_counters_read(self.h, C.byref(c), 1 if reset else 0))
+        return c
+
+    def measure_l2_bandwidth(self, nbytes=32 << 20, iters=10):
+        out = C.c_double()
+        self.check(self.L.rt3_measure_l2_bandwidth(self.h, nbytes, iters, C.byref(out)))
+        return out.value
+
+
+class RenderWorld:
+    """Global vertex / index / geometry / instance buffers and the acceleration structure."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+        self.num_instances = 0
+        self.build_stats = None
+
+    def push_vertices(self, vertices):
+        v = np.ascontiguousarray(vertices)
+        first = C.c_uint32()
+        self.ctx.check(self.ctx.L.rt3_scene_push_vertices(self.ctx.h, ptr(v), len(v), C.byref(first)))
+        return first.value
+
+    def push_indices(self, indices):
+        i = np.ascontiguousarray(indices, np.uint32)
+        first = C.c_uint32()
+        self.ctx.check(self.ctx.L.rt3_scene_push_indices(self.ctx.h, ptr(i), len(i), C.byref(first)))
+        return first.value
+
+    def push_geometry(self, geometry):
+        g = np.ascontiguousarray(geometry)
+        out = C.c_uint32()
+        self.ctx.check(self.ctx.L.rt3_scene_push_geometry(self.ctx.h, ptr(g), C.byref(out)))
+        return out.value
+
+    def push_instance(self, first_geometry, geometry_count, xform3x4):
+        x = np.ascontiguousarray(xform3x4, np.float32).reshape(12)
+        out = C.c_uint32()
+        self.ctx.check(self.ctx.L.rt3_scene_push_instance(self.ctx.h, first_geometry, geometry_count, ptr(x), C.byref(out)))
+        self.num_instances += 1
+        return out.value
+
+    def set_texture(self, slot, rgba8):
+        img = np.ascontiguousarray(rgba8, np.uint8)
+        self.ctx.check(self.ctx.L.rt3_scene_set_texture(self.ctx.h, slot, img.shape[1], img.shape[0], ptr(img)))
+
+    def set_environment(self, rgb):
+        img = np.ascontiguousarray(rgb, np.float32)
+        self.ctx.check(self.ctx.L.rt3_scene_set_environment(self.ctx.h, img.shape[1], img.shape[0], ptr(img)))
+
+    def set_bluenoise(self, rgba8):
+        img = np.ascontiguousarray(rgba8, np.uint8)
+        self.ctx.check(self.ctx.L.rt3_scene_set_bluenoise(self.ctx.h, img.shape[1], img.shape[0], ptr(img)))
+
+    def clear(self):
+        self.ctx.check(self.ctx.L.rt3_scene_clear(self.ctx.h))
+        self.num_instances = 0
+
+    def load_scene(self, scene):
+        """Upload a scenes.py dict; geometry offsets in the dict are relative to the dict's own buffers."""
+        v0 = self.push_vertices(scene["vertices"])
+        i0 = self.push_indices(scene["indices"])
+        g0 = None
+        for g in scene["geometries"]:
+            g = np.array(g, copy=True).reshape(1)
+            g["vertex_offset"] += v0
+            g["index_offset"] += i0
+            k = self.push_geometry(g)
+            g0 = k if g0 is None else g0
+        for first, count, xf in scene.get("instances") or []:
+            self.push_instance((g0 or 0) + first, count, xf)
+        for slot, img in (scene.get("textures") or {}).items():
+            self.set_texture(slot, img)
+        if scene.get("environment") is not None:
+            self.set_environment(scene["environment"])
+        if scene.get("bluenoise") is not None:
+            self.set_bluenoise(scene["bluenoise"])
+
+    def create_acceleration_structure(self, flags=1):
+        """RayTracingContext::create_acceleration_structure (raytracing.rs:88-148), PREFER_FAST_TRACE by default."""
+        bs = BuildStats()
+        self.ctx.check(self.ctx.L.rt3_accel_build(self.ctx.h, flags, self.ctx.stream(), C.byref(bs)))
+        self.build_stats = bs
+        return bs
+
+    def download_accel(self):
+        """(nodes [n,20] u32, tris [m,12] u32 view of the 48-byte records) of the built acceleration structure."""
+        bs = self.build_stats
+        nodes = np.zeros((bs.wide_nodes, 20), np.uint32)
+        tris = np.zeros((bs.triangles, 12), np.uint32)
+        self.ctx.check(self.ctx.L.rt3_accel_download(self.ctx.h, ptr(nodes), nodes.nbytes, ptr(tris), tris.nbytes))
+        return nodes, tris
+
+    def resolve_prim(self, prim):
+        a, b, c = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self.ctx.check(self.ctx.L.rt3_resolve_prim(self.ctx.h, int(prim), C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    # raw queries ---------------------------------------------------------------------------------
+    def trace_closest(self, rays_dev, hits_dev=None):
+        torch = _torch()
+        n = rays_dev.shape[0]
+        if hits_dev is None:
+            hits_dev = torch.empty((n, 4), dtype=torch.float32, device=rays_dev.device)
+        self.ctx.check(self.ctx.L.rt3_trace_closest(self.ctx.h, rays_dev.data_ptr(), n, hits_dev.data_ptr(), self.ctx.stream()))
+        return hits_dev
+
+    def trace_any(self, rays_dev, bits_dev=None):
+        torch = _torch()
+        n = rays_dev.shape[0]
+        if bits_dev is None:
+            bits_dev = torch.empty(((n + 31) // 32,), dtype=torch.int32, device=rays_dev.device)
+        self.ctx.check(self.ctx.L.rt3_trace_any(self.ctx.h, rays_dev.data_ptr(), n, bits_dev.data_ptr(), self.ctx.stream()))
+        return bits_dev
+
+    def trace_closest_host(self, rays, out=None):
+        from .types import HIT
+        rays = np.ascontiguousarray(rays)
+        out = np.empty(len(rays), HIT) if out is None else out
+        self.ctx.check(self.ctx.L.rt3_trace_closest_host(self.ctx.h, ptr(rays), len(rays), ptr(out)))
+        return out
+
+    def trace_any_host(self, rays, out=None):
+        rays = np.ascontiguousarray(rays)
+        out = np.empty((len(rays) + 31) // 32, np.uint32) if out is None else out
+        self.ctx.check(self.ctx.L.rt3_trace_any_host(self.ctx.h, ptr(rays), len(rays), ptr(out)))
+        return out
+
+    def trace_stats(self, rays_dev):
+        ts = TraceStats()
+        self.ctx.check(self.ctx.L.rt3_trace_closest_stats(self.ctx.h, rays_dev.data_ptr(), rays_dev.shape[0], C.byref(ts)))
+        return ts
+
+
+@dataclass(frozen=True)
+class WorkSize2D:
+    """executions.rs:57-78"""
+    kind: str = "FullScreen"
+    x: int = 0
+    y: int = 0
+
+    @staticmethod
+    def FullScreen():
+        return WorkSize2D("FullScreen")
+
+    @staticmethod
+    def FractionalFullScreen(x, y):
+        return WorkSize2D("FractionalFullScreen", x, y)
+
+    @staticmethod
+    def X(x):
+        return WorkSize2D("X", x, 1)
+
+    @staticmethod
+    def XY(x, y):
+        return WorkSize2D("XY", x, y)
+
+    def size(self, window):
+        w, h = window
+        if self.kind == "FullScreen":
+            return w, h
+        if self.kind == "FractionalFullScreen":
+            return -(-w // self.x), -(-h // self.y)
+        return self.x, self.y
+
+
+_FORMATS = {"RGBA32UI": ("int32", 4), "R32F": ("float32", 1), "RGBA32F": ("float32", 4), "RG32UI": ("int32", 2), "RG32F": ("float32", 2)}
+
+
+class RenderGraph:
+    """Named full-screen images backed by torch CUDA tensors (render_graph/mod.rs:440-483); passes run in
+    declaration order on the current stream, so no barrier synthesis is needed."""
+
+    def __init__(self, ctx, world, window_size):
+        self.ctx, self.world = ctx, world
+        self.window = (int(window_size[0]), int(window_size[1]))
+        self.resources = {}
+        self.frame_number = 0
+
+    def image(self, fmt, name):
+        torch = _torch()
+        if name not in self.resources:
+            dt, ch = _FORMATS[fmt]
+            w, h = self.window
+            shape = (h, w, ch) if ch > 1 else (h, w)
+            self.resources[name] = torch.zeros(shape, dtype=getattr(torch, dt), device=f"cuda:{self.ctx.device}")
+        return name
+
+    def tensor(self, name):
+        return self.resources[name]
+
+
+class _PassBuilder:
+    def __init__(self, rg, name):
+        self.rg, self.name = rg, name
+        self._shader, self._entry, self._constants = "", "main", None
+        self._bind = {}
+
+    def shader(self, path):
+        self._shader = path
+        return self
+
+    def entry(self, name):
+        self._entry = name
+        return self
+
+    def constants(self, gconst):
+        p = np.ascontiguousarray(gconst)
+        assert p.dtype == PARAMS and p.size == 1
+        self._constants = p
+        return self
+
+    def read(self, slot, res):
+        self._bind[slot] = res
+        return self
+
+    write = read
+    read_write = read
+
+    def _ptr(self, slot, required=True):
+        if slot not in self._bind:
+            if required:
+                raise KeyError(f"pass '{self.name}' ({self._shader}): resource slot '{slot}' not bound")
+            return None
+        return C.c_void_p(self.rg.tensor(self._bind[slot]).data_ptr())
+
+
+class RayTracingPass(_PassBuilder):
+    """RayTracingPass::new(rg, name) ... .launch(WorkSize2D) -> vkCmdTraceRaysKHR(x, y, 1)."""
+
+    @staticmethod
+    def new(rg, name):
+        return RayTracingPass(rg, name)
+
+    def launch(self, work=WorkSize2D.FullScreen()):
+        ctx = self.rg.ctx
+        if self._constants is None:
+            raise ValueError("constants(&gconst) not set")
+        x, y = work.size(self.rg.window)
+        rect = Rect(0, 0, x, y)
+        p = ptr(self._constants)
+        if self._shader == "gbuffer":
+            st = ctx.L.rt3_pass_gbuffer(ctx.h, p, rect, self._ptr("gbuffer"), self._ptr("gbuffer_depth"), self._ptr("ids", False),
+                                        self._ptr("bary", False), ctx.stream())
+        elif self._shader == "refrence_mode":
+            st = ctx.L.rt3_pass_reference(ctx.h, p, rect, self._ptr("gbuffer"), self._ptr("gbuffer_depth"), self._ptr("PrevLight", False),
+                                          self._ptr("Light"), ctx.stream())
+        else:
+            raise ValueError(f"unknown ray-tracing shader '{self._shader}' (known: gbuffer, refrence_mode)")
+        ctx.check(st)
+        return self.name
+
+
+class ComputePass(_PassBuilder):
+    @staticmethod
+    def new(rg, name):
+        return ComputePass(rg, name)
+
+    def dispatch(self, work=WorkSize2D.FullScreen()):
+        ctx = self.rg.ctx
+        x, y = work.size(self.rg.window)
+        if self._shader != "postprocess":
+            raise ValueError(f"unknown compute shader '{self._shader}' (known: postprocess)")
+        ctx.check(ctx.L.rt3_pass_postprocess(ctx.h, ptr(self._constants), Rect(0, 0, x, y), self._ptr("Depth"), self._ptr("In"), self._ptr("Out"),
+                                             ctx.stream()))
+        return self.name
+
+
+class Renderer:
+    """The per-frame `commands` system (src/renderer/mod.rs:65-106) for the ray-tracing path:
+    gbuffer pass -> reference-mode pass (ping-pong Light/PrevLight) -> optional postprocess."""
+
+    def __init__(self, ctx, world, width, height):
+        self.ctx, self.world = ctx, world
+        self.rg = RenderGraph(ctx, world, (width, height))
+        rg = self.rg
+        rg.image("RGBA32UI", "gbuffer"); rg.image("R32F", "gbuffer_depth"); rg.image("RG32UI", "ids"); rg.image("RG32F", "bary")
+        rg.image("RGBA32F", "light0"); rg.image("RGBA32F", "light1"); rg.image("RGBA32F", "out")
+        self.cur = 0
+
+    def frame(self, gconst, postprocess=False, debug_ids=False):
+        rg = self.rg
+        light, prev = f"light{self.cur}", f"light{1 - self.cur}"
+        b = RayTracingPass.new(rg, "gbuffer").shader("gbuffer").constants(gconst).write("gbuffer", "gbuffer").write("gbuffer_depth", "gbuffer_depth")
+        if debug_ids:
+            b.write("ids", "ids").write("bary", "bary")
+        b.launch(WorkSize2D.FullScreen())
+        (RayTracingPass.new(rg, "reference").shader("refrence_mode").constants(gconst).read("gbuffer", "gbuffer").read("gbuffer_depth", "gbuffer_depth")
+         .read("PrevLight", prev).write("Light", light).launch(WorkSize2D.FullScreen()))
+        if postprocess:
+            (ComputePass.new(rg, "postprocess").shader("postprocess").constants(gconst).read("Depth", "gbuffer_depth").read("In", light)
+             .write("Out", "out").dispatch(WorkSize2D.FullScreen()))
+        self.cur = 1 - self.cur
+        rg.frame_number += 1
+        return rg.tensor(light)
+
+    def render_frame_host(self, gconst, light_host, prev_light_host=None):
+        """End-to-end path with HOST buffers (params in, framebuffer out)."""
+        p = np.ascontiguousarray(gconst)
+        self.ctx.check(self.ctx.L.rt3_render_frame_host(self.ctx.h, ptr(p), None if prev_light_host is None else C.c_void_p(prev_light_host),
+                                                        C.c_void_p(light_host), None, None))

@@ -99,6 +99,18 @@ EmuBvh* emu_build(const float* tris9, uint32_t n) {
     b->n_nodes = node_counter; b->n_tris = tri_counter;
     return b;
 }
+/* wrap an acceleration structure built elsewhere (downloaded from the GPU) so that it can be traversed here */
+EmuBvh* emu_wrap(const uint32_t* nodes20, uint32_t n_nodes, const uint32_t* tris12, uint32_t n_tris) {
+    EmuBvh* b = new EmuBvh();
+    b->nodes.resize(n_nodes ? n_nodes : 1);
+    memcpy(b->nodes.data(), nodes20, (size_t)n_nodes * sizeof(WideNode));
+    b->tris_out.resize(n_tris);
+    memcpy(b->tris_out.data(), tris12, (size_t)n_tris * sizeof(Tri48));
+    b->tris_in.resize(n_tris);
+    for (uint32_t i = 0; i < n_tris; ++i) if (b->tris_out[i].prim < n_tris) b->tris_in[b->tris_out[i].prim] = b->tris_out[i];
+    b->n_nodes = n_nodes; b->n_tris = n_tris;
+    return b;
+}
 void emu_destroy(EmuBvh* b) { delete b; }
 void emu_info(const EmuBvh* b, uint32_t* out4, float* sah2) {
     out4[0] = b->n_nodes; out4[1] = b->n_tris; out4[2] = b->levels; out4[3] = (uint32_t)b->tris_in.size();

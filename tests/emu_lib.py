@@ -1,0 +1,72 @@
+"""ctypes wrapper over tests/emu/libemu.so (CPU emulation of the device BVH logic; test infrastructure)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from raytracer3_b200.types import HIT, ptr
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "emu", "libemu.so")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        src = os.path.join(_HERE, "emu", "emu.cpp")
+        hdr = os.path.join(_HERE, "..", "raytracer3_b200", "csrc", "bvh_logic.h")
+        if not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas",
+                                   "-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", _SO, src])
+        L = C.CDLL(_SO)
+        L.emu_build.restype = C.c_void_p
+        L.emu_build.argtypes = [C.c_void_p, C.c_uint32]
+        L.emu_wrap.restype = C.c_void_p
+        L.emu_wrap.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+        L.emu_destroy.argtypes = [C.c_void_p]
+        L.emu_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.emu_check_triangles.restype = C.c_uint32
+        L.emu_check_triangles.argtypes = [C.c_void_p]
+        L.emu_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int, C.c_void_p]
+        L.emu_trace_any.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]
+        _lib = L
+    return _lib
+
+
+class EmuBvh:
+    def __init__(self, tris=None, nodes=None, tri_records=None):
+        self.L = lib()
+        if tris is not None:
+            t = np.ascontiguousarray(tris, np.float32)
+            self.h = self.L.emu_build(ptr(t), len(t))
+        else:
+            n, r = np.ascontiguousarray(nodes, np.uint32), np.ascontiguousarray(tri_records, np.uint32)
+            self.h = self.L.emu_wrap(ptr(n), len(n), ptr(r), len(r))
+
+    def __del__(self):
+        try:
+            self.L.emu_destroy(self.h)
+        except Exception:
+            pass
+
+    def info(self):
+        a, s = np.zeros(4, np.uint32), np.zeros(2, np.float32)
+        self.L.emu_info(self.h, ptr(a), ptr(s))
+        return dict(nodes=int(a[0]), tris=int(a[1]), levels=int(a[2]), input_tris=int(a[3]), sah_nodes=float(s[0]), sah_tris=float(s[1]))
+
+    def check_triangles(self):
+        return self.L.emu_check_triangles(self.h)
+
+    def trace_closest(self, rays, brute=False):
+        rays = np.ascontiguousarray(rays)
+        out, st = np.zeros(len(rays), HIT), np.zeros(2)
+        self.L.emu_trace_closest(self.h, ptr(rays), len(rays), ptr(out), 1 if brute else 0, ptr(st))
+        return out, st
+
+    def trace_any(self, rays, brute=False):
+        rays = np.ascontiguousarray(rays)
+        out = np.zeros((len(rays) + 31) // 32, np.uint32)
+        self.L.emu_trace_any(self.h, ptr(rays), len(rays), ptr(out), 1 if brute else 0)
+        return out
