@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the path: Mrays/s (and spp/s) of the ray-traced G-buffer + 4-bounce reference-mode path
+tracer at 1920x1080, 1 spp, environment light + blue-noise sampling (BASELINE.json configs[1]) on the synthetic atrium
+(sponza_scene.glb / skybox2.exr are absent from the reference mount; every number is tagged scene=synthetic_atrium).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU under torchrun for N > 1)
+  python bench.py --impl reference --gpus N --steps K ...  # the CPU restatement of the reference's shader passes (oracle/), all host threads
+
+A step = one frame: G-buffer pass + reference-mode pass (+ for N > 1 the NCCL gather of the finished tiles).
+N > 1 is WEAK scaling over screen tiles: every rank owns 1920x1080 pixels' worth of 64x64 tiles of an N-times larger frame
+(N=2: 3840x1080, N=4: 3840x2160, N=8: 7680x2160), scene and BVH replicated, one all_gather of the framebuffer slabs per frame.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FRAME_DIMS = {1: (1920, 1080), 2: (3840, 1080), 4: (3840, 2160), 8: (7680, 2160)}
+BOUNCES, SAMPLES = 4, 1
+HBM_BYTES_PER_RAY = 48          # 32 B rt3_ray read + 16 B rt3_hit written
+FALLBACK_HBM_GBS = 6650.0       # /opt/skills/guides/B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+
+
+def make_scene():
+    from raytracer3_b200 import scenes
+    sc = scenes.synthetic_atrium(scenes.SPONZA_DETAIL)
+    sc["bluenoise"] = scenes.blue_noise_tile()
+    return sc
+
+
+def frame_dims(n):
+    if n in FRAME_DIMS:
+        return FRAME_DIMS[n]
+    return 1920 * n, 1080
+
+
+def params_for(sc, W, H, frame, flags):
+    from raytracer3_b200.camera import camera_for, make_params
+    return make_params(camera_for(sc, "cam0", W, H), W, H, frame=frame, bounces=BOUNCES, samples=SAMPLES, blendfactor=1.0, flags=flags)
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            with open(p) as f:
+                return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = str(e)
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.02)
+
+    def __enter__(self):
+        if self.ok:
+            self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        if self.ok:
+            self.t.join()
+
+    def summary(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "NVML unavailable"}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def cpu_frame(orc, sc, W, H, frame, flags, buffers=None):
+    """One frame of both passes on the CPU oracle; returns (seconds, rays, non-background pixels)."""
+    p = params_for(sc, W, H, frame, flags)
+    if buffers is None:
+        buffers = (np.zeros((H, W, 4), np.uint32), np.zeros((H, W), np.float32), np.zeros((H, W, 4), np.float32))
+    gb, dp, lt = buffers
+    t0 = time.perf_counter()
+    orc.pass_gbuffer(p, gbuffer=gb, depth=dp)
+    _, cnt = orc.pass_reference(p, gb, dp, light=lt)
+    dt = time.perf_counter() - t0
+    return dt, W * H + cnt.rays_secondary, int((dp != 100000.0).sum())
+
+
+def run_reference(args):
+    """The reference's own implementation of the path cannot run here (Rust nightly + Slang + Vulkan RT; no toolchain, no
+    graphics stack, shaders include a file missing from the tree): this arm times the CPU restatement of its shader passes
+    (oracle/, kind "port") on all host threads, same config / metric / unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle.oracle_py import OracleScene
+    from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV
+    flags = FLAG_ENV | FLAG_BLUENOISE
+    sc = make_scene()
+    orc = OracleScene(sc)
+    W, H = frame_dims(1)      # the CPU arm always renders the N=1 frame: a bounded sample of the N-GPU workload
+    buffers = (np.zeros((H, W, 4), np.uint32), np.zeros((H, W), np.float32), np.zeros((H, W, 4), np.float32))
+    for i in range(args.warmup):
+        cpu_frame(orc, sc, W, H, i, flags, buffers)
+    tot_t = tot_r = tot_px = 0
+    for i in range(args.steps):
+        dt, rays, px = cpu_frame(orc, sc, W, H, args.warmup + i, flags, buffers)
+        tot_t += dt; tot_r += rays; tot_px += px
+    val = tot_r / tot_t / 1e6
+    line = {
+        "impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "spp_per_s": tot_px * SAMPLES / tot_t,
+        "config": {"workload": f"synthetic_atrium {W}x{H} path tracing, bounces={BOUNCES}, {SAMPLES} spp, env light + blue noise (BASELINE configs[1])",
+                   "scene": "synthetic_atrium", "triangles": orc.num_triangles, "flags": "ENV|BLUENOISE"},
+        "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": orc.threads, "kind": "port",
+                         "sample": f"full {W}x{H} frame per step, {args.steps} steps (CPU oracle: scalar BVH2 + restated Slang passes, std::thread)"},
+        "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ CUDA arm
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+    from raytracer3_b200 import scenes
+    from raytracer3_b200.host import RenderContext, Renderer, RenderWorld, TiledRenderer
+    from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, RAY
+
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    n_gpus = world_size
+    flags = FLAG_ENV | FLAG_BLUENOISE
+    W, H = frame_dims(n_gpus)
+
+    sc = make_scene()
+    ctx = RenderContext(local_rank)
+    world = RenderWorld(ctx)
+    world.load_scene(sc)
+    bs = world.create_acceleration_structure()
+
+    tiled = n_gpus > 1
+    if tiled:
+        R = TiledRenderer(ctx, world, W, H, rank, world_size, tile=64)
+    else:
+        R = Renderer(ctx, world, W, H)
+
+    def step(i):
+        p = params_for(sc, W, H, i, flags)
+        if tiled:
+            return R.gather(R.frame(p))
+        return R.frame(p)
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    ctx.counters(reset=True)
+    ctx.profile_enable(True)
+    launches0 = ctx.kernel_launches()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        ev0.record()
+        for i in range(args.steps):
+            step(args.warmup + i)
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        launches = ctx.kernel_launches() - launches0
+        cnt = ctx.counters(reset=True)
+        trace_ms, trace_launches = ctx.profile_read()
+        ctx.profile_enable(False)
+
+        # ---- end to end through the host-buffer C ABI call (N = 1) / tile path + gather + D2H (N > 1)
+        host_light = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
+        e2e_steps = max(3, min(args.steps, 20))
+
+        def e2e_step(i):
+            p = params_for(sc, W, H, i, flags)
+            if tiled:
+                fb = R.gather(R.frame(p))                       # params go H2D inside the pass calls
+                if rank == 0:
+                    host_light.copy_(fb, non_blocking=True)
+                torch.cuda.synchronize()
+            else:
+                R.render_frame_host(p, host_light.data_ptr())  # synchronous: params H2D, frame D2H
+        for i in range(2):
+            e2e_step(i)
+        barrier()
+        ctx.counters(reset=True)
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            e2e_step(100 + i)
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        e2e_cnt = ctx.counters(reset=True)
+
+    rays_local = cnt.rays_primary + cnt.rays_secondary
+    stats = torch.tensor([ms, float(rays_local), float(cnt.paths_started), float(e2e_s), float(e2e_cnt.rays_primary + e2e_cnt.rays_secondary),
+                          float(launches), float(cnt.rays_secondary), float(trace_ms), float(trace_launches)], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world_size > 1:
+        mx = stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms, e2e_s = float(mx[0]), float(mx[3])
+        rays, paths, e2e_rays, launches_all = float(sm[1]), float(sm[2]), float(sm[4]), float(sm[5])
+    else:
+        rays, paths, e2e_rays, launches_all = float(stats[1]), float(stats[2]), float(stats[4]), float(stats[5])
+
+    if rank == 0:
+        value = rays / (ms * 1e-3) / 1e6
+        peak, peak_src = hbm_peak()
+        # dominant kernel: k_trace (closest hit over the secondary-ray queues); algorithmic HBM bytes = 48 B per ray
+        t_rays, t_ms, t_n = float(stats[6]), float(stats[7]), max(1.0, float(stats[8]))
+        achieved = (HBM_BYTES_PER_RAY * t_rays / t_n) / (t_ms / t_n * 1e-3) / 1e9 if t_ms > 0 else 0.0
+        line = {
+            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "spp_per_s": paths / (ms * 1e-3), "rays_per_step": rays / args.steps,
+            "config": {"workload": f"synthetic_atrium {W}x{H} path tracing, bounces={BOUNCES}, {SAMPLES} spp, env light + blue noise (BASELINE configs[1]"
+                                   + (f", weak-scaled to {n_gpus} x 1920x1080 pixels over 64x64 screen tiles + NCCL all_gather per frame)" if tiled else ")"),
+                       "scene": "synthetic_atrium", "triangles": int(bs.triangles), "wide_nodes": int(bs.wide_nodes), "bvh_mb": (bs.node_bytes + bs.tri_bytes) / 1e6,
+                       "build_ms": bs.ms_total, "flags": "ENV|BLUENOISE", "parallelism": f"tiles{n_gpus}",
+                       "l2_policy": "per-frame buffers (G-buffer, depth, Light, ray/hit/path queues: ~%d MB) exceed the 126 MB L2 between steps; the "
+                                    "scene + BVH stay L2-resident across frames by design (static scene)" % int(W * H / n_gpus * (16 + 4 + 16 + 2 * 32 + 16 + 2 * 16 + 20) / 1e6)},
+            "clocks": clocks.summary(),
+            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 304 * (n_gpus if tiled else 1),
+                    "d2h_bytes_per_step": W * H * 16, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
+                    "path": "rt3_render_frame_host (params H2D, RGBA32F frame D2H to pinned memory)" if not tiled else
+                            "rt3_pass_*_tiles + all_gather + rt3_untile + full-frame D2H on rank 0"},
+            "gpu_launches": int(launches_all),
+            "roofline": {"kernel": "k_trace<closest> (secondary-ray queues)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "bytes_per_ray": HBM_BYTES_PER_RAY,
+                         "kernel_ms_per_launch": t_ms / t_n, "rays_per_launch": t_rays / t_n, "launches": int(t_n),
+                         "kernel_share_of_step": t_ms / ms if ms > 0 else None,
+                         "note": "traversal is L2-latency/issue bound, not HBM bound: the BVH is L2-resident, HBM only streams 48 B per ray (see roofline_l2)"},
+        }
+        if not args.no_extras:
+            line.update(extras(ctx, world, sc, bs, t_rays / (t_ms * 1e-3) if t_ms > 0 else 0.0))
+            line["cpu_baseline"] = cpu_baseline(sc, flags)
+        print(json.dumps(line), flush=True)
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def extras(ctx, world, sc, bs, trace_rays_per_s):
+    """L2 roofline of the traversal kernel + the config-4 incoherent-ray microbenchmark (N = 1, outside the timed region)."""
+    import torch
+    from raytracer3_b200 import scenes
+    out = {}
+    n = 1 << 22
+    closest, anyr = scenes.incoherent_rays(sc, n)
+    dc = torch.from_numpy(closest.view(np.float32).reshape(n, 8)).cuda()
+    da = torch.from_numpy(anyr.view(np.float32).reshape(n, 8)).cuda()
+    hits = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    bits = torch.empty(((n + 31) // 32,), dtype=torch.int32, device="cuda")
+    res = {}
+    for name, fn in (("closest", lambda: world.trace_closest(dc, hits)), ("any", lambda: world.trace_any(da, bits))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        res[name] = n * 10 / (e0.elapsed_time(e1) * 1e-3) / 1e6
+    ts = world.trace_stats(dc[: 1 << 20])
+    l2_peak = ctx.measure_l2_bandwidth(32 << 20, 10)
+    l2_bytes = ts.node_bytes_per_ray + ts.tri_bytes_per_ray
+    out["incoherent"] = {"rays": n, "closest_mrays_s": res["closest"], "any_mrays_s": res["any"],
+                         "note": "BASELINE configs[3] generator on a 2^22-ray subset, device-resident, 10 launches each"}
+    ach = l2_bytes * res["closest"] * 1e6 / 1e9
+    out["roofline_l2"] = {"kernel": "k_trace<closest> on the incoherent set", "bound": "l2", "achieved": ach, "peak": l2_peak, "unit": "GB/s",
+                          "frac": ach / l2_peak if l2_peak else None, "nodes_per_ray": ts.nodes_per_ray, "tris_per_ray": ts.tris_per_ray,
+                          "bytes_per_ray": l2_bytes, "peak_source": "measured here: ld.global.cg sweep of a 32 MB L2-resident buffer, best of 10"}
+    return out
+
+
+def cpu_baseline(sc, flags):
+    from oracle.oracle_py import OracleScene
+    orc = OracleScene(sc)
+    W, H = frame_dims(1)
+    cpu_frame(orc, sc, W, H, 0, flags)
+    dt, rays, _ = cpu_frame(orc, sc, W, H, 1, flags)
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": orc.threads, "kind": "port",
+            "sample": f"one full {W}x{H} frame (after one warm-up frame) of the same workload on the CPU oracle, {rays} rays in {dt:.2f} s"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the microbench / L2 roofline / cpu_baseline legs")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
+    import __graft_entry__ as g
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        g.build()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()

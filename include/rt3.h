@@ -196,6 +196,10 @@ RT3_API rt3_status rt3_measure_l2_bandwidth(rt3_context*, size_t bytes, int iter
 typedef struct { double nodes_per_ray, tris_per_ray, node_bytes_per_ray, tri_bytes_per_ray; } rt3_trace_stats;
 RT3_API rt3_status rt3_trace_closest_stats(rt3_context*, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out);
 
+/* Per-kernel timing of the closest-hit traversal launches made by the passes: while enabled, every launch is bracketed by
+ * CUDA events on its own stream; rt3_profile_read synchronises, returns the summed duration and launch count, and resets. */
+RT3_API rt3_status rt3_profile_enable(rt3_context*, int enable);
+RT3_API rt3_status rt3_profile_read(rt3_context*, double* trace_ms, uint64_t* trace_launches);
 /* Copy the built acceleration structure to host memory (80-byte wide nodes, 48-byte triangle records; sizes from
  * rt3_build_stats.node_bytes / tri_bytes).  Lets tests prove with an order-independent check that the build kept every
  * triangle exactly once, and replay the traversal on the CPU. */

@@ -176,13 +176,14 @@ inline float safe_inv(float d) {
     if (abs_(d) < tiny) d = (as_uint(d) >> 31) ? -tiny : tiny;
     return 1.0f / d;
 }
-inline bool slab(const Box& b, vec3 o, vec3 id, float tmin, float tmax) {
+/* Returns the entry distance, or a negative value when the (padded) slab test fails. */
+inline float slab(const Box& b, vec3 o, vec3 id, float tmin, float tmax) {
     float x1 = (b.lo.x - o.x) * id.x, x2 = (b.hi.x - o.x) * id.x;
     float y1 = (b.lo.y - o.y) * id.y, y2 = (b.hi.y - o.y) * id.y;
     float z1 = (b.lo.z - o.z) * id.z, z2 = (b.hi.z - o.z) * id.z;
     float tn = max_(max_(min_(x1, x2), min_(y1, y2)), max_(min_(z1, z2), tmin));
     float tf = min_(min_(max_(x1, x2), max_(y1, y2)), min_(max_(z1, z2), tmax));
-    return tn <= tf * 1.0000005f;
+    return tn <= tf * 1.0000005f ? tn : -1.0f;
 }
 
 /* trace(): closest hit.  The payload semantics follow default_hit.slang:4-8 / default_miss.slang:4-7. */
@@ -205,10 +206,13 @@ rt3_hit closest_bvh(const orc_scene& s, const rt3_ray& r) {
     if (s.nodes.empty()) return h;
     vec3 o = v3(r.o), d = v3(r.d);
     vec3 id = v3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
-    uint32_t stack[128]; int sp = 0; stack[sp++] = 0;
+    if (slab(s.nodes[0].box, o, id, r.tmin, h.t) < 0.0f) return h;
+    struct Entry { uint32_t node; float tn; };
+    Entry stack[128]; int sp = 0; stack[sp++] = {0, 0.0f};
     while (sp) {
-        const Node2& nd = s.nodes[stack[--sp]];
-        if (!slab(nd.box, o, id, r.tmin, h.t)) continue;
+        Entry e = stack[--sp];
+        if (e.tn > h.t) continue;                     /* entered farther than the current hit (ties are kept: tn <= t) */
+        const Node2& nd = s.nodes[e.node];
         if (nd.count) {
             for (uint32_t k = nd.left; k < nd.left + nd.count; ++k) {
                 uint32_t i = s.order[k];
@@ -220,7 +224,13 @@ rt3_hit closest_bvh(const orc_scene& s, const rt3_ray& r) {
             }
         } else {
             if (sp + 2 > 128) abort();
-            stack[sp++] = nd.left; stack[sp++] = nd.left + 1;
+            float ta = slab(s.nodes[nd.left].box, o, id, r.tmin, h.t), tb = slab(s.nodes[nd.left + 1].box, o, id, r.tmin, h.t);
+            /* near child on top of the stack; traversal order does not change the result (closer_hit is order independent) */
+            if (ta >= 0.0f && tb >= 0.0f) {
+                if (ta <= tb) { stack[sp++] = {nd.left + 1, tb}; stack[sp++] = {nd.left, ta}; }
+                else { stack[sp++] = {nd.left, ta}; stack[sp++] = {nd.left + 1, tb}; }
+            } else if (ta >= 0.0f) stack[sp++] = {nd.left, ta};
+            else if (tb >= 0.0f) stack[sp++] = {nd.left + 1, tb};
         }
     }
     return h;
@@ -240,7 +250,7 @@ bool any_bvh(const orc_scene& s, const rt3_ray& r) {
     uint32_t stack[128]; int sp = 0; stack[sp++] = 0;
     while (sp) {
         const Node2& nd = s.nodes[stack[--sp]];
-        if (!slab(nd.box, o, id, r.tmin, r.tmax)) continue;
+        if (slab(nd.box, o, id, r.tmin, r.tmax) < 0.0f) continue;
         if (nd.count) {
             for (uint32_t k = nd.left; k < nd.left + nd.count; ++k) {
                 float t, u, v;

@@ -69,6 +69,8 @@ def load():
         "rt3_kernel_launches": (u64, [vp]),
         "rt3_measure_l2_bandwidth": (i32, [vp, C.c_size_t, i32, P(C.c_double)]),
         "rt3_trace_closest_stats": (i32, [vp, vp, u64, P(TraceStats)]),
+        "rt3_profile_enable": (i32, [vp, i32]),
+        "rt3_profile_read": (i32, [vp, P(C.c_double), P(u64)]),
         "rt3_accel_download": (i32, [vp, vp, C.c_size_t, vp, C.c_size_t]),
     }
     for name, (res, args) in sig.items():

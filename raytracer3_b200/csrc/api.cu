@@ -216,6 +216,7 @@ void rt3_destroy(rt3_context* c) {
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();
     for (int i = 0; i < 8; ++i) cudaEventDestroy(c->ev[i]);
+    for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
     delete c;
 }
 
@@ -472,6 +473,26 @@ rt3_status rt3_trace_closest_stats(rt3_context* c, const rt3_ray* rays, uint64_t
     });
 }
 
+rt3_status rt3_profile_enable(rt3_context* c, int enable) {
+    return guarded(c, [&]() {
+        RT3_CUDA(c, cudaDeviceSynchronize());
+        c->prof_on = enable != 0; c->prof_used = 0; c->prof_trace_ms = 0; c->prof_trace_launches = 0;
+    });
+}
+rt3_status rt3_profile_read(rt3_context* c, double* trace_ms, uint64_t* trace_launches) {
+    return guarded(c, [&]() {
+        RT3_CUDA(c, cudaDeviceSynchronize());
+        for (size_t i = 0; i + 1 < c->prof_used; i += 2) {
+            float ms = 0;
+            RT3_CUDA(c, cudaEventElapsedTime(&ms, c->prof_events[i], c->prof_events[i + 1]));
+            c->prof_trace_ms += ms; c->prof_trace_launches++;
+        }
+        c->prof_used = 0;
+        if (trace_ms) *trace_ms = c->prof_trace_ms;
+        if (trace_launches) *trace_launches = c->prof_trace_launches;
+        c->prof_trace_ms = 0; c->prof_trace_launches = 0;
+    });
+}
 rt3_status rt3_accel_download(rt3_context* c, void* nodes_host, size_t nodes_bytes, void* tris_host, size_t tris_bytes) {
     return guarded(c, [&]() {
         require_accel(c);

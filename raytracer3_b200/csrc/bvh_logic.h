@@ -338,17 +338,60 @@ RT3_HD RayPrep prepare_ray(const rt3_ray& r) {
 
 RT3_HD uint32_t byte_of(uint32_t w, int j) { return (w >> (8 * j)) & 0xFFu; }
 
+/* Byte j of w as the float 32768 + q, built with one byte permute instead of an integer-to-float conversion
+ * (I2F runs at a quarter of the FMA rate): bits = 0x47000000 | q << 8, i.e. exponent 2^15 with q in mantissa bits 8..15. */
+template <int J>
+RT3_HD float byte_as_biased_float(uint32_t w) {
+#ifdef __CUDA_ARCH__
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(0x47000000u), "n"(0x7604 | (J << 4)));
+    return __uint_as_float(r);
+#else
+    return rt3m::as_float(0x47000000u | (((w >> (8 * J)) & 0xFFu) << 8));
+#endif
+}
+/* min / max for the slab test only: no NaN can occur there (directions are clamped away from 0), so the
+ * single-instruction FMNMX forms are exact equivalents of the a<b?a:b forms used by the shader math. */
+RT3_HD float bmin(float a, float b) {
+#ifdef __CUDA_ARCH__
+    return fminf(a, b);
+#else
+    return a < b ? a : b;
+#endif
+}
+RT3_HD float bmax(float a, float b) {
+#ifdef __CUDA_ARCH__
+    return fmaxf(a, b);
+#else
+    return a > b ? a : b;
+#endif
+}
+
+template <int J>
+RT3_HD uint32_t slab_child(uint32_t nx, uint32_t fx, uint32_t ny, uint32_t fy, uint32_t nz, uint32_t fz, float sx, float sy, float sz, float bx,
+                           float by, float bz, float tmin, float tmax, uint32_t child_bits4, uint32_t bit_index4) {
+    const float t0x = rt3m::fma_(byte_as_biased_float<J>(nx), sx, bx), t1x = rt3m::fma_(byte_as_biased_float<J>(fx), sx, bx);
+    const float t0y = rt3m::fma_(byte_as_biased_float<J>(ny), sy, by), t1y = rt3m::fma_(byte_as_biased_float<J>(fy), sy, by);
+    const float t0z = rt3m::fma_(byte_as_biased_float<J>(nz), sz, bz), t1z = rt3m::fma_(byte_as_biased_float<J>(fz), sz, bz);
+    const float tn = bmax(bmax(t0x, t0y), bmax(t0z, tmin));
+    const float tf = bmin(bmin(t1x, t1y), bmin(t1z, tmax));
+    return (tn <= tf) ? (((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu)) : 0u;
+}
+
 /* Intersect the 8 quantised child boxes of one node.  Returns the hit mask: bits 24..31 = inner
- * children in near-to-far priority order for this ray's octant, bits 0..23 = triangles of hit leaves. */
+ * children in near-to-far priority order for this ray's octant, bits 0..23 = triangles of hit leaves.
+ * Plane distance = (p + q 2^e - o) / d = (32768 + q) * s + (b - 32768 s) with s = 2^e / d, b = (p - o) / d: one PRMT and
+ * one FFMA per plane.  The rounding of (b - 32768 s) costs at most 1/512 of a quantisation step, which the
+ * builder's triangle-box padding (scene extent / 65536) covers. */
 RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n0, const u32x4& n1, const u32x4& n2,
                                     const u32x4& n3, const u32x4& n4) {
     const uint32_t e = n0.w;
     const float sx = rt3m::as_float((e & 0xFFu) << 23) * r.idx;
     const float sy = rt3m::as_float(((e >> 8) & 0xFFu) << 23) * r.idy;
     const float sz = rt3m::as_float(((e >> 16) & 0xFFu) << 23) * r.idz;
-    const float bx = (rt3m::as_float(n0.x) - r.ox) * r.idx;
-    const float by = (rt3m::as_float(n0.y) - r.oy) * r.idy;
-    const float bz = (rt3m::as_float(n0.z) - r.oz) * r.idz;
+    const float bx = rt3m::fma_(-32768.0f, sx, (rt3m::as_float(n0.x) - r.ox) * r.idx);
+    const float by = rt3m::fma_(-32768.0f, sy, (rt3m::as_float(n0.y) - r.oy) * r.idy);
+    const float bz = rt3m::fma_(-32768.0f, sz, (rt3m::as_float(n0.z) - r.oz) * r.idz);
     uint32_t hitmask = 0;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
@@ -362,15 +405,10 @@ RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n
         const uint32_t nx = r.idx < 0.0f ? qhx : qlx, fx = r.idx < 0.0f ? qlx : qhx;
         const uint32_t ny = r.idy < 0.0f ? qhy : qly, fy = r.idy < 0.0f ? qly : qhy;
         const uint32_t nz = r.idz < 0.0f ? qhz : qlz, fz = r.idz < 0.0f ? qlz : qhz;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float t0x = rt3m::fma_((float)byte_of(nx, j), sx, bx), t1x = rt3m::fma_((float)byte_of(fx, j), sx, bx);
-            float t0y = rt3m::fma_((float)byte_of(ny, j), sy, by), t1y = rt3m::fma_((float)byte_of(fy, j), sy, by);
-            float t0z = rt3m::fma_((float)byte_of(nz, j), sz, bz), t1z = rt3m::fma_((float)byte_of(fz, j), sz, bz);
-            float tn = rt3m::max_(rt3m::max_(t0x, t0y), rt3m::max_(t0z, r.tmin));
-            float tf = rt3m::min_(rt3m::min_(t1x, t1y), rt3m::min_(t1z, tmax));
-            if (tn <= tf) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
-        }
+        hitmask |= slab_child<0>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
+        hitmask |= slab_child<1>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
+        hitmask |= slab_child<2>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
+        hitmask |= slab_child<3>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
     }
     return hitmask;
 }

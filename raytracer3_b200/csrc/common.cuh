@@ -104,6 +104,12 @@ struct rt3_context {
     Scratch f_gbuffer, f_depth, f_light, f_prev, f_rays, f_hits, f_bits, l2_buf;
     DeviceCounters* d_counters = nullptr;
     cudaEvent_t ev[8];
+
+    /* optional per-kernel timing of the traversal launches (rt3_profile_*): event pairs on the launch stream */
+    bool prof_on = false;
+    std::vector<cudaEvent_t> prof_events;
+    size_t prof_used = 0;
+    double prof_trace_ms = 0; uint64_t prof_trace_launches = 0;
 };
 
 template <class T>

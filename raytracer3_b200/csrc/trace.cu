@@ -11,6 +11,9 @@
  */
 #include "common.cuh"
 
+#include <algorithm>
+#include <cstdlib>
+
 using namespace rt3b;
 
 namespace {
@@ -66,6 +69,104 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
     }
 }
 
+/*
+ * Production traversal kernel: persistent warps with DYNAMIC RAY FETCH.  A warp that keeps its 32 rays until the
+ * slowest one finishes runs at the mean/max traversal length (measured: 7.5 of 32 lanes active on the secondary-ray
+ * queues); here a lane whose ray terminates writes its result and, once fewer than KEEP lanes of the warp are still
+ * busy, the idle lanes pull new rays from the global queue with one warp-aggregated atomic.
+ */
+template <bool ANY, int KEEP>
+__global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
+                                                             const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
+                                                             rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter) {
+    const uint64_t n = d_count ? (uint64_t)*d_count : n_static;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    RayPrep r;
+    float ray_tmax = 0.f;
+    uint64_t my_index = 0;
+    rt3_hit h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+    uint32_t ng_base = 0, ng_hits = 0;
+    uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
+    int sp = 0;
+    bool active = false, exhausted = false;
+    r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.idx = r.idy = r.idz = r.tmin = 0.f; r.octinv4 = 0;
+    for (;;) {
+        /* ---- refill idle lanes */
+        const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (idle && !exhausted) {
+            const int leader = __ffs(idle) - 1;
+            const uint32_t want = __popc(idle);
+            unsigned long long base = 0;
+            if ((int)lane == leader) base = atomicAdd(work_counter, (unsigned long long)want);
+            base = __shfl_sync(0xFFFFFFFFu, base, leader);
+            if (!active) {
+                const uint64_t i = base + __popc(idle & lt_mask);
+                if (i < n) {
+                    const rt3_ray ray = load_ray(rays, i);
+                    r = prepare_ray(ray);
+                    ray_tmax = ray.tmax;
+                    h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+                    ng_base = 0; ng_hits = 0x80000000u; sp = 0;
+                    my_index = i;
+                    active = true;
+                }
+            }
+            if (base + want >= n) exhausted = true;
+        }
+        if (__ballot_sync(0xFFFFFFFFu, active) == 0u) break;
+        const int keep = exhausted ? 1 : KEEP;
+        /* ---- traverse until too few lanes are busy */
+        do {
+            if (active) {
+                uint32_t tg_base, tg_hits;
+                if (ng_hits > 0x00FFFFFFu) {
+                    const int bit = bfind32(ng_hits);
+                    const uint32_t imask = ng_hits & 0xFFu;
+                    ng_hits &= ~(1u << bit);
+                    if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
+                    const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
+                    const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
+                    const WideNode* nd = nodes + (ng_base + rel);
+                    const u32x4 n0 = ld_u32x4(nd->w), n1 = ld_u32x4(nd->w + 4), n2 = ld_u32x4(nd->w + 8), n3 = ld_u32x4(nd->w + 12),
+                                n4 = ld_u32x4(nd->w + 16);
+                    const uint32_t hm = intersect_wide_node(r, h.t, n0, n1, n2, n3, n4);
+                    ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
+                    tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
+                } else {
+                    tg_base = ng_base; tg_hits = ng_hits;
+                    ng_hits = 0;
+                }
+                bool found_any = false;
+                while (tg_hits) {
+                    const int bit = bfind32(tg_hits);
+                    tg_hits &= ~(1u << bit);
+                    const Tri48* tp = tris + (tg_base + (uint32_t)bit);
+                    const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
+                    float t, u, v;
+                    const rt3m::vec3 v0 = rt3m::v3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
+                    const rt3m::vec3 e1 = rt3m::v3(__uint_as_float(b.x), __uint_as_float(b.y), __uint_as_float(b.z));
+                    const rt3m::vec3 e2 = rt3m::v3(__uint_as_float(c.x), __uint_as_float(c.y), __uint_as_float(c.z));
+                    if (rt3m::ray_triangle(rt3m::v3(r.ox, r.oy, r.oz), rt3m::v3(r.dx, r.dy, r.dz), v0, e1, e2, t, u, v) && t > r.tmin && t < ray_tmax) {
+                        if (ANY) { found_any = true; tg_hits = 0; }
+                        else if (rt3m::closer_hit(t, a.w, h.t, h.prim)) { h.t = t; h.u = u; h.v = v; h.prim = a.w; }
+                    }
+                }
+                bool done = found_any;
+                if (!done && ng_hits <= 0x00FFFFFFu) {
+                    if (sp == 0) done = true;
+                    else { sp--; ng_base = stack_base[sp]; ng_hits = stack_hits[sp]; }
+                }
+                if (done) {
+                    if (ANY) { if (found_any) atomicOr(bits + (my_index >> 5), 1u << (my_index & 31u)); }
+                    else __stcs((float4*)(hits + my_index), make_float4(h.t, h.u, h.v, __uint_as_float(h.prim)));
+                    active = false;
+                }
+            }
+        } while (__popc(__ballot_sync(0xFFFFFFFFu, active)) >= keep);
+    }
+}
+
 __global__ void __launch_bounds__(256) k_l2_sweep(const uint4* __restrict__ buf, size_t n_vec, int reps, uint4* sink) {
     uint4 acc = make_uint4(0, 0, 0, 0);
     const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -83,22 +184,54 @@ unsigned long long* work_counter(rt3_context* c, cudaStream_t st) {
     return w;
 }
 
+cudaEvent_t prof_event(rt3_context* c) {
+    if (c->prof_used == c->prof_events.size()) {
+        cudaEvent_t e;
+        RT3_CUDA(c, cudaEventCreate(&e));
+        c->prof_events.push_back(e);
+    }
+    return c->prof_events[c->prof_used++];
+}
+
+/* KEEP (lanes that must stay busy before the warp refills) and the resident-warp budget are tunables; the environment
+ * overrides exist for the profiling sweeps recorded under profiles/. */
+int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
+
+template <bool ANY>
+void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, uint32_t* bits, cudaStream_t st) {
+    static const int keep = env_int("RT3_TRACE_KEEP", 24);
+    static const int waves = env_int("RT3_TRACE_BLOCKS_PER_SM", 8);
+    static const int legacy = env_int("RT3_TRACE_STATIC", 0);
+    unsigned long long* w = work_counter(c, st);
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * waves, (n_max + TRACE_THREADS - 1) / TRACE_THREADS);
+    const WideNode* nodes = c->bvh_nodes.as<WideNode>();
+    const Tri48* tris = c->bvh_tris.as<Tri48>();
+    if (legacy) {
+        RT3_LAUNCH(c, (k_trace<ANY, false>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w, (unsigned long long*)nullptr);
+        return;
+    }
+    if (ANY) RT3_CUDA(c, cudaMemsetAsync(bits, 0, ((n_max + 31) / 32) * 4, st));
+    switch (keep) {
+        case 16: RT3_LAUNCH(c, (k_trace_dyn<ANY, 16>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
+        case 20: RT3_LAUNCH(c, (k_trace_dyn<ANY, 20>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
+        case 28: RT3_LAUNCH(c, (k_trace_dyn<ANY, 28>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
+        case 32: RT3_LAUNCH(c, (k_trace_dyn<ANY, 32>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
+        default: RT3_LAUNCH(c, (k_trace_dyn<ANY, 24>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
+    }
+}
+
 }  // namespace
 
 void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, cudaStream_t st) {
     if (n_max == 0) return;
-    unsigned long long* w = work_counter(c, st);
-    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * 12, (n_max + TRACE_THREADS - 1) / TRACE_THREADS);
-    RT3_LAUNCH(c, (k_trace<false, false>), grid, TRACE_THREADS, 0, st, c->bvh_nodes.as<WideNode>(), c->bvh_tris.as<Tri48>(), rays, d_count, n_max, hits,
-               (uint32_t*)nullptr, w, (unsigned long long*)nullptr);
+    if (c->prof_on) RT3_CUDA(c, cudaEventRecord(prof_event(c), st));
+    launch_dyn<false>(c, rays, d_count, n_max, hits, nullptr, st);
+    if (c->prof_on) RT3_CUDA(c, cudaEventRecord(prof_event(c), st));
 }
 
 void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, uint64_t n, uint32_t* bits, cudaStream_t st) {
     if (n == 0) return;
-    unsigned long long* w = work_counter(c, st);
-    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * 12, (n + TRACE_THREADS - 1) / TRACE_THREADS);
-    RT3_LAUNCH(c, (k_trace<true, false>), grid, TRACE_THREADS, 0, st, c->bvh_nodes.as<WideNode>(), c->bvh_tris.as<Tri48>(), rays, (const uint32_t*)nullptr, n,
-               (rt3_hit*)nullptr, bits, w, (unsigned long long*)nullptr);
+    launch_dyn<true>(c, rays, nullptr, n, nullptr, bits, st);
 }
 
 void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out) {

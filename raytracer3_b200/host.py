@@ -71,6 +71,14 @@ class RenderContext:
         self.check(self.L.rt3_counters_read(self.h, C.byref(c), 1 if reset else 0))
         return c
 
+    def profile_enable(self, on=True):
+        self.check(self.L.rt3_profile_enable(self.h, 1 if on else 0))
+
+    def profile_read(self):
+        ms, n = C.c_double(), C.c_uint64()
+        self.check(self.L.rt3_profile_read(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
     def measure_l2_bandwidth(self, nbytes=32 << 20, iters=10):
         out = C.c_double()
         self.check(self.L.rt3_measure_l2_bandwidth(self.h, nbytes, iters, C.byref(out)))
@@ -369,3 +377,50 @@ class Renderer:
         p = np.ascontiguousarray(gconst)
         self.ctx.check(self.ctx.L.rt3_render_frame_host(self.ctx.h, ptr(p), None if prev_light_host is None else C.c_void_p(prev_light_host),
                                                         C.c_void_p(light_host), None, None))
+
+
+class TiledRenderer:
+    """Rank-local renderer for screen-tile sharding: this rank's tiles of a W x H frame are rendered
+    into tile-major slabs; `gather` all-gathers the Light slabs over NCCL (torch.distributed) and un-tiles them."""
+
+    def __init__(self, ctx, world, width, height, rank, world_size, tile=64):
+        import ctypes as C
+        torch = _torch()
+        from .tiles import all_tiles, rank_tiles
+        self.ctx, self.world = ctx, world
+        self.W, self.H, self.rank, self.world_size, self.tile = width, height, rank, world_size, tile
+        self.rects = np.ascontiguousarray(rank_tiles(width, height, rank, world_size, tile))
+        self.all_rects = np.ascontiguousarray(all_tiles(width, height, world_size, tile))
+        assert self.rects["w"].max() == tile and self.rects["h"].max() == tile, "every rank needs at least one full tile"
+        n = len(self.rects)
+        dev = f"cuda:{ctx.device}"
+        self.gbuffer = torch.zeros((n, tile, tile, 4), dtype=torch.int32, device=dev)
+        self.depth = torch.zeros((n, tile, tile), dtype=torch.float32, device=dev)
+        self.light = [torch.zeros((n, tile, tile, 4), dtype=torch.float32, device=dev) for _ in range(2)]
+        self.gathered = torch.zeros((world_size * n, tile, tile, 4), dtype=torch.float32, device=dev) if world_size > 1 else None
+        self.frame_buf = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
+        self.cur = 0
+        self.pixels = int((self.rects["w"].astype(np.int64) * self.rects["h"]).sum())
+
+    def frame(self, gconst):
+        L, h, st = self.ctx.L, self.ctx.h, self.ctx.stream()
+        p = np.ascontiguousarray(gconst)
+        light, prev = self.light[self.cur], self.light[1 - self.cur]
+        self.ctx.check(L.rt3_pass_gbuffer_tiles(h, ptr(p), ptr(self.rects), len(self.rects), self.gbuffer.data_ptr(), self.depth.data_ptr(), st))
+        self.ctx.check(L.rt3_pass_reference_tiles(h, ptr(p), ptr(self.rects), len(self.rects), self.gbuffer.data_ptr(), self.depth.data_ptr(),
+                                                   prev.data_ptr(), light.data_ptr(), st))
+        self.cur = 1 - self.cur
+        return light
+
+    def gather(self, light):
+        """One all_gather of the rank-local slabs + un-tile into the full frame (every rank gets the image)."""
+        torch = _torch()
+        if self.world_size > 1:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(self.gathered, light)
+            slab, rects = self.gathered, self.all_rects
+        else:
+            slab, rects = light, self.rects
+        self.ctx.check(self.ctx.L.rt3_untile_rgba32f(self.ctx.h, ptr(rects), len(rects), self.tile, self.tile, slab.data_ptr(),
+                                                     self.frame_buf.data_ptr(), self.W, self.H, self.ctx.stream()))
+        return self.frame_buf

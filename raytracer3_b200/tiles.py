@@ -1,0 +1,61 @@
+"""Screen-tile sharding across GPUs (no reference counterpart: the reference is single-GPU).
+
+Pixels are independent (the RNG is keyed by pixel coordinate and frame, shaders/include/random.slang:42-46), so a frame
+shards by screen tile with the scene and BVH replicated and NO data-path collective while samples accumulate; the only
+exchange is one gather of the finished rank-local slabs per output image.
+
+  tile order   row-major over ceil(W/T) x ceil(H/T) tiles of T x T pixels (edge tiles are clipped)
+  ownership    owner(tx, ty) = (tx + ty * rotation) mod world_size: interleaved, rotated per row so that vertical
+               structures do not land on one rank
+  slab         each rank stores its tiles contiguously, tile k at [k*T*T, (k+1)*T*T) row-major inside the tile
+               (the layout rt3_pass_*_tiles write and rt3_untile_rgba32f reads); lists are padded with empty rects to
+               the same length on every rank so that the gather is a plain all_gather of equal slabs
+"""
+import numpy as np
+
+RECT = np.dtype([("x0", "<u4"), ("y0", "<u4"), ("w", "<u4"), ("h", "<u4")])
+
+
+def tile_grid(width, height, tile=64):
+    return -(-width // tile), -(-height // tile)
+
+
+def owner(tx, ty, tiles_x, world_size):
+    rot = max(1, world_size // 2 + 1) if world_size > 2 else 1
+    return (tx + ty * rot) % world_size
+
+
+def rank_tiles(width, height, rank, world_size, tile=64):
+    """RECT array of the tiles `rank` owns, padded with empty rects to the common per-rank length."""
+    nx, ny = tile_grid(width, height, tile)
+    per_rank = [[] for _ in range(world_size)]
+    for ty in range(ny):
+        for tx in range(nx):
+            x0, y0 = tx * tile, ty * tile
+            per_rank[owner(tx, ty, nx, world_size)].append((x0, y0, min(tile, width - x0), min(tile, height - y0)))
+    n = max(len(p) for p in per_rank)
+    mine = per_rank[rank] + [(0, 0, 0, 0)] * (n - len(per_rank[rank]))
+    return np.array(mine, RECT)
+
+
+def all_tiles(width, height, world_size, tile=64):
+    """Concatenation of every rank's padded list, in rank order == the layout of the all_gather'ed slab."""
+    return np.concatenate([rank_tiles(width, height, r, world_size, tile) for r in range(world_size)])
+
+
+def untile_host(slab, rects, tile, frame):
+    """numpy mirror of rt3_untile_rgba32f (used by the CPU tests of the sharding logic)."""
+    slab = slab.reshape(len(rects), tile, tile, -1)
+    for k, r in enumerate(rects):
+        if r["w"] and r["h"]:
+            frame[r["y0"]:r["y0"] + r["h"], r["x0"]:r["x0"] + r["w"]] = slab[k, :r["h"], :r["w"]]
+    return frame
+
+
+def tile_host(frame, rects, tile):
+    """Inverse of untile_host: cut a full frame into a slab."""
+    slab = np.zeros((len(rects), tile, tile, frame.shape[-1]), frame.dtype)
+    for k, r in enumerate(rects):
+        if r["w"] and r["h"]:
+            slab[k, :r["h"], :r["w"]] = frame[r["y0"]:r["y0"] + r["h"], r["x0"]:r["x0"] + r["w"]]
+    return slab
