@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
  * queues); here a lane whose ray terminates writes its result and, once fewer than KEEP lanes of the warp are still
  * busy, the idle lanes pull new rays from the global queue with one warp-aggregated atomic.
  */
-template <bool ANY, int KEEP>
+template <bool ANY, int KEEP, int TRIS>
 __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
                                                              const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
                                                              rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter) {
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
     float ray_tmax = 0.f;
     uint64_t my_index = 0;
     rt3_hit h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
-    uint32_t ng_base = 0, ng_hits = 0;
+    uint32_t ng_base = 0, ng_hits = 0, tg_base = 0, tg_hits = 0;
     uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
     int sp = 0;
     bool active = false, exhausted = false;
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                     r = prepare_ray(ray);
                     ray_tmax = ray.tmax;
                     h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
-                    ng_base = 0; ng_hits = 0x80000000u; sp = 0;
+                    ng_base = 0; ng_hits = 0x80000000u; tg_hits = 0; sp = 0;
                     my_index = i;
                     active = true;
                 }
@@ -116,29 +116,29 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
         }
         if (__ballot_sync(0xFFFFFFFFu, active) == 0u) break;
         const int keep = exhausted ? 1 : KEEP;
-        /* ---- traverse until too few lanes are busy */
+        /* ---- traverse until too few lanes are busy.  One iteration = a node step for the lanes that have no triangle
+         * pending, then ONE triangle test for every lane that has one pending: the warp re-converges between the two
+         * phases, so triangle tests of different lanes share issue slots instead of running 3-of-32 wide in a per-lane
+         * loop (ncu source page of the per-lane-loop version: profiles/r1b_*). */
         do {
-            if (active) {
-                uint32_t tg_base, tg_hits;
-                if (ng_hits > 0x00FFFFFFu) {
-                    const int bit = bfind32(ng_hits);
-                    const uint32_t imask = ng_hits & 0xFFu;
-                    ng_hits &= ~(1u << bit);
-                    if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
-                    const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
-                    const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
-                    const WideNode* nd = nodes + (ng_base + rel);
-                    const u32x4 n0 = ld_u32x4(nd->w), n1 = ld_u32x4(nd->w + 4), n2 = ld_u32x4(nd->w + 8), n3 = ld_u32x4(nd->w + 12),
-                                n4 = ld_u32x4(nd->w + 16);
-                    const uint32_t hm = intersect_wide_node(r, h.t, n0, n1, n2, n3, n4);
-                    ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
-                    tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
-                } else {
-                    tg_base = ng_base; tg_hits = ng_hits;
-                    ng_hits = 0;
-                }
-                bool found_any = false;
-                while (tg_hits) {
+            if (active && tg_hits == 0u && ng_hits > 0x00FFFFFFu) {
+                const int bit = bfind32(ng_hits);
+                const uint32_t imask = ng_hits & 0xFFu;
+                ng_hits &= ~(1u << bit);
+                if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
+                const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
+                const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
+                const WideNode* nd = nodes + (ng_base + rel);
+                const u32x4 n0 = ld_u32x4(nd->w), n1 = ld_u32x4(nd->w + 4), n2 = ld_u32x4(nd->w + 8), n3 = ld_u32x4(nd->w + 12),
+                            n4 = ld_u32x4(nd->w + 16);
+                const uint32_t hm = intersect_wide_node(r, h.t, n0, n1, n2, n3, n4);
+                ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
+                tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
+            }
+            bool found_any = false;
+#pragma unroll
+            for (int rep = 0; rep < TRIS; ++rep) {
+                if (active && tg_hits) {
                     const int bit = bfind32(tg_hits);
                     tg_hits &= ~(1u << bit);
                     const Tri48* tp = tris + (tg_base + (uint32_t)bit);
@@ -152,16 +152,13 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                         else if (rt3m::closer_hit(t, a.w, h.t, h.prim)) { h.t = t; h.u = u; h.v = v; h.prim = a.w; }
                     }
                 }
-                bool done = found_any;
-                if (!done && ng_hits <= 0x00FFFFFFu) {
-                    if (sp == 0) done = true;
-                    else { sp--; ng_base = stack_base[sp]; ng_hits = stack_hits[sp]; }
-                }
-                if (done) {
+            }
+            if (active && (found_any || (tg_hits == 0u && ng_hits <= 0x00FFFFFFu))) {
+                if (found_any || sp == 0) {
                     if (ANY) { if (found_any) atomicOr(bits + (my_index >> 5), 1u << (my_index & 31u)); }
                     else __stcs((float4*)(hits + my_index), make_float4(h.t, h.u, h.v, __uint_as_float(h.prim)));
                     active = false;
-                }
+                } else { sp--; ng_base = stack_base[sp]; ng_hits = stack_hits[sp]; }
             }
         } while (__popc(__ballot_sync(0xFFFFFFFFu, active)) >= keep);
     }
@@ -211,13 +208,15 @@ void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, ui
         return;
     }
     if (ANY) RT3_CUDA(c, cudaMemsetAsync(bits, 0, ((n_max + 31) / 32) * 4, st));
-    switch (keep) {
-        case 16: RT3_LAUNCH(c, (k_trace_dyn<ANY, 16>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
-        case 20: RT3_LAUNCH(c, (k_trace_dyn<ANY, 20>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
-        case 28: RT3_LAUNCH(c, (k_trace_dyn<ANY, 28>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
-        case 32: RT3_LAUNCH(c, (k_trace_dyn<ANY, 32>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
-        default: RT3_LAUNCH(c, (k_trace_dyn<ANY, 24>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w); break;
+    static const int tris_per_iter = env_int("RT3_TRACE_TRIS", 1);
+#define RT3_DYN(K, T) RT3_LAUNCH(c, (k_trace_dyn<ANY, K, T>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w)
+    if (tris_per_iter == 2) {
+        if (keep == 16) RT3_DYN(16, 2); else if (keep == 28) RT3_DYN(28, 2); else RT3_DYN(24, 2);
+    } else {
+        if (keep == 16) RT3_DYN(16, 1); else if (keep == 20) RT3_DYN(20, 1); else if (keep == 28) RT3_DYN(28, 1); else if (keep == 32) RT3_DYN(32, 1);
+        else RT3_DYN(24, 1);
     }
+#undef RT3_DYN
 }
 
 }  // namespace
