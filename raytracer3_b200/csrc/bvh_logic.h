@@ -319,14 +319,17 @@ struct RayPrep {
     float idx, idy, idz;               /* safe reciprocal direction                */
     uint32_t octinv4;                  /* (7 - octant) replicated in 4 bytes       */
     float tmin;
+    uint32_t magic;                    /* 0x47000000 held in a REGISTER: ptxas then encodes the PRMT selector as the immediate
+                                          (with both constant it materialises each selector with an extra move per plane) */
 };
 RT3_HD float safe_rcp_dir(float d) {
     const float tiny = 1e-20f;
     if (rt3m::abs_(d) < tiny) d = (rt3m::as_uint(d) >> 31) ? -tiny : tiny;
     return 1.0f / d;
 }
-RT3_HD RayPrep prepare_ray(const rt3_ray& r) {
+RT3_HD RayPrep prepare_ray(const rt3_ray& r, uint32_t magic = 0x47000000u) {
     RayPrep p;
+    p.magic = magic;
     p.ox = r.o[0]; p.oy = r.o[1]; p.oz = r.o[2];
     p.dx = r.d[0]; p.dy = r.d[1]; p.dz = r.d[2];
     p.idx = safe_rcp_dir(p.dx); p.idy = safe_rcp_dir(p.dy); p.idz = safe_rcp_dir(p.dz);
@@ -341,13 +344,13 @@ RT3_HD uint32_t byte_of(uint32_t w, int j) { return (w >> (8 * j)) & 0xFFu; }
 /* Byte j of w as the float 32768 + q, built with one byte permute instead of an integer-to-float conversion
  * (I2F runs at a quarter of the FMA rate): bits = 0x47000000 | q << 8, i.e. exponent 2^15 with q in mantissa bits 8..15. */
 template <int J>
-RT3_HD float byte_as_biased_float(uint32_t w) {
+RT3_HD float byte_as_biased_float(uint32_t w, uint32_t magic) {
 #ifdef __CUDA_ARCH__
     uint32_t r;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(0x47000000u), "n"(0x7604 | (J << 4)));
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(magic), "n"(0x7604 | (J << 4)));
     return __uint_as_float(r);
 #else
-    return rt3m::as_float(0x47000000u | (((w >> (8 * J)) & 0xFFu) << 8));
+    return rt3m::as_float(magic | (((w >> (8 * J)) & 0xFFu) << 8));
 #endif
 }
 /* min / max for the slab test only: no NaN can occur there (directions are clamped away from 0), so the
@@ -369,10 +372,10 @@ RT3_HD float bmax(float a, float b) {
 
 template <int J>
 RT3_HD uint32_t slab_child(uint32_t nx, uint32_t fx, uint32_t ny, uint32_t fy, uint32_t nz, uint32_t fz, float sx, float sy, float sz, float bx,
-                           float by, float bz, float tmin, float tmax, uint32_t child_bits4, uint32_t bit_index4) {
-    const float t0x = rt3m::fma_(byte_as_biased_float<J>(nx), sx, bx), t1x = rt3m::fma_(byte_as_biased_float<J>(fx), sx, bx);
-    const float t0y = rt3m::fma_(byte_as_biased_float<J>(ny), sy, by), t1y = rt3m::fma_(byte_as_biased_float<J>(fy), sy, by);
-    const float t0z = rt3m::fma_(byte_as_biased_float<J>(nz), sz, bz), t1z = rt3m::fma_(byte_as_biased_float<J>(fz), sz, bz);
+                           float by, float bz, float tmin, float tmax, uint32_t child_bits4, uint32_t bit_index4, uint32_t mg) {
+    const float t0x = rt3m::fma_(byte_as_biased_float<J>(nx, mg), sx, bx), t1x = rt3m::fma_(byte_as_biased_float<J>(fx, mg), sx, bx);
+    const float t0y = rt3m::fma_(byte_as_biased_float<J>(ny, mg), sy, by), t1y = rt3m::fma_(byte_as_biased_float<J>(fy, mg), sy, by);
+    const float t0z = rt3m::fma_(byte_as_biased_float<J>(nz, mg), sz, bz), t1z = rt3m::fma_(byte_as_biased_float<J>(fz, mg), sz, bz);
     const float tn = bmax(bmax(t0x, t0y), bmax(t0z, tmin));
     const float tf = bmin(bmin(t1x, t1y), bmin(t1z, tmax));
     return (tn <= tf) ? (((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu)) : 0u;
@@ -405,10 +408,10 @@ RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n
         const uint32_t nx = r.idx < 0.0f ? qhx : qlx, fx = r.idx < 0.0f ? qlx : qhx;
         const uint32_t ny = r.idy < 0.0f ? qhy : qly, fy = r.idy < 0.0f ? qly : qhy;
         const uint32_t nz = r.idz < 0.0f ? qhz : qlz, fz = r.idz < 0.0f ? qlz : qhz;
-        hitmask |= slab_child<0>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
-        hitmask |= slab_child<1>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
-        hitmask |= slab_child<2>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
-        hitmask |= slab_child<3>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4);
+        hitmask |= slab_child<0>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4, r.magic);
+        hitmask |= slab_child<1>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4, r.magic);
+        hitmask |= slab_child<2>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4, r.magic);
+        hitmask |= slab_child<3>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, child_bits4, bit_index4, r.magic);
     }
     return hitmask;
 }
@@ -418,21 +421,27 @@ struct TraverseStats { uint32_t nodes, tris; };
 /* Closest hit (ANY = false) or first hit found (ANY = true).  `hit.t` must come in as the ray's tmax and
  * hit.prim as RT3_MISS.  Returns true if something was hit. */
 template <bool ANY>
-RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ray& ray, rt3_hit& hit, TraverseStats* stats) {
+RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ray& ray, rt3_hit& hit, TraverseStats* stats, bool active = true) {
     RayPrep r = prepare_ray(ray);
     const vec3 o = rt3m::v3(r.ox, r.oy, r.oz), d = rt3m::v3(r.dx, r.dy, r.dz);
     uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
     int sp = 0;
     uint32_t ng_base = 0, ng_hits = 0x80000000u;   /* node group: root */
     uint32_t tg_base = 0, tg_hits = 0;             /* triangle group   */
-    for (;;) {
-        if (ng_hits > 0x00FFFFFFu) {
+    /* Two-phase iteration (same shape as k_trace_dyn): a node step for rays with no triangle pending, then ONE triangle
+     * test per ray that has one pending.  On the device the loop is warp-synchronous (every lane of the warp must call this
+     * function; lanes without a ray pass active = false) so that both phases run converged. */
+#ifdef __CUDA_ARCH__
+#define RT3_WARP_ANY(x) __any_sync(0xFFFFFFFFu, (x))
+#else
+#define RT3_WARP_ANY(x) (x)
+#endif
+    while (RT3_WARP_ANY(active)) {
+        if (active && tg_hits == 0u && ng_hits > 0x00FFFFFFu) {
             const int bit = bfind32(ng_hits);
             const uint32_t imask = ng_hits & 0xFFu;
             ng_hits &= ~(1u << bit);
-            if (ng_hits > 0x00FFFFFFu) {
-                if (sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
-            }
+            if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
             const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
             const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
             const WideNode* n = nodes + (ng_base + rel);
@@ -441,11 +450,9 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
             const uint32_t hm = intersect_wide_node(r, hit.t, n0, n1, n2, n3, n4);
             ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
             tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
-        } else {
-            tg_base = ng_base; tg_hits = ng_hits;
-            ng_hits = 0;
         }
-        while (tg_hits) {
+        bool found_any = false;
+        if (active && tg_hits) {
             const int bit = bfind32(tg_hits);
             tg_hits &= ~(1u << bit);
             const Tri48* tp = tris + (tg_base + (uint32_t)bit);
@@ -455,20 +462,17 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
             const vec3 v0 = rt3m::v3(rt3m::as_float(a.x), rt3m::as_float(a.y), rt3m::as_float(a.z));
             const vec3 e1 = rt3m::v3(rt3m::as_float(b.x), rt3m::as_float(b.y), rt3m::as_float(b.z));
             const vec3 e2 = rt3m::v3(rt3m::as_float(c.x), rt3m::as_float(c.y), rt3m::as_float(c.z));
-            if (rt3m::ray_triangle(o, d, v0, e1, e2, t, u, v) && t > ray.tmin) {
-                if (ANY) {
-                    if (t < ray.tmax) { hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w; return true; }
-                } else if (t < ray.tmax && rt3m::closer_hit(t, a.w, hit.t, hit.prim)) {
-                    hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w;
-                }
+            if (rt3m::ray_triangle(o, d, v0, e1, e2, t, u, v) && t > ray.tmin && t < ray.tmax) {
+                if (ANY) { hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w; found_any = true; }
+                else if (rt3m::closer_hit(t, a.w, hit.t, hit.prim)) { hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w; }
             }
         }
-        if (ng_hits <= 0x00FFFFFFu) {
-            if (sp == 0) break;
-            sp--;
-            ng_base = stack_base[sp]; ng_hits = stack_hits[sp];
+        if (active && (found_any || (tg_hits == 0u && ng_hits <= 0x00FFFFFFu))) {
+            if (found_any || sp == 0) active = false;
+            else { sp--; ng_base = stack_base[sp]; ng_hits = stack_hits[sp]; }
         }
     }
+#undef RT3_WARP_ANY
     return hit.prim != RT3_MISS;
 }
 

@@ -39,10 +39,12 @@ __global__ void __launch_bounds__(128) k_gbuffer(SceneView s, const WideNode* __
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t x, y; size_t px;
     const bool valid = idx < m.work && pixel_of(m, idx, x, y, px);
+    rt3_ray ray;
+    if (valid) ray = setup_primary_ray(x, y, p);                            /* gbuffer.slang:10 */
+    else { ray.o[0] = ray.o[1] = ray.o[2] = 0.f; ray.d[0] = ray.d[1] = 0.f; ray.d[2] = 1.f; ray.tmin = 0.f; ray.tmax = 0.f; }
+    rt3_hit h; h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+    traverse_wide<false>(nodes, tris, ray, h, nullptr, valid);              /* gbuffer.slang:12 (warp-synchronous: all lanes call) */
     if (valid) {
-        rt3_ray ray = setup_primary_ray(x, y, p);                           /* gbuffer.slang:10 */
-        rt3_hit h; h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
-        traverse_wide<false>(nodes, tris, ray, h, nullptr);                 /* gbuffer.slang:12 */
         if (h.prim == RT3_MISS) {                                           /* gbuffer.slang:14-16 */
             depth[px] = RT3_BACKGROUND_DEPTH;
             if (ids) { ids[2 * px] = RT3_MISS; ids[2 * px + 1] = RT3_MISS; }

@@ -46,13 +46,13 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
         const bool valid = i < n;
         rt3_hit h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
         bool any = false;
-        if (valid) {
-            rt3_ray r = load_ray(rays, i);
-            h.t = r.tmax;
-            TraverseStats ts = {0, 0};
-            any = traverse_wide<ANY>(nodes, tris, r, h, STATS ? &ts : nullptr);
-            if (STATS) { st_nodes += ts.nodes; st_tris += ts.tris; }
-        }
+        rt3_ray r;
+        if (valid) r = load_ray(rays, i);
+        else { r.o[0] = r.o[1] = r.o[2] = 0.f; r.d[0] = r.d[1] = 0.f; r.d[2] = 1.f; r.tmin = 0.f; r.tmax = 0.f; }
+        h.t = r.tmax;
+        TraverseStats ts = {0, 0};
+        any = traverse_wide<ANY>(nodes, tris, r, h, STATS ? &ts : nullptr, valid);   /* warp-synchronous: every lane calls */
+        if (STATS) { st_nodes += ts.nodes; st_tris += ts.tris; }
         if (ANY) {
             uint32_t word = __ballot_sync(0xFFFFFFFFu, any);
             if (lane == 0) bits[base >> 5] = word;
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
 template <bool ANY, int KEEP, int TRIS>
 __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
                                                              const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
-                                                             rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter) {
+                                                             rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter, uint32_t magic) {
     const uint64_t n = d_count ? (uint64_t)*d_count : n_static;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
     uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
     int sp = 0;
     bool active = false, exhausted = false;
-    r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.idx = r.idy = r.idz = r.tmin = 0.f; r.octinv4 = 0;
+    r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.idx = r.idy = r.idz = r.tmin = 0.f; r.octinv4 = 0; r.magic = magic;
     for (;;) {
         /* ---- refill idle lanes */
         const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                 const uint64_t i = base + __popc(idle & lt_mask);
                 if (i < n) {
                     const rt3_ray ray = load_ray(rays, i);
-                    r = prepare_ray(ray);
+                    r = prepare_ray(ray, magic);
                     ray_tmax = ray.tmax;
                     h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
                     ng_base = 0; ng_hits = 0x80000000u; tg_hits = 0; sp = 0;
@@ -196,7 +196,7 @@ int env_int(const char* name, int dflt) { const char* v = getenv(name); return v
 
 template <bool ANY>
 void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, uint32_t* bits, cudaStream_t st) {
-    static const int keep = env_int("RT3_TRACE_KEEP", 24);
+    static const int keep = env_int("RT3_TRACE_KEEP", 28);
     static const int waves = env_int("RT3_TRACE_BLOCKS_PER_SM", 8);
     static const int legacy = env_int("RT3_TRACE_STATIC", 0);
     unsigned long long* w = work_counter(c, st);
@@ -209,7 +209,7 @@ void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, ui
     }
     if (ANY) RT3_CUDA(c, cudaMemsetAsync(bits, 0, ((n_max + 31) / 32) * 4, st));
     static const int tris_per_iter = env_int("RT3_TRACE_TRIS", 1);
-#define RT3_DYN(K, T) RT3_LAUNCH(c, (k_trace_dyn<ANY, K, T>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w)
+#define RT3_DYN(K, T) RT3_LAUNCH(c, (k_trace_dyn<ANY, K, T>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w, 0x47000000u)
     if (tris_per_iter == 2) {
         if (keep == 16) RT3_DYN(16, 2); else if (keep == 28) RT3_DYN(28, 2); else RT3_DYN(24, 2);
     } else {

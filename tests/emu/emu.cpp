@@ -167,3 +167,91 @@ void emu_trace_any(const EmuBvh* b, const rt3_ray* rays, uint64_t n, uint32_t* b
     }
 }
 }
+
+/* EXPERIMENT: top-down binned-SAH BVH2 (CPU) fed to the same collapse, to measure how much traversal work the LBVH topology costs. */
+namespace {
+struct SahBuilder {
+    std::vector<Bvh2Node>& n2; std::vector<uint32_t>& counts; const std::vector<Tri48>& tris; float pad; uint32_t n;
+    std::vector<uint32_t> order; std::vector<float> lo, hi, cen;
+    uint32_t next_internal = 0;
+    std::vector<uint32_t> leaf_of;   /* position in order -> leaf index (sorted position) */
+    SahBuilder(std::vector<Bvh2Node>& a, std::vector<uint32_t>& c, const std::vector<Tri48>& t, float p) : n2(a), counts(c), tris(t), pad(p), n((uint32_t)t.size()) {
+        order.resize(n); lo.resize(3 * n); hi.resize(3 * n); cen.resize(3 * n);
+        for (uint32_t i = 0; i < n; ++i) { order[i] = i; tri_bounds(tris[i], pad, &lo[3 * i], &hi[3 * i]); for (int a2 = 0; a2 < 3; ++a2) cen[3 * i + a2] = 0.5f * (lo[3 * i + a2] + hi[3 * i + a2]); }
+    }
+    /* returns ref; leaves reference position in `order` (the caller reorders triangles accordingly) */
+    uint32_t build(uint32_t first, uint32_t count) {
+        if (count == 1) {
+            Bvh2Node& leaf = n2[n - 1 + first];
+            for (int a = 0; a < 3; ++a) { leaf.lo[a] = lo[3 * order[first] + a]; leaf.hi[a] = hi[3 * order[first] + a]; }
+            leaf.left = leaf.right = 0;
+            return LEAF_FLAG | first;
+        }
+        float blo[3] = {3e38f, 3e38f, 3e38f}, bhi[3] = {-3e38f, -3e38f, -3e38f}, clo[3] = {3e38f, 3e38f, 3e38f}, chi[3] = {-3e38f, -3e38f, -3e38f};
+        for (uint32_t i = first; i < first + count; ++i) for (int a = 0; a < 3; ++a) {
+            uint32_t id = order[i];
+            blo[a] = std::min(blo[a], lo[3 * id + a]); bhi[a] = std::max(bhi[a], hi[3 * id + a]);
+            clo[a] = std::min(clo[a], cen[3 * id + a]); chi[a] = std::max(chi[a], cen[3 * id + a]);
+        }
+        const int NB = 32;
+        float best = 3e38f; int baxis = -1, bsplit = -1;
+        for (int a = 0; a < 3; ++a) {
+            if (!(chi[a] > clo[a])) continue;
+            float l[NB][3], h[NB][3]; uint32_t c[NB];
+            for (int k = 0; k < NB; ++k) { c[k] = 0; for (int x = 0; x < 3; ++x) { l[k][x] = 3e38f; h[k][x] = -3e38f; } }
+            float scale = NB / (chi[a] - clo[a]);
+            for (uint32_t i = first; i < first + count; ++i) {
+                uint32_t id = order[i]; int k = std::min(NB - 1, (int)((cen[3 * id + a] - clo[a]) * scale));
+                c[k]++; for (int x = 0; x < 3; ++x) { l[k][x] = std::min(l[k][x], lo[3 * id + x]); h[k][x] = std::max(h[k][x], hi[3 * id + x]); }
+            }
+            float la[NB], ra[NB]; uint32_t lc[NB], rc[NB];
+            float al[3] = {3e38f, 3e38f, 3e38f}, ah[3] = {-3e38f, -3e38f, -3e38f}; uint32_t cc = 0;
+            for (int k = 0; k < NB - 1; ++k) { for (int x = 0; x < 3; ++x) { al[x] = std::min(al[x], l[k][x]); ah[x] = std::max(ah[x], h[k][x]); } cc += c[k]; lc[k] = cc; la[k] = cc ? box_area(al, ah) : 0; }
+            for (int x = 0; x < 3; ++x) { al[x] = 3e38f; ah[x] = -3e38f; } cc = 0;
+            for (int k = NB - 1; k > 0; --k) { for (int x = 0; x < 3; ++x) { al[x] = std::min(al[x], l[k][x]); ah[x] = std::max(ah[x], h[k][x]); } cc += c[k]; rc[k - 1] = cc; ra[k - 1] = cc ? box_area(al, ah) : 0; }
+            for (int k = 0; k < NB - 1; ++k) if (lc[k] && rc[k]) { float cost = la[k] * lc[k] + ra[k] * rc[k]; if (cost < best) { best = cost; baxis = a; bsplit = k; } }
+        }
+        uint32_t mid;
+        if (baxis >= 0) {
+            float scale = NB / (chi[baxis] - clo[baxis]);
+            auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](uint32_t id) { return std::min(NB - 1, (int)((cen[3 * id + baxis] - clo[baxis]) * scale)) <= bsplit; });
+            mid = (uint32_t)(it - order.begin());
+        } else mid = first + count / 2;
+        if (mid == first || mid == first + count) mid = first + count / 2;
+        uint32_t me = next_internal++;
+        uint32_t l = build(first, mid - first), r = build(mid, first + count - mid);
+        Bvh2Node& nd = n2[me];
+        nd.left = l; nd.right = r;
+        for (int a = 0; a < 3; ++a) { nd.lo[a] = blo[a]; nd.hi[a] = bhi[a]; }
+        counts[me] = count;
+        return me;
+    }
+};
+}
+extern "C" EmuBvh* emu_build_sah(const float* tris9, uint32_t n) {
+    EmuBvh* b = new EmuBvh();
+    b->tris_in.resize(n);
+    for (int a = 0; a < 3; ++a) { b->lo[a] = 3.4e38f; b->hi[a] = -3.4e38f; }
+    for (uint32_t i = 0; i < n; ++i) {
+        const float* p = tris9 + 9 * (size_t)i; Tri48& t = b->tris_in[i];
+        for (int a = 0; a < 3; ++a) { t.v0[a] = p[a]; t.e1[a] = p[3 + a] - p[a]; t.e2[a] = p[6 + a] - p[a];
+            for (int k = 0; k < 3; ++k) { b->lo[a] = std::min(b->lo[a], p[3 * k + a]); b->hi[a] = std::max(b->hi[a], p[3 * k + a]); } }
+        t.prim = i; t.pad0 = t.pad1 = 0;
+    }
+    float ext = std::max(b->hi[0] - b->lo[0], std::max(b->hi[1] - b->lo[1], b->hi[2] - b->lo[2]));
+    b->pad = ext * (1.0f / 65536.0f);
+    std::vector<Bvh2Node> n2(2 * (size_t)n - 1); std::vector<uint32_t> counts(n, 0);
+    SahBuilder sb(n2, counts, b->tris_in, b->pad);
+    uint32_t root = sb.build(0, n);
+    b->tris_sorted.resize(n);
+    for (uint32_t i = 0; i < n; ++i) b->tris_sorted[i] = b->tris_in[sb.order[i]];
+    b->nodes.resize(n); b->tris_out.resize(n);
+    std::vector<uint32_t> q(2 * (size_t)n + 2), qn(2 * (size_t)n + 2);
+    uint32_t node_counter = 1, tri_counter = 0, q_count = 1, next_count = 0;
+    q[0] = root; q[1] = 0;
+    CollapseCtx c; c.nodes = n2.data(); c.counts = counts.data(); c.tris_sorted = b->tris_sorted.data(); c.n_leaves = n;
+    c.out_nodes = b->nodes.data(); c.out_tris = b->tris_out.data(); c.node_counter = &node_counter; c.tri_counter = &tri_counter; c.next_count = &next_count; c.sah_accum = b->sah;
+    while (q_count) { next_count = 0; c.next_items = qn.data(); for (uint32_t i = 0; i < q_count; ++i) collapse_one(c, q[2 * i], q[2 * i + 1]); q.swap(qn); q_count = next_count; b->levels++; }
+    b->n_nodes = node_counter; b->n_tris = tri_counter;
+    return b;
+}

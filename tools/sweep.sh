@@ -1,5 +1,5 @@
 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-for cfg in "24 1" "28 1" "24 2" "28 2" "16 1"; do set -- $cfg; echo "KEEP=$1 TRIS=$2"; RT3_TRACE_KEEP=$1 RT3_TRACE_TRIS=$2 python bench.py --steps 30 --warmup 5 2>&1 | python -c "
+for cfg in "28 1" "24 1"; do set -- $cfg; echo "KEEP=$1 TRIS=$2"; RT3_TRACE_KEEP=$1 RT3_TRACE_TRIS=$2 python bench.py --steps 30 --warmup 5 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
