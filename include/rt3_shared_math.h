@@ -498,8 +498,12 @@ struct SceneView {
     const uint32_t* tex_dim;        /* 2 per slot */
     uint32_t n_textures;
     const float* srgb_lut;          /* 256 floats: sRGB byte -> linear */
-    /* environment */
+    /* environment (+ importance tables built by build_env_tables: RT3_FLAG_NEE) */
     const float* env; uint32_t env_w, env_h;
+    const float* env_func;          /* w*h: luminance * sin(theta_row)                  */
+    const float* env_marginal;      /* h+1: CDF over rows                                */
+    const float* env_conditional;   /* h*(w+1): CDF over columns inside each row         */
+    float env_total;                /* sum of env_func                                   */
     /* blue noise */
     const uint8_t* bn; uint32_t bn_w, bn_h;
 };
@@ -606,6 +610,81 @@ RT3_HD GbufferData hit_info(const SceneView& s, uint32_t prim, float bu, float b
     o.normal = n;
     o.albedo = color;
     return o;
+}
+
+/* ---------------------------------------------------------------- environment importance sampling
+ * No reference counterpart (the reference has no importance sampling, no CDF, no shadow rays); this
+ * is the north star's "skybox2.exr environment importance lookup" + any-hit shadow rays, enabled by RT3_FLAG_NEE.
+ * Piecewise-constant density over texels proportional to luminance * sin(theta), sampled by two binary searches. */
+RT3_HD vec3 equirect_uv_to_direction(float u, float v) {   /* inverse of direction_to_equirect_uv (math.slang:6-12) */
+    float s2, c2, se, ce;
+    sincos_2pi(frac_(u), s2, c2);                          /* phi = 2 pi u - pi: cos(phi) = -cos(2 pi u), sin(phi) = -sin(2 pi u) */
+    sincos_2pi(clamp_(v, 0.0f, 1.0f) * 0.5f, se, ce);      /* elevation = (0.5 - v) pi: sin(el) = cos(pi v), cos(el) = sin(pi v) */
+    return v3(-c2 * se, ce, -s2 * se);
+}
+RT3_HD uint32_t cdf_find(const float* cdf, uint32_t n, float u) {   /* largest k in [0,n) with cdf[k] <= u; cdf has n+1 entries */
+    uint32_t lo = 0, hi = n;
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (cdf[mid] <= u) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+/* pdf with respect to solid angle of the texel density at texel (i, j), for a direction whose |cos(elevation)| is sin_theta */
+RT3_HD float env_pdf_texel(const SceneView& s, uint32_t i, uint32_t j, float sin_theta) {
+    if (!(s.env_total > 0.0f)) return 0.0f;
+    float f = s.env_func[(size_t)j * s.env_w + i];
+    return (f / s.env_total) * (float(s.env_w) * float(s.env_h)) / (19.7392088021787172f * max_(sin_theta, 1e-6f));   /* 2 pi^2 */
+}
+RT3_HD float env_pdf(const SceneView& s, vec3 dir) {
+    if (s.env_func == nullptr) return 0.0f;
+    vec2 uv = direction_to_equirect_uv(dir);
+    uint32_t i = (uint32_t)min_(max_(uv.x * float(s.env_w), 0.0f), float(s.env_w - 1));
+    uint32_t j = (uint32_t)min_(max_(uv.y * float(s.env_h), 0.0f), float(s.env_h - 1));
+    return env_pdf_texel(s, i, j, sqrt_(max_(0.0f, fma_(-dir.y, dir.y, 1.0f))));
+}
+RT3_HD vec3 env_sample(const SceneView& s, float u1, float u2, float& pdf) {
+    pdf = 0.0f;
+    if (s.env_func == nullptr || !(s.env_total > 0.0f)) return v3(0.f, 1.f, 0.f);
+    uint32_t j = cdf_find(s.env_marginal, s.env_h, u2);
+    float m0 = s.env_marginal[j], m1 = s.env_marginal[j + 1];
+    float dv = (m1 > m0) ? (u2 - m0) / (m1 - m0) : 0.5f;
+    const float* row = s.env_conditional + (size_t)j * (s.env_w + 1);
+    uint32_t i = cdf_find(row, s.env_w, u1);
+    float c0 = row[i], c1 = row[i + 1];
+    float du = (c1 > c0) ? (u1 - c0) / (c1 - c0) : 0.5f;
+    float u = (float(i) + clamp_(du, 0.0f, 0.99999994f)) / float(s.env_w);
+    float v = (float(j) + clamp_(dv, 0.0f, 0.99999994f)) / float(s.env_h);
+    vec3 d = equirect_uv_to_direction(u, v);
+    pdf = env_pdf_texel(s, i, j, sqrt_(max_(0.0f, fma_(-d.y, d.y, 1.0f))));
+    return d;
+}
+/* Host-side table build (double accumulation, rounded once); identical code runs in librt3 and in the oracle. */
+inline void build_env_tables(const float* rgb, uint32_t w, uint32_t h, float* func, float* marginal, float* conditional, float* total) {
+    double sum = 0.0;
+    for (uint32_t j = 0; j < h; ++j) {
+        double st = sin(3.14159265358979323846 * (j + 0.5) / h);
+        for (uint32_t i = 0; i < w; ++i) {
+            const float* p = rgb + 3 * ((size_t)j * w + i);
+            double lum = 0.299 * p[0] + 0.587 * p[1] + 0.114 * p[2];
+            float f = (float)((lum > 0 ? lum : 0) * st);
+            func[(size_t)j * w + i] = f;
+            sum += f;
+        }
+    }
+    *total = (float)sum;
+    double acc = 0.0;
+    for (uint32_t j = 0; j < h; ++j) {
+        double rs = 0.0;
+        for (uint32_t i = 0; i < w; ++i) rs += func[(size_t)j * w + i];
+        marginal[j] = sum > 0 ? (float)(acc / sum) : (float)j / h;
+        float* row = conditional + (size_t)j * (w + 1);
+        double ra = 0.0;
+        for (uint32_t i = 0; i < w; ++i) { row[i] = rs > 0 ? (float)(ra / rs) : (float)i / w; ra += func[(size_t)j * w + i]; }
+        row[w] = 1.0f;
+        acc += rs;
+    }
+    marginal[h] = 1.0f;
 }
 
 /* ---------------------------------------------------------------- samplers ------------------- */

@@ -185,6 +185,10 @@ rt3_status rt3_create(int cuda_device, rt3_context** out) {
         cudaDeviceProp prop;
         RT3_CUDA(c, cudaGetDeviceProperties(&prop, cuda_device));
         c->sm_count = prop.multiProcessorCount;
+        cudaMemPool_t pool;                                   /* keep build temporaries cached in the stream-ordered pool */
+        RT3_CUDA(c, cudaDeviceGetDefaultMemPool(&pool, cuda_device));
+        uint64_t keep_all = UINT64_MAX;
+        RT3_CUDA(c, cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep_all));
         for (int i = 0; i < 8; ++i) RT3_CUDA(c, cudaEventCreate(&c->ev[i]));
         RT3_CUDA(c, cudaMalloc(&c->d_counters, sizeof(DeviceCounters)));
         RT3_CUDA(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));

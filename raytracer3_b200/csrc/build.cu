@@ -202,6 +202,21 @@ __global__ void k_empty_root(WideNode* nodes) {
     if (threadIdx.x < 20) nodes[0].w[threadIdx.x] = 0;
 }
 
+/* Build temporaries come from the stream-ordered pool (cudaMallocAsync): the context raises the pool's release threshold, so
+ * rebuilds reuse the memory instead of paying cudaMalloc/cudaFree (each a device-wide synchronisation) per buffer. */
+struct PoolBuf {
+    void* ptr = nullptr;
+    cudaStream_t st = 0;
+    void release() { if (ptr) cudaFreeAsync(ptr, st); ptr = nullptr; }
+};
+template <class T>
+T* palloc(rt3_context* c, PoolBuf& b, size_t count, cudaStream_t st) {
+    b.release();
+    b.st = st;
+    RT3_CUDA(c, cudaMallocAsync(&b.ptr, (count ? count : 1) * sizeof(T), st));
+    return (T*)b.ptr;
+}
+
 struct StageTimer {
     rt3_context* c; cudaStream_t st; cudaEvent_t a, b;
     StageTimer(rt3_context* c_, cudaStream_t s) : c(c_), st(s) { a = c->ev[0]; b = c->ev[1]; }
@@ -231,15 +246,15 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         if (out) *out = bs;
         return;
     }
-    Scratch s_tris, s_sorted, s_keys[2], s_vals[2], s_hist, s_nodes2, s_parent, s_flags, s_counts, s_items[2], s_misc;
+    PoolBuf s_tris, s_sorted, s_keys[2], s_vals[2], s_hist, s_nodes2, s_parent, s_flags, s_counts, s_items[2], s_misc;
     auto cleanup = [&]() {
         s_tris.release(); s_sorted.release(); s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release();
         s_nodes2.release(); s_parent.release(); s_flags.release(); s_counts.release(); s_items[0].release(); s_items[1].release(); s_misc.release();
     };
     try {
         /* flatten */
-        Tri48* tris = ensure<Tri48>(c, s_tris, n);
-        int* d_bounds = (int*)ensure<uint32_t>(c, s_misc, 16);   /* [0..5] bounds, [8] node ctr, [9] tri ctr, [10] queue ctr, [12],[13] sah */
+        Tri48* tris = palloc<Tri48>(c, s_tris, n, st);
+        int* d_bounds = (int*)palloc<uint32_t>(c, s_misc, 16, st);   /* [0..5] bounds, [8] node ctr, [9] tri ctr, [10] queue ctr, [12],[13] sah */
         tm.begin();
         RT3_LAUNCH(c, k_init_bounds, 1, 32, 0, st, d_bounds);
         RT3_LAUNCH(c, k_flatten, div_up(n, 256), 256, 0, st, c->view, n, tris, d_bounds);
@@ -251,10 +266,10 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         float ext = fmaxf(hi[0] - lo[0], fmaxf(hi[1] - lo[1], hi[2] - lo[2]));
         const float pad = ext * (1.0f / 65536.0f);
         /* morton */
-        uint64_t* keys0 = ensure<uint64_t>(c, s_keys[0], n);
-        uint64_t* keys1 = ensure<uint64_t>(c, s_keys[1], n);
-        uint32_t* vals0 = ensure<uint32_t>(c, s_vals[0], n);
-        uint32_t* vals1 = ensure<uint32_t>(c, s_vals[1], n);
+        uint64_t* keys0 = palloc<uint64_t>(c, s_keys[0], n, st);
+        uint64_t* keys1 = palloc<uint64_t>(c, s_keys[1], n, st);
+        uint32_t* vals0 = palloc<uint32_t>(c, s_vals[0], n, st);
+        uint32_t* vals1 = palloc<uint32_t>(c, s_vals[1], n, st);
         tm.begin();
         float3 flo = make_float3(lo[0], lo[1], lo[2]);
         float3 inv = make_float3(hi[0] > lo[0] ? 1.0f / (hi[0] - lo[0]) : 0.f, hi[1] > lo[1] ? 1.0f / (hi[1] - lo[1]) : 0.f,
@@ -263,7 +278,7 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         bs.ms_morton = tm.end();
         /* sort */
         const uint32_t nblocks = div_up(n, RADIX_TILE);
-        uint32_t* hist = ensure<uint32_t>(c, s_hist, 256 * (size_t)nblocks);
+        uint32_t* hist = palloc<uint32_t>(c, s_hist, 256 * (size_t)nblocks, st);
         tm.begin();
         for (int pass = 0; pass < 8; ++pass) {
             const uint64_t* ki = (pass & 1) ? keys1 : keys0; uint64_t* ko = (pass & 1) ? keys0 : keys1;
@@ -272,15 +287,15 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
             RT3_LAUNCH(c, k_radix_scan, 1, 1024, 0, st, hist, 256u * nblocks);
             RT3_LAUNCH(c, k_radix_scatter, nblocks, RADIX_THREADS, 0, st, ki, vi, ko, vo, n, pass * 8, hist, nblocks);
         }
-        Tri48* sorted = ensure<Tri48>(c, s_sorted, n);
+        Tri48* sorted = palloc<Tri48>(c, s_sorted, n, st);
         RT3_LAUNCH(c, k_gather_sorted, div_up(n, 256), 256, 0, st, tris, vals0, n, sorted);
         bs.ms_sort = tm.end();
         s_tris.release();
         /* hierarchy */
-        Bvh2Node* nodes2 = ensure<Bvh2Node>(c, s_nodes2, 2 * (size_t)n);
-        uint32_t* parent = ensure<uint32_t>(c, s_parent, 2 * (size_t)n);
-        uint32_t* nflags = ensure<uint32_t>(c, s_flags, n);
-        uint32_t* counts = ensure<uint32_t>(c, s_counts, n);
+        Bvh2Node* nodes2 = palloc<Bvh2Node>(c, s_nodes2, 2 * (size_t)n, st);
+        uint32_t* parent = palloc<uint32_t>(c, s_parent, 2 * (size_t)n, st);
+        uint32_t* nflags = palloc<uint32_t>(c, s_flags, n, st);
+        uint32_t* counts = palloc<uint32_t>(c, s_counts, n, st);
         tm.begin();
         RT3_CUDA(c, cudaMemsetAsync(parent, 0xFF, sizeof(uint32_t) * 2 * (size_t)n, st));
         RT3_CUDA(c, cudaMemsetAsync(nflags, 0, sizeof(uint32_t) * n, st));
@@ -293,8 +308,8 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release(); s_parent.release(); s_flags.release();
         /* collapse */
         WideNode* wide = ensure<WideNode>(c, c->bvh_nodes, n);
-        uint32_t* items0 = ensure<uint32_t>(c, s_items[0], 2 * (size_t)n + 2);
-        uint32_t* items1 = ensure<uint32_t>(c, s_items[1], 2 * (size_t)n + 2);
+        uint32_t* items0 = palloc<uint32_t>(c, s_items[0], 2 * (size_t)n + 2, st);
+        uint32_t* items1 = palloc<uint32_t>(c, s_items[1], 2 * (size_t)n + 2, st);
         uint32_t* ctr = (uint32_t*)d_bounds + 8;
         tm.begin();
         uint32_t init_ctr[8] = {1u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
