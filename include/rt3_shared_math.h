@@ -719,7 +719,7 @@ RT3_HD vec2 sample_2d(const SceneView& s, uint32_t flags, uint32_t px, uint32_t 
  * advance the ray to the hit point, gather emission, update throughput. */
 struct PathVertexOut { vec3 origin, dir; };
 RT3_HD PathVertexOut bounce_step(const GbufferData& surface, vec3 ray_o, vec3 ray_d, float depth, vec2 urand, vec3& radiance,
-                                 vec3& ray_color) {
+                                 vec3& ray_color, float* out_pdf = nullptr) {
     onb t = build_orthonormal_basis(surface.normal);
     vec3 wi = diffuse_sample_wi(urand.x, urand.y);
     PathVertexOut o;
@@ -727,7 +727,37 @@ RT3_HD PathVertexOut bounce_step(const GbufferData& surface, vec3 ray_o, vec3 ra
     o.dir = onb_to_world(t, wi);
     radiance = radiance + ray_color * surface.emissive;
     ray_color = ray_color * surface.albedo;
+    if (out_pdf) *out_pdf = wi.z * 0.31830988618379067154f;   /* cos(theta) / pi: solid-angle pdf of the cosine lobe */
     return o;
+}
+
+/* ---- next-event estimation of the environment (RT3_FLAG_NEE; needs RT3_FLAG_ENV and the importance tables) ----------
+ * At every vertex from which a BRDF ray is traced, one environment direction is drawn from the luminance tables and a
+ * shadow (any-hit) ray is cast; the BRDF-sampled escape and the light sample are combined with the balance heuristic. */
+RT3_HD bool nee_enabled(uint32_t flags) { return (flags & (RT3_FLAG_NEE | RT3_FLAG_ENV)) == (RT3_FLAG_NEE | RT3_FLAG_ENV); }
+struct NeeSample { vec3 dir, contribution; bool valid; };
+/* `throughput_after` = ray_color AFTER bounce_step (already multiplied by the albedo). */
+RT3_HD NeeSample nee_sample(const SceneView& s, const GbufferData& surface, vec3 throughput_after, vec2 u) {
+    NeeSample r;
+    float pl;
+    r.dir = env_sample(s, u.x, u.y, pl);
+    float cosl = dot(surface.normal, r.dir);
+    r.valid = (pl > 0.0f) && (cosl > 0.0f);
+    r.contribution = v3(0.f, 0.f, 0.f);
+    if (r.valid) {
+        float pb = cosl * 0.31830988618379067154f;
+        float w = pl / (pl + pb);
+        float k = (cosl * 0.31830988618379067154f / pl) * w;
+        r.contribution = throughput_after * (sample_environment(s, r.dir) * k);
+    }
+    return r;
+}
+/* MIS weight of an environment hit reached by BRDF sampling with solid-angle pdf `pdf_brdf` (1 when NEE is off). */
+RT3_HD float escape_weight(const SceneView& s, uint32_t flags, vec3 dir, float pdf_brdf) {
+    if (!nee_enabled(flags)) return 1.0f;
+    float pl = env_pdf(s, dir);
+    float d = pdf_brdf + pl;
+    return d > 0.0f ? pdf_brdf / d : 0.0f;
 }
 /* shaders/old/refrence_mode.slang:59-65 */
 RT3_HD vec3 temporal_blend(vec3 prev, vec3 radiance, float blendfactor) {

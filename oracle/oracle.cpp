@@ -54,7 +54,8 @@ struct orc_scene {
     std::vector<std::vector<uint8_t>> textures;
     std::vector<const uint8_t*> tex_ptr;
     std::vector<uint32_t> tex_dim;
-    std::vector<float> env;
+    std::vector<float> env, env_func, env_marginal, env_conditional;
+    float env_total = 0.f;
     uint32_t env_w = 0, env_h = 0;
     std::vector<uint8_t> bn;
     uint32_t bn_w = 0, bn_h = 0;
@@ -73,6 +74,8 @@ struct orc_scene {
         s.tex_data = tex_ptr.data(); s.tex_dim = tex_dim.data(); s.n_textures = (uint32_t)tex_ptr.size();
         s.srgb_lut = srgb_lut;
         s.env = env.empty() ? nullptr : env.data(); s.env_w = env_w; s.env_h = env_h;
+        s.env_func = env_func.empty() ? nullptr : env_func.data(); s.env_marginal = env_marginal.data(); s.env_conditional = env_conditional.data();
+        s.env_total = env_total;
         s.bn = bn.empty() ? nullptr : bn.data(); s.bn_w = bn_w; s.bn_h = bn_h;
         return s;
     }
@@ -293,7 +296,11 @@ void orc_scene_set_texture(orc_scene* s, uint32_t slot, uint32_t w, uint32_t h, 
     s->tex_ptr.resize(s->textures.size());
     for (size_t i = 0; i < s->textures.size(); ++i) s->tex_ptr[i] = s->textures[i].empty() ? nullptr : s->textures[i].data();
 }
-void orc_scene_set_environment(orc_scene* s, uint32_t w, uint32_t h, const float* rgb) { s->env.assign(rgb, rgb + 3 * (size_t)w * h); s->env_w = w; s->env_h = h; }
+void orc_scene_set_environment(orc_scene* s, uint32_t w, uint32_t h, const float* rgb) {
+    s->env.assign(rgb, rgb + 3 * (size_t)w * h); s->env_w = w; s->env_h = h;
+    s->env_func.resize((size_t)w * h); s->env_marginal.resize(h + 1); s->env_conditional.resize((size_t)h * (w + 1));
+    build_env_tables(rgb, w, h, s->env_func.data(), s->env_marginal.data(), s->env_conditional.data(), &s->env_total);
+}
 void orc_scene_set_bluenoise(orc_scene* s, uint32_t w, uint32_t h, const uint8_t* rgba8) { s->bn.assign(rgba8, rgba8 + 4 * (size_t)w * h); s->bn_w = w; s->bn_h = h; }
 
 double orc_scene_build(orc_scene* s) {
@@ -391,9 +398,9 @@ void orc_pass_reference(const orc_scene* s, const rt3_params* p, rt3_rect rc, co
                         float* light, int threads, rt3_counters* opt_counters) {
     SceneView sv = s->view();
     uint32_t pitch = (uint32_t)p->window_size[0];
-    std::atomic<uint64_t> n_secondary(0), n_started(0), n_escaped(0);
+    std::atomic<uint64_t> n_secondary(0), n_started(0), n_escaped(0), n_shadow(0);
     parallel_for(rc.h, threads, 4, [&](uint64_t y0, uint64_t y1) {
-        uint64_t secondary = 0, started = 0, escaped = 0;
+        uint64_t secondary = 0, started = 0, escaped = 0, shadow = 0;
         for (uint32_t y = rc.y0 + (uint32_t)y0; y < rc.y0 + (uint32_t)y1; ++y)
             for (uint32_t x = rc.x0; x < rc.x0 + rc.w; ++x) {
                 size_t px = (size_t)y * pitch + x;
@@ -412,14 +419,23 @@ void orc_pass_reference(const orc_scene* s, const rt3_params* p, rt3_rect rc, co
                     float hit_t = gdepth;
                     bool missed = false;                                                /* payload.geometryIndex = 0, :34 */
                     started++;
+                    float pdf_brdf = 0.f;                                               /* pdf of the direction the current ray was sampled with */
                     for (uint32_t b = 0; b < p->bounces; ++b) {                         /* :36 */
                         if (missed) {                                                   /* :37-40 */
-                            if (p->flags & RT3_FLAG_ENV) radiance = radiance + ray_color * sample_environment(sv, rd);
+                            if (p->flags & RT3_FLAG_ENV) radiance = radiance + ray_color * (sample_environment(sv, rd) * escape_weight(sv, p->flags, rd, pdf_brdf));
                             break;
                         }
                         vec2 urand = sample_2d(sv, p->flags, x, y, p->frame, rng);     /* :43 */
-                        PathVertexOut nv = bounce_step(surface, ro, rd, hit_t, urand, radiance, ray_color); /* :44-51 */
+                        PathVertexOut nv = bounce_step(surface, ro, rd, hit_t, urand, radiance, ray_color, &pdf_brdf); /* :44-51 */
                         ro = nv.origin; rd = nv.dir;
+                        if (nee_enabled(p->flags) && b != p->bounces - 1) {             /* next-event estimation (no reference counterpart) */
+                            vec2 ul = sample_2d(sv, p->flags, x, y, p->frame, rng);
+                            NeeSample ns = nee_sample(sv, surface, ray_color, ul);
+                            if (ns.valid) {
+                                shadow++;
+                                if (!any_bvh(*s, make_ray(ro, ns.dir, tmin, tmax))) radiance = radiance + ns.contribution;
+                            }
+                        }
                         if (b != p->bounces - 1) {                                      /* :53-56 */
                             rt3_hit h = closest_bvh(*s, make_ray(ro, rd, tmin, tmax));
                             secondary++;
@@ -435,10 +451,11 @@ void orc_pass_reference(const orc_scene* s, const rt3_params* p, rt3_rect rc, co
                 vec3 o = temporal_blend(prev, radiance, p->blendfactor);                /* :61-65 */
                 light[4 * px] = o.x; light[4 * px + 1] = o.y; light[4 * px + 2] = o.z; light[4 * px + 3] = 0.f;
             }
-        n_secondary += secondary; n_started += started; n_escaped += escaped;
+        n_secondary += secondary; n_started += started; n_escaped += escaped; n_shadow += shadow;
     });
     if (opt_counters) {
         opt_counters->rays_secondary += n_secondary; opt_counters->paths_started += n_started; opt_counters->paths_escaped += n_escaped;
+        opt_counters->rays_shadow += n_shadow;
     }
 }
 

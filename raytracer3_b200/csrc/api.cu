@@ -51,6 +51,17 @@ T* upload(rt3_context* c, Scratch& s, const std::vector<T>& v) {
     return d;
 }
 
+static void free_environment(rt3_context* c) {
+    float** ps[] = {&c->d_env, &c->d_env_func, &c->d_env_marginal, &c->d_env_conditional};
+    for (float** p : ps) { if (*p) cudaFree(*p); *p = nullptr; }
+    c->env_w = c->env_h = 0; c->env_total = 0.f;
+}
+static void publish_environment(rt3_context* c) {
+    rt3m::SceneView& v = c->view;
+    v.env = c->d_env; v.env_w = c->env_w; v.env_h = c->env_h;
+    v.env_func = c->d_env_func; v.env_marginal = c->d_env_marginal; v.env_conditional = c->d_env_conditional; v.env_total = c->env_total;
+}
+
 /* Segment table + SceneView (device pointers) from the current scene state. */
 void refresh_scene_tables(rt3_context* c) {
     const uint32_t ng = (uint32_t)c->h_geometries.size();
@@ -101,7 +112,7 @@ void refresh_scene_tables(rt3_context* c) {
     v.tex_dim = upload(c, c->d_tex_dim, td);
     v.n_textures = (uint32_t)c->textures.size();
     v.srgb_lut = c->d_srgb_lut;
-    v.env = c->d_env; v.env_w = c->env_w; v.env_h = c->env_h;
+    publish_environment(c);
     v.bn = c->d_bn; v.bn_w = c->bn_w; v.bn_h = c->bn_h;
     c->scene_dirty = false;
 }
@@ -145,7 +156,8 @@ PixelMap tiles_map(rt3_context* c, const rt3_params* p, const rt3_rect* tiles, u
 void check_params(rt3_context* c, const rt3_params* p) {
     if (!p) RT3_FAIL(c, RT3_ERR_INVALID, "params is NULL");
     if (p->samples == 0) RT3_FAIL(c, RT3_ERR_INVALID, "samples must be >= 1");
-    if ((p->flags & RT3_FLAG_ENV) && !c->d_env) RT3_FAIL(c, RT3_ERR_STATE, "RT3_FLAG_ENV without rt3_scene_set_environment");
+    if ((p->flags & (RT3_FLAG_ENV | RT3_FLAG_NEE)) && !c->d_env) RT3_FAIL(c, RT3_ERR_STATE, "RT3_FLAG_ENV / RT3_FLAG_NEE without rt3_scene_set_environment");
+    if ((p->flags & RT3_FLAG_NEE) && !(p->flags & RT3_FLAG_ENV)) RT3_FAIL(c, RT3_ERR_INVALID, "RT3_FLAG_NEE requires RT3_FLAG_ENV");
     if ((p->flags & RT3_FLAG_BLUENOISE) && !c->d_bn) RT3_FAIL(c, RT3_ERR_STATE, "RT3_FLAG_BLUENOISE without rt3_scene_set_bluenoise");
 }
 
@@ -210,12 +222,12 @@ void rt3_destroy(rt3_context* c) {
     cudaDeviceSynchronize();
     c->vertices.release(); c->indices.release();
     for (TextureRec& t : c->textures) if (t.data) cudaFree(t.data);
-    if (c->d_env) cudaFree(c->d_env);
+    free_environment(c);
     if (c->d_bn) cudaFree(c->d_bn);
     if (c->d_srgb_lut) cudaFree(c->d_srgb_lut);
     if (c->d_counters) cudaFree(c->d_counters);
     Scratch* all[] = {&c->d_geometries, &c->d_seg_first, &c->d_seg_geo, &c->d_seg_inst, &c->d_inst_xform, &c->d_tex_ptr, &c->d_tex_dim, &c->bvh_nodes,
-                      &c->bvh_tris, &c->q_rays[0], &c->q_rays[1], &c->q_hits, &c->q_thr[0], &c->q_thr[1], &c->q_pix[0], &c->q_pix[1], &c->px_radiance,
+                      &c->bvh_tris, &c->q_rays[0], &c->q_rays[1], &c->q_hits, &c->q_thr[0], &c->q_thr[1], &c->q_pix[0], &c->q_pix[1], &c->q_pdf[0], &c->q_pdf[1], &c->q_srays, &c->q_scontrib, &c->q_sbits, &c->px_radiance,
                       &c->px_rng, &c->d_counts, &c->d_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();
@@ -232,7 +244,7 @@ rt3_status rt3_scene_clear(rt3_context* c) {
         c->h_geometries.clear(); c->h_instances.clear();
         for (TextureRec& t : c->textures) if (t.data) cudaFree(t.data);
         c->textures.clear();
-        if (c->d_env) { cudaFree(c->d_env); c->d_env = nullptr; } c->env_w = c->env_h = 0;
+        free_environment(c);
         if (c->d_bn) { cudaFree(c->d_bn); c->d_bn = nullptr; } c->bn_w = c->bn_h = 0;
         c->scene_dirty = true; c->accel_valid = false; c->n_triangles = 0;
     });
@@ -286,11 +298,22 @@ rt3_status rt3_scene_set_texture(rt3_context* c, uint32_t slot, uint32_t w, uint
 rt3_status rt3_scene_set_environment(rt3_context* c, uint32_t w, uint32_t h, const float* rgb) {
     return guarded(c, [&]() {
         if (!rgb || !w || !h) RT3_FAIL(c, RT3_ERR_INVALID, "bad environment arguments");
-        if (c->d_env) { RT3_CUDA(c, cudaDeviceSynchronize()); cudaFree(c->d_env); c->d_env = nullptr; }
-        RT3_CUDA(c, cudaMalloc((void**)&c->d_env, 12 * (size_t)w * h));
-        RT3_CUDA(c, cudaMemcpy(c->d_env, rgb, 12 * (size_t)w * h, cudaMemcpyHostToDevice));
+        RT3_CUDA(c, cudaDeviceSynchronize());
+        free_environment(c);
+        const size_t px = (size_t)w * h;
+        RT3_CUDA(c, cudaMalloc((void**)&c->d_env, 12 * px));
+        RT3_CUDA(c, cudaMemcpy(c->d_env, rgb, 12 * px, cudaMemcpyHostToDevice));
+        /* importance tables for RT3_FLAG_NEE: host-side build (same function as the oracle), uploaded once */
+        std::vector<float> func(px), marg(h + 1), cond((size_t)h * (w + 1));
+        rt3m::build_env_tables(rgb, w, h, func.data(), marg.data(), cond.data(), &c->env_total);
+        RT3_CUDA(c, cudaMalloc((void**)&c->d_env_func, 4 * func.size()));
+        RT3_CUDA(c, cudaMalloc((void**)&c->d_env_marginal, 4 * marg.size()));
+        RT3_CUDA(c, cudaMalloc((void**)&c->d_env_conditional, 4 * cond.size()));
+        RT3_CUDA(c, cudaMemcpy(c->d_env_func, func.data(), 4 * func.size(), cudaMemcpyHostToDevice));
+        RT3_CUDA(c, cudaMemcpy(c->d_env_marginal, marg.data(), 4 * marg.size(), cudaMemcpyHostToDevice));
+        RT3_CUDA(c, cudaMemcpy(c->d_env_conditional, cond.data(), 4 * cond.size(), cudaMemcpyHostToDevice));
         c->env_w = w; c->env_h = h;
-        c->view.env = c->d_env; c->view.env_w = w; c->view.env_h = h;
+        publish_environment(c);
     });
 }
 rt3_status rt3_scene_set_bluenoise(rt3_context* c, uint32_t w, uint32_t h, const uint8_t* rgba8) {
@@ -387,7 +410,7 @@ rt3_status rt3_trace_any(rt3_context* c, const rt3_ray* rays, uint64_t n, uint32
     return guarded(c, [&]() {
         require_accel(c);
         if (n && (!rays || !out_bits)) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
-        rt3_launch_trace_any(c, rays, n, out_bits, (cudaStream_t)st);
+        rt3_launch_trace_any(c, rays, nullptr, n, out_bits, (cudaStream_t)st);
     });
 }
 
@@ -444,7 +467,7 @@ rt3_status rt3_trace_any_host(rt3_context* c, const rt3_ray* rays_host, uint64_t
         rt3_ray* r = ensure<rt3_ray>(c, c->f_rays, n);
         uint32_t* b = ensure<uint32_t>(c, c->f_bits, words);
         RT3_CUDA(c, cudaMemcpyAsync(r, rays_host, n * sizeof(rt3_ray), cudaMemcpyHostToDevice, 0));
-        rt3_launch_trace_any(c, r, n, b, 0);
+        rt3_launch_trace_any(c, r, nullptr, n, b, 0);
         RT3_CUDA(c, cudaMemcpyAsync(out_bits_host, b, words * 4, cudaMemcpyDeviceToHost, 0));
         RT3_CUDA(c, cudaStreamSynchronize(0));
     });

@@ -83,6 +83,7 @@ struct rt3_context {
     std::vector<InstanceRec> h_instances;
     std::vector<TextureRec> textures;
     float* d_env = nullptr; uint32_t env_w = 0, env_h = 0;
+    float *d_env_func = nullptr, *d_env_marginal = nullptr, *d_env_conditional = nullptr; float env_total = 0.f;   /* RT3_FLAG_NEE tables */
     uint8_t* d_bn = nullptr; uint32_t bn_w = 0, bn_h = 0;
     float* d_srgb_lut = nullptr;
     bool scene_dirty = true;
@@ -100,7 +101,7 @@ struct rt3_context {
     rt3_build_stats last_build;
 
     /* pass scratch */
-    Scratch q_rays[2], q_hits, q_thr[2], q_pix[2], px_radiance, px_rng, d_counts, d_rects, d_params;
+    Scratch q_rays[2], q_hits, q_thr[2], q_pix[2], q_pdf[2], q_srays, q_scontrib, q_sbits, px_radiance, px_rng, d_counts, d_rects, d_params;
     Scratch f_gbuffer, f_depth, f_light, f_prev, f_rays, f_hits, f_bits, l2_buf;
     DeviceCounters* d_counters = nullptr;
     cudaEvent_t ev[8];
@@ -151,7 +152,7 @@ __device__ __forceinline__ bool pixel_of(const PixelMap& m, uint32_t idx, uint32
 /* implemented in build.cu / trace.cu / passes.cu */
 void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out);
 void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, cudaStream_t st);
-void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, uint64_t n, uint32_t* bits, cudaStream_t st);
+void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits, cudaStream_t st);
 void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out);
 void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary,
                         cudaStream_t st);

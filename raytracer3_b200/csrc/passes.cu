@@ -62,6 +62,11 @@ __global__ void __launch_bounds__(128) k_gbuffer(SceneView s, const WideNode* __
 }
 
 /* ---- pass 2, wavefront --------------------------------------------------------------------- */
+/* RT3_FLAG_NEE plumbing: shadow-ray queue (ray, contribution + pixel slot) and the BRDF pdf carried with every live path. */
+struct NeeQueues {
+    rt3_ray* srays; float4* scontrib; uint32_t* scount;
+    const float* pdf_in; float* pdf_out;
+};
 __device__ __forceinline__ uint32_t warp_enqueue(bool alive, uint32_t* count) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);
@@ -83,14 +88,16 @@ __device__ __forceinline__ void store_ray(rt3_ray* q, uint32_t pos, vec3 o, vec3
 __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_params p, PixelMap m, const uint32_t* __restrict__ gbuffer,
                                                            const float* __restrict__ depth, float4* __restrict__ px_radiance, uint32_t* __restrict__ px_rng,
                                                            int first_sample, rt3_ray* __restrict__ q_rays, float4* __restrict__ q_thr, uint32_t* q_count,
-                                                           DeviceCounters* counters) {
-    unsigned long long started = 0;
+                                                           NeeQueues nq, DeviceCounters* counters) {
+    unsigned long long started = 0, shadows = 0;
+    const bool nee = nee_enabled(p.flags);
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t base = blockIdx.x * blockDim.x; base < m.work; base += stride) {   /* block-uniform trip count */
         const uint32_t idx = base + threadIdx.x;
         uint32_t x, y; size_t px;
-        bool alive = false;
-        vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0);
+        bool alive = false, shadow = false;
+        float pdf_brdf = 0.f;
+        vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0), sdir = v3(0, 0, 0), scon = v3(0, 0, 0);
         if (idx < m.work && pixel_of(m, idx, x, y, px)) {
             const float gdepth = depth[px];
             if (gdepth != RT3_BACKGROUND_DEPTH) {                                     /* :18-21 */
@@ -109,9 +116,14 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_para
                     rt3_ray pr = setup_primary_ray(x, y, p);                           /* :30 */
                     vec3 ray_color = v3(1.f, 1.f, 1.f);
                     vec2 urand = sample_2d(s, p.flags, x, y, p.frame, rng);            /* :43 */
-                    PathVertexOut nv = bounce_step(surface, v3(pr.o), v3(pr.d), gdepth, urand, radiance, ray_color);   /* :44-51 */
+                    PathVertexOut nv = bounce_step(surface, v3(pr.o), v3(pr.d), gdepth, urand, radiance, ray_color, &pdf_brdf);   /* :44-51 */
                     o = nv.origin; d = nv.dir; thr = ray_color;
                     alive = p.bounces > 1;                                             /* :53 */
+                    if (nee && alive) {
+                        vec2 ul = sample_2d(s, p.flags, x, y, p.frame, rng);
+                        NeeSample ns = nee_sample(s, surface, ray_color, ul);
+                        shadow = ns.valid; sdir = ns.dir; scon = ns.contribution;
+                    }
                 }
                 px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);   /* w = 1: pixel is not background */
                 px_rng[idx] = rng.index;
@@ -125,9 +137,19 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_para
         if (alive) {
             store_ray(q_rays, pos, o, d, 0.001f, RT3_BACKGROUND_DEPTH);               /* :31, TMax of setupPrimaryRay */
             q_thr[pos] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(idx));
+            if (nee) nq.pdf_out[pos] = pdf_brdf;
+        }
+        if (nee) {
+            const uint32_t sp = warp_enqueue(shadow, nq.scount);
+            if (shadow) {
+                shadows++;
+                store_ray(nq.srays, sp, o, sdir, 0.001f, RT3_BACKGROUND_DEPTH);
+                nq.scontrib[sp] = make_float4(scon.x, scon.y, scon.z, __uint_as_float(idx));
+            }
         }
     }
     flush_counter(started, &counters->paths_started);
+    if (nee) flush_counter(shadows, &counters->rays_shadow);
 }
 
 /* Loop iteration b >= 1 of refrence_mode.slang:36-57 for every path whose ray was traced at b-1. */
@@ -135,14 +157,16 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_shade(SceneView s, rt3_par
                                                             const rt3_hit* __restrict__ hits, const float4* __restrict__ thr_in,
                                                             const uint32_t* __restrict__ count_in, rt3_ray* __restrict__ rays_out,
                                                             float4* __restrict__ thr_out, uint32_t* count_out, float4* __restrict__ px_radiance,
-                                                            uint32_t* __restrict__ px_rng, DeviceCounters* counters) {
+                                                            uint32_t* __restrict__ px_rng, NeeQueues nq, DeviceCounters* counters) {
     const uint32_t n = *count_in;
-    unsigned long long traced = 0, escaped = 0;
+    unsigned long long traced = 0, escaped = 0, shadows = 0;
+    const bool nee = nee_enabled(p.flags);
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {
         const uint32_t i = base + threadIdx.x;
-        bool alive = false;
-        vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0);
+        bool alive = false, shadow = false;
+        float pdf_brdf = 0.f;
+        vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0), sdir = v3(0, 0, 0), scon = v3(0, 0, 0);
         uint32_t idx = 0;
         if (i < n) {
             traced++;
@@ -158,7 +182,8 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_shade(SceneView s, rt3_par
             if (prim == RT3_MISS) {                                                    /* :37-40 */
                 escaped++;
                 if (p.flags & RT3_FLAG_ENV) {
-                    radiance = radiance + ray_color * sample_environment(s, rd);       /* :38 (commented out in the reference) */
+                    const float wgt = escape_weight(s, p.flags, rd, nee ? nq.pdf_in[i] : 0.f);       /* 1 unless RT3_FLAG_NEE */
+                    radiance = radiance + ray_color * (sample_environment(s, rd) * wgt);   /* :38 (commented out in the reference) */
                     px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
                 }
             } else {
@@ -168,21 +193,52 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_shade(SceneView s, rt3_par
                 RandomSamplerState rng = rng_init(x, y, p.frame);
                 rng.index = px_rng[idx];
                 vec2 urand = sample_2d(s, p.flags, x, y, p.frame, rng);               /* :43 */
-                PathVertexOut nv = bounce_step(surface, ro, rd, h4.x, urand, radiance, ray_color);   /* :44-51 */
-                px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
-                px_rng[idx] = rng.index;
+                PathVertexOut nv = bounce_step(surface, ro, rd, h4.x, urand, radiance, ray_color, &pdf_brdf);   /* :44-51 */
                 o = nv.origin; d = nv.dir; thr = ray_color;
                 alive = (b != p.bounces - 1);                                          /* :53 */
+                if (nee && alive) {
+                    vec2 ul = sample_2d(s, p.flags, x, y, p.frame, rng);
+                    NeeSample ns = nee_sample(s, surface, ray_color, ul);
+                    shadow = ns.valid; sdir = ns.dir; scon = ns.contribution;
+                }
+                px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
+                px_rng[idx] = rng.index;
             }
         }
         const uint32_t pos = warp_enqueue(alive, count_out);
         if (alive) {
             store_ray(rays_out, pos, o, d, 0.001f, RT3_BACKGROUND_DEPTH);
             thr_out[pos] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(idx));
+            if (nee) nq.pdf_out[pos] = pdf_brdf;
+        }
+        if (nee) {
+            const uint32_t sp = warp_enqueue(shadow, nq.scount);
+            if (shadow) {
+                shadows++;
+                store_ray(nq.srays, sp, o, sdir, 0.001f, RT3_BACKGROUND_DEPTH);
+                nq.scontrib[sp] = make_float4(scon.x, scon.y, scon.z, __uint_as_float(idx));
+            }
         }
     }
+    if (nee) flush_counter(shadows, &counters->rays_shadow);
     flush_counter(traced, &counters->rays_secondary);
     flush_counter(escaped, &counters->paths_escaped);
+}
+
+/* RT3_FLAG_NEE: add the light-sample contribution of every unoccluded shadow ray (one per pixel and bounce at most, so
+ * no atomics; it lands between the emission of this bounce and whatever the next bounce adds, as in the oracle's loop). */
+__global__ void __launch_bounds__(PASS_THREADS) k_ref_shadow(const float4* __restrict__ scontrib, const uint32_t* __restrict__ occluded_bits,
+                                                             const uint32_t* __restrict__ scount, float4* __restrict__ px_radiance) {
+    const uint32_t n = *scount;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        if ((occluded_bits[i >> 5] >> (i & 31u)) & 1u) continue;
+        const float4 c4 = scontrib[i];
+        const uint32_t idx = __float_as_uint(c4.w);
+        float4 r = px_radiance[idx];
+        r.x = r.x + c4.x; r.y = r.y + c4.y; r.z = r.z + c4.z;
+        px_radiance[idx] = r;
+    }
 }
 
 /* refrence_mode.slang:59-65 */
@@ -238,23 +294,41 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
                           float* light, cudaStream_t st) {
     if (!m.work) return;
     const size_t W = m.work;
+    const bool nee = nee_enabled(p.flags);
     rt3_ray* q_rays[2] = {ensure<rt3_ray>(c, c->q_rays[0], W), ensure<rt3_ray>(c, c->q_rays[1], W)};
     float4* q_thr[2] = {ensure<float4>(c, c->q_thr[0], W), ensure<float4>(c, c->q_thr[1], W)};
     rt3_hit* q_hits = ensure<rt3_hit>(c, c->q_hits, W);
     float4* px_radiance = ensure<float4>(c, c->px_radiance, W);
     uint32_t* px_rng = ensure<uint32_t>(c, c->px_rng, W);
-    uint32_t* counts = (uint32_t*)ensure<unsigned long long>(c, c->d_counts, 64);
+    uint32_t* counts = (uint32_t*)ensure<unsigned long long>(c, c->d_counts, 64);   /* [0],[1] path queues, [2] shadow queue */
+    float* q_pdf[2] = {nullptr, nullptr};
+    NeeQueues nq = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    uint32_t* sbits = nullptr;
+    if (nee) {
+        q_pdf[0] = ensure<float>(c, c->q_pdf[0], W); q_pdf[1] = ensure<float>(c, c->q_pdf[1], W);
+        nq.srays = ensure<rt3_ray>(c, c->q_srays, W); nq.scontrib = ensure<float4>(c, c->q_scontrib, W); nq.scount = counts + 2;
+        sbits = ensure<uint32_t>(c, c->q_sbits, (W + 31) / 32);
+    }
     const unsigned grid = std::min<unsigned>(div_up(W, PASS_THREADS), (unsigned)c->sm_count * 8u);
+    auto resolve_shadows = [&]() {                      /* any-hit pass over the shadow queue, then add the unoccluded contributions */
+        rt3_launch_trace_any(c, nq.srays, nq.scount, W, sbits, st);
+        RT3_LAUNCH(c, k_ref_shadow, grid, PASS_THREADS, 0, st, nq.scontrib, sbits, nq.scount, px_radiance);
+    };
     for (uint32_t sidx = 0; sidx < p.samples; ++sidx) {
-        RT3_CUDA(c, cudaMemsetAsync(counts, 0, 8, st));
+        RT3_CUDA(c, cudaMemsetAsync(counts, 0, 12, st));
+        nq.pdf_in = nullptr; nq.pdf_out = q_pdf[0];
         RT3_LAUNCH(c, k_ref_init, grid, PASS_THREADS, 0, st, c->view, p, m, gbuffer, depth, px_radiance, px_rng, sidx == 0 ? 1 : 0, q_rays[0], q_thr[0], counts,
-                   c->d_counters);
+                   nq, c->d_counters);
+        if (nee && p.bounces > 1) resolve_shadows();
         int cur = 0;
         for (uint32_t b = 1; b < p.bounces; ++b) {
             rt3_launch_trace_closest(c, q_rays[cur], counts + cur, W, q_hits, st);
             RT3_CUDA(c, cudaMemsetAsync(counts + (1 - cur), 0, 4, st));
+            if (nee) RT3_CUDA(c, cudaMemsetAsync(counts + 2, 0, 4, st));
+            nq.pdf_in = q_pdf[cur]; nq.pdf_out = q_pdf[1 - cur];
             RT3_LAUNCH(c, k_ref_shade, grid, PASS_THREADS, 0, st, c->view, p, m, b, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur], q_thr[1 - cur],
-                       counts + (1 - cur), px_radiance, px_rng, c->d_counters);
+                       counts + (1 - cur), px_radiance, px_rng, nq, c->d_counters);
+            if (nee && b != p.bounces - 1) resolve_shadows();
             cur = 1 - cur;
         }
     }

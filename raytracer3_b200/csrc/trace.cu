@@ -228,9 +228,9 @@ void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_
     if (c->prof_on) RT3_CUDA(c, cudaEventRecord(prof_event(c), st));
 }
 
-void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, uint64_t n, uint32_t* bits, cudaStream_t st) {
-    if (n == 0) return;
-    launch_dyn<true>(c, rays, nullptr, n, nullptr, bits, st);
+void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits, cudaStream_t st) {
+    if (n_max == 0) return;
+    launch_dyn<true>(c, rays, d_count, n_max, nullptr, bits, st);
 }
 
 void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out) {

@@ -10,7 +10,7 @@ import pytest
 
 from raytracer3_b200 import scenes
 from raytracer3_b200.camera import camera_for, make_params
-from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, HIT, MISS, RAY
+from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, FLAG_NEE, HIT, MISS, RAY
 
 pytestmark = pytest.mark.gpu
 
@@ -108,6 +108,7 @@ def test_gbuffer_pass_bit_exact(gpu_ctx, name, wh):
 @pytest.mark.parametrize("name,flags,bounces,samples", [
     ("cornell", 0, 4, 3), ("cornell", 0, 1, 1), ("cornell", 0, 2, 2),
     ("atrium_small", 0, 4, 2), ("atrium_small", FLAG_ENV, 4, 2), ("atrium_small", FLAG_ENV | FLAG_BLUENOISE, 4, 2),
+    ("atrium_small", FLAG_ENV | FLAG_NEE, 4, 2), ("atrium_small", FLAG_ENV | FLAG_BLUENOISE | FLAG_NEE, 3, 1), ("cornell", FLAG_ENV | FLAG_NEE, 2, 2),
 ])
 def test_reference_pass_matches_oracle(gpu_ctx, name, flags, bounces, samples):
     from raytracer3_b200.host import Renderer
@@ -121,6 +122,8 @@ def test_reference_pass_matches_oracle(gpu_ctx, name, flags, bounces, samples):
     orc = _oracle(sc)
     r = Renderer(gpu_ctx, w, W, H)
     prev = None
+    gpu_ctx.counters(reset=True)
+    shadow_want = 0
     for frame in range(2):   # second frame exercises the PrevLight blend
         p = make_params(camera_for(sc, "cam0", W, H), W, H, frame=frame, bounces=bounces, samples=samples,
                         blendfactor=1.0 if frame == 0 else 0.5, flags=flags)
@@ -128,12 +131,14 @@ def test_reference_pass_matches_oracle(gpu_ctx, name, flags, bounces, samples):
         gb, dp, _, _ = orc.pass_gbuffer(p)
         want, cnt = orc.pass_reference(p, gb, dp, prev_light=prev)
         prev = want
+        shadow_want += cnt.rays_shadow
         diff = np.abs(light - want)
         rmse = float(np.sqrt((diff[..., :3] ** 2).mean()))
         assert rmse <= 1e-3, rmse
         assert (_bits(light) == _bits(want)).all(), f"radiance not bit-identical: rmse {rmse}, max {diff.max()}"
     c = gpu_ctx.counters(reset=True)
     assert c.rays_primary > 0
+    assert c.rays_shadow == shadow_want and (shadow_want > 0) == bool(flags & FLAG_NEE)
 
 
 def test_render_frame_host_and_counters(gpu_ctx):
