@@ -94,7 +94,9 @@ enum {
     RT3_FLAG_ENV       = 1u << 0, /* miss adds throughput * environment(dir): the term commented out at
                                      shaders/old/refrence_mode.slang:38 */
     RT3_FLAG_BLUENOISE = 1u << 1, /* blue-noise tile + R2 offsets instead of the murmur3 stream */
-    RT3_FLAG_NEE       = 1u << 2  /* environment importance sampling with any-hit shadow rays */
+    RT3_FLAG_NEE       = 1u << 2, /* environment importance sampling with any-hit shadow rays */
+    RT3_FLAG_SPECULAR  = 1u << 3  /* material evaluation = DiffuseBrdf + SpecularBrdf (GGX VNDF, Smith, Schlick:
+                                     shaders/include/brdf.slang:95-318) layered by metalness, instead of DiffuseBrdf only */
 };
 
 typedef struct { uint32_t x0, y0, w, h; } rt3_rect;                /* tile; full frame = {0,0,W,H} */
@@ -184,6 +186,18 @@ RT3_API rt3_status rt3_trace_any(rt3_context*, const rt3_ray* rays, uint64_t n, 
  * to `light_host` (pinned or pageable).  prev_light_host may be NULL (blendfactor >= 1).  Synchronous. */
 RT3_API rt3_status rt3_render_frame_host(rt3_context*, const rt3_params*, const float* prev_light_host, float* light_host,
                                          float* opt_depth_host, uint32_t* opt_gbuffer_host);
+/* Frames in flight — the reference keeps FRAMES_IN_FLIGHT = 3 frames queued behind a timeline semaphore
+ * (src/renderer/vulkan/swapchain.rs:8, src/renderer/render_graph/mod.rs:656-665).  rt3_frame_submit_host enqueues one
+ * frame of both passes on the context's own compute stream and its read-back into `light_host` on a copy stream, and
+ * returns at once with a ticket; rt3_frame_wait blocks until that frame (and every older one) is in host memory.  At most
+ * 3 frames are in flight: a 4th submit first waits for the oldest.  `light_host` (and prev_light_host) should be pinned
+ * (rt3_host_alloc or cudaHostRegister) or the copy degrades to a synchronous one; they must stay valid until the wait.
+ * Do not interleave with other pass calls on the same context without waiting for the outstanding tickets. */
+RT3_API rt3_status rt3_frame_submit_host(rt3_context*, const rt3_params*, const float* prev_light_host, float* light_host,
+                                         uint64_t* out_ticket);
+RT3_API rt3_status rt3_frame_wait(rt3_context*, uint64_t ticket);
+RT3_API rt3_status rt3_host_alloc(rt3_context*, size_t bytes, void** out);        /* pinned host memory */
+RT3_API rt3_status rt3_host_free(rt3_context*, void* p);
 RT3_API rt3_status rt3_trace_closest_host(rt3_context*, const rt3_ray* rays_host, uint64_t n, rt3_hit* out_host);
 RT3_API rt3_status rt3_trace_any_host(rt3_context*, const rt3_ray* rays_host, uint64_t n, uint32_t* out_bits_host);
 

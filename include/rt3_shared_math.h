@@ -714,6 +714,186 @@ RT3_HD vec2 sample_2d(const SceneView& s, uint32_t flags, uint32_t px, uint32_t 
     return u;
 }
 
+/* ---------------------------------------------------------------- brdf.slang: specular lobe ---
+ * shaders/include/brdf.slang:95-322 restated: Schlick Fresnel, height-correlated Smith masking, GGX NDF, VNDF sampling
+ * (Heitz 2018 via Falcor, USE_GGX_VNDF_SAMPLING = 1, USE_GGX_CORRELATED_MASKING = 1).  All quantities are in tangent
+ * space (z = normal) and "defined wrt the projected solid angle metric" (brdf.slang:30) exactly as in the reference.
+ * pow(x, 5) is DEFINED as ((x*x)*(x*x))*x; sin/cos(2 pi u) are the shared deterministic kernels. */
+static const float BRDF_SAMPLING_MIN_COS = 1e-5f;                                /* brdf.slang:8 */
+static const float RT3_PI = 3.14159265358979323846f;
+
+RT3_HD vec3 eval_fresnel_schlick(vec3 f0, vec3 f90, float cos_theta) {           /* brdf.slang:95-97 */
+    float x = max_(0.0f, 1.0f - cos_theta);
+    float x2 = x * x;
+    float x5 = (x2 * x2) * x;
+    return v3(f0.x + (f90.x - f0.x) * x5, f0.y + (f90.y - f0.y) * x5, f0.z + (f90.z - f0.z) * x5);
+}
+RT3_HD float g_smith_ggx_correlated(float ndotv, float ndotl, float a2) {        /* brdf.slang:108-113 */
+    float lambda_v = ndotl * sqrt_((-ndotv * a2 + ndotv) * ndotv + a2);
+    float lambda_l = ndotv * sqrt_((-ndotl * a2 + ndotl) * ndotl + a2);
+    return 2.0f * ndotl * ndotv / (lambda_v + lambda_l);
+}
+RT3_HD float g_smith_ggx1(float ndotv, float a2) {                               /* brdf.slang:115-118 */
+    float tan2_v = (1.0f - ndotv * ndotv) / (ndotv * ndotv);
+    return 2.0f / (1.0f + sqrt_(1.0f + a2 * tan2_v));
+}
+struct SmithShadowingMasking { float g, g_over_g1_wo; };
+RT3_HD SmithShadowingMasking smith_eval(float ndotv, float ndotl, float a2) {    /* brdf.slang:128-139 */
+    SmithShadowingMasking r;
+    r.g = g_smith_ggx_correlated(ndotv, ndotl, a2);
+    r.g_over_g1_wo = r.g / g_smith_ggx1(ndotv, a2);
+    return r;
+}
+RT3_HD float ggx_ndf(float a2, float cos_theta) {                                /* brdf.slang:147-150 */
+    float denom_sqrt = cos_theta * cos_theta * (a2 - 1.0f) + 1.0f;
+    return a2 / (RT3_PI * denom_sqrt * denom_sqrt);
+}
+RT3_HD float pdf_ggx_vn(float a2, vec3 wo, vec3 h) {                             /* brdf.slang:162-166 */
+    float g1 = g_smith_ggx1(wo.z, a2);
+    float d = ggx_ndf(a2, h.z);
+    return g1 * d * max_(0.0f, dot(wo, h)) / wo.z;
+}
+struct NdfSample { vec3 m; float pdf; };
+RT3_HD NdfSample sample_vndf(float alpha, vec3 wo, vec2 urand) {                 /* brdf.slang:186-218 */
+    float a2 = alpha * alpha;
+    vec3 Vh = normalize(v3(alpha * wo.x, alpha * wo.y, wo.z));
+    vec3 T1 = (Vh.z < 0.9999f) ? normalize(cross(v3(0.f, 0.f, 1.f), Vh)) : v3(1.f, 0.f, 0.f);
+    vec3 T2 = cross(Vh, T1);
+    float r = sqrt_(urand.x);
+    float sp, cp;
+    sincos_2pi(urand.y, sp, cp);
+    float t1 = r * cp;
+    float t2 = r * sp;
+    float sc = 0.5f * (1.0f + Vh.z);
+    t2 = (1.0f - sc) * sqrt_(max_(0.0f, 1.0f - t1 * t1)) + sc * t2;
+    float nz = sqrt_(max_(0.0f, 1.0f - t1 * t1 - t2 * t2));
+    vec3 Nh = v3(t1 * T1.x + t2 * T2.x + nz * Vh.x, t1 * T1.y + t2 * T2.y + nz * Vh.y, t1 * T1.z + t2 * T2.z + nz * Vh.z);
+    vec3 h = normalize(v3(alpha * Nh.x, alpha * Nh.y, max_(0.0f, Nh.z)));
+    NdfSample res;
+    res.m = h;
+    res.pdf = pdf_ggx_vn(a2, wo, h);
+    return res;
+}
+/* BrdfValue / BrdfSample of brdf.slang:14-50 */
+struct BrdfValue { vec3 value_over_pdf, value; float pdf; vec3 transmission_fraction; };
+struct BrdfSample { vec3 value_over_pdf, value; float pdf; vec3 transmission_fraction; vec3 wi; float approx_roughness; };
+RT3_HD BrdfSample brdf_sample_invalid() {                                        /* brdf.slang:36-44 */
+    BrdfSample r;
+    r.value_over_pdf = v3(0.f, 0.f, 0.f); r.value = v3(0.f, 0.f, 0.f); r.pdf = 0.0f; r.wi = v3(0.f, 0.f, -1.f);
+    r.transmission_fraction = v3(0.f, 0.f, 0.f); r.approx_roughness = 0.0f;
+    return r;
+}
+RT3_HD bool brdf_sample_is_valid(const BrdfSample& s) { return s.wi.z > 1e-6f; } /* brdf.slang:46-48 */
+RT3_HD vec3 reflect_(vec3 i, vec3 n) { float k = 2.0f * dot(i, n); return v3(i.x - k * n.x, i.y - k * n.y, i.z - k * n.z); }
+
+RT3_HD BrdfSample specular_sample(float roughness, vec3 albedo, vec3 wo, vec2 urand) {   /* SpecularBrdf::sample, brdf.slang:220-267 */
+    NdfSample ndf = sample_vndf(roughness, wo, urand);
+    vec3 wi = reflect_(v3(-wo.x, -wo.y, -wo.z), ndf.m);
+    if (ndf.m.z <= BRDF_SAMPLING_MIN_COS || wi.z <= BRDF_SAMPLING_MIN_COS || wo.z <= BRDF_SAMPLING_MIN_COS) return brdf_sample_invalid();
+    float jacobian = 1.0f / (4.0f * dot(wi, ndf.m));
+    vec3 fresnel = eval_fresnel_schlick(albedo, v3(1.f, 1.f, 1.f), dot(ndf.m, wi));
+    float a2 = roughness * roughness;
+    float cos_theta = ndf.m.z;
+    SmithShadowingMasking sm = smith_eval(wo.z, wi.z, a2);
+    BrdfSample res;
+    res.pdf = ndf.pdf * jacobian / wi.z;
+    res.wi = wi;
+    res.transmission_fraction = v3(1.0f - fresnel.x, 1.0f - fresnel.y, 1.0f - fresnel.z);
+    res.approx_roughness = roughness;
+    res.value_over_pdf = fresnel * sm.g_over_g1_wo;
+    float k = sm.g * ggx_ndf(a2, cos_theta) / (4.0f * wo.z * wi.z);
+    res.value = fresnel * k;
+    return res;
+}
+RT3_HD BrdfValue specular_evaluate(float roughness, vec3 albedo, vec3 wo, vec3 wi) {     /* SpecularBrdf::evaluate, brdf.slang:269-314 */
+    BrdfValue res;
+    res.value_over_pdf = v3(0.f, 0.f, 0.f); res.value = v3(0.f, 0.f, 0.f); res.pdf = 0.0f; res.transmission_fraction = v3(0.f, 0.f, 0.f);
+    if (wi.z <= 0.0f || wo.z <= 0.0f) return res;
+    float a2 = roughness * roughness;
+    vec3 m = normalize(wo + wi);
+    float cos_theta = m.z;
+    float pdf_h = pdf_ggx_vn(a2, wo, m);
+    float jacobian = 1.0f / (4.0f * dot(wi, m));
+    vec3 fresnel = eval_fresnel_schlick(albedo, v3(1.f, 1.f, 1.f), dot(m, wi));
+    SmithShadowingMasking sm = smith_eval(wo.z, wi.z, a2);
+    res.pdf = pdf_h * jacobian / wi.z;
+    res.transmission_fraction = v3(1.0f - fresnel.x, 1.0f - fresnel.y, 1.0f - fresnel.z);
+    res.value_over_pdf = fresnel * sm.g_over_g1_wo;
+    float k = sm.g * ggx_ndf(a2, cos_theta) / (4.0f * wo.z * wi.z);
+    res.value = fresnel * k;
+    return res;
+}
+RT3_HD vec3 specular_dominant_direction(vec3 n, vec3 v, float roughness) {       /* brdf.slang:318-322 */
+    vec3 r = reflect_(v3(-v.x, -v.y, -v.z), n);
+    float f = (1.0f - roughness) * (sqrt_(1.0f - roughness) + roughness);
+    return normalize(v3(n.x + (r.x - n.x) * f, n.y + (r.y - n.y) * f, n.z + (r.z - n.z) * f));
+}
+
+/* ---- layered material (RT3_FLAG_SPECULAR) -----------------------------------------------------------------------------
+ * The reference's path tracer samples DiffuseBrdf only (refrence_mode.slang:44-51); its brdf.slang also carries the
+ * SpecularBrdf above, and roughness / metalness already flow through hit_info and the G-buffer, but no shader in the tree
+ * combines the two lobes.  The combination is therefore DEFINED here (metalness workflow, one-sample lobe selection):
+ *   f0 = lerp(0.04, albedo, metalness)        specular reflectance at normal incidence (SpecularBrdf.albedo)
+ *   kd = albedo * (1 - metalness)             DiffuseBrdf.albedo
+ *   alpha = max(roughness, 0.001)             SpecularBrdf.roughness (GbufferData.roughness is already alpha:
+ *                                             gbuffer_helpers.slang:27,64 store its square root as "perceptual")
+ *   p_spec = lum(f0) / (lum(f0) + lum(kd)), 0 when the surface is seen from behind (wo.z <= MIN_COS)
+ * urand.x selects the lobe and is rescaled to [0,1) inside the chosen one; the path weight is the chosen lobe's
+ * value_over_pdf / p_lobe; an invalid specular sample (brdf.slang:226-228) ends the path. */
+struct LayeredMaterial {
+    onb t;
+    vec3 wo;            /* tangent-space direction towards the previous vertex */
+    vec3 f0, kd;
+    float alpha, p_spec;
+};
+RT3_HD vec3 world_to_onb(const onb& t, vec3 w) { return v3(dot(w, t.b1), dot(w, t.b2), dot(w, t.n)); }
+RT3_HD LayeredMaterial layered_setup(const GbufferData& surface, vec3 ray_d) {
+    LayeredMaterial m;
+    m.t = build_orthonormal_basis(surface.normal);
+    m.wo = world_to_onb(m.t, v3(-ray_d.x, -ray_d.y, -ray_d.z));
+    float mt = clamp_(surface.metalness, 0.0f, 1.0f);
+    m.f0 = v3(0.04f + (surface.albedo.x - 0.04f) * mt, 0.04f + (surface.albedo.y - 0.04f) * mt, 0.04f + (surface.albedo.z - 0.04f) * mt);
+    m.kd = surface.albedo * (1.0f - mt);
+    m.alpha = max_(surface.roughness, 0.001f);
+    float ls = luminance(m.f0), ld = luminance(m.kd);
+    m.p_spec = (m.wo.z > BRDF_SAMPLING_MIN_COS && (ls + ld) > 0.0f) ? ls / (ls + ld) : 0.0f;
+    return m;
+}
+/* BRDF value (projected-solid-angle convention: multiply by cos for the rendering equation) and solid-angle pdf of the
+ * lobe mixture for a tangent-space direction wi. */
+RT3_HD void layered_evaluate(const LayeredMaterial& m, vec3 wi, vec3& value, float& pdf_solid) {
+    value = v3(0.f, 0.f, 0.f); pdf_solid = 0.0f;
+    if (wi.z <= 0.0f) return;
+    const float inv_pi = 0.31830988618379067154f;
+    value = m.kd * inv_pi;
+    pdf_solid = (1.0f - m.p_spec) * (wi.z * inv_pi);
+    if (m.p_spec > 0.0f) {
+        BrdfValue sv = specular_evaluate(m.alpha, m.f0, m.wo, wi);
+        value = value + sv.value;
+        pdf_solid = pdf_solid + m.p_spec * (sv.pdf * wi.z);
+    }
+}
+struct LayeredSample { vec3 wi; vec3 weight; bool valid; bool specular; };
+RT3_HD LayeredSample layered_sample(const LayeredMaterial& m, vec2 urand) {
+    LayeredSample r;
+    r.valid = true;
+    if (urand.x < m.p_spec) {
+        vec2 u; u.x = min_(urand.x / m.p_spec, 0.99999994f); u.y = urand.y;
+        BrdfSample sp = specular_sample(m.alpha, m.f0, m.wo, u);
+        r.specular = true;
+        r.valid = brdf_sample_is_valid(sp);
+        r.wi = sp.wi;
+        r.weight = sp.value_over_pdf * (1.0f / m.p_spec);
+    } else {
+        float q = 1.0f - m.p_spec;
+        float ux = min_((urand.x - m.p_spec) / q, 0.99999994f);
+        r.specular = false;
+        r.wi = diffuse_sample_wi(ux, urand.y);
+        r.weight = m.kd * (1.0f / q);
+    }
+    return r;
+}
+
 /* ---------------------------------------------------------------- path tracing step ---------- */
 /* One bounce of shaders/old/refrence_mode.slang:42-51: sample the diffuse lobe at `surface`,
  * advance the ray to the hit point, gather emission, update throughput. */
@@ -728,6 +908,26 @@ RT3_HD PathVertexOut bounce_step(const GbufferData& surface, vec3 ray_o, vec3 ra
     radiance = radiance + ray_color * surface.emissive;
     ray_color = ray_color * surface.albedo;
     if (out_pdf) *out_pdf = wi.z * 0.31830988618379067154f;   /* cos(theta) / pi: solid-angle pdf of the cosine lobe */
+    return o;
+}
+
+/* RT3_FLAG_SPECULAR variant of bounce_step: same bookkeeping, layered material instead of the diffuse lobe.  Returns
+ * false in `alive` when the sampled lobe yields no direction (the path ends after its emission has been gathered). */
+RT3_HD PathVertexOut bounce_step_layered(const GbufferData& surface, vec3 ray_o, vec3 ray_d, float depth, vec2 urand, vec3& radiance,
+                                         vec3& ray_color, LayeredMaterial& m, bool& alive, float* out_pdf = nullptr) {
+    m = layered_setup(surface, ray_d);
+    LayeredSample ls = layered_sample(m, urand);
+    PathVertexOut o;
+    o.origin = v3(ray_o.x + depth * ray_d.x, ray_o.y + depth * ray_d.y, ray_o.z + depth * ray_d.z);
+    o.dir = onb_to_world(m.t, ls.wi);
+    radiance = radiance + ray_color * surface.emissive;
+    alive = ls.valid;
+    if (out_pdf) {
+        vec3 val; float pdf = 0.0f;
+        if (ls.valid) layered_evaluate(m, ls.wi, val, pdf);
+        *out_pdf = pdf;
+    }
+    ray_color = ls.valid ? ray_color * ls.weight : v3(0.f, 0.f, 0.f);
     return o;
 }
 
@@ -749,6 +949,23 @@ RT3_HD NeeSample nee_sample(const SceneView& s, const GbufferData& surface, vec3
         float w = pl / (pl + pb);
         float k = (cosl * 0.31830988618379067154f / pl) * w;
         r.contribution = throughput_after * (sample_environment(s, r.dir) * k);
+    }
+    return r;
+}
+/* Layered-material variant: `throughput_before` = ray_color BEFORE bounce_step_layered. */
+RT3_HD NeeSample nee_sample_layered(const SceneView& s, const LayeredMaterial& m, vec3 throughput_before, vec2 u) {
+    NeeSample r;
+    float pl;
+    r.dir = env_sample(s, u.x, u.y, pl);
+    vec3 wl = world_to_onb(m.t, r.dir);
+    r.valid = (pl > 0.0f) && (wl.z > 0.0f);
+    r.contribution = v3(0.f, 0.f, 0.f);
+    if (r.valid) {
+        vec3 f; float pb;
+        layered_evaluate(m, wl, f, pb);
+        float w = pl / (pl + pb);
+        float k = (wl.z / pl) * w;
+        r.contribution = throughput_before * (f * sample_environment(s, r.dir)) * k;
     }
     return r;
 }

@@ -63,6 +63,10 @@ def load():
         "rt3_trace_closest": (i32, [vp, vp, u64, vp, vp]),
         "rt3_trace_any": (i32, [vp, vp, u64, vp, vp]),
         "rt3_render_frame_host": (i32, [vp, vp, vp, vp, vp, vp]),
+        "rt3_frame_submit_host": (i32, [vp, vp, vp, vp, P(u64)]),
+        "rt3_frame_wait": (i32, [vp, u64]),
+        "rt3_host_alloc": (i32, [vp, C.c_size_t, P(vp)]),
+        "rt3_host_free": (i32, [vp, vp]),
         "rt3_trace_closest_host": (i32, [vp, vp, u64, vp]),
         "rt3_trace_any_host": (i32, [vp, vp, u64, vp]),
         "rt3_counters_read": (i32, [vp, P(Counters), i32]),

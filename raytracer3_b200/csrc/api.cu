@@ -210,6 +210,12 @@ rt3_status rt3_create(int cuda_device, rt3_context** out) {
         RT3_CUDA(c, cudaMemcpy(c->d_srgb_lut, lut, sizeof(lut), cudaMemcpyHostToDevice));
         ensure<unsigned long long>(c, c->d_counts, 64);
         RT3_CUDA(c, cudaMemset(c->d_counts.ptr, 0, 64 * 8));
+        RT3_CUDA(c, cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
+        RT3_CUDA(c, cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+        for (auto& fs : c->slots) {
+            RT3_CUDA(c, cudaEventCreateWithFlags(&fs.rendered, cudaEventDisableTiming));
+            RT3_CUDA(c, cudaEventCreateWithFlags(&fs.copied, cudaEventDisableTiming));
+        }
     });
     if (s != RT3_OK) { g_create_error = c->error; delete c; return s; }
     *out = c;
@@ -231,6 +237,13 @@ void rt3_destroy(rt3_context* c) {
                       &c->px_rng, &c->d_counts, &c->d_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();
+    for (auto& fs : c->slots) {
+        fs.gb.release(); fs.dp.release(); fs.lt.release(); fs.pv.release();
+        if (fs.rendered) cudaEventDestroy(fs.rendered);
+        if (fs.copied) cudaEventDestroy(fs.copied);
+    }
+    if (c->s_compute) cudaStreamDestroy(c->s_compute);
+    if (c->s_copy) cudaStreamDestroy(c->s_copy);
     for (int i = 0; i < 8; ++i) cudaEventDestroy(c->ev[i]);
     for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
     delete c;
@@ -444,6 +457,62 @@ rt3_status rt3_render_frame_host(rt3_context* c, const rt3_params* p, const floa
         if (opt_gbuffer_host) RT3_CUDA(c, cudaMemcpyAsync(opt_gbuffer_host, gb, 16 * px, cudaMemcpyDeviceToHost, st));
         RT3_CUDA(c, cudaStreamSynchronize(st));
     });
+}
+/* Frames in flight: render on the compute stream, read back on the copy stream, up to 3 frames deep. */
+rt3_status rt3_frame_submit_host(rt3_context* c, const rt3_params* p, const float* prev_light_host, float* light_host, uint64_t* out_ticket) {
+    return guarded(c, [&]() {
+        check_params(c, p); require_accel(c);
+        if (!light_host || !out_ticket) RT3_FAIL(c, RT3_ERR_INVALID, "light_host / out_ticket is NULL");
+        if (p->blendfactor < 1.0f && !prev_light_host) RT3_FAIL(c, RT3_ERR_INVALID, "prev_light_host is NULL with blendfactor < 1");
+        if (c->scene_dirty) refresh_scene_tables(c);
+        const uint32_t W = (uint32_t)p->window_size[0], H = (uint32_t)p->window_size[1];
+        const size_t px = (size_t)W * H;
+        rt3_rect full = {0, 0, W, H};
+        PixelMap m = single_rect_map(c, p, full);
+        const uint64_t ticket = c->next_ticket;
+        rt3_context::FrameSlot& fs = c->slots[ticket % 3];
+        if (fs.busy) { RT3_CUDA(c, cudaEventSynchronize(fs.copied)); fs.busy = false; }   /* the slot's previous frame (ticket - 3) must have left */
+        uint32_t* gb = ensure<uint32_t>(c, fs.gb, 4 * px);
+        float* dp = ensure<float>(c, fs.dp, px);
+        float* lt = ensure<float>(c, fs.lt, 4 * px);
+        float* pv = nullptr;
+        cudaStream_t st = c->s_compute;
+        if (p->blendfactor < 1.0f) {
+            pv = ensure<float>(c, fs.pv, 4 * px);
+            RT3_CUDA(c, cudaMemcpyAsync(pv, prev_light_host, 16 * px, cudaMemcpyHostToDevice, st));
+        }
+        RT3_CUDA(c, cudaMemsetAsync(lt, 0, 16 * px, st));
+        rt3_launch_gbuffer(c, *p, m, gb, dp, nullptr, nullptr, st);
+        rt3_launch_reference(c, *p, m, gb, dp, pv, lt, st);
+        RT3_CUDA(c, cudaEventRecord(fs.rendered, st));
+        RT3_CUDA(c, cudaStreamWaitEvent(c->s_copy, fs.rendered, 0));
+        RT3_CUDA(c, cudaMemcpyAsync(light_host, lt, 16 * px, cudaMemcpyDeviceToHost, c->s_copy));
+        RT3_CUDA(c, cudaEventRecord(fs.copied, c->s_copy));
+        fs.busy = true;
+        c->next_ticket = ticket + 1;
+        *out_ticket = ticket;
+    });
+}
+rt3_status rt3_frame_wait(rt3_context* c, uint64_t ticket) {
+    return guarded(c, [&]() {
+        if (ticket >= c->next_ticket) RT3_FAIL(c, RT3_ERR_INVALID, "ticket was never issued");
+        if (ticket + 3 < c->next_ticket) return;                    /* its slot has been reused: that frame completed long ago */
+        /* frames complete in submission order on both streams: waiting for `ticket` covers every older frame */
+        for (uint64_t t = (c->next_ticket > 3 ? c->next_ticket - 3 : 0); t <= ticket; ++t) {
+            rt3_context::FrameSlot& fs = c->slots[t % 3];
+            if (fs.busy) { RT3_CUDA(c, cudaEventSynchronize(fs.copied)); fs.busy = false; }
+        }
+    });
+}
+rt3_status rt3_host_alloc(rt3_context* c, size_t bytes, void** out) {
+    return guarded(c, [&]() {
+        if (!out) RT3_FAIL(c, RT3_ERR_INVALID, "out is NULL");
+        *out = nullptr;
+        RT3_CUDA(c, cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    });
+}
+rt3_status rt3_host_free(rt3_context* c, void* p) {
+    return guarded(c, [&]() { if (p) RT3_CUDA(c, cudaFreeHost(p)); });
 }
 rt3_status rt3_trace_closest_host(rt3_context* c, const rt3_ray* rays_host, uint64_t n, rt3_hit* out_host) {
     return guarded(c, [&]() {

@@ -106,6 +106,12 @@ struct rt3_context {
     DeviceCounters* d_counters = nullptr;
     cudaEvent_t ev[8];
 
+    /* frames in flight (rt3_frame_submit_host / rt3_frame_wait): FRAMES_IN_FLIGHT = 3 of the reference's swapchain.rs:8 */
+    struct FrameSlot { Scratch gb, dp, lt, pv; cudaEvent_t rendered = nullptr, copied = nullptr; bool busy = false; };
+    FrameSlot slots[3];
+    cudaStream_t s_compute = nullptr, s_copy = nullptr;
+    uint64_t next_ticket = 0;
+
     /* optional per-kernel timing of the traversal launches (rt3_profile_*): event pairs on the launch stream */
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_events;

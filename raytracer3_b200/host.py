@@ -379,6 +379,18 @@ class Renderer:
                                                         C.c_void_p(light_host), None, None))
 
 
+    def submit_frame_host(self, gconst, light_host, prev_light_host=None):
+        """Frames in flight (FRAMES_IN_FLIGHT = 3, swapchain.rs:8): enqueue one frame and its read-back, return a ticket."""
+        p = np.ascontiguousarray(gconst)
+        t = C.c_uint64(0)
+        self.ctx.check(self.ctx.L.rt3_frame_submit_host(self.ctx.h, ptr(p), None if prev_light_host is None else C.c_void_p(prev_light_host),
+                                                        C.c_void_p(light_host), C.byref(t)))
+        return t.value
+
+    def wait_frame(self, ticket):
+        self.ctx.check(self.ctx.L.rt3_frame_wait(self.ctx.h, ticket))
+
+
 class TiledRenderer:
     """Rank-local renderer for screen-tile sharding: this rank's tiles of a W x H frame are rendered
     into tile-major slabs; `gather` all-gathers the Light slabs over NCCL (torch.distributed) and un-tiles them."""

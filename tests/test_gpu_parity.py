@@ -160,6 +160,33 @@ def test_render_frame_host_and_counters(gpu_ctx):
     assert c.rays_secondary == cnt.rays_secondary and c.paths_escaped == cnt.paths_escaped and c.paths_started == cnt.paths_started
 
 
+def test_frames_in_flight_match_synchronous_frames(gpu_ctx):
+    """rt3_frame_submit_host / rt3_frame_wait (3 frames in flight, swapchain.rs:8) deliver the same bits as the synchronous call."""
+    import torch
+    sc = SCENES["cornell"]()
+    w, _ = _world(gpu_ctx, sc)
+    from raytracer3_b200.host import Renderer
+    W, H = 160, 96
+    r = Renderer(gpu_ctx, w, W, H)
+    cam = camera_for(sc, "cam0", W, H)
+    n = 7
+    ps = [make_params(cam, W, H, frame=10 + i, bounces=3, samples=1) for i in range(n)]
+    want = []
+    for p in ps:
+        o = np.zeros((H, W, 4), np.float32)
+        r.render_frame_host(p, o.ctypes.data)
+        want.append(o)
+    outs = [torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() for _ in range(n)]
+    tickets = [r.submit_frame_host(ps[i], outs[i].data_ptr()) for i in range(n)]     # the 4th submit waits for the 1st by itself
+    assert tickets == list(range(tickets[0], tickets[0] + n))
+    r.wait_frame(tickets[-1])                                                          # covers every older frame
+    for i in range(n):
+        assert (_bits(outs[i].numpy()) == _bits(want[i])).all(), f"frame {i} differs"
+    from raytracer3_b200 import _lib
+    with pytest.raises(_lib.Rt3Error):
+        r.wait_frame(tickets[-1] + 1)
+
+
 def test_errors_are_returned_not_raised_across_abi(gpu_ctx):
     from raytracer3_b200 import _lib
     from raytracer3_b200.host import RenderWorld
