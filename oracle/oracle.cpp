@@ -426,11 +426,17 @@ void orc_pass_reference(const orc_scene* s, const rt3_params* p, rt3_rect rc, co
                             break;
                         }
                         vec2 urand = sample_2d(sv, p->flags, x, y, p->frame, rng);     /* :43 */
-                        PathVertexOut nv = bounce_step(surface, ro, rd, hit_t, urand, radiance, ray_color, &pdf_brdf); /* :44-51 */
+                        const bool layered = (p->flags & RT3_FLAG_SPECULAR) != 0;         /* DiffuseBrdf + SpecularBrdf (brdf.slang:95-318) */
+                        LayeredMaterial lm = LayeredMaterial();
+                        bool lobe_ok = true;
+                        const vec3 thr_before = ray_color;
+                        PathVertexOut nv = layered ? bounce_step_layered(surface, ro, rd, hit_t, urand, radiance, ray_color, lm, lobe_ok, &pdf_brdf)
+                                                   : bounce_step(surface, ro, rd, hit_t, urand, radiance, ray_color, &pdf_brdf); /* :44-51 */
                         ro = nv.origin; rd = nv.dir;
+                        if (!lobe_ok) break;                                            /* invalid specular sample (brdf.slang:226-228): path ends */
                         if (nee_enabled(p->flags) && b != p->bounces - 1) {             /* next-event estimation (no reference counterpart) */
                             vec2 ul = sample_2d(sv, p->flags, x, y, p->frame, rng);
-                            NeeSample ns = nee_sample(sv, surface, ray_color, ul);
+                            NeeSample ns = layered ? nee_sample_layered(sv, lm, thr_before, ul) : nee_sample(sv, surface, ray_color, ul);
                             if (ns.valid) {
                                 shadow++;
                                 if (!any_bvh(*s, make_ray(ro, ns.dir, tmin, tmax))) radiance = radiance + ns.contribution;
@@ -522,5 +528,43 @@ void orc_sample_2d(const orc_scene* s, uint32_t flags, uint32_t px, uint32_t py,
 }
 void orc_agx(const float in3[3], float out3[3]) { vec3 c = agx_eotf(agx_look(agx(v3(in3)))); out3[0] = c.x; out3[1] = c.y; out3[2] = c.z; }
 float orc_contract_probe(float a, float b, float c) { return contract_probe(a, b, c); }
+/* SpecularBrdf::sample / ::evaluate (brdf.slang:220-314).  out12 = value_over_pdf[3], value[3], pdf, transmission[3], (sample only) wi... */
+int orc_specular_sample(float roughness, const float albedo[3], const float wo[3], float ux, float uy, float out14[14]) {
+    vec2 u; u.x = ux; u.y = uy;
+    BrdfSample r = specular_sample(roughness, v3(albedo), v3(wo), u);
+    const float o[14] = {r.value_over_pdf.x, r.value_over_pdf.y, r.value_over_pdf.z, r.value.x, r.value.y, r.value.z, r.pdf, r.transmission_fraction.x,
+                         r.transmission_fraction.y, r.transmission_fraction.z, r.wi.x, r.wi.y, r.wi.z, r.approx_roughness};
+    memcpy(out14, o, sizeof(o));
+    return brdf_sample_is_valid(r) ? 1 : 0;
+}
+void orc_specular_evaluate(float roughness, const float albedo[3], const float wo[3], const float wi[3], float out10[10]) {
+    BrdfValue r = specular_evaluate(roughness, v3(albedo), v3(wo), v3(wi));
+    const float o[10] = {r.value_over_pdf.x, r.value_over_pdf.y, r.value_over_pdf.z, r.value.x, r.value.y, r.value.z, r.pdf, r.transmission_fraction.x,
+                         r.transmission_fraction.y, r.transmission_fraction.z};
+    memcpy(out10, o, sizeof(o));
+}
+void orc_specular_dominant_direction(const float n[3], const float v[3], float roughness, float out3[3]) {
+    vec3 r = specular_dominant_direction(v3(n), v3(v), roughness); out3[0] = r.x; out3[1] = r.y; out3[2] = r.z;
+}
+/* Layered material (RT3_FLAG_SPECULAR): one sample.  out8 = world wi[3], weight[3], solid-angle pdf of the mixture, p_spec.  Returns valid | specular << 1. */
+int orc_layered_sample(const float albedo[3], const float normal[3], float roughness, float metalness, const float ray_d[3], float ux, float uy, float out8[8]) {
+    GbufferData g; g.albedo = v3(albedo); g.normal = v3(normal); g.roughness = roughness; g.metalness = metalness; g.emissive = v3(0.f, 0.f, 0.f);
+    LayeredMaterial m = layered_setup(g, v3(ray_d));
+    vec2 u; u.x = ux; u.y = uy;
+    LayeredSample ls = layered_sample(m, u);
+    vec3 w = onb_to_world(m.t, ls.wi), val; float pdf = 0.f;
+    if (ls.valid) layered_evaluate(m, ls.wi, val, pdf);
+    const float o[8] = {w.x, w.y, w.z, ls.weight.x, ls.weight.y, ls.weight.z, pdf, m.p_spec};
+    memcpy(out8, o, sizeof(o));
+    return (ls.valid ? 1 : 0) | (ls.specular ? 2 : 0);
+}
+/* Layered material evaluated for a world-space direction: out4 = BRDF value[3] (projected-solid-angle convention), solid-angle pdf. */
+void orc_layered_evaluate(const float albedo[3], const float normal[3], float roughness, float metalness, const float ray_d[3], const float wi_world[3], float out4[4]) {
+    GbufferData g; g.albedo = v3(albedo); g.normal = v3(normal); g.roughness = roughness; g.metalness = metalness; g.emissive = v3(0.f, 0.f, 0.f);
+    LayeredMaterial m = layered_setup(g, v3(ray_d));
+    vec3 val; float pdf;
+    layered_evaluate(m, world_to_onb(m.t, v3(wi_world)), val, pdf);
+    out4[0] = val.x; out4[1] = val.y; out4[2] = val.z; out4[3] = pdf;
+}
 
 }  // extern "C"

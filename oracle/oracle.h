@@ -78,6 +78,11 @@ float orc_vdc(uint32_t bits);
 void orc_sample_2d(const orc_scene*, uint32_t flags, uint32_t px, uint32_t py, uint32_t frame, uint32_t index, float out2[2]);
 void orc_agx(const float in3[3], float out3[3]);
 float orc_contract_probe(float a, float b, float c);
+int orc_specular_sample(float roughness, const float albedo[3], const float wo[3], float ux, float uy, float out14[14]);
+void orc_specular_evaluate(float roughness, const float albedo[3], const float wo[3], const float wi[3], float out10[10]);
+void orc_specular_dominant_direction(const float n[3], const float v[3], float roughness, float out3[3]);
+int orc_layered_sample(const float albedo[3], const float normal[3], float roughness, float metalness, const float ray_d[3], float ux, float uy, float out8[8]);
+void orc_layered_evaluate(const float albedo[3], const float normal[3], float roughness, float metalness, const float ray_d[3], const float wi_world[3], float out4[4]);
 
 #ifdef __cplusplus
 }

@@ -66,6 +66,9 @@ def lib():
             "orc_primary_ray": (None, [vp, u32, u32, vp]), "orc_ray_triangle": (C.c_int, [vp, vp, vp, vp, vp, vp]),
             "orc_r2": (None, [u32, vp]), "orc_vdc": (f32, [u32]), "orc_sample_2d": (None, [vp, u32, u32, u32, u32, u32, vp]),
             "orc_agx": (None, [vp, vp]), "orc_contract_probe": (f32, [f32, f32, f32]),
+            "orc_specular_sample": (C.c_int, [f32, vp, vp, f32, f32, vp]), "orc_specular_evaluate": (None, [f32, vp, vp, vp, vp]),
+            "orc_specular_dominant_direction": (None, [vp, vp, f32, vp]),
+            "orc_layered_sample": (C.c_int, [vp, vp, f32, f32, vp, f32, f32, vp]), "orc_layered_evaluate": (None, [vp, vp, f32, f32, vp, vp, vp]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)

@@ -84,7 +84,9 @@ __device__ __forceinline__ void store_ray(rt3_ray* q, uint32_t pos, vec3 o, vec3
     p[1] = make_float4(d.x, d.y, d.z, tmax);
 }
 
-/* refrence_mode.slang:18-34 + bounce 0 of the loop at :36-51 (the surface comes from the G-buffer). */
+/* refrence_mode.slang:18-34 + bounce 0 of the loop at :36-51 (the surface comes from the G-buffer).
+ * LAYERED = RT3_FLAG_SPECULAR: DiffuseBrdf + SpecularBrdf (brdf.slang:95-318) instead of DiffuseBrdf only. */
+template <bool LAYERED>
 __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_params p, PixelMap m, const uint32_t* __restrict__ gbuffer,
                                                            const float* __restrict__ depth, float4* __restrict__ px_radiance, uint32_t* __restrict__ px_rng,
                                                            int first_sample, rt3_ray* __restrict__ q_rays, float4* __restrict__ q_thr, uint32_t* q_count,
@@ -116,12 +118,16 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_para
                     rt3_ray pr = setup_primary_ray(x, y, p);                           /* :30 */
                     vec3 ray_color = v3(1.f, 1.f, 1.f);
                     vec2 urand = sample_2d(s, p.flags, x, y, p.frame, rng);            /* :43 */
-                    PathVertexOut nv = bounce_step(surface, v3(pr.o), v3(pr.d), gdepth, urand, radiance, ray_color, &pdf_brdf);   /* :44-51 */
+                    LayeredMaterial lm;
+                    bool lobe_ok = true;
+                    const vec3 thr_before = ray_color;
+                    PathVertexOut nv = LAYERED ? bounce_step_layered(surface, v3(pr.o), v3(pr.d), gdepth, urand, radiance, ray_color, lm, lobe_ok, &pdf_brdf)
+                                               : bounce_step(surface, v3(pr.o), v3(pr.d), gdepth, urand, radiance, ray_color, &pdf_brdf);   /* :44-51 */
                     o = nv.origin; d = nv.dir; thr = ray_color;
-                    alive = p.bounces > 1;                                             /* :53 */
+                    alive = lobe_ok && p.bounces > 1;                                  /* :53 */
                     if (nee && alive) {
                         vec2 ul = sample_2d(s, p.flags, x, y, p.frame, rng);
-                        NeeSample ns = nee_sample(s, surface, ray_color, ul);
+                        NeeSample ns = LAYERED ? nee_sample_layered(s, lm, thr_before, ul) : nee_sample(s, surface, ray_color, ul);
                         shadow = ns.valid; sdir = ns.dir; scon = ns.contribution;
                     }
                 }
@@ -153,6 +159,7 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_para
 }
 
 /* Loop iteration b >= 1 of refrence_mode.slang:36-57 for every path whose ray was traced at b-1. */
+template <bool LAYERED>
 __global__ void __launch_bounds__(PASS_THREADS) k_ref_shade(SceneView s, rt3_params p, PixelMap m, uint32_t b, const rt3_ray* __restrict__ rays_in,
                                                             const rt3_hit* __restrict__ hits, const float4* __restrict__ thr_in,
                                                             const uint32_t* __restrict__ count_in, rt3_ray* __restrict__ rays_out,
@@ -193,12 +200,16 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_shade(SceneView s, rt3_par
                 RandomSamplerState rng = rng_init(x, y, p.frame);
                 rng.index = px_rng[idx];
                 vec2 urand = sample_2d(s, p.flags, x, y, p.frame, rng);               /* :43 */
-                PathVertexOut nv = bounce_step(surface, ro, rd, h4.x, urand, radiance, ray_color, &pdf_brdf);   /* :44-51 */
+                LayeredMaterial lm;
+                bool lobe_ok = true;
+                const vec3 thr_before = ray_color;
+                PathVertexOut nv = LAYERED ? bounce_step_layered(surface, ro, rd, h4.x, urand, radiance, ray_color, lm, lobe_ok, &pdf_brdf)
+                                           : bounce_step(surface, ro, rd, h4.x, urand, radiance, ray_color, &pdf_brdf);   /* :44-51 */
                 o = nv.origin; d = nv.dir; thr = ray_color;
-                alive = (b != p.bounces - 1);                                          /* :53 */
+                alive = lobe_ok && (b != p.bounces - 1);                               /* :53 */
                 if (nee && alive) {
                     vec2 ul = sample_2d(s, p.flags, x, y, p.frame, rng);
-                    NeeSample ns = nee_sample(s, surface, ray_color, ul);
+                    NeeSample ns = LAYERED ? nee_sample_layered(s, lm, thr_before, ul) : nee_sample(s, surface, ray_color, ul);
                     shadow = ns.valid; sdir = ns.dir; scon = ns.contribution;
                 }
                 px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
@@ -295,6 +306,7 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
     if (!m.work) return;
     const size_t W = m.work;
     const bool nee = nee_enabled(p.flags);
+    const bool layered = (p.flags & RT3_FLAG_SPECULAR) != 0;
     rt3_ray* q_rays[2] = {ensure<rt3_ray>(c, c->q_rays[0], W), ensure<rt3_ray>(c, c->q_rays[1], W)};
     float4* q_thr[2] = {ensure<float4>(c, c->q_thr[0], W), ensure<float4>(c, c->q_thr[1], W)};
     rt3_hit* q_hits = ensure<rt3_hit>(c, c->q_hits, W);
@@ -317,8 +329,12 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
     for (uint32_t sidx = 0; sidx < p.samples; ++sidx) {
         RT3_CUDA(c, cudaMemsetAsync(counts, 0, 12, st));
         nq.pdf_in = nullptr; nq.pdf_out = q_pdf[0];
-        RT3_LAUNCH(c, k_ref_init, grid, PASS_THREADS, 0, st, c->view, p, m, gbuffer, depth, px_radiance, px_rng, sidx == 0 ? 1 : 0, q_rays[0], q_thr[0], counts,
-                   nq, c->d_counters);
+        if (layered)
+            RT3_LAUNCH(c, k_ref_init<true>, grid, PASS_THREADS, 0, st, c->view, p, m, gbuffer, depth, px_radiance, px_rng, sidx == 0 ? 1 : 0, q_rays[0], q_thr[0],
+                       counts, nq, c->d_counters);
+        else
+            RT3_LAUNCH(c, k_ref_init<false>, grid, PASS_THREADS, 0, st, c->view, p, m, gbuffer, depth, px_radiance, px_rng, sidx == 0 ? 1 : 0, q_rays[0], q_thr[0],
+                       counts, nq, c->d_counters);
         if (nee && p.bounces > 1) resolve_shadows();
         int cur = 0;
         for (uint32_t b = 1; b < p.bounces; ++b) {
@@ -326,8 +342,12 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
             RT3_CUDA(c, cudaMemsetAsync(counts + (1 - cur), 0, 4, st));
             if (nee) RT3_CUDA(c, cudaMemsetAsync(counts + 2, 0, 4, st));
             nq.pdf_in = q_pdf[cur]; nq.pdf_out = q_pdf[1 - cur];
-            RT3_LAUNCH(c, k_ref_shade, grid, PASS_THREADS, 0, st, c->view, p, m, b, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur], q_thr[1 - cur],
-                       counts + (1 - cur), px_radiance, px_rng, nq, c->d_counters);
+            if (layered)
+                RT3_LAUNCH(c, k_ref_shade<true>, grid, PASS_THREADS, 0, st, c->view, p, m, b, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur],
+                           q_thr[1 - cur], counts + (1 - cur), px_radiance, px_rng, nq, c->d_counters);
+            else
+                RT3_LAUNCH(c, k_ref_shade<false>, grid, PASS_THREADS, 0, st, c->view, p, m, b, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur],
+                           q_thr[1 - cur], counts + (1 - cur), px_radiance, px_rng, nq, c->d_counters);
             if (nee && b != p.bounces - 1) resolve_shadows();
             cur = 1 - cur;
         }

@@ -246,6 +246,19 @@ def cornell_box(light_emission=1.4):
     return _scene(mb, cams, name="cornell_box")
 
 
+def metal_cornell_box():
+    """Cornell box with glossy / metallic materials: exercises RT3_FLAG_SPECULAR (brdf.slang:95-318)."""
+    sc = cornell_box()
+    g = sc["geometries"]
+    g["metallic"][:] = 0.0
+    g["roughness"][:] = 0.6
+    g["metallic"][-2:] = 1.0          # the two boxes: polished metal
+    g["roughness"][-2:] = 0.15
+    g["roughness"][0] = 0.25          # first wall: glossy dielectric
+    sc["name"] = "metal_cornell"
+    return sc
+
+
 def furnace_box(albedo=0.5, emission=0.25 / 12.0):
     """Closed cube, uniform albedo rho and emission e (x12 in hit_logic.slang:36): every path vertex sees
     the same surface, so radiance after B bounces is exactly e*12 * sum_{k<B} rho^k."""

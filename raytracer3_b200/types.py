@@ -56,6 +56,7 @@ BACKGROUND_DEPTH = np.float32(100000.0)  # shaders/include/datatypes.slang:3
 FLAG_ENV = 1
 FLAG_BLUENOISE = 2
 FLAG_NEE = 4
+FLAG_SPECULAR = 8
 
 IDENTITY_3X4 = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], dtype=np.float32)
 

@@ -12,7 +12,7 @@ sys.path.insert(0, ROOT)
 from oracle.oracle_py import OracleScene, lib  # noqa: E402
 from raytracer3_b200 import scenes  # noqa: E402
 from raytracer3_b200.camera import camera_for, make_params  # noqa: E402
-from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV  # noqa: E402
+from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, FLAG_NEE, FLAG_SPECULAR  # noqa: E402
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -20,6 +20,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 def case(name):
     if name == "cornell":
         return scenes.cornell_box(), 0, (64, 40), dict(frame=3, bounces=4, samples=2)
+    if name == "metal":      # layered diffuse + specular material with environment NEE (RT3_FLAG_SPECULAR | NEE | ENV)
+        sc = scenes.metal_cornell_box()
+        sc["environment"] = scenes.analytic_sky(64, 32)
+        return sc, FLAG_ENV | FLAG_NEE | FLAG_SPECULAR, (64, 40), dict(frame=5, bounces=4, samples=2)
     sc = scenes.synthetic_atrium(0.01)
     sc["environment"] = scenes.analytic_sky(64, 32)
     sc["bluenoise"] = scenes.blue_noise_tile(32, seed=7, iters=3)
@@ -72,8 +76,10 @@ def kat_tables():
 
 
 if __name__ == "__main__":
-    for name in ("cornell", "atrium"):
+    only = sys.argv[1:]          # optional: names to (re)generate; the other fixtures stay frozen
+    for name in (only or ("cornell", "atrium", "metal")):
         _, _, out = render(name)
         np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
-    np.savez_compressed(os.path.join(HERE, "kat.npz"), **kat_tables())
+    if not only:
+        np.savez_compressed(os.path.join(HERE, "kat.npz"), **kat_tables())
     print("golden written")

@@ -14,7 +14,7 @@ def _bits(a):
     return np.ascontiguousarray(a).view(np.uint8)
 
 
-@pytest.mark.parametrize("name", ["cornell", "atrium"])
+@pytest.mark.parametrize("name", ["cornell", "atrium", "metal"])
 def test_oracle_reproduces_golden(name):
     g = np.load(os.path.join(HERE, "golden", f"{name}.npz"))
     sc0 = make_golden.case(name)[0]
@@ -32,7 +32,7 @@ def test_kat_tables():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["cornell", "atrium"])
+@pytest.mark.parametrize("name", ["cornell", "atrium", "metal"])
 def test_gpu_reproduces_golden(gpu_ctx, name):
     """The CUDA path against the committed fixtures (no oracle involved at run time)."""
     from raytracer3_b200.camera import camera_for, make_params

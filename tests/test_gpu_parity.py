@@ -10,7 +10,7 @@ import pytest
 
 from raytracer3_b200 import scenes
 from raytracer3_b200.camera import camera_for, make_params
-from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, FLAG_NEE, HIT, MISS, RAY
+from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, FLAG_NEE, FLAG_SPECULAR, HIT, MISS, RAY
 
 pytestmark = pytest.mark.gpu
 
@@ -37,6 +37,7 @@ SCENES = {
     "cornell": lambda: scenes.cornell_box(),
     "soup": lambda: scenes.random_soup(4000, seed=5),
     "atrium_small": lambda: scenes.synthetic_atrium(0.03, environment=False),
+    "metal_cornell": lambda: scenes.metal_cornell_box(),
 }
 
 
@@ -109,6 +110,9 @@ def test_gbuffer_pass_bit_exact(gpu_ctx, name, wh):
     ("cornell", 0, 4, 3), ("cornell", 0, 1, 1), ("cornell", 0, 2, 2),
     ("atrium_small", 0, 4, 2), ("atrium_small", FLAG_ENV, 4, 2), ("atrium_small", FLAG_ENV | FLAG_BLUENOISE, 4, 2),
     ("atrium_small", FLAG_ENV | FLAG_NEE, 4, 2), ("atrium_small", FLAG_ENV | FLAG_BLUENOISE | FLAG_NEE, 3, 1), ("cornell", FLAG_ENV | FLAG_NEE, 2, 2),
+    # RT3_FLAG_SPECULAR: DiffuseBrdf + SpecularBrdf (brdf.slang:95-318) layered by metalness
+    ("metal_cornell", FLAG_SPECULAR, 4, 2), ("metal_cornell", FLAG_ENV | FLAG_NEE | FLAG_SPECULAR, 3, 2),
+    ("atrium_small", FLAG_ENV | FLAG_BLUENOISE | FLAG_SPECULAR, 4, 1), ("atrium_small", FLAG_ENV | FLAG_BLUENOISE | FLAG_NEE | FLAG_SPECULAR, 4, 1),
 ])
 def test_reference_pass_matches_oracle(gpu_ctx, name, flags, bounces, samples):
     from raytracer3_b200.host import Renderer
