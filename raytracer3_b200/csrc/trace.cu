@@ -75,6 +75,13 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
  * queues); here a lane whose ray terminates writes its result and, once fewer than KEEP lanes of the warp are still
  * busy, the idle lanes pull new rays from the global queue with one warp-aggregated atomic.
  */
+/* Optional: the first RT3_SMEM_STACK traversal-stack entries of every thread in shared memory ([entry][thread]: conflict-free,
+ * two wavefronts per warp access), deeper entries in thread-local memory.  Local-memory stack traffic is 16 % of the kernel's L1
+ * sectors (profiles/r1d_trace_summary.txt), but the kernel is bound by the ALU pipe, not by L1: measured on B200 (1080p 4-bounce)
+ * depth 0 / 4 / 8 / 12 = 0.539 / 0.548 / 0.549 / 0.550 ms per launch, so the default keeps the stack in local memory. */
+#ifndef RT3_SMEM_STACK
+#define RT3_SMEM_STACK 0
+#endif
 template <bool ANY, int KEEP, int TRIS>
 __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
                                                              const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
@@ -87,7 +94,12 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
     uint64_t my_index = 0;
     rt3_hit h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
     uint32_t ng_base = 0, ng_hits = 0, tg_base = 0, tg_hits = 0;
+#if RT3_SMEM_STACK > 0
+    __shared__ uint2 s_stack[RT3_SMEM_STACK][TRACE_THREADS];
+    uint32_t stack_base[RT3_MAX_STACK - RT3_SMEM_STACK], stack_hits[RT3_MAX_STACK - RT3_SMEM_STACK];
+#else
     uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
+#endif
     int sp = 0;
     bool active = false, exhausted = false;
     r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.idx = r.idy = r.idz = r.tmin = 0.f; r.octinv4 = 0; r.magic = magic;
@@ -125,7 +137,15 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                 const int bit = bfind32(ng_hits);
                 const uint32_t imask = ng_hits & 0xFFu;
                 ng_hits &= ~(1u << bit);
-                if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
+                if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) {
+#if RT3_SMEM_STACK > 0
+                    if (sp < RT3_SMEM_STACK) s_stack[sp][threadIdx.x] = make_uint2(ng_base, ng_hits);
+                    else { stack_base[sp - RT3_SMEM_STACK] = ng_base; stack_hits[sp - RT3_SMEM_STACK] = ng_hits; }
+#else
+                    stack_base[sp] = ng_base; stack_hits[sp] = ng_hits;
+#endif
+                    sp++;
+                }
                 const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
                 const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
                 const WideNode* nd = nodes + (ng_base + rel);
@@ -158,7 +178,15 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                     if (ANY) { if (found_any) atomicOr(bits + (my_index >> 5), 1u << (my_index & 31u)); }
                     else __stcs((float4*)(hits + my_index), make_float4(h.t, h.u, h.v, __uint_as_float(h.prim)));
                     active = false;
-                } else { sp--; ng_base = stack_base[sp]; ng_hits = stack_hits[sp]; }
+                } else {
+                    sp--;
+#if RT3_SMEM_STACK > 0
+                    if (sp < RT3_SMEM_STACK) { const uint2 e = s_stack[sp][threadIdx.x]; ng_base = e.x; ng_hits = e.y; }
+                    else { ng_base = stack_base[sp - RT3_SMEM_STACK]; ng_hits = stack_hits[sp - RT3_SMEM_STACK]; }
+#else
+                    ng_base = stack_base[sp]; ng_hits = stack_hits[sp];
+#endif
+                }
             }
         } while (__popc(__ballot_sync(0xFFFFFFFFu, active)) >= keep);
     }
