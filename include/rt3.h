@@ -106,7 +106,10 @@ typedef struct { float t, u, v; uint32_t prim; } rt3_hit;           /* 16 B; pri
 #define RT3_MISS 0xFFFFFFFFu
 #define RT3_BACKGROUND_DEPTH 100000.0f                              /* datatypes.slang:3 */
 
-enum { RT3_BUILD_FAST_TRACE = 1u, RT3_BUILD_FAST_BUILD = 2u };
+/* RT3_BUILD_TWO_LEVEL: one bottom-level tree per distinct mesh (= distinct geometry range of rt3_scene_push_instance) and a
+ * top-level tree over the instances — the BLAS / TLAS split of VK_KHR_acceleration_structure (raytracing.rs:88-148 builds
+ * either level).  Default: instances are flattened into one world-space tree.  Hits are bit-identical in both modes. */
+enum { RT3_BUILD_FAST_TRACE = 1u, RT3_BUILD_FAST_BUILD = 2u, RT3_BUILD_TWO_LEVEL = 4u };
 
 typedef struct {
     double   ms_flatten, ms_morton, ms_sort, ms_hierarchy, ms_refit, ms_collapse, ms_total;

@@ -233,7 +233,7 @@ void rt3_destroy(rt3_context* c) {
     if (c->d_srgb_lut) cudaFree(c->d_srgb_lut);
     if (c->d_counters) cudaFree(c->d_counters);
     Scratch* all[] = {&c->d_geometries, &c->d_seg_first, &c->d_seg_geo, &c->d_seg_inst, &c->d_inst_xform, &c->d_tex_ptr, &c->d_tex_dim, &c->bvh_nodes,
-                      &c->bvh_tris, &c->q_rays[0], &c->q_rays[1], &c->q_hits, &c->q_thr[0], &c->q_thr[1], &c->q_pix[0], &c->q_pix[1], &c->q_pdf[0], &c->q_pdf[1], &c->q_srays, &c->q_scontrib, &c->q_sbits, &c->px_radiance,
+                      &c->bvh_tris, &c->d_insts, &c->q_rays[0], &c->q_rays[1], &c->q_hits, &c->q_thr[0], &c->q_thr[1], &c->q_pix[0], &c->q_pix[1], &c->q_pdf[0], &c->q_pdf[1], &c->q_srays, &c->q_scontrib, &c->q_sbits, &c->px_radiance,
                       &c->px_rng, &c->d_counts, &c->d_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();
@@ -592,7 +592,7 @@ rt3_status rt3_profile_read(rt3_context* c, double* trace_ms, uint64_t* trace_la
 rt3_status rt3_accel_download(rt3_context* c, void* nodes_host, size_t nodes_bytes, void* tris_host, size_t tris_bytes) {
     return guarded(c, [&]() {
         require_accel(c);
-        if (nodes_bytes > (size_t)c->n_wide_nodes * sizeof(rt3b::WideNode) || tris_bytes > (size_t)c->n_triangles * sizeof(rt3b::Tri48))
+        if (nodes_bytes > (size_t)c->n_wide_nodes * sizeof(rt3b::WideNode) || tris_bytes > (size_t)c->n_leaf_records * sizeof(rt3b::Tri48))
             RT3_FAIL(c, RT3_ERR_INVALID, "download larger than the acceleration structure");
         RT3_CUDA(c, cudaDeviceSynchronize());
         if (nodes_bytes) RT3_CUDA(c, cudaMemcpy(nodes_host, c->bvh_nodes.ptr, nodes_bytes, cudaMemcpyDeviceToHost));

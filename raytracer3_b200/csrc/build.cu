@@ -67,11 +67,49 @@ __global__ void __launch_bounds__(256) k_flatten(rt3m::SceneView s, uint32_t n, 
     }
 }
 
-__global__ void __launch_bounds__(256) k_morton(const Tri48* tris, uint32_t n, float3 lo, float3 inv_ext, uint64_t* keys, uint32_t* vals) {
+/* Bottom level of the two-level build: the triangles of one mesh (segments [seg0, ...) of its first instance, global ids
+ * [prim0, prim0 + n)) in OBJECT space — geometry transform applied, instance transform not — stored as VERTICES with the
+ * mesh-local id (REC_TRI_VERTS).  The vertex arithmetic is that of rt3m::world_triangle up to the instance transform. */
+__global__ void __launch_bounds__(256) k_flatten_object(rt3m::SceneView s, uint32_t prim0, uint32_t n, Tri48* tris, int* bounds) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+    if (i < n) {
+        const uint32_t prim = prim0 + i;
+        const uint32_t seg = rt3m::find_segment(s, prim);
+        const rt3_geometry_info& g = s.geometries[s.seg_geometry[seg]];
+        const uint32_t io = g.index_offset + 3u * (prim - s.seg_first_prim[seg]);
+        const uint32_t i0 = g.vertex_offset + s.indices[io], i1 = g.vertex_offset + s.indices[io + 1], i2 = g.vertex_offset + s.indices[io + 2];
+        rt3m::vec3 a = rt3m::v3(s.vertices[i0].p), b = rt3m::v3(s.vertices[i1].p), c = rt3m::v3(s.vertices[i2].p);
+        if (!rt3m::xform_is_identity(g.xform)) { a = rt3m::xform_point(g.xform, a); b = rt3m::xform_point(g.xform, b); c = rt3m::xform_point(g.xform, c); }
+        float4* o = (float4*)(tris + i);
+        o[0] = make_float4(a.x, a.y, a.z, __uint_as_float(i));
+        o[1] = make_float4(b.x, b.y, b.z, 0.f);
+        o[2] = make_float4(c.x, c.y, c.z, 0.f);
+        lo[0] = fminf(a.x, fminf(b.x, c.x)); hi[0] = fmaxf(a.x, fmaxf(b.x, c.x));
+        lo[1] = fminf(a.y, fminf(b.y, c.y)); hi[1] = fmaxf(a.y, fmaxf(b.y, c.y));
+        lo[2] = fminf(a.z, fminf(b.z, c.z)); hi[2] = fmaxf(a.z, fmaxf(b.z, c.z));
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        for (int off = 16; off; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xFFFFFFFFu, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xFFFFFFFFu, hi[k], off));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(bounds + k, float_to_ordered(lo[k]));
+            atomicMax(bounds + 3 + k, float_to_ordered(hi[k]));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_morton(const Tri48* tris, uint32_t n, int kind, float3 lo, float3 inv_ext, uint64_t* keys, uint32_t* vals) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float l[3], h[3];
-    tri_bounds(tris[i], 0.f, l, h);
+    tri_bounds(tris[i], 0.f, l, h, kind);
     float cx = (0.5f * (l[0] + h[0]) - lo.x) * inv_ext.x, cy = (0.5f * (l[1] + h[1]) - lo.y) * inv_ext.y, cz = (0.5f * (l[2] + h[2]) - lo.z) * inv_ext.z;
     keys[i] = morton63(cx, cy, cz);
     vals[i] = i;
@@ -169,12 +207,12 @@ __global__ void __launch_bounds__(256) k_lbvh_hierarchy(const uint64_t* keys, in
     if (i < n - 1) lbvh_build_node(keys, n, i, nodes, parent);
 }
 
-__global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_t n, float pad, Bvh2Node* nodes, const uint32_t* parent, uint32_t* flags,
-                                               uint32_t* counts) {
+__global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_t n, int kind, float pad, Bvh2Node* nodes, const uint32_t* parent,
+                                               uint32_t* flags, uint32_t* counts) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     Bvh2Node leaf;
-    tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi);
+    tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi, kind);
     leaf.left = leaf.right = 0;
     nodes[n - 1 + k] = leaf;
     uint32_t cur = parent[n - 1 + k];
@@ -226,45 +264,27 @@ struct StageTimer {
 
 }  // namespace
 
-void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out) {
-    (void)flags;
-    rt3_build_stats bs;
-    memset(&bs, 0, sizeof(bs));
-    const uint32_t n = c->n_triangles;
-    bs.triangles = n;
-    StageTimer tm(c, st);
-    cudaEvent_t total_a = c->ev[2], total_b = c->ev[3];
-    cudaEventRecord(total_a, st);
+/* One wide BVH over `n` 48-byte leaf records (Morton -> sort -> LBVH -> refit -> collapse).  Nodes go into `wide`: the root at
+ * root_index, the rest from first_free_node on; leaf records are copied in leaf order into out_recs from first_free_rec on.
+ * `recs` (pool memory, n records) is consumed.  Stage times are ADDED to bs. */
+struct WideBuild {
+    PoolBuf* recs; uint32_t n; int kind; float pad; float lo[3], hi[3];
+    WideNode* wide; uint32_t root_index, first_free_node;
+    Tri48* out_recs; uint32_t first_free_rec;
+    uint32_t nodes_end = 0, recs_end = 0, levels = 0; float sah_nodes = 0.f, sah_recs = 0.f;   /* results */
+};
 
-    Tri48* out_tris = ensure<Tri48>(c, c->bvh_tris, n ? n : 1);
-    if (n == 0) {
-        WideNode* nodes = ensure<WideNode>(c, c->bvh_nodes, 1);
-        RT3_LAUNCH(c, k_empty_root, 1, 32, 0, st, nodes);
-        RT3_CUDA(c, cudaStreamSynchronize(st));
-        c->n_wide_nodes = 1; bs.wide_nodes = 1; bs.node_bytes = sizeof(WideNode);
-        c->accel_valid = true; c->last_build = bs;
-        if (out) *out = bs;
-        return;
-    }
-    PoolBuf s_tris, s_sorted, s_keys[2], s_vals[2], s_hist, s_nodes2, s_parent, s_flags, s_counts, s_items[2], s_misc;
+static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build_stats& bs, int* d_misc) {
+    const uint32_t n = io.n;
+    StageTimer tm(c, st);
+    PoolBuf s_sorted, s_keys[2], s_vals[2], s_hist, s_nodes2, s_parent, s_flags, s_counts, s_items[2];
     auto cleanup = [&]() {
-        s_tris.release(); s_sorted.release(); s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release();
-        s_nodes2.release(); s_parent.release(); s_flags.release(); s_counts.release(); s_items[0].release(); s_items[1].release(); s_misc.release();
+        io.recs->release(); s_sorted.release(); s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release();
+        s_nodes2.release(); s_parent.release(); s_flags.release(); s_counts.release(); s_items[0].release(); s_items[1].release();
     };
     try {
-        /* flatten */
-        Tri48* tris = palloc<Tri48>(c, s_tris, n, st);
-        int* d_bounds = (int*)palloc<uint32_t>(c, s_misc, 16, st);   /* [0..5] bounds, [8] node ctr, [9] tri ctr, [10] queue ctr, [12],[13] sah */
-        tm.begin();
-        RT3_LAUNCH(c, k_init_bounds, 1, 32, 0, st, d_bounds);
-        RT3_LAUNCH(c, k_flatten, div_up(n, 256), 256, 0, st, c->view, n, tris, d_bounds);
-        int hb[6];
-        RT3_CUDA(c, cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, st));
-        bs.ms_flatten = tm.end();
-        float lo[3], hi[3];
-        for (int k = 0; k < 3; ++k) { lo[k] = ordered_to_float(hb[k]); hi[k] = ordered_to_float(hb[3 + k]); bs.scene_lo[k] = lo[k]; bs.scene_hi[k] = hi[k]; }
-        float ext = fmaxf(hi[0] - lo[0], fmaxf(hi[1] - lo[1], hi[2] - lo[2]));
-        const float pad = ext * (1.0f / 65536.0f);
+        const Tri48* tris = (const Tri48*)io.recs->ptr;
+        const float* lo = io.lo; const float* hi = io.hi;
         /* morton */
         uint64_t* keys0 = palloc<uint64_t>(c, s_keys[0], n, st);
         uint64_t* keys1 = palloc<uint64_t>(c, s_keys[1], n, st);
@@ -274,8 +294,8 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         float3 flo = make_float3(lo[0], lo[1], lo[2]);
         float3 inv = make_float3(hi[0] > lo[0] ? 1.0f / (hi[0] - lo[0]) : 0.f, hi[1] > lo[1] ? 1.0f / (hi[1] - lo[1]) : 0.f,
                                  hi[2] > lo[2] ? 1.0f / (hi[2] - lo[2]) : 0.f);
-        RT3_LAUNCH(c, k_morton, div_up(n, 256), 256, 0, st, tris, n, flo, inv, keys0, vals0);
-        bs.ms_morton = tm.end();
+        RT3_LAUNCH(c, k_morton, div_up(n, 256), 256, 0, st, tris, n, io.kind, flo, inv, keys0, vals0);
+        bs.ms_morton += tm.end();
         /* sort */
         const uint32_t nblocks = div_up(n, RADIX_TILE);
         uint32_t* hist = palloc<uint32_t>(c, s_hist, 256 * (size_t)nblocks, st);
@@ -289,8 +309,8 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         }
         Tri48* sorted = palloc<Tri48>(c, s_sorted, n, st);
         RT3_LAUNCH(c, k_gather_sorted, div_up(n, 256), 256, 0, st, tris, vals0, n, sorted);
-        bs.ms_sort = tm.end();
-        s_tris.release();
+        bs.ms_sort += tm.end();
+        io.recs->release();
         /* hierarchy */
         Bvh2Node* nodes2 = palloc<Bvh2Node>(c, s_nodes2, 2 * (size_t)n, st);
         uint32_t* parent = palloc<uint32_t>(c, s_parent, 2 * (size_t)n, st);
@@ -301,23 +321,22 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         RT3_CUDA(c, cudaMemsetAsync(nflags, 0, sizeof(uint32_t) * n, st));
         RT3_CUDA(c, cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n, st));
         if (n > 1) RT3_LAUNCH(c, k_lbvh_hierarchy, div_up(n - 1, 256), 256, 0, st, keys0, (int)n, nodes2, parent);
-        bs.ms_hierarchy = tm.end();
+        bs.ms_hierarchy += tm.end();
         tm.begin();
-        RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, pad, nodes2, parent, nflags, counts);
-        bs.ms_refit = tm.end();
+        RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts);
+        bs.ms_refit += tm.end();
         s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release(); s_parent.release(); s_flags.release();
         /* collapse */
-        WideNode* wide = ensure<WideNode>(c, c->bvh_nodes, n);
         uint32_t* items0 = palloc<uint32_t>(c, s_items[0], 2 * (size_t)n + 2, st);
         uint32_t* items1 = palloc<uint32_t>(c, s_items[1], 2 * (size_t)n + 2, st);
-        uint32_t* ctr = (uint32_t*)d_bounds + 8;
+        uint32_t* ctr = (uint32_t*)d_misc + 8;      /* [8] node ctr, [9] record ctr, [10] queue ctr, [12],[13] sah */
         tm.begin();
-        uint32_t init_ctr[8] = {1u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        uint32_t init_ctr[8] = {io.first_free_node, io.first_free_rec, 0u, 0u, 0u, 0u, 0u, 0u};
         RT3_CUDA(c, cudaMemcpyAsync(ctr, init_ctr, sizeof(init_ctr), cudaMemcpyHostToDevice, st));
-        uint32_t first_item[2] = {n == 1 ? (LEAF_FLAG | 0u) : 0u, 0u};
+        uint32_t first_item[2] = {n == 1 ? (LEAF_FLAG | 0u) : 0u, io.root_index};
         RT3_CUDA(c, cudaMemcpyAsync(items0, first_item, sizeof(first_item), cudaMemcpyHostToDevice, st));
         CollapseCtx cc;
-        cc.nodes = nodes2; cc.counts = counts; cc.tris_sorted = sorted; cc.n_leaves = n; cc.out_nodes = wide; cc.out_tris = out_tris;
+        cc.nodes = nodes2; cc.counts = counts; cc.tris_sorted = sorted; cc.n_leaves = n; cc.out_nodes = io.wide; cc.out_tris = io.out_recs;
         cc.node_counter = ctr; cc.tri_counter = ctr + 1; cc.next_count = ctr + 2; cc.sah_accum = (float*)(ctr + 4);
         uint32_t count = 1, levels = 0;
         uint32_t* cur = items0; uint32_t* nxt = items1;
@@ -333,22 +352,213 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         }
         uint32_t fin[8];
         RT3_CUDA(c, cudaMemcpyAsync(fin, ctr, sizeof(fin), cudaMemcpyDeviceToHost, st));
-        bs.ms_collapse = tm.end();
-        if (levels >= RT3_MAX_STACK) RT3_FAIL(c, RT3_ERR_STATE, "wide BVH deeper than the traversal stack");
-        if (fin[1] != n) RT3_FAIL(c, RT3_ERR_STATE, "BVH collapse lost triangles");
-        c->n_wide_nodes = fin[0];
-        bs.wide_nodes = fin[0]; bs.bvh2_nodes = 2 * n - 1; bs.levels = levels;
-        bs.node_bytes = (uint64_t)fin[0] * sizeof(WideNode); bs.tri_bytes = (uint64_t)n * sizeof(Tri48);
-        float sah_nodes, sah_tris;
-        memcpy(&sah_nodes, &fin[4], 4); memcpy(&sah_tris, &fin[5], 4);
-        float ex = hi[0] - lo[0] + 2 * pad, ey = hi[1] - lo[1] + 2 * pad, ez = hi[2] - lo[2] + 2 * pad;
-        float root_area = 2.0f * (ex * ey + ey * ez + ez * ex);
-        bs.sah_cost = root_area > 0 ? (sah_nodes + sah_tris) / root_area : 0.f;
+        bs.ms_collapse += tm.end();
+        if (fin[1] != io.first_free_rec + n) RT3_FAIL(c, RT3_ERR_STATE, "BVH collapse lost leaf records");
+        io.nodes_end = fin[0]; io.recs_end = fin[1]; io.levels = levels;
+        memcpy(&io.sah_nodes, &fin[4], 4); memcpy(&io.sah_recs, &fin[5], 4);
     } catch (...) {
         cleanup();
         throw;
     }
     cleanup();
+}
+
+static void read_bounds(rt3_context* c, cudaStream_t st, const int* d_bounds, float lo[3], float hi[3]) {
+    int hb[6];
+    RT3_CUDA(c, cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    RT3_CUDA(c, cudaStreamSynchronize(st));
+    for (int k = 0; k < 3; ++k) { lo[k] = ordered_to_float(hb[k]); hi[k] = ordered_to_float(hb[3 + k]); }
+}
+static float max_extent(const float lo[3], const float hi[3]) { return fmaxf(hi[0] - lo[0], fmaxf(hi[1] - lo[1], hi[2] - lo[2])); }
+
+/* row-major 3x4 affine inverse (double arithmetic, rounded once) */
+static bool invert_affine(const float m[12], float out[12]) {
+    const double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+    const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    if (!(fabs(det) > 1e-30)) return false;
+    const double r[9] = {(e * i - f * h) / det, (c * h - b * i) / det, (b * f - c * e) / det, (f * g - d * i) / det, (a * i - c * g) / det,
+                         (c * d - a * f) / det, (d * h - e * g) / det, (b * g - a * h) / det, (a * e - b * d) / det};
+    for (int row = 0; row < 3; ++row) {
+        for (int col = 0; col < 3; ++col) out[4 * row + col] = (float)r[3 * row + col];
+        out[4 * row + 3] = (float)-(r[3 * row] * m[3] + r[3 * row + 1] * m[7] + r[3 * row + 2] * m[11]);
+    }
+    return true;
+}
+
+/* ---- single level: every instance flattened to world space (the default) -------------------------------------------- */
+static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs) {
+    const uint32_t n = c->n_triangles;
+    StageTimer tm(c, st);
+    Tri48* out_tris = ensure<Tri48>(c, c->bvh_tris, n);
+    PoolBuf s_tris, s_misc;
+    try {
+        Tri48* tris = palloc<Tri48>(c, s_tris, n, st);
+        int* d_misc = (int*)palloc<uint32_t>(c, s_misc, 16, st);
+        tm.begin();
+        RT3_LAUNCH(c, k_init_bounds, 1, 32, 0, st, d_misc);
+        RT3_LAUNCH(c, k_flatten, div_up(n, 256), 256, 0, st, c->view, n, tris, d_misc);
+        float lo[3], hi[3];
+        read_bounds(c, st, d_misc, lo, hi);
+        bs.ms_flatten += tm.end();
+        for (int k = 0; k < 3; ++k) { bs.scene_lo[k] = lo[k]; bs.scene_hi[k] = hi[k]; }
+        WideBuild io;
+        io.recs = &s_tris; io.n = n; io.kind = REC_TRI_EDGES; io.pad = max_extent(lo, hi) * (1.0f / 65536.0f);
+        memcpy(io.lo, lo, sizeof(lo)); memcpy(io.hi, hi, sizeof(hi));
+        io.wide = ensure<WideNode>(c, c->bvh_nodes, n); io.root_index = 0; io.first_free_node = 1;
+        io.out_recs = out_tris; io.first_free_rec = 0;
+        build_wide(c, st, io, bs, d_misc);
+        if (io.levels >= RT3_MAX_STACK) RT3_FAIL(c, RT3_ERR_STATE, "wide BVH deeper than the traversal stack");
+        c->n_wide_nodes = io.nodes_end; c->n_leaf_records = n;
+        bs.wide_nodes = io.nodes_end; bs.bvh2_nodes = 2 * n - 1; bs.levels = io.levels;
+        bs.node_bytes = (uint64_t)io.nodes_end * sizeof(WideNode); bs.tri_bytes = (uint64_t)n * sizeof(Tri48);
+        const float pad = io.pad, ex = hi[0] - lo[0] + 2 * pad, ey = hi[1] - lo[1] + 2 * pad, ez = hi[2] - lo[2] + 2 * pad;
+        const float root_area = 2.0f * (ex * ey + ey * ez + ez * ex);
+        bs.sah_cost = root_area > 0 ? (io.sah_nodes + io.sah_recs) / root_area : 0.f;
+    } catch (...) { s_tris.release(); s_misc.release(); throw; }
+    s_tris.release(); s_misc.release();
+    c->two_level = false;
+}
+
+/* ---- two levels (RT3_BUILD_TWO_LEVEL): one bottom-level tree per distinct mesh, one top-level tree over the instances ---- */
+static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs) {
+    StageTimer tm(c, st);
+    const std::vector<InstanceRec>& inst = c->h_instances;
+    const uint32_t ni = (uint32_t)inst.size();
+    /* distinct meshes = distinct (first_geometry, geometry_count); segments of instance i start at seg0[i] */
+    struct MeshInfo { uint32_t first_geometry, geometry_count, seg0, prim0, n, root, first_inst; float lo[3], hi[3]; };
+    std::vector<MeshInfo> meshes;
+    std::vector<uint32_t> inst_mesh(ni), inst_seg0(ni);
+    uint32_t seg = 0;
+    uint64_t blas_tris = 0;
+    for (uint32_t i = 0; i < ni; ++i) {
+        inst_seg0[i] = seg;
+        uint32_t m = 0;
+        for (; m < meshes.size(); ++m) if (meshes[m].first_geometry == inst[i].first_geometry && meshes[m].geometry_count == inst[i].geometry_count) break;
+        if (m == meshes.size()) {
+            MeshInfo mi; memset(&mi, 0, sizeof(mi));
+            mi.first_geometry = inst[i].first_geometry; mi.geometry_count = inst[i].geometry_count; mi.seg0 = seg; mi.first_inst = i;
+            mi.prim0 = c->h_seg_first[seg]; mi.n = c->h_seg_first[seg + inst[i].geometry_count] - mi.prim0;
+            meshes.push_back(mi);
+            blas_tris += mi.n;
+        }
+        inst_mesh[i] = m;
+        seg += inst[i].geometry_count;
+    }
+    const uint64_t total_recs = blas_tris + ni;
+    if (total_recs >= 0x7FFFFFFFull) RT3_FAIL(c, RT3_ERR_INVALID, "too many leaf records");
+    WideNode* wide = ensure<WideNode>(c, c->bvh_nodes, (size_t)total_recs + meshes.size() + 1);
+    Tri48* out_recs = ensure<Tri48>(c, c->bvh_tris, (size_t)total_recs);
+    PoolBuf s_recs, s_misc;
+    try {
+        int* d_misc = (int*)palloc<uint32_t>(c, s_misc, 16, st);
+        /* pass 1: object-space bounds of every mesh (needed for the world boxes, which give the padding) */
+        std::vector<InstRec> recs(ni);
+        float wlo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, whi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+        std::vector<PoolBuf> mesh_tris(meshes.size());
+        tm.begin();
+        for (size_t m = 0; m < meshes.size(); ++m) {
+            MeshInfo& mi = meshes[m];
+            if (mi.n == 0) continue;
+            Tri48* t = palloc<Tri48>(c, mesh_tris[m], mi.n, st);
+            RT3_LAUNCH(c, k_init_bounds, 1, 32, 0, st, d_misc);
+            RT3_LAUNCH(c, k_flatten_object, div_up(mi.n, 256), 256, 0, st, c->view, mi.prim0, mi.n, t, d_misc);
+            read_bounds(c, st, d_misc, mi.lo, mi.hi);
+        }
+        bs.ms_flatten += tm.end();
+        std::vector<float> inst_lo(3 * ni), inst_hi(3 * ni);
+        std::vector<float> mesh_inv_scale(meshes.size(), 0.f);
+        for (uint32_t i = 0; i < ni; ++i) {
+            const MeshInfo& mi = meshes[inst_mesh[i]];
+            InstRec& r = recs[i];
+            memcpy(r.xform, inst[i].xform, sizeof(r.xform));
+            if (!invert_affine(r.xform, r.inv)) RT3_FAIL(c, RT3_ERR_INVALID, "instance transform is singular (two-level build)");
+            r.first_prim = c->h_seg_first[inst_seg0[i]]; r.pad0 = r.pad1 = 0; r.root = 0;
+            for (int k = 0; k < 3; ++k) { inst_lo[3 * i + k] = 3.4e38f; inst_hi[3 * i + k] = -3.4e38f; }
+            if (mi.n == 0) { for (int k = 0; k < 3; ++k) inst_lo[3 * i + k] = inst_hi[3 * i + k] = r.xform[4 * k + 3]; }
+            else for (int corner = 0; corner < 8; ++corner) {
+                const float p[3] = {(corner & 1) ? mi.hi[0] : mi.lo[0], (corner & 2) ? mi.hi[1] : mi.lo[1], (corner & 4) ? mi.hi[2] : mi.lo[2]};
+                for (int k = 0; k < 3; ++k) {
+                    const float w = r.xform[4 * k] * p[0] + r.xform[4 * k + 1] * p[1] + r.xform[4 * k + 2] * p[2] + r.xform[4 * k + 3];
+                    inst_lo[3 * i + k] = fminf(inst_lo[3 * i + k], w); inst_hi[3 * i + k] = fmaxf(inst_hi[3 * i + k], w);
+                }
+            }
+            for (int k = 0; k < 3; ++k) { wlo[k] = fminf(wlo[k], inst_lo[3 * i + k]); whi[k] = fmaxf(whi[k], inst_hi[3 * i + k]); }
+            float sc = 0.f;
+            for (int row = 0; row < 3; ++row) sc = fmaxf(sc, fabsf(r.inv[4 * row]) + fabsf(r.inv[4 * row + 1]) + fabsf(r.inv[4 * row + 2]));
+            mesh_inv_scale[inst_mesh[i]] = fmaxf(mesh_inv_scale[inst_mesh[i]], sc);
+        }
+        const float world_ext = max_extent(wlo, whi);
+        for (int k = 0; k < 3; ++k) { bs.scene_lo[k] = wlo[k]; bs.scene_hi[k] = whi[k]; }
+        /* pass 2: bottom-level trees, concatenated in one node / record array (node 0 is the top-level root) */
+        uint32_t next_node = 1, next_rec = 0, max_levels = 0;
+        for (size_t m = 0; m < meshes.size(); ++m) {
+            MeshInfo& mi = meshes[m];
+            mi.root = next_node;
+            if (mi.n == 0) { RT3_LAUNCH(c, k_empty_root, 1, 32, 0, st, wide + mi.root); next_node++; continue; }
+            WideBuild io;
+            io.recs = &mesh_tris[m]; io.n = mi.n; io.kind = REC_TRI_VERTS;
+            /* padding covers the intersection slop and node quantisation (object extent / 65536, as in the single-level build) AND the
+             * rounding of the world -> object ray transform, which grows with the distance of the ray origin in object units */
+            io.pad = (max_extent(mi.lo, mi.hi) + world_ext * mesh_inv_scale[m]) * (1.0f / 65536.0f);
+            memcpy(io.lo, mi.lo, sizeof(mi.lo)); memcpy(io.hi, mi.hi, sizeof(mi.hi));
+            io.wide = wide; io.root_index = mi.root; io.first_free_node = mi.root + 1;
+            io.out_recs = out_recs; io.first_free_rec = next_rec;
+            build_wide(c, st, io, bs, d_misc);
+            next_node = io.nodes_end; next_rec = io.recs_end; max_levels = std::max(max_levels, io.levels);
+        }
+        /* pass 3: top level over the instance boxes */
+        std::vector<Tri48> boxes(ni);
+        const float top_pad = world_ext * (1.0f / 65536.0f);
+        for (uint32_t i = 0; i < ni; ++i) {
+            recs[i].root = meshes[inst_mesh[i]].root;
+            const float bpad = meshes[inst_mesh[i]].n ? (max_extent(meshes[inst_mesh[i]].lo, meshes[inst_mesh[i]].hi) + world_ext * mesh_inv_scale[inst_mesh[i]]) * (1.0f / 65536.0f) : 0.f;
+            float rs = 0.f;   /* object-space padding seen in world space */
+            for (int row = 0; row < 3; ++row) rs = fmaxf(rs, fabsf(recs[i].xform[4 * row]) + fabsf(recs[i].xform[4 * row + 1]) + fabsf(recs[i].xform[4 * row + 2]));
+            Tri48& b = boxes[i];
+            memset(&b, 0, sizeof(b));
+            for (int k = 0; k < 3; ++k) { b.v0[k] = inst_lo[3 * i + k] - bpad * rs; b.e1[k] = inst_hi[3 * i + k] + bpad * rs; }
+            b.prim = i;
+        }
+        Tri48* d_boxes = palloc<Tri48>(c, s_recs, ni, st);
+        RT3_CUDA(c, cudaMemcpyAsync(d_boxes, boxes.data(), ni * sizeof(Tri48), cudaMemcpyHostToDevice, st));
+        WideBuild top;
+        top.recs = &s_recs; top.n = ni; top.kind = REC_BOX; top.pad = top_pad;
+        memcpy(top.lo, wlo, sizeof(wlo)); memcpy(top.hi, whi, sizeof(whi));
+        top.wide = wide; top.root_index = 0; top.first_free_node = next_node;
+        top.out_recs = out_recs; top.first_free_rec = next_rec;
+        build_wide(c, st, top, bs, d_misc);
+        if (top.levels + 3 + max_levels >= RT3_MAX_STACK) RT3_FAIL(c, RT3_ERR_STATE, "two-level BVH deeper than the traversal stack");
+        InstRec* d_insts = ensure<InstRec>(c, c->d_insts, ni);
+        RT3_CUDA(c, cudaMemcpyAsync(d_insts, recs.data(), ni * sizeof(InstRec), cudaMemcpyHostToDevice, st));
+        RT3_CUDA(c, cudaStreamSynchronize(st));
+        c->n_wide_nodes = top.nodes_end; c->n_leaf_records = top.recs_end;
+        bs.wide_nodes = top.nodes_end; bs.bvh2_nodes = 0; bs.levels = top.levels + max_levels;
+        bs.node_bytes = (uint64_t)top.nodes_end * sizeof(WideNode); bs.tri_bytes = (uint64_t)top.recs_end * sizeof(Tri48) + (uint64_t)ni * sizeof(InstRec);
+        bs.sah_cost = 0.f;
+        for (PoolBuf& b : mesh_tris) b.release();
+    } catch (...) { s_recs.release(); s_misc.release(); throw; }
+    s_recs.release(); s_misc.release();
+    c->two_level = true;
+}
+
+void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out) {
+    rt3_build_stats bs;
+    memset(&bs, 0, sizeof(bs));
+    const uint32_t n = c->n_triangles;
+    bs.triangles = n;
+    cudaEvent_t total_a = c->ev[2], total_b = c->ev[3];
+    cudaEventRecord(total_a, st);
+    if (n == 0) {
+        WideNode* nodes = ensure<WideNode>(c, c->bvh_nodes, 1);
+        ensure<Tri48>(c, c->bvh_tris, 1);
+        RT3_LAUNCH(c, k_empty_root, 1, 32, 0, st, nodes);
+        RT3_CUDA(c, cudaStreamSynchronize(st));
+        c->n_wide_nodes = 1; c->n_leaf_records = 0; c->two_level = false; bs.wide_nodes = 1; bs.node_bytes = sizeof(WideNode);
+    } else if ((flags & RT3_BUILD_TWO_LEVEL) && !c->h_instances.empty()) {
+        build_two_level(c, st, bs);
+    } else {
+        build_single_level(c, st, bs);
+    }
     cudaEventRecord(total_b, st); cudaEventSynchronize(total_b);
     float ms = 0; cudaEventElapsedTime(&ms, total_a, total_b); bs.ms_total = ms;
     c->accel_valid = true; c->last_build = bs;

@@ -133,13 +133,29 @@ RT3_HD void lbvh_build_node(const uint64_t* keys, int n, int i, Bvh2Node* nodes,
     if (i == 0) parent[0] = 0xFFFFFFFFu;
 }
 
-RT3_HD void tri_bounds(const Tri48& t, float pad, float lo[3], float hi[3]) {
+/* Leaf records are 48 bytes in three interpretations (the builder only needs their bounds):
+ *   REC_TRI_EDGES  (v0, e1, e2, global id)            single-level BVH over world-space triangles
+ *   REC_TRI_VERTS  (a, b, c, mesh-local id)           bottom level of the two-level BVH: object-space VERTICES, so that the
+ *                                                     traversal can rebuild the world-space triangle with exactly the arithmetic
+ *                                                     of the flattening kernel (bit-identical hits in both modes)
+ *   REC_BOX        (lo, instance id, hi)              top level: one record per instance (world-space box of its BLAS root) */
+enum { REC_TRI_EDGES = 0, REC_TRI_VERTS = 1, REC_BOX = 2 };
+RT3_HD void tri_bounds(const Tri48& t, float pad, float lo[3], float hi[3], int kind = REC_TRI_EDGES) {
     for (int a = 0; a < 3; ++a) {
-        float p0 = t.v0[a], p1 = t.v0[a] + t.e1[a], p2 = t.v0[a] + t.e2[a];
+        if (kind == REC_BOX) { lo[a] = t.v0[a] - pad; hi[a] = t.e1[a] + pad; continue; }
+        float p0 = t.v0[a], p1 = kind == REC_TRI_VERTS ? t.e1[a] : t.v0[a] + t.e1[a], p2 = kind == REC_TRI_VERTS ? t.e2[a] : t.v0[a] + t.e2[a];
         lo[a] = rt3m::min_(p0, rt3m::min_(p1, p2)) - pad;
         hi[a] = rt3m::max_(p0, rt3m::max_(p1, p2)) + pad;
     }
 }
+/* Instance table entry of the two-level BVH (InstanceInfo of world/mod.rs:32-37 + what the traversal needs). */
+struct InstRec {
+    float xform[12];        /* object -> world, row-major 3x4 (as pushed)           */
+    float inv[12];          /* world -> object                                       */
+    uint32_t root;          /* wide-node index of the instance's BLAS root           */
+    uint32_t first_prim;    /* global id of the instance's first triangle            */
+    uint32_t pad0, pad1;
+};
 RT3_HD float box_area(const float lo[3], const float hi[3]) {
     float ex = hi[0] - lo[0], ey = hi[1] - lo[1], ez = hi[2] - lo[2];
     return 2.0f * (ex * ey + ey * ez + ez * ex);
@@ -418,18 +434,41 @@ RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n
 
 struct TraverseStats { uint32_t nodes, tris; };
 
+/* World -> object ray for the bottom level: same parameter t (the direction is not renormalised). */
+RT3_HD rt3_ray object_ray(const InstRec& in, const rt3_ray& w) {
+    rt3_ray o;
+    const vec3 p = rt3m::xform_point(in.inv, rt3m::v3(w.o)), d = rt3m::xform_dir(in.inv, rt3m::v3(w.d));
+    o.o[0] = p.x; o.o[1] = p.y; o.o[2] = p.z; o.d[0] = d.x; o.d[1] = d.y; o.d[2] = d.z; o.tmin = w.tmin; o.tmax = w.tmax;
+    return o;
+}
+/* World-space (v0, e1, e2) of a bottom-level record: the instance transform applied to the stored vertices, then the edge
+ * subtractions — the operations of k_flatten (build.cu) / world_triangle (rt3_shared_math.h) in the same order. */
+RT3_HD void instance_triangle(const InstRec& in, const u32x4& a, const u32x4& b, const u32x4& c, vec3& v0, vec3& e1, vec3& e2) {
+    vec3 pa = rt3m::v3(rt3m::as_float(a.x), rt3m::as_float(a.y), rt3m::as_float(a.z));
+    vec3 pb = rt3m::v3(rt3m::as_float(b.x), rt3m::as_float(b.y), rt3m::as_float(b.z));
+    vec3 pc = rt3m::v3(rt3m::as_float(c.x), rt3m::as_float(c.y), rt3m::as_float(c.z));
+    if (!rt3m::xform_is_identity(in.xform)) { pa = rt3m::xform_point(in.xform, pa); pb = rt3m::xform_point(in.xform, pb); pc = rt3m::xform_point(in.xform, pc); }
+    v0 = pa; e1 = pb - pa; e2 = pc - pa;
+}
+#define RT3_STACK_SENTINEL 0xFFFFFFFFu
+
 /* Closest hit (ANY = false) or first hit found (ANY = true).  `hit.t` must come in as the ray's tmax and
- * hit.prim as RT3_MISS.  Returns true if something was hit. */
+ * hit.prim as RT3_MISS.  Returns true if something was hit.
+ * insts == nullptr: single-level BVH over world-space triangles.  insts != nullptr: two-level — the top level's leaf records
+ * are instances; entering one pushes the pending node group, the pending record group and a sentinel, switches to the
+ * object-space ray and restarts at the instance's root; popping the sentinel restores the world-space ray. */
 template <bool ANY>
-RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ray& ray, rt3_hit& hit, TraverseStats* stats, bool active = true) {
+RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ray& ray, rt3_hit& hit, TraverseStats* stats, bool active = true,
+                          const InstRec* insts = nullptr) {
     RayPrep r = prepare_ray(ray);
-    const vec3 o = rt3m::v3(r.ox, r.oy, r.oz), d = rt3m::v3(r.dx, r.dy, r.dz);
+    const vec3 o = rt3m::v3(ray.o), d = rt3m::v3(ray.d);
     uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
     int sp = 0;
     uint32_t ng_base = 0, ng_hits = 0x80000000u;   /* node group: root */
-    uint32_t tg_base = 0, tg_hits = 0;             /* triangle group   */
-    /* Two-phase iteration (same shape as k_trace_dyn): a node step for rays with no triangle pending, then ONE triangle
-     * test per ray that has one pending.  On the device the loop is warp-synchronous (every lane of the warp must call this
+    uint32_t tg_base = 0, tg_hits = 0;             /* record group     */
+    uint32_t cur_inst = RT3_STACK_SENTINEL;        /* two-level: instance being traversed, or none (top level) */
+    /* Two-phase iteration (same shape as k_trace_dyn): a node step for rays with no record pending, then ONE record
+     * per ray that has one pending.  On the device the loop is warp-synchronous (every lane of the warp must call this
      * function; lanes without a ray pass active = false) so that both phases run converged. */
 #ifdef __CUDA_ARCH__
 #define RT3_WARP_ANY(x) __any_sync(0xFFFFFFFFu, (x))
@@ -457,19 +496,38 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
             tg_hits &= ~(1u << bit);
             const Tri48* tp = tris + (tg_base + (uint32_t)bit);
             const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
-            if (stats) stats->tris++;
-            float t, u, v;
-            const vec3 v0 = rt3m::v3(rt3m::as_float(a.x), rt3m::as_float(a.y), rt3m::as_float(a.z));
-            const vec3 e1 = rt3m::v3(rt3m::as_float(b.x), rt3m::as_float(b.y), rt3m::as_float(b.z));
-            const vec3 e2 = rt3m::v3(rt3m::as_float(c.x), rt3m::as_float(c.y), rt3m::as_float(c.z));
-            if (rt3m::ray_triangle(o, d, v0, e1, e2, t, u, v) && t > ray.tmin && t < ray.tmax) {
-                if (ANY) { hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w; found_any = true; }
-                else if (rt3m::closer_hit(t, a.w, hit.t, hit.prim)) { hit.t = t; hit.u = u; hit.v = v; hit.prim = a.w; }
+            if (insts != nullptr && cur_inst == RT3_STACK_SENTINEL) {
+                /* top-level record = instance: save what is pending here, dive into its bottom-level tree */
+                if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
+                if (tg_hits && sp < RT3_MAX_STACK) { stack_base[sp] = tg_base; stack_hits[sp] = tg_hits; sp++; }
+                if (sp < RT3_MAX_STACK) { stack_base[sp] = RT3_STACK_SENTINEL; stack_hits[sp] = 0u; sp++; }
+                cur_inst = a.w;
+                r = prepare_ray(object_ray(insts[cur_inst], ray));
+                ng_base = insts[cur_inst].root; ng_hits = 0x80000000u; tg_hits = 0u;
+            } else {
+                if (stats) stats->tris++;
+                float t, u, v;
+                vec3 v0, e1, e2;
+                uint32_t prim = a.w;
+                if (insts != nullptr) { instance_triangle(insts[cur_inst], a, b, c, v0, e1, e2); prim += insts[cur_inst].first_prim; }
+                else {
+                    v0 = rt3m::v3(rt3m::as_float(a.x), rt3m::as_float(a.y), rt3m::as_float(a.z));
+                    e1 = rt3m::v3(rt3m::as_float(b.x), rt3m::as_float(b.y), rt3m::as_float(b.z));
+                    e2 = rt3m::v3(rt3m::as_float(c.x), rt3m::as_float(c.y), rt3m::as_float(c.z));
+                }
+                if (rt3m::ray_triangle(o, d, v0, e1, e2, t, u, v) && t > ray.tmin && t < ray.tmax) {
+                    if (ANY) { hit.t = t; hit.u = u; hit.v = v; hit.prim = prim; found_any = true; }
+                    else if (rt3m::closer_hit(t, prim, hit.t, hit.prim)) { hit.t = t; hit.u = u; hit.v = v; hit.prim = prim; }
+                }
             }
         }
-        if (active && (found_any || (tg_hits == 0u && ng_hits <= 0x00FFFFFFu))) {
-            if (found_any || sp == 0) active = false;
-            else { sp--; ng_base = stack_base[sp]; ng_hits = stack_hits[sp]; }
+        if (active && found_any) active = false;
+        while (active && tg_hits == 0u && ng_hits <= 0x00FFFFFFu) {       /* nothing pending here: pop (more than once only across a sentinel) */
+            if (sp == 0) { active = false; break; }
+            sp--;
+            const uint32_t eb = stack_base[sp], eh = stack_hits[sp];
+            if (eb == RT3_STACK_SENTINEL && eh == 0u) { cur_inst = RT3_STACK_SENTINEL; r = prepare_ray(ray); continue; }
+            if (eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; ng_hits = 0u; }
         }
     }
 #undef RT3_WARP_ANY

@@ -95,8 +95,9 @@ struct rt3_context {
     rt3m::SceneView view;           /* device pointers */
 
     /* acceleration structure */
-    Scratch bvh_nodes, bvh_tris;
-    uint32_t n_wide_nodes = 0;
+    Scratch bvh_nodes, bvh_tris, d_insts;   /* d_insts: rt3b::InstRec table of the two-level structure */
+    uint32_t n_wide_nodes = 0, n_leaf_records = 0;
+    bool two_level = false;
     bool accel_valid = false;
     rt3_build_stats last_build;
 

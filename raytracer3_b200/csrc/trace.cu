@@ -33,7 +33,7 @@ template <bool ANY, bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
                                                          const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
                                                          rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter,
-                                                         unsigned long long* stat_counters) {
+                                                         unsigned long long* stat_counters, const InstRec* __restrict__ insts) {
     const uint64_t n = d_count ? (uint64_t)*d_count : n_static;
     const uint32_t lane = threadIdx.x & 31u;
     unsigned long long st_nodes = 0, st_tris = 0;
@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
         else { r.o[0] = r.o[1] = r.o[2] = 0.f; r.d[0] = r.d[1] = 0.f; r.d[2] = 1.f; r.tmin = 0.f; r.tmax = 0.f; }
         h.t = r.tmax;
         TraverseStats ts = {0, 0};
-        any = traverse_wide<ANY>(nodes, tris, r, h, STATS ? &ts : nullptr, valid);   /* warp-synchronous: every lane calls */
+        any = traverse_wide<ANY>(nodes, tris, r, h, STATS ? &ts : nullptr, valid, insts);   /* warp-synchronous: every lane calls */
         if (STATS) { st_nodes += ts.nodes; st_tris += ts.tris; }
         if (ANY) {
             uint32_t word = __ballot_sync(0xFFFFFFFFu, any);
@@ -82,23 +82,33 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
 #ifndef RT3_SMEM_STACK
 #define RT3_SMEM_STACK 0
 #endif
-template <bool ANY, int KEEP, int TRIS>
+/* TWO = two-level structure (RT3_BUILD_TWO_LEVEL): top-level leaf records are instances; see traverse_wide in bvh_logic.h for the
+ * stack protocol (node group, record group, sentinel).  The world-space ray stays in registers for the triangle test, which
+ * rebuilds the world-space triangle from the stored object-space vertices (bit-identical to the flattened build). */
+template <bool ANY, int KEEP, bool TWO>
 __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
                                                              const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
-                                                             rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter, uint32_t magic) {
+                                                             rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter, uint32_t magic,
+                                                             const InstRec* __restrict__ insts) {
     const uint64_t n = d_count ? (uint64_t)*d_count : n_static;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     RayPrep r;
     float ray_tmax = 0.f;
+    float wox = 0.f, woy = 0.f, woz = 0.f, wdx = 0.f, wdy = 0.f, wdz = 1.f;    /* TWO: the world-space ray (r is the current level's) */
+    uint32_t cur_inst = RT3_STACK_SENTINEL;
     uint64_t my_index = 0;
     rt3_hit h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
     uint32_t ng_base = 0, ng_hits = 0, tg_base = 0, tg_hits = 0;
 #if RT3_SMEM_STACK > 0
     __shared__ uint2 s_stack[RT3_SMEM_STACK][TRACE_THREADS];
     uint32_t stack_base[RT3_MAX_STACK - RT3_SMEM_STACK], stack_hits[RT3_MAX_STACK - RT3_SMEM_STACK];
+#define RT3_PUSH(B, H) do { if (sp < RT3_SMEM_STACK) s_stack[sp][threadIdx.x] = make_uint2((B), (H)); else { stack_base[sp - RT3_SMEM_STACK] = (B); stack_hits[sp - RT3_SMEM_STACK] = (H); } sp++; } while (0)
+#define RT3_POP(B, H) do { sp--; if (sp < RT3_SMEM_STACK) { const uint2 e_ = s_stack[sp][threadIdx.x]; (B) = e_.x; (H) = e_.y; } else { (B) = stack_base[sp - RT3_SMEM_STACK]; (H) = stack_hits[sp - RT3_SMEM_STACK]; } } while (0)
 #else
     uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
+#define RT3_PUSH(B, H) do { stack_base[sp] = (B); stack_hits[sp] = (H); sp++; } while (0)
+#define RT3_POP(B, H) do { sp--; (B) = stack_base[sp]; (H) = stack_hits[sp]; } while (0)
 #endif
     int sp = 0;
     bool active = false, exhausted = false;
@@ -117,6 +127,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                 if (i < n) {
                     const rt3_ray ray = load_ray(rays, i);
                     r = prepare_ray(ray, magic);
+                    if (TWO) { wox = ray.o[0]; woy = ray.o[1]; woz = ray.o[2]; wdx = ray.d[0]; wdy = ray.d[1]; wdz = ray.d[2]; cur_inst = RT3_STACK_SENTINEL; }
                     ray_tmax = ray.tmax;
                     h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
                     ng_base = 0; ng_hits = 0x80000000u; tg_hits = 0; sp = 0;
@@ -128,24 +139,16 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
         }
         if (__ballot_sync(0xFFFFFFFFu, active) == 0u) break;
         const int keep = exhausted ? 1 : KEEP;
-        /* ---- traverse until too few lanes are busy.  One iteration = a node step for the lanes that have no triangle
-         * pending, then ONE triangle test for every lane that has one pending: the warp re-converges between the two
-         * phases, so triangle tests of different lanes share issue slots instead of running 3-of-32 wide in a per-lane
-         * loop (ncu source page of the per-lane-loop version: profiles/r1b_*). */
+        /* ---- traverse until too few lanes are busy.  One iteration = a node step for the lanes that have no record
+         * pending, then ONE record (triangle test / instance entry) for every lane that has one pending: the warp re-converges
+         * between the two phases, so triangle tests of different lanes share issue slots instead of running 3-of-32 wide in a
+         * per-lane loop (ncu source page of the per-lane-loop version: profiles/r1b_*). */
         do {
             if (active && tg_hits == 0u && ng_hits > 0x00FFFFFFu) {
                 const int bit = bfind32(ng_hits);
                 const uint32_t imask = ng_hits & 0xFFu;
                 ng_hits &= ~(1u << bit);
-                if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) {
-#if RT3_SMEM_STACK > 0
-                    if (sp < RT3_SMEM_STACK) s_stack[sp][threadIdx.x] = make_uint2(ng_base, ng_hits);
-                    else { stack_base[sp - RT3_SMEM_STACK] = ng_base; stack_hits[sp - RT3_SMEM_STACK] = ng_hits; }
-#else
-                    stack_base[sp] = ng_base; stack_hits[sp] = ng_hits;
-#endif
-                    sp++;
-                }
+                if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) RT3_PUSH(ng_base, ng_hits);
                 const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
                 const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
                 const WideNode* nd = nodes + (ng_base + rel);
@@ -156,40 +159,63 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                 tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
             }
             bool found_any = false;
-#pragma unroll
-            for (int rep = 0; rep < TRIS; ++rep) {
-                if (active && tg_hits) {
-                    const int bit = bfind32(tg_hits);
-                    tg_hits &= ~(1u << bit);
-                    const Tri48* tp = tris + (tg_base + (uint32_t)bit);
-                    const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
+            if (active && tg_hits) {
+                const int bit = bfind32(tg_hits);
+                tg_hits &= ~(1u << bit);
+                const Tri48* tp = tris + (tg_base + (uint32_t)bit);
+                const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
+                if (TWO && cur_inst == RT3_STACK_SENTINEL) {
+                    if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) RT3_PUSH(ng_base, ng_hits);
+                    if (tg_hits && sp < RT3_MAX_STACK) RT3_PUSH(tg_base, tg_hits);
+                    if (sp < RT3_MAX_STACK) RT3_PUSH(RT3_STACK_SENTINEL, 0u);
+                    cur_inst = a.w;
+                    rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
+                    r = prepare_ray(object_ray(insts[cur_inst], wr), magic);
+                    ng_base = insts[cur_inst].root; ng_hits = 0x80000000u; tg_hits = 0u;
+                } else {
                     float t, u, v;
-                    const rt3m::vec3 v0 = rt3m::v3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
-                    const rt3m::vec3 e1 = rt3m::v3(__uint_as_float(b.x), __uint_as_float(b.y), __uint_as_float(b.z));
-                    const rt3m::vec3 e2 = rt3m::v3(__uint_as_float(c.x), __uint_as_float(c.y), __uint_as_float(c.z));
-                    if (rt3m::ray_triangle(rt3m::v3(r.ox, r.oy, r.oz), rt3m::v3(r.dx, r.dy, r.dz), v0, e1, e2, t, u, v) && t > r.tmin && t < ray_tmax) {
+                    rt3m::vec3 v0, e1, e2, ro, rd;
+                    uint32_t prim = a.w;
+                    if (TWO) {
+                        instance_triangle(insts[cur_inst], a, b, c, v0, e1, e2);
+                        prim += insts[cur_inst].first_prim;
+                        ro = rt3m::v3(wox, woy, woz); rd = rt3m::v3(wdx, wdy, wdz);
+                    } else {
+                        v0 = rt3m::v3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
+                        e1 = rt3m::v3(__uint_as_float(b.x), __uint_as_float(b.y), __uint_as_float(b.z));
+                        e2 = rt3m::v3(__uint_as_float(c.x), __uint_as_float(c.y), __uint_as_float(c.z));
+                        ro = rt3m::v3(r.ox, r.oy, r.oz); rd = rt3m::v3(r.dx, r.dy, r.dz);
+                    }
+                    if (rt3m::ray_triangle(ro, rd, v0, e1, e2, t, u, v) && t > r.tmin && t < ray_tmax) {
                         if (ANY) { found_any = true; tg_hits = 0; }
-                        else if (rt3m::closer_hit(t, a.w, h.t, h.prim)) { h.t = t; h.u = u; h.v = v; h.prim = a.w; }
+                        else if (rt3m::closer_hit(t, prim, h.t, h.prim)) { h.t = t; h.u = u; h.v = v; h.prim = prim; }
                     }
                 }
             }
             if (active && (found_any || (tg_hits == 0u && ng_hits <= 0x00FFFFFFu))) {
-                if (found_any || sp == 0) {
+                bool done = found_any;
+                while (!done && tg_hits == 0u && ng_hits <= 0x00FFFFFFu) {     /* pop; more than once only across a sentinel */
+                    if (sp == 0) { done = true; break; }
+                    uint32_t eb, eh;
+                    RT3_POP(eb, eh);
+                    if (TWO && eb == RT3_STACK_SENTINEL && eh == 0u) {
+                        cur_inst = RT3_STACK_SENTINEL;
+                        rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
+                        r = prepare_ray(wr, magic);
+                        continue;
+                    }
+                    if (!TWO || eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; ng_hits = 0u; }
+                }
+                if (done) {
                     if (ANY) { if (found_any) atomicOr(bits + (my_index >> 5), 1u << (my_index & 31u)); }
                     else __stcs((float4*)(hits + my_index), make_float4(h.t, h.u, h.v, __uint_as_float(h.prim)));
                     active = false;
-                } else {
-                    sp--;
-#if RT3_SMEM_STACK > 0
-                    if (sp < RT3_SMEM_STACK) { const uint2 e = s_stack[sp][threadIdx.x]; ng_base = e.x; ng_hits = e.y; }
-                    else { ng_base = stack_base[sp - RT3_SMEM_STACK]; ng_hits = stack_hits[sp - RT3_SMEM_STACK]; }
-#else
-                    ng_base = stack_base[sp]; ng_hits = stack_hits[sp];
-#endif
                 }
             }
         } while (__popc(__ballot_sync(0xFFFFFFFFu, active)) >= keep);
     }
+#undef RT3_PUSH
+#undef RT3_POP
 }
 
 __global__ void __launch_bounds__(256) k_l2_sweep(const uint4* __restrict__ buf, size_t n_vec, int reps, uint4* sink) {
@@ -231,19 +257,18 @@ void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, ui
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * waves, (n_max + TRACE_THREADS - 1) / TRACE_THREADS);
     const WideNode* nodes = c->bvh_nodes.as<WideNode>();
     const Tri48* tris = c->bvh_tris.as<Tri48>();
+    const InstRec* insts = c->two_level ? c->d_insts.as<InstRec>() : nullptr;
     if (legacy) {
-        RT3_LAUNCH(c, (k_trace<ANY, false>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w, (unsigned long long*)nullptr);
+        RT3_LAUNCH(c, (k_trace<ANY, false>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w, (unsigned long long*)nullptr, insts);
         return;
     }
     if (ANY) RT3_CUDA(c, cudaMemsetAsync(bits, 0, ((n_max + 31) / 32) * 4, st));
-    static const int tris_per_iter = env_int("RT3_TRACE_TRIS", 1);
-#define RT3_DYN(K, T) RT3_LAUNCH(c, (k_trace_dyn<ANY, K, T>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w, 0x47000000u)
-    if (tris_per_iter == 2) {
-        if (keep == 16) RT3_DYN(16, 2); else if (keep == 28) RT3_DYN(28, 2); else RT3_DYN(24, 2);
-    } else {
-        if (keep == 16) RT3_DYN(16, 1); else if (keep == 20) RT3_DYN(20, 1); else if (keep == 28) RT3_DYN(28, 1); else if (keep == 32) RT3_DYN(32, 1);
-        else RT3_DYN(24, 1);
-    }
+#define RT3_DYN(K, T) RT3_LAUNCH(c, (k_trace_dyn<ANY, K, T>), grid, TRACE_THREADS, 0, st, nodes, tris, rays, d_count, n_max, hits, bits, w, 0x47000000u, insts)
+    if (c->two_level) RT3_DYN(28, true);
+    else if (keep == 16) RT3_DYN(16, false);
+    else if (keep == 24) RT3_DYN(24, false);
+    else if (keep == 32) RT3_DYN(32, false);
+    else RT3_DYN(28, false);
 #undef RT3_DYN
 }
 
@@ -269,7 +294,7 @@ void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3
     rt3_hit* hits = ensure<rt3_hit>(c, c->f_hits, n);
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * 12, (n + TRACE_THREADS - 1) / TRACE_THREADS);
     RT3_LAUNCH(c, (k_trace<false, true>), grid, TRACE_THREADS, 0, st, c->bvh_nodes.as<WideNode>(), c->bvh_tris.as<Tri48>(), rays, (const uint32_t*)nullptr, n, hits,
-               (uint32_t*)nullptr, w, w + 1);
+               (uint32_t*)nullptr, w, w + 1, c->two_level ? c->d_insts.as<InstRec>() : (const InstRec*)nullptr);
     unsigned long long h[3];
     RT3_CUDA(c, cudaMemcpy(h, w, sizeof(h), cudaMemcpyDeviceToHost));
     out->nodes_per_ray = (double)h[1] / (double)n;

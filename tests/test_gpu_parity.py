@@ -213,6 +213,71 @@ def test_glb_imported_scene_renders_like_the_original(gpu_ctx):
     assert (outs[1][1][..., 0] != MISS).mean() > 0.2
 
 
+def _instanced_scene():
+    """Nine placements of one small atrium: translations, a rotation about Y with non-uniform scale, a mirrored copy."""
+    base = scenes.synthetic_atrium(0.012, environment=False)
+    sc = scenes.instanced_grid(base, 3)
+    inst = list(sc["instances"])
+    c, s_ = np.cos(0.7), np.sin(0.7)
+    f, n, m = inst[4]
+    m = m.copy(); m[[0, 2, 8, 10]] = [1.3 * c, 0.8 * s_, -1.3 * s_, 0.8 * c]; m[5] = 1.1
+    inst[4] = (f, n, m)
+    f, n, m = inst[7]
+    m = m.copy(); m[0] = -1.0
+    inst[7] = (f, n, m)
+    sc["instances"] = inst
+    return sc
+
+
+def test_two_level_build_matches_flattened_and_oracle(gpu_ctx):
+    """RT3_BUILD_TWO_LEVEL (BLAS per distinct mesh + TLAS over instances): hits, G-buffer and radiance bit-identical to the
+    flattened single-level structure and to the CPU oracle (which always flattens)."""
+    from raytracer3_b200.host import Renderer, RenderWorld
+    from raytracer3_b200.types import BUILD_TWO_LEVEL
+    sc = _instanced_scene()
+    orc = _oracle(sc)
+    c, a = scenes.incoherent_rays(sc, 30000, seed=21)
+    rays = np.concatenate([c, scenes.random_rays(sc, 30000, seed=22)])
+    want, want_any = orc.trace_closest(rays), orc.trace_any(a)
+    W, H = 320, 184
+    p = make_params(camera_for(sc, "cam_grid", W, H), W, H, frame=2, bounces=4, samples=1)
+    gb, dp, oids, _ = orc.pass_gbuffer(p)
+    olight, _ = orc.pass_reference(p, gb, dp)
+    sizes = {}
+    for flags in (1, 1 | BUILD_TWO_LEVEL):
+        w = RenderWorld(gpu_ctx)
+        w.clear()
+        w.load_scene(sc)
+        bs = w.create_acceleration_structure(flags)
+        sizes[flags] = bs.node_bytes + bs.tri_bytes
+        got = w.trace_closest_host(rays)
+        assert (got["prim"] == want["prim"]).all(), (flags, int((got["prim"] != want["prim"]).sum()))
+        for f in ("t", "u", "v"):
+            assert (_bits(got[f]) == _bits(want[f])).all(), (flags, f)
+        assert (w.trace_any_host(a) == want_any).all(), flags
+        r = Renderer(gpu_ctx, w, W, H)
+        light = r.frame(p, debug_ids=True).cpu().numpy()
+        assert (r.rg.tensor("ids").cpu().numpy().view(np.uint32) == oids).all(), flags
+        assert (_bits(r.rg.tensor("gbuffer_depth").cpu().numpy()) == _bits(dp)).all(), flags
+        assert (_bits(light) == _bits(olight)).all(), flags
+    assert (want["prim"] != MISS).mean() > 0.3
+    assert sizes[1 | BUILD_TWO_LEVEL] * 4 < sizes[1]                  # one mesh stored once instead of nine times
+    # no instances pushed: the flag falls back to the single-level build
+    w = RenderWorld(gpu_ctx)
+    w.clear()
+    w.load_scene(scenes.cornell_box())
+    assert w.create_acceleration_structure(1 | BUILD_TWO_LEVEL).triangles == 36
+    # singular instance transform is an error in two-level mode
+    bad = _instanced_scene()
+    f, n, m = bad["instances"][0]
+    bad["instances"][0] = (f, n, np.zeros(12, np.float32))
+    from raytracer3_b200 import _lib
+    w.clear()
+    w.load_scene(bad)
+    with pytest.raises(_lib.Rt3Error):
+        w.create_acceleration_structure(1 | BUILD_TWO_LEVEL)
+
+
 def test_errors_are_returned_not_raised_across_abi(gpu_ctx):
     from raytracer3_b200 import _lib
     from raytracer3_b200.host import RenderWorld
