@@ -274,8 +274,19 @@ struct WideBuild {
     uint32_t nodes_end = 0, recs_end = 0, levels = 0; float sah_nodes = 0.f, sah_recs = 0.f;   /* results */
 };
 
+#include <chrono>
+static void dbg_mark(const char* what) {
+    static const bool on = getenv("RT3_BUILD_DEBUG") != nullptr;
+    static auto t0 = std::chrono::steady_clock::now();
+    if (!on) return;
+    cudaDeviceSynchronize();
+    auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[build] %-24s +%.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = std::chrono::steady_clock::now();
+}
 static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build_stats& bs, int* d_misc) {
     const uint32_t n = io.n;
+    dbg_mark("enter build_wide");
     StageTimer tm(c, st);
     PoolBuf s_sorted, s_keys[2], s_vals[2], s_hist, s_nodes2, s_parent, s_flags, s_counts, s_items[2];
     auto cleanup = [&]() {
@@ -296,6 +307,7 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
                                  hi[2] > lo[2] ? 1.0f / (hi[2] - lo[2]) : 0.f);
         RT3_LAUNCH(c, k_morton, div_up(n, 256), 256, 0, st, tris, n, io.kind, flo, inv, keys0, vals0);
         bs.ms_morton += tm.end();
+        dbg_mark("morton");
         /* sort */
         const uint32_t nblocks = div_up(n, RADIX_TILE);
         uint32_t* hist = palloc<uint32_t>(c, s_hist, 256 * (size_t)nblocks, st);
@@ -310,7 +322,9 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         Tri48* sorted = palloc<Tri48>(c, s_sorted, n, st);
         RT3_LAUNCH(c, k_gather_sorted, div_up(n, 256), 256, 0, st, tris, vals0, n, sorted);
         bs.ms_sort += tm.end();
+        dbg_mark("sort");
         io.recs->release();
+        dbg_mark("release recs");
         /* hierarchy */
         Bvh2Node* nodes2 = palloc<Bvh2Node>(c, s_nodes2, 2 * (size_t)n, st);
         uint32_t* parent = palloc<uint32_t>(c, s_parent, 2 * (size_t)n, st);
@@ -322,9 +336,11 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         RT3_CUDA(c, cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n, st));
         if (n > 1) RT3_LAUNCH(c, k_lbvh_hierarchy, div_up(n - 1, 256), 256, 0, st, keys0, (int)n, nodes2, parent);
         bs.ms_hierarchy += tm.end();
+        dbg_mark("hierarchy");
         tm.begin();
         RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts);
         bs.ms_refit += tm.end();
+        dbg_mark("refit");
         s_keys[0].release(); s_keys[1].release(); s_vals[0].release(); s_vals[1].release(); s_hist.release(); s_parent.release(); s_flags.release();
         /* collapse */
         uint32_t* items0 = palloc<uint32_t>(c, s_items[0], 2 * (size_t)n + 2, st);
@@ -353,6 +369,7 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         uint32_t fin[8];
         RT3_CUDA(c, cudaMemcpyAsync(fin, ctr, sizeof(fin), cudaMemcpyDeviceToHost, st));
         bs.ms_collapse += tm.end();
+        dbg_mark("collapse");
         if (fin[1] != io.first_free_rec + n) RT3_FAIL(c, RT3_ERR_STATE, "BVH collapse lost leaf records");
         io.nodes_end = fin[0]; io.recs_end = fin[1]; io.levels = levels;
         memcpy(&io.sah_nodes, &fin[4], 4); memcpy(&io.sah_recs, &fin[5], 4);
@@ -361,6 +378,7 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         throw;
     }
     cleanup();
+    dbg_mark("cleanup");
 }
 
 static void read_bounds(rt3_context* c, cudaStream_t st, const int* d_bounds, float lo[3], float hi[3]) {
@@ -389,7 +407,9 @@ static bool invert_affine(const float m[12], float out[12]) {
 static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs) {
     const uint32_t n = c->n_triangles;
     StageTimer tm(c, st);
+    dbg_mark("enter single");
     Tri48* out_tris = ensure<Tri48>(c, c->bvh_tris, n);
+    dbg_mark("ensure tris");
     PoolBuf s_tris, s_misc;
     try {
         Tri48* tris = palloc<Tri48>(c, s_tris, n, st);
@@ -400,6 +420,7 @@ static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats&
         float lo[3], hi[3];
         read_bounds(c, st, d_misc, lo, hi);
         bs.ms_flatten += tm.end();
+        dbg_mark("flatten");
         for (int k = 0; k < 3; ++k) { bs.scene_lo[k] = lo[k]; bs.scene_hi[k] = hi[k]; }
         WideBuild io;
         io.recs = &s_tris; io.n = n; io.kind = REC_TRI_EDGES; io.pad = max_extent(lo, hi) * (1.0f / 65536.0f);

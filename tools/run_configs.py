@@ -126,25 +126,34 @@ def cfg4(ctx, log2n=25):
 
 
 def cfg5(ctx, grid=8):
-    """configs[4] on ONE GPU: grid x grid instanced atrium flattened to one BVH (build time) + 1080p 4-bounce path tracing."""
+    """configs[4] on ONE GPU: grid x grid instanced atrium, flattened single-level BVH and two-level (shared BLAS + TLAS over the
+    instances): build time + 1080p 4-bounce path tracing for both; the two images must be bit-identical."""
+    from raytracer3_b200.types import BUILD_TWO_LEVEL
     base = atrium()
     sc = scenes.instanced_grid(base, grid)
     w = RenderWorld(ctx); w.clear(); w.load_scene(sc)
-    bs = w.create_acceleration_structure()
-    bs2 = w.create_acceleration_structure()      # second build: allocations warm
     W, H = 1920, 1080
-    r = Renderer(ctx, w, W, H)
     cam = camera_for(sc, "cam_grid", W, H)
-    def frame(n):
-        r.frame(make_params(cam, W, H, frame=n, bounces=4, samples=1, flags=FLAGS))
-    for n in range(3):
-        frame(n)
-    ctx.counters(reset=True)
-    ms = timed(frame, 20)
-    c = ctx.counters(reset=True)
-    rays = (c.rays_primary + c.rays_secondary) / 20
-    return {"config": f"cfg5 {grid}x{grid} instanced synthetic_atrium flattened, 1 GPU", "triangles": bs.triangles, "build_first": bs.as_dict(), "build_warm": bs2.as_dict(),
-            "frame_ms": ms, "rays_per_frame": rays, "mrays_s": rays / ms / 1e3}
+    out = {"config": f"cfg5 {grid}x{grid} instanced synthetic_atrium, 1 GPU"}
+    images = []
+    for tag, flags in (("flattened", 1), ("two_level", 1 | BUILD_TWO_LEVEL)):
+        bs = w.create_acceleration_structure(flags)
+        bs2 = w.create_acceleration_structure(flags)      # second build: allocations warm
+        r = Renderer(ctx, w, W, H)
+        def frame(n):
+            return r.frame(make_params(cam, W, H, frame=n, bounces=4, samples=1, flags=FLAGS))
+        for n in range(3):
+            frame(n)
+        ctx.counters(reset=True)
+        ms = timed(frame, 20)
+        c = ctx.counters(reset=True)
+        rays = (c.rays_primary + c.rays_secondary) / 20
+        images.append(frame(5).clone())
+        out[tag] = {"triangles": bs.triangles, "bvh_mb": (bs2.node_bytes + bs2.tri_bytes) / 1e6, "build_first": bs.as_dict(), "build_warm": bs2.as_dict(),
+                    "frame_ms": ms, "rays_per_frame": rays, "mrays_s": rays / ms / 1e3}
+        del r
+    out["images_bit_identical"] = bool(torch.equal(images[0].view(torch.int32), images[1].view(torch.int32)))
+    return out
 
 
 if __name__ == "__main__":
