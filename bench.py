@@ -191,7 +191,7 @@ def run_cuda(args):
     def step(i):
         p = params_for(sc, W, H, i, flags)
         if tiled:
-            return R.gather(R.frame(p))
+            return R.frame_gather_overlapped(p)     # the NCCL gather + un-tile of frame i overlap the tracing of frame i+1
         return R.frame(p)
 
     def barrier():
@@ -211,6 +211,8 @@ def run_cuda(args):
         ev0.record()
         for i in range(args.steps):
             step(args.warmup + i)
+        if tiled:
+            R.drain()                                # the last frame's gather must be inside the timed region
         ev1.record()
         barrier()
         ms = ev0.elapsed_time(ev1)
@@ -225,14 +227,28 @@ def run_cuda(args):
         FRAMES_IN_FLIGHT = 3                                   # the reference's swapchain.rs:8
         host_ring = [host_light] + [torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() for _ in range(FRAMES_IN_FLIGHT - 1)] if not tiled else []
         tickets = []
+        shm_path = None
+        if tiled:
+            # one host framebuffer ring shared by the ranks of the node (POSIX shared memory, page-locked in every process): each
+            # rank reads back its own band of rows of the gathered frame, so D2H per GPU stays at 1920x1080x16 B for every N
+            shm_path = f"/dev/shm/rt3_bench_{os.environ.get('MASTER_PORT', '0')}_{W}x{H}"
+            nbytes = FRAMES_IN_FLIGHT * H * W * 16
+            if rank == 0:
+                with open(shm_path, "wb") as f:
+                    f.truncate(nbytes)
+            barrier()
+            shared = torch.from_file(shm_path, shared=True, size=FRAMES_IN_FLIGHT * H * W * 4, dtype=torch.float32).view(FRAMES_IN_FLIGHT, H, W, 4)
+            err = torch.cuda.cudart().cudaHostRegister(shared.data_ptr(), nbytes, 0)
+            assert int(err) == 0, f"cudaHostRegister failed: {err}"
+            band = H // world_size
+            R.enable_host_output([shared[k] for k in range(FRAMES_IN_FLIGHT)], rank * band, H if rank == world_size - 1 else (rank + 1) * band)
 
         def e2e_step(i):
             p = params_for(sc, W, H, i, flags)
-            if tiled:
-                fb = R.gather(R.frame(p))                       # params go H2D inside the pass calls
-                if rank == 0:
-                    host_light.copy_(fb, non_blocking=True)
-                torch.cuda.synchronize()
+            if tiled:                                           # params go H2D inside the pass calls
+                tickets.append(R.submit_frame_host(p))
+                if len(tickets) >= FRAMES_IN_FLIGHT:
+                    R.wait_frame(tickets.pop(0))
             else:
                 # frames in flight: frame i renders while frame i-1 is read back; a frame's host buffer is handed back after its wait
                 tickets.append(R.submit_frame_host(p, host_ring[i % FRAMES_IN_FLIGHT].data_ptr()))
@@ -254,6 +270,17 @@ def run_cuda(args):
         barrier()
         e2e_s = time.perf_counter() - t0
         e2e_cnt = ctx.counters(reset=True)
+        e2e_verified = None
+        if tiled:
+            # outside the timed region: the frame assembled in shared host memory from the ranks' bands == the gathered device frame
+            k_last = (R.next_ticket - 1) % FRAMES_IN_FLIGHT
+            if rank == 0:
+                e2e_verified = bool(torch.equal(shared[k_last], R.frame_ring[k_last].cpu()))
+                assert e2e_verified, "host frame assembled from the ranks' row bands differs from the gathered device frame"
+            torch.cuda.cudart().cudaHostUnregister(shared.data_ptr())
+            barrier()
+            if rank == 0:
+                os.unlink(shm_path)
         sync_e2e_ms = None
         if not tiled:                                          # also the synchronous single-call path, for comparison
             t1 = time.perf_counter()
@@ -292,8 +319,9 @@ def run_cuda(args):
                     "d2h_bytes_per_step": W * H * 16, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "path": "rt3_frame_submit_host / rt3_frame_wait, 3 frames in flight (params H2D, RGBA32F frame D2H to pinned memory, every frame "
                             "waited for inside the timed region)" if not tiled else
-                            "rt3_pass_*_tiles + all_gather + rt3_untile + full-frame D2H on rank 0",
-                    "sync_ms_per_step": sync_e2e_ms},
+                            "rt3_pass_*_tiles + all_gather + rt3_untile, 3 frames in flight; every rank reads its band of rows of the gathered frame back "
+                            "into one page-locked host frame shared by the ranks (POSIX shm), every frame waited for inside the timed region",
+                    "sync_ms_per_step": sync_e2e_ms, "host_frame_verified": e2e_verified},
             "gpu_launches": int(launches_all),
             "roofline": {"kernel": "k_trace<closest> (secondary-ray queues)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "bytes_per_ray": HBM_BYTES_PER_RAY,

@@ -102,7 +102,7 @@ struct rt3_context {
     rt3_build_stats last_build;
 
     /* pass scratch */
-    Scratch q_rays[2], q_hits, q_thr[2], q_pix[2], q_pdf[2], q_srays, q_scontrib, q_sbits, px_radiance, px_rng, d_counts, d_rects, d_params;
+    Scratch q_rays[2], q_hits, q_thr[2], q_pix[2], q_pdf[2], q_srays, q_scontrib, q_sbits, px_radiance, px_rng, d_counts, d_rects, d_untile_rects, d_params;   /* d_untile_rects: un-tiling may run on another stream than the passes */
     Scratch f_gbuffer, f_depth, f_light, f_prev, f_rays, f_hits, f_bits, l2_buf;
     DeviceCounters* d_counters = nullptr;
     cudaEvent_t ev[8];

@@ -411,7 +411,13 @@ class TiledRenderer:
         self.light = [torch.zeros((n, tile, tile, 4), dtype=torch.float32, device=dev) for _ in range(2)]
         self.gathered = torch.zeros((world_size * n, tile, tile, 4), dtype=torch.float32, device=dev) if world_size > 1 else None
         self.frame_buf = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
+        self.frame_ring = [self.frame_buf]      # grown to FRAMES_IN_FLIGHT by enable_host_output
         self.cur = 0
+        # the gather of frame i (side stream) overlaps the rendering of frame i+1 (caller's stream)
+        self.side = torch.cuda.Stream(device=dev)
+        self.ev_rendered_slab = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ev_gathered_slab = [None, None]
+        self.ev_last_gather = None
         self.pixels = int((self.rects["w"].astype(np.int64) * self.rects["h"]).sum())
 
     def frame(self, gconst):
@@ -423,6 +429,67 @@ class TiledRenderer:
                                                    prev.data_ptr(), light.data_ptr(), st))
         self.cur = 1 - self.cur
         return light
+
+    def frame_gather_overlapped(self, gconst):
+        """frame() on the current stream, gather() + un-tile on the side stream: NCCL traffic and the un-tile of frame i run while
+        frame i+1 is traced.  The Light slab a frame writes is the one gathered two frames earlier, so the current stream first
+        waits for that gather.  Call drain() before reading frame_buf or stopping a clock."""
+        torch = _torch()
+        cur = torch.cuda.current_stream()
+        c = self.cur
+        if self.ev_gathered_slab[c] is not None:
+            cur.wait_event(self.ev_gathered_slab[c])
+        light = self.frame(gconst)
+        self.ev_rendered_slab[c].record(cur)
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(self.ev_rendered_slab[c])
+            fb = self.gather(light)
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+        self.ev_gathered_slab[c] = ev
+        self.ev_last_gather = ev
+        return fb
+
+    def drain(self):
+        if self.ev_last_gather is not None:
+            _torch().cuda.current_stream().wait_event(self.ev_last_gather)
+
+    # ---- end-to-end host output, frames in flight (swapchain.rs:8) ------------------------------------------------------
+    def enable_host_output(self, host_frames, row0, row1):
+        """`host_frames`: FRAMES_IN_FLIGHT pinned host tensors [H, W, 4] (shared between the ranks of a node: every rank reads
+        back ITS band of rows [row0, row1) of the gathered frame over its own PCIe link, so the read-back does not grow with
+        the number of GPUs)."""
+        torch = _torch()
+        self.host_frames, self.row0, self.row1 = host_frames, row0, row1
+        n = len(host_frames)
+        self.frame_ring = [self.frame_buf] + [torch.zeros_like(self.frame_buf) for _ in range(n - 1)]
+        self.ev_copied = [torch.cuda.Event() for _ in range(n)]
+        self.busy = [False] * n
+        self.next_ticket = 0
+
+    def submit_frame_host(self, gconst):
+        torch = _torch()
+        t = self.next_ticket
+        k = t % len(self.host_frames)
+        if self.busy[k]:
+            self.ev_copied[k].synchronize()
+            self.busy[k] = False
+        self.frame_buf = self.frame_ring[k]
+        fb = self.frame_gather_overlapped(gconst)            # gather + un-tile on the side stream ...
+        with torch.cuda.stream(self.side):                    # ... followed there by this rank's band of the read-back
+            self.host_frames[k][self.row0:self.row1].copy_(fb[self.row0:self.row1], non_blocking=True)
+            self.ev_copied[k].record(self.side)
+        self.busy[k] = True
+        self.next_ticket = t + 1
+        return t
+
+    def wait_frame(self, ticket):
+        lo = max(0, self.next_ticket - len(self.host_frames))
+        for t in range(lo, ticket + 1):
+            k = t % len(self.host_frames)
+            if self.busy[k]:
+                self.ev_copied[k].synchronize()
+                self.busy[k] = False
 
     def gather(self, light):
         """One all_gather of the rank-local slabs + un-tile into the full frame (every rank gets the image)."""
