@@ -167,6 +167,20 @@ RT3_API rt3_status rt3_pass_reference(rt3_context*, const rt3_params*, rt3_rect,
 RT3_API rt3_status rt3_pass_postprocess(rt3_context*, const rt3_params*, rt3_rect, const float* depth_r32f,
                                         const float* in_rgba32f, float* out_rgba32f, void* cuda_stream);
 
+/* Screen-space probe GI: shaders/old/trace_probes.slang, spherical_harmonic_conversion.slang,
+ * interpolate_probes.slang.  One probe per 16x16 pixels, 8x8 octahedral directions per probe.
+ *   atlas       (W/16*8) x (H/16*8) RGBA32F: rgb = radiance along the direction (blended with prev_atlas by blendfactor), a = hit distance
+ *   directions  optional u16 per atlas texel (structured_importance_sampling.slang:55-69: bit 15 = mip, low bits = direction index);
+ *               NULL = the uniform assignment (texel k of a probe traces octahedral cell k)
+ *   sh          rt3_probe_layout().sh_records records of 9 floats (float3x3 = SH L2), Z-curve indexed by (probe.x * 3 + channel, probe.y)
+ * The probe shaders of the reference are in a debug state; include/rt3_shared_math.h documents line by line what is restated. */
+RT3_API rt3_status rt3_probe_layout(const rt3_params*, uint32_t* atlas_w, uint32_t* atlas_h, uint32_t* sh_records);
+RT3_API rt3_status rt3_pass_probe_trace(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, const float* depth_r32f,
+                                        const uint16_t* opt_directions_r16ui, const float* prev_atlas_rgba32f, float* atlas_rgba32f, void* cuda_stream);
+RT3_API rt3_status rt3_pass_probe_sh(rt3_context*, const rt3_params*, const float* atlas_rgba32f, float* sh, void* cuda_stream);
+RT3_API rt3_status rt3_pass_probe_interpolate(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, const float* depth_r32f,
+                                              const float* sh, float* light_rgba32f, void* cuda_stream);
+
 /* Multi-tile variants used for screen-tile sharding across GPUs.  `tiles` is a HOST array of
  * n_tiles rects (all inside the frame).  Images are rank-local tile-major SLABS: tile k occupies
  * elements [k*tile_w*tile_h, (k+1)*tile_w*tile_h) row-major inside the tile, where tile_w/tile_h

@@ -983,6 +983,201 @@ RT3_HD vec3 temporal_blend(vec3 prev, vec3 radiance, float blendfactor) {
               prev.z + (radiance.z - prev.z) * blendfactor);
 }
 
+/* ---------------------------------------------------------------- screen-space probe GI (row F4) ----
+ * shaders/old/{structured_importance_sampling,trace_probes,spherical_harmonic_conversion,interpolate_probes}.slang and
+ * shaders/include/spherical_harmonics.slang.  One probe per 16x16 pixels (anchored at the tile's first pixel), 8x8 octahedral
+ * directions per probe in an atlas of (W/16*8) x (H/16*8) RGBA32F texels, projected to 3 x SH-L2 per probe, interpolated per
+ * pixel from the 4 surrounding probes.  The reference's probe shaders are in a debug state (trace_probes.slang:75 writes the
+ * direction as a colour; the importance-sampling pass refines nothing because its culling test `brdf_pdf < 0` never holds):
+ * where a line is debug output, the intended expression that stands commented beside it is the one restated, and it is
+ * said so at the line. */
+RT3_HD float sign_step(float v) { return (v >= 0.0f) ? 1.0f : -1.0f; }               /* step(0, v) * 2 - 1 */
+RT3_HD vec2 octa_wrap(vec2 v) {                                                      /* packing.slang:64-66 */
+    vec2 r; r.x = (1.0f - abs_(v.y)) * sign_step(v.x); r.y = (1.0f - abs_(v.x)) * sign_step(v.y); return r;
+}
+RT3_HD vec2 octa_encode(vec3 n) {                                                    /* packing.slang:68-75 */
+    float k = abs_(n.x) + abs_(n.y) + abs_(n.z);
+    vec2 e; e.x = n.x / k; e.y = n.y / k;
+    if (n.z / k < 0.0f) e = octa_wrap(e);
+    e.x = e.x * 0.5f + 0.5f; e.y = e.y * 0.5f + 0.5f;
+    return e;
+}
+RT3_HD vec3 octa_decode(vec2 f) {                                                    /* packing.slang:77-86 */
+    float fx = f.x * 2.0f - 1.0f, fy = f.y * 2.0f - 1.0f;
+    vec3 n = v3(fx, fy, 1.0f - abs_(fx) - abs_(fy));
+    float t = clamp_(-n.z, 0.0f, 1.0f);
+    n.x = n.x - sign_step(n.x) * t;
+    n.y = n.y - sign_step(n.y) * t;
+    return normalize(n);
+}
+RT3_HD vec3 world_pos_from_depth(float depth, uint32_t px, uint32_t py, const rt3_params& p) {   /* gbuffer_helpers.slang:81-83 */
+    vec3 c = camera_position(p), d = view_dir(px, py, p);
+    return v3(c.x + d.x * depth, c.y + d.y * depth, c.z + d.z * depth);
+}
+/* sh3 = float3x3 (spherical_harmonics.slang:9), row-major c[3*row + col] */
+struct sh3 { float c[9]; };
+RT3_HD sh3 sh3_evaluate(vec3 d) {                                                    /* spherical_harmonics.slang:32-46 */
+    sh3 r;
+    r.c[0] = 0.28209479177387814347403972578039f;
+    r.c[1] = -0.48860251190291992158638462283836f * d.y;
+    r.c[2] = 0.48860251190291992158638462283836f * d.z;
+    r.c[3] = -0.48860251190291992158638462283836f * d.x;
+    r.c[4] = 1.09254843059207907054338570580268f * d.x * d.y;
+    r.c[5] = 1.09254843059207907054338570580268f * d.y * d.z;
+    r.c[6] = 0.31539156525252000603089369029571f * (3.0f * d.z * d.z - 1.0f);
+    r.c[7] = 1.09254843059207907054338570580268f * d.x * d.z;
+    r.c[8] = 0.54627421529603953527169285290134f * (d.x * d.x - d.y * d.y);
+    return r;
+}
+RT3_HD float sh3_dot(const sh3& a, const sh3& b) {                                   /* matrix_dot, spherical_harmonics.slang:61-65 (left to right) */
+    float r = a.c[0] * b.c[0];
+    for (int i = 1; i < 9; ++i) r = r + a.c[i] * b.c[i];
+    return r;
+}
+RT3_HD sh3 sh3_transform_cos_lobe(vec3 normal) {                                     /* spherical_harmonics.slang:74-91 */
+    sh3 s = sh3_evaluate(normal);
+    s.c[0] *= 3.1415926536f;
+    s.c[1] *= 2.0943951023931954923f; s.c[2] *= 2.0943951023931954923f; s.c[3] *= 2.0943951023931954923f;
+    for (int i = 4; i < 9; ++i) s.c[i] *= 0.7853981633974483096f;
+    return s;
+}
+RT3_HD vec3 sh3_unproject_cos_lobe(const sh3& r, const sh3& g, const sh3& b, vec3 normal) {   /* spherical_harmonics.slang:106-110 */
+    sh3 s = sh3_transform_cos_lobe(normal);
+    return v3(sh3_dot(r, s), sh3_dot(g, s), sh3_dot(b, s));
+}
+/* Probe-atlas geometry for a W x H frame. */
+RT3_HD uint32_t probe_count_x(const rt3_params& p) { return (uint32_t)p.window_size[0] / 16u; }
+RT3_HD uint32_t probe_count_y(const rt3_params& p) { return (uint32_t)p.window_size[1] / 16u; }
+/* Direction word of an atlas texel (structured_importance_sampling.slang:55-69): bit 15 = mip, low 15 bits = direction index on
+ * a grid of (8 << mip)^2 cells.  The reference's refinement never triggers (see above), leaving the uniform assignment of its
+ * else-branch (:67): mip 0, index = thread index inside the probe. */
+RT3_HD uint32_t probe_uniform_direction(uint32_t ax, uint32_t ay) { return (ay & 7u) * 8u + (ax & 7u); }
+struct ProbeRay { rt3_ray ray; uint32_t target_x, target_y; bool background; };
+/* trace_probes.slang:16-56: the ray of atlas texel (ax, ay). */
+RT3_HD ProbeRay probe_setup_ray(const rt3_params& p, uint32_t ax, uint32_t ay, float probe_pixel_depth, uint32_t direction_word) {
+    ProbeRay o;
+    const uint32_t pcx = ax / 8u, pcy = ay / 8u;                                     /* :18 */
+    const uint32_t px = pcx * 16u, py = pcy * 16u;                                   /* :23 */
+    o.background = probe_pixel_depth == RT3_BACKGROUND_DEPTH;                        /* :28 */
+    RandomSamplerState rng = rng_init(ax, ay, p.frame);                              /* :21 ray_rng */
+    const uint32_t index = direction_word & 0x7FFFu, mip = direction_word >> 15;     /* :40-42 */
+    const uint32_t size = (1u << mip) * 8u;
+    const float dx = float(index % size), dy = float(index / size);                  /* :44 */
+    const float u0 = rng_uniform_float(rng), u1 = rng_uniform_float(rng);            /* :46, x drawn first */
+    vec2 f; f.x = (dx + u0) / float(size); f.y = (dy + u1) / float(size);
+    const vec3 dir = octa_decode(f);
+    const vec3 org = world_pos_from_depth(probe_pixel_depth, px, py, p);             /* :52 */
+    o.ray.o[0] = org.x; o.ray.o[1] = org.y; o.ray.o[2] = org.z; o.ray.tmin = 0.0005f;   /* :54 */
+    o.ray.d[0] = dir.x; o.ray.d[1] = dir.y; o.ray.d[2] = dir.z; o.ray.tmax = RT3_BACKGROUND_DEPTH;
+    o.target_x = pcx * 8u + (uint32_t)(dx / float(size) * 8.0f);                     /* :75 (target texel of the debug line) */
+    o.target_y = pcy * 8u + (uint32_t)(dy / float(size) * 8.0f);
+    return o;
+}
+/* trace_probes.slang:58-75: the texel value.  :75 writes the direction as a debug colour; restated is the expression
+ * commented beside it: float4(lerp(prev.xyz, radiance, blendfactor), probe_depth) with radiance = the hit's emission (:63).
+ * A miss (the reference reads hit_info of an unwritten payload there: undefined) is DEFINED as radiance 0, or the sky with
+ * RT3_FLAG_ENV, at depth BACKGROUND_DEPTH. */
+RT3_HD vec4 probe_texel(const SceneView& s, const rt3_params& p, const rt3_ray& ray, const rt3_hit& h, vec3 prev) {
+    vec3 radiance = v3(0.f, 0.f, 0.f);
+    float depth = RT3_BACKGROUND_DEPTH;
+    if (h.prim != RT3_MISS) { radiance = hit_info(s, h.prim, h.u, h.v).emissive; depth = h.t; }
+    else if (p.flags & RT3_FLAG_ENV) radiance = sample_environment(s, v3(ray.d));
+    vec3 o = temporal_blend(prev, radiance, p.blendfactor);
+    vec4 r; r.x = o.x; r.y = o.y; r.z = o.z; r.w = depth;
+    return r;
+}
+/* spherical_harmonic_conversion.slang:11-32 for one (probe, colour channel): sum over the 64 directions in index order (the
+ * shader's WaveActiveSum leaves the order to the hardware and covers 64 lanes only on wave64 parts), times 4 pi / 64. */
+RT3_HD sh3 probe_project_sh(const float* atlas_rgba, uint32_t atlas_w, uint32_t pcx, uint32_t pcy, uint32_t channel) {
+    sh3 acc;
+    for (int i = 0; i < 9; ++i) acc.c[i] = 0.0f;
+    for (uint32_t k = 0; k < 64u; ++k) {
+        vec2 f; f.x = (float(k % 8u) + 0.5f) / 8.0f; f.y = (float(k / 8u) + 0.5f) / 8.0f;       /* :13-14 */
+        const sh3 b = sh3_evaluate(octa_decode(f));
+        const float v = atlas_rgba[4u * ((size_t)(pcy * 8u + k / 8u) * atlas_w + (pcx * 8u + k % 8u)) + channel];   /* :16 */
+        for (int i = 0; i < 9; ++i) acc.c[i] = acc.c[i] + b.c[i] * v;
+    }
+    const float factor = 4.0f * 3.1415926536f / 64.0f;                                            /* :25 */
+    for (int i = 0; i < 9; ++i) acc.c[i] = acc.c[i] * factor;
+    return acc;
+}
+RT3_HD uint32_t probe_sh_index(uint32_t pcx, uint32_t pcy, uint32_t channel) { return zcurve_to_linear_index(pcx * 3u + channel, pcy); }   /* :29-31 */
+RT3_HD uint32_t probe_sh_capacity(const rt3_params& p) {       /* number of sh3 records addressed by probe_sh_index */
+    uint32_t m = probe_count_x(p) * 3u; if (probe_count_y(p) > m) m = probe_count_y(p);
+    uint32_t n = 1; while (n < m) n <<= 1;
+    return n * n;
+}
+/* interpolate_probes.slang:13-103 for pixel (x, y).  Returns 0 when nothing is written, 1 for a radiance written at the pixel itself,
+ * 2 for the "interpolation failed" marker, which the shader writes at the JITTERED pixel.  In the shader those stray writes race with
+ * the regular write of the pixel they land on; here the markers are applied after all regular writes (oracle and kernels alike). */
+RT3_HD int probe_interpolate_pixel(const rt3_params& p, uint32_t x, uint32_t y, const uint32_t* gbuffer, const float* depth_img,
+                                    const float* sh, uint32_t& out_x, uint32_t& out_y, vec4& value) {
+    const uint32_t W = (uint32_t)p.window_size[0], H = (uint32_t)p.window_size[1];
+    if (float(x) > p.window_size[0] || float(y) > p.window_size[1] || x >= W || y >= H) return 0;   /* :14-16 (+ image bounds) */
+    uint32_t pcx_ = x, pcy_ = y;
+    const float pixel_depth = depth_img[(size_t)y * W + x];
+    if (pixel_depth == RT3_BACKGROUND_DEPTH) return 0;                                                   /* :20-22 */
+    RandomSamplerState rng = rng_init(x, y, p.frame);                                                    /* :24 */
+    const uint32_t* g = gbuffer + 4u * ((size_t)y * W + x);
+    uint4_ packed = {g[0], g[1], g[2], g[3]};
+    const GbufferData surface = gbuffer_unpack(packed);                                                  /* :26 */
+    const vec3 pixel_pos = world_pos_from_depth(pixel_depth, x, y, p);                                   /* :28 */
+    const float u0 = rng_uniform_float(rng), u1 = rng_uniform_float(rng);
+    const int jx = (int)((2.0f * u0 - 1.0f) * 16.0f), jy = (int)((2.0f * u1 - 1.0f) * 16.0f);          /* :31 */
+    int qx = (int)x + jx, qy = (int)y + jy;
+    qx = qx < 0 ? 0 : (qx > (int)W - 1 ? (int)W - 1 : qx); qy = qy < 0 ? 0 : (qy > (int)H - 1 ? (int)H - 1 : qy);   /* :32 */
+    const float jdepth = depth_img[(size_t)qy * W + qx];
+    const vec3 jpos = world_pos_from_depth(jdepth, (uint32_t)qx, (uint32_t)qy, p);                       /* :34 */
+    if (abs_(dot(normalize(jpos - pixel_pos), surface.normal)) < 0.01f) { pcx_ = (uint32_t)qx; pcy_ = (uint32_t)qy; }   /* :36-38 */
+    const uint32_t lx = pcx_ / 16u, ly = pcy_ / 16u;                                                     /* :40 */
+    const uint32_t pxs[4] = {lx, lx + 1u, lx, lx + 1u}, pys[4] = {ly, ly, ly + 1u, ly + 1u};             /* :42-47 */
+    float wgt[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int i = 0; i < 4; ++i) {                                                                        /* :51-68 */
+        if (pxs[i] >= W / 16u || pys[i] >= H / 16u) continue;                                            /* :56 (bounds first: the depth read must stay inside the image) */
+        const uint32_t ppx = pxs[i] * 16u, ppy = pys[i] * 16u;
+        const float pd = depth_img[(size_t)ppy * W + ppx];
+        if (pd == RT3_BACKGROUND_DEPTH) continue;
+        const vec3 ppos = world_pos_from_depth(pd, ppx, ppy, p);                                         /* :60 */
+        if (abs_(dot(normalize(ppos - pixel_pos), surface.normal)) > 0.01f) wgt[i] = 0.0f;               /* :62-63 */
+        else {
+            float w = clamp_(1.0f - abs_(pd - pixel_depth) / pixel_depth, 0.0f, 1.0f);                   /* :65 */
+            const vec3 pn = unpack_normal_11_10_11(gbuffer[4u * ((size_t)ppy * W + ppx) + 1u]);
+            w = w * max_(dot(surface.normal, pn), 0.0f);                                                 /* :66 */
+            const float w2 = w * w, w4 = w2 * w2;
+            wgt[i] = w4 * w4;                                                                            /* :67 pow(w, 8) */
+        }
+    }
+    const float ww = wgt[0] * wgt[0] + wgt[1] * wgt[1] + wgt[2] * wgt[2] + wgt[3] * wgt[3];
+    if (ww == 0.0f) {                                                                                    /* :71-76: "Interpolation failed", written at the JITTERED pixel */
+        out_x = pcx_; out_y = pcy_; value.x = 1.0f; value.y = 0.0f; value.z = 0.0f; value.w = 1.0f;
+        return 2;
+    }
+    const float wsum = wgt[0] + wgt[1] + wgt[2] + wgt[3];                                                /* :78 */
+    vec3 radiance = v3(0.f, 0.f, 0.f);
+    for (int i = 0; i < 4; ++i) {                                                                        /* :81-98 */
+        const float w = wgt[i] / wsum;
+        vec3 pr;
+        if (w == 0.0f) continue;                         /* a probe outside the grid has weight 0; its coefficients are not addressed */
+        if (p.proberng == 1u) {                                                                          /* :84-88: debug view, probe normal as colour */
+            const vec3 pn = unpack_normal_11_10_11(gbuffer[4u * ((size_t)(pys[i] * 16u) * W + pxs[i] * 16u) + 1u]);
+            pr = v3((pn.x + 1.0f) / 2.0f, (pn.y + 1.0f) / 2.0f, (pn.z + 1.0f) / 2.0f);
+        } else {                                                                                         /* :90-95 */
+            sh3 r, gg, b;
+            const float* sr = sh + 9u * (size_t)probe_sh_index(pxs[i], pys[i], 0u);
+            const float* sg = sh + 9u * (size_t)probe_sh_index(pxs[i], pys[i], 1u);
+            const float* sb = sh + 9u * (size_t)probe_sh_index(pxs[i], pys[i], 2u);
+            for (int k = 0; k < 9; ++k) { r.c[k] = sr[k]; gg.c[k] = sg[k]; b.c[k] = sb[k]; }
+            pr = sh3_unproject_cos_lobe(r, gg, b, surface.normal);
+        }
+        radiance = v3(radiance.x + w * max_(0.0f, pr.x), radiance.y + w * max_(0.0f, pr.y), radiance.z + w * max_(0.0f, pr.z));   /* :97 */
+    }
+    const float inv_pi = 0.31830988618379067153f;
+    radiance = v3(radiance.x * (surface.albedo.x * inv_pi), radiance.y * (surface.albedo.y * inv_pi), radiance.z * (surface.albedo.z * inv_pi));   /* :100 */
+    radiance = radiance + surface.emissive;                                                              /* :101 */
+    out_x = x; out_y = y; value.x = radiance.x; value.y = radiance.y; value.z = radiance.z; value.w = 1.0f;   /* :103: Light[threadId.xy] */
+    return 1;
+}
+
 /* ---------------------------------------------------------------- postprocess.slang ---------- */
 /* shaders/old/postprocess.slang:13-24 */
 RT3_HD float agx_contrast(float x) {

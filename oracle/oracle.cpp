@@ -479,6 +479,61 @@ void orc_pass_postprocess(const orc_scene* s, const rt3_params* p, rt3_rect rc, 
     });
 }
 
+/* ---- screen-space probes (row F4) ----------------------------------------------------------------
+ * shaders/old/trace_probes.slang: one ray per atlas texel; directions == NULL selects the uniform assignment. */
+void orc_pass_probe_trace(const orc_scene* s, const rt3_params* p, const uint32_t* gbuffer, const float* depth, const uint16_t* directions,
+                          const float* prev_atlas, float* atlas, int threads) {
+    (void)gbuffer;
+    SceneView sv = s->view();
+    const uint32_t W = (uint32_t)p->window_size[0], aw = probe_count_x(*p) * 8u, ah = probe_count_y(*p) * 8u;
+    parallel_for(ah, threads, 8, [&](uint64_t y0, uint64_t y1) {
+        for (uint32_t ay = (uint32_t)y0; ay < (uint32_t)y1; ++ay)
+            for (uint32_t ax = 0; ax < aw; ++ax) {
+                const size_t ai = (size_t)ay * aw + ax;
+                const float pd = depth[(size_t)(ay / 8u * 16u) * W + ax / 8u * 16u];
+                const uint32_t word = directions ? directions[ai] : probe_uniform_direction(ax, ay);
+                ProbeRay pr = probe_setup_ray(*p, ax, ay, pd, word);
+                if (pr.background) { atlas[4 * ai] = 0.f; atlas[4 * ai + 1] = 0.f; atlas[4 * ai + 2] = 0.f; atlas[4 * ai + 3] = RT3_BACKGROUND_DEPTH; continue; }   /* :28-31 */
+                rt3_hit h = closest_bvh(*s, pr.ray);
+                const size_t ti = (size_t)pr.target_y * aw + pr.target_x;
+                vec3 prev = v3(0.f, 0.f, 0.f);
+                if (p->blendfactor < 1.0f && prev_atlas) prev = v3(prev_atlas[4 * ai], prev_atlas[4 * ai + 1], prev_atlas[4 * ai + 2]);
+                vec4 t = probe_texel(sv, *p, pr.ray, h, prev);
+                atlas[4 * ti] = t.x; atlas[4 * ti + 1] = t.y; atlas[4 * ti + 2] = t.z; atlas[4 * ti + 3] = t.w;
+            }
+    });
+}
+/* shaders/old/spherical_harmonic_conversion.slang */
+void orc_pass_probe_sh(const rt3_params* p, const float* atlas, float* sh, int threads) {
+    const uint32_t pw = probe_count_x(*p), ph = probe_count_y(*p), aw = pw * 8u;
+    parallel_for(ph, threads, 1, [&](uint64_t y0, uint64_t y1) {
+        for (uint32_t py = (uint32_t)y0; py < (uint32_t)y1; ++py)
+            for (uint32_t px = 0; px < pw; ++px)
+                for (uint32_t c = 0; c < 3; ++c) {
+                    sh3 r = probe_project_sh(atlas, aw, px, py, c);
+                    memcpy(sh + 9u * (size_t)probe_sh_index(px, py, c), r.c, sizeof(r.c));
+                }
+    });
+}
+/* shaders/old/interpolate_probes.slang */
+void orc_pass_probe_interpolate(const rt3_params* p, const uint32_t* gbuffer, const float* depth, const float* sh, float* light, int threads) {
+    const uint32_t W = (uint32_t)p->window_size[0], H = (uint32_t)p->window_size[1];
+    std::vector<uint8_t> failed((size_t)W * H, 0);
+    std::vector<uint32_t> fx((size_t)W * H), fy((size_t)W * H);
+    parallel_for(H, threads, 4, [&](uint64_t y0, uint64_t y1) {
+        for (uint32_t y = (uint32_t)y0; y < (uint32_t)y1; ++y)
+            for (uint32_t x = 0; x < W; ++x) {
+                uint32_t ox, oy; vec4 v;
+                int k = probe_interpolate_pixel(*p, x, y, gbuffer, depth, sh, ox, oy, v);
+                const size_t i = (size_t)y * W + x;
+                if (k == 1) { light[4 * i] = v.x; light[4 * i + 1] = v.y; light[4 * i + 2] = v.z; light[4 * i + 3] = v.w; }
+                else if (k == 2) { failed[i] = 1; fx[i] = ox; fy[i] = oy; }
+            }
+    });
+    for (size_t i = 0; i < failed.size(); ++i)
+        if (failed[i]) { const size_t t = (size_t)fy[i] * W + fx[i]; light[4 * t] = 1.f; light[4 * t + 1] = 0.f; light[4 * t + 2] = 0.f; light[4 * t + 3] = 1.f; }
+}
+
 /* ---- known-answer hooks -------------------------------------------------------------------- */
 uint32_t orc_hash_jenkins(uint32_t a) { return hash_jenkins(a); }
 uint32_t orc_zcurve(uint32_t x, uint32_t y) { return zcurve_to_linear_index(x, y); }
@@ -528,6 +583,17 @@ void orc_sample_2d(const orc_scene* s, uint32_t flags, uint32_t px, uint32_t py,
 }
 void orc_agx(const float in3[3], float out3[3]) { vec3 c = agx_eotf(agx_look(agx(v3(in3)))); out3[0] = c.x; out3[1] = c.y; out3[2] = c.z; }
 float orc_contract_probe(float a, float b, float c) { return contract_probe(a, b, c); }
+void orc_octa_decode(float fx, float fy, float out3[3]) { vec2 f; f.x = fx; f.y = fy; vec3 d = octa_decode(f); out3[0] = d.x; out3[1] = d.y; out3[2] = d.z; }
+void orc_octa_encode(const float n[3], float out2[2]) { vec2 e = octa_encode(v3(n)); out2[0] = e.x; out2[1] = e.y; }
+void orc_sh3_evaluate(const float d[3], float out9[9]) { sh3 s = sh3_evaluate(v3(d)); memcpy(out9, s.c, sizeof(s.c)); }
+void orc_sh3_unproject_cos_lobe(const float sh27[27], const float n[3], float out3[3]) {
+    sh3 r, g, b; memcpy(r.c, sh27, 36); memcpy(g.c, sh27 + 9, 36); memcpy(b.c, sh27 + 18, 36);
+    vec3 v = sh3_unproject_cos_lobe(r, g, b, v3(n)); out3[0] = v.x; out3[1] = v.y; out3[2] = v.z;
+}
+void orc_world_pos_from_depth(const rt3_params* p, uint32_t px, uint32_t py, float depth, float out3[3]) {
+    vec3 v = world_pos_from_depth(depth, px, py, *p); out3[0] = v.x; out3[1] = v.y; out3[2] = v.z;
+}
+uint32_t orc_probe_sh_capacity(const rt3_params* p) { return probe_sh_capacity(*p); }
 /* SpecularBrdf::sample / ::evaluate (brdf.slang:220-314).  out12 = value_over_pdf[3], value[3], pdf, transmission[3], (sample only) wi... */
 int orc_specular_sample(float roughness, const float albedo[3], const float wo[3], float ux, float uy, float out14[14]) {
     vec2 u; u.x = ux; u.y = uy;

@@ -47,6 +47,13 @@ void orc_pass_reference(const orc_scene*, const rt3_params*, rt3_rect, const uin
                         float* light, int threads, rt3_counters* opt_counters);
 void orc_pass_postprocess(const orc_scene*, const rt3_params*, rt3_rect, const float* depth, const float* in, float* out, int threads);
 
+/* Screen-space probe passes (shaders/old/trace_probes, spherical_harmonic_conversion, interpolate_probes .slang).
+ * atlas: (W/16*8) x (H/16*8) RGBA32F; sh: orc_probe_sh_capacity() records of 9 floats, Z-curve indexed; directions may be NULL. */
+void orc_pass_probe_trace(const orc_scene*, const rt3_params*, const uint32_t* gbuffer, const float* depth, const uint16_t* directions,
+                          const float* prev_atlas, float* atlas, int threads);
+void orc_pass_probe_sh(const rt3_params*, const float* atlas, float* sh, int threads);
+void orc_pass_probe_interpolate(const rt3_params*, const uint32_t* gbuffer, const float* depth, const float* sh, float* light, int threads);
+
 /* Known-answer hooks into rt3_shared_math.h (one call evaluates one function). */
 uint32_t orc_hash_jenkins(uint32_t a);
 uint32_t orc_zcurve(uint32_t x, uint32_t y);
@@ -78,6 +85,12 @@ float orc_vdc(uint32_t bits);
 void orc_sample_2d(const orc_scene*, uint32_t flags, uint32_t px, uint32_t py, uint32_t frame, uint32_t index, float out2[2]);
 void orc_agx(const float in3[3], float out3[3]);
 float orc_contract_probe(float a, float b, float c);
+void orc_octa_decode(float fx, float fy, float out3[3]);
+void orc_octa_encode(const float n[3], float out2[2]);
+void orc_sh3_evaluate(const float d[3], float out9[9]);
+void orc_sh3_unproject_cos_lobe(const float sh27[27], const float n[3], float out3[3]);
+void orc_world_pos_from_depth(const rt3_params*, uint32_t px, uint32_t py, float depth, float out3[3]);
+uint32_t orc_probe_sh_capacity(const rt3_params*);
 int orc_specular_sample(float roughness, const float albedo[3], const float wo[3], float ux, float uy, float out14[14]);
 void orc_specular_evaluate(float roughness, const float albedo[3], const float wo[3], const float wi[3], float out10[10]);
 void orc_specular_dominant_direction(const float n[3], const float v[3], float roughness, float out3[3]);

@@ -52,6 +52,9 @@ def lib():
         L.orc_pass_gbuffer.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_reference.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_pass_postprocess.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_pass_probe_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_pass_probe_sh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_pass_probe_interpolate.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         # KAT hooks
         u32, f32, vp = C.c_uint32, C.c_float, C.c_void_p
         sig = {
@@ -69,6 +72,9 @@ def lib():
             "orc_specular_sample": (C.c_int, [f32, vp, vp, f32, f32, vp]), "orc_specular_evaluate": (None, [f32, vp, vp, vp, vp]),
             "orc_specular_dominant_direction": (None, [vp, vp, f32, vp]),
             "orc_layered_sample": (C.c_int, [vp, vp, f32, f32, vp, f32, f32, vp]), "orc_layered_evaluate": (None, [vp, vp, f32, f32, vp, vp, vp]),
+            "orc_octa_decode": (None, [f32, f32, vp]), "orc_octa_encode": (None, [vp, vp]), "orc_sh3_evaluate": (None, [vp, vp]),
+            "orc_sh3_unproject_cos_lobe": (None, [vp, vp, vp]), "orc_world_pos_from_depth": (None, [vp, u32, u32, f32, vp]),
+            "orc_probe_sh_capacity": (u32, [vp]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
@@ -163,6 +169,27 @@ class OracleScene:
         self.L.orc_pass_reference(self.h, ptr(params), Rect(*rect), ptr(gbuffer), ptr(depth), ptr(prev_light), ptr(lt), self.threads,
                                   C.byref(cnt))
         return lt, cnt
+
+    def pass_probe_trace(self, params, gbuffer, depth, prev_atlas=None, directions=None):
+        """trace_probes.slang -> probe atlas [(H/16)*8, (W/16)*8, 4]."""
+        w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])
+        atlas = np.zeros((h // 16 * 8, w // 16 * 8, 4), np.float32)
+        self.L.orc_pass_probe_trace(self.h, ptr(params), ptr(gbuffer), ptr(depth), None if directions is None else ptr(directions),
+                                    None if prev_atlas is None else ptr(prev_atlas), ptr(atlas), self.threads)
+        return atlas
+
+    def pass_probe_sh(self, params, atlas):
+        """spherical_harmonic_conversion.slang -> [capacity, 9] SH-L2 records, Z-curve indexed by (probe.x * 3 + channel, probe.y)."""
+        sh = np.zeros((self.L.orc_probe_sh_capacity(ptr(params)), 9), np.float32)
+        self.L.orc_pass_probe_sh(ptr(params), ptr(atlas), ptr(sh), self.threads)
+        return sh
+
+    def pass_probe_interpolate(self, params, gbuffer, depth, sh, light=None):
+        """interpolate_probes.slang -> Light (pixels that the shader leaves untouched keep the values of `light`)."""
+        w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])
+        out = np.zeros((h, w, 4), np.float32) if light is None else np.array(light, np.float32, copy=True)
+        self.L.orc_pass_probe_interpolate(ptr(params), ptr(gbuffer), ptr(depth), ptr(sh), ptr(out), self.threads)
+        return out
 
     def pass_postprocess(self, params, depth, inp, rect=None):
         w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])

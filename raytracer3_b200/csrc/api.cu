@@ -383,6 +383,37 @@ rt3_status rt3_pass_postprocess(rt3_context* c, const rt3_params* p, rt3_rect r,
         rt3_launch_postprocess(c, *p, single_rect_map(c, p, r), depth, in, out, (cudaStream_t)st);
     });
 }
+/* ---- screen-space probes (row F4) ---- */
+rt3_status rt3_probe_layout(const rt3_params* p, uint32_t* atlas_w, uint32_t* atlas_h, uint32_t* sh_records) {
+    if (!p) return RT3_ERR_INVALID;
+    if (atlas_w) *atlas_w = rt3m::probe_count_x(*p) * 8u;
+    if (atlas_h) *atlas_h = rt3m::probe_count_y(*p) * 8u;
+    if (sh_records) *sh_records = rt3m::probe_sh_capacity(*p);
+    return RT3_OK;
+}
+rt3_status rt3_pass_probe_trace(rt3_context* c, const rt3_params* p, const uint32_t* gbuffer, const float* depth, const uint16_t* directions,
+                                const float* prev_atlas, float* atlas, void* st) {
+    return guarded(c, [&]() {
+        check_params(c, p); require_accel(c);
+        (void)gbuffer;
+        if (!depth || !atlas) RT3_FAIL(c, RT3_ERR_INVALID, "depth/atlas is NULL");
+        if (p->blendfactor < 1.0f && !prev_atlas) RT3_FAIL(c, RT3_ERR_INVALID, "prev_atlas is NULL with blendfactor < 1");
+        if (c->scene_dirty) refresh_scene_tables(c);
+        rt3_launch_probe_trace(c, *p, depth, directions, prev_atlas, atlas, (cudaStream_t)st);
+    });
+}
+rt3_status rt3_pass_probe_sh(rt3_context* c, const rt3_params* p, const float* atlas, float* sh, void* st) {
+    return guarded(c, [&]() {
+        if (!p || !atlas || !sh) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        rt3_launch_probe_sh(c, *p, atlas, sh, (cudaStream_t)st);
+    });
+}
+rt3_status rt3_pass_probe_interpolate(rt3_context* c, const rt3_params* p, const uint32_t* gbuffer, const float* depth, const float* sh, float* light, void* st) {
+    return guarded(c, [&]() {
+        if (!p || !gbuffer || !depth || !sh || !light) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        rt3_launch_probe_interpolate(c, *p, gbuffer, depth, sh, light, (cudaStream_t)st);
+    });
+}
 rt3_status rt3_pass_gbuffer_tiles(rt3_context* c, const rt3_params* p, const rt3_rect* tiles, uint32_t n, uint32_t* gbuffer, float* depth, void* st) {
     return guarded(c, [&]() {
         check_params(c, p); require_accel(c);

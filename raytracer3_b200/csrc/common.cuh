@@ -168,4 +168,9 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
 void rt3_launch_postprocess(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, float* out, cudaStream_t st);
 void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h, const float* slab, float* frame,
                        uint32_t frame_w, uint32_t frame_h, cudaStream_t st);
+void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,
+                            cudaStream_t st);
+void rt3_launch_probe_sh(rt3_context* c, const rt3_params& p, const float* atlas, float* sh, cudaStream_t st);
+void rt3_launch_probe_interpolate(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, const float* depth, const float* sh, float* light,
+                                  cudaStream_t st);
 double rt3_run_l2_sweep(rt3_context* c, size_t bytes, int iters);

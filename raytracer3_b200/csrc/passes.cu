@@ -279,6 +279,69 @@ __global__ void __launch_bounds__(PASS_THREADS) k_postprocess(SceneView s, rt3_p
     ((float4*)out)[px] = make_float4(r.x, r.y, r.z, 1.0f);
 }
 
+/* ---- screen-space probes ------------------------------------------------------------------------
+ * trace_probes.slang as raygen -> k_trace_dyn -> texel kernel; spherical_harmonic_conversion.slang; interpolate_probes.slang */
+__global__ void __launch_bounds__(PASS_THREADS) k_probe_raygen(rt3_params p, uint32_t aw, uint32_t ah, const float* __restrict__ depth,
+                                                               const uint16_t* __restrict__ directions, rt3_ray* __restrict__ rays) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= aw * ah) return;
+    const uint32_t ax = i % aw, ay = i / aw, W = (uint32_t)p.window_size[0];
+    const float pd = depth[(size_t)(ay / 8u * 16u) * W + ax / 8u * 16u];
+    ProbeRay pr = probe_setup_ray(p, ax, ay, pd, directions ? (uint32_t)directions[i] : probe_uniform_direction(ax, ay));
+    if (pr.background) { pr.ray.tmin = 0.f; pr.ray.tmax = 0.f; }                 /* nothing to trace (trace_probes.slang:28-31) */
+    store_ray(rays, i, v3(pr.ray.o), v3(pr.ray.d), pr.ray.tmin, pr.ray.tmax);
+}
+__global__ void __launch_bounds__(PASS_THREADS) k_probe_texel(SceneView s, rt3_params p, uint32_t aw, uint32_t ah, const float* __restrict__ depth,
+                                                              const uint16_t* __restrict__ directions, const rt3_ray* __restrict__ rays,
+                                                              const rt3_hit* __restrict__ hits, const float4* __restrict__ prev_atlas,
+                                                              float4* __restrict__ atlas, DeviceCounters* counters) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long traced = 0;
+    if (i < aw * ah) {
+        const uint32_t ax = i % aw, ay = i / aw, W = (uint32_t)p.window_size[0];
+        const float pd = depth[(size_t)(ay / 8u * 16u) * W + ax / 8u * 16u];
+        if (pd == RT3_BACKGROUND_DEPTH) atlas[i] = make_float4(0.f, 0.f, 0.f, RT3_BACKGROUND_DEPTH);
+        else {
+            traced = 1;
+            const ProbeRay pr = probe_setup_ray(p, ax, ay, pd, directions ? (uint32_t)directions[i] : probe_uniform_direction(ax, ay));
+            const float4 h4 = ((const float4*)hits)[i];
+            rt3_hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = __float_as_uint(h4.w);
+            vec3 prev = v3(0.f, 0.f, 0.f);
+            if (p.blendfactor < 1.0f && prev_atlas) { const float4 q = prev_atlas[i]; prev = v3(q.x, q.y, q.z); }
+            const vec4 t = probe_texel(s, p, pr.ray, h, prev);
+            atlas[(size_t)pr.target_y * aw + pr.target_x] = make_float4(t.x, t.y, t.z, t.w);
+        }
+    }
+    flush_counter(traced, &counters->rays_secondary);
+}
+__global__ void __launch_bounds__(PASS_THREADS) k_probe_sh(rt3_params p, const float* __restrict__ atlas, float* __restrict__ sh) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t pw = probe_count_x(p), ph = probe_count_y(p);
+    if (i >= pw * ph * 3u) return;
+    const uint32_t c = i % 3u, px = (i / 3u) % pw, py = i / (3u * pw);
+    const sh3 r = probe_project_sh(atlas, pw * 8u, px, py, c);
+    float* o = sh + 9u * (size_t)probe_sh_index(px, py, c);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) o[k] = r.c[k];
+}
+__global__ void __launch_bounds__(PASS_THREADS) k_probe_interpolate(rt3_params p, const uint32_t* __restrict__ gbuffer, const float* __restrict__ depth,
+                                                                    const float* __restrict__ sh, float4* __restrict__ light, uint32_t* __restrict__ failed_target) {
+    const uint32_t W = (uint32_t)p.window_size[0], H = (uint32_t)p.window_size[1];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= W * H) return;
+    uint32_t ox, oy; vec4 v;
+    const int k = probe_interpolate_pixel(p, i % W, i / W, gbuffer, depth, sh, ox, oy, v);
+    failed_target[i] = (k == 2) ? oy * W + ox : 0xFFFFFFFFu;
+    if (k == 1) light[i] = make_float4(v.x, v.y, v.z, v.w);
+}
+/* the "interpolation failed" markers (interpolate_probes.slang:71-76) land on other pixels: applied after every regular write */
+__global__ void __launch_bounds__(PASS_THREADS) k_probe_failed(uint32_t n, const uint32_t* __restrict__ failed_target, float4* __restrict__ light) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t t = failed_target[i];
+    if (t != 0xFFFFFFFFu) light[t] = make_float4(1.f, 0.f, 0.f, 1.f);
+}
+
 __global__ void __launch_bounds__(PASS_THREADS) k_untile(const rt3_rect* __restrict__ rects, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h,
                                                          const float4* __restrict__ slab, float4* __restrict__ frame, uint32_t frame_w, uint32_t frame_h) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -358,6 +421,32 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
 void rt3_launch_postprocess(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, float* out, cudaStream_t st) {
     if (!m.work) return;
     RT3_LAUNCH(c, k_postprocess, div_up(m.work, PASS_THREADS), PASS_THREADS, 0, st, c->view, p, m, depth, in, out);
+}
+
+void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,
+                            cudaStream_t st) {
+    const uint32_t aw = probe_count_x(p) * 8u, ah = probe_count_y(p) * 8u;
+    const size_t n = (size_t)aw * ah;
+    if (!n) return;
+    rt3_ray* rays = ensure<rt3_ray>(c, c->q_rays[0], std::max<size_t>(n, 1));
+    rt3_hit* hits = ensure<rt3_hit>(c, c->q_hits, std::max<size_t>(n, 1));
+    RT3_LAUNCH(c, k_probe_raygen, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, p, aw, ah, depth, directions, rays);
+    rt3_launch_trace_closest(c, rays, nullptr, n, hits, st);
+    RT3_LAUNCH(c, k_probe_texel, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, c->view, p, aw, ah, depth, directions, rays, hits, (const float4*)prev_atlas,
+               (float4*)atlas, c->d_counters);
+}
+void rt3_launch_probe_sh(rt3_context* c, const rt3_params& p, const float* atlas, float* sh, cudaStream_t st) {
+    const size_t n = (size_t)probe_count_x(p) * probe_count_y(p) * 3u;
+    if (!n) return;
+    RT3_LAUNCH(c, k_probe_sh, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, p, atlas, sh);
+}
+void rt3_launch_probe_interpolate(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, const float* depth, const float* sh, float* light,
+                                  cudaStream_t st) {
+    const size_t n = (size_t)p.window_size[0] * (size_t)p.window_size[1];
+    if (!n) return;
+    uint32_t* failed = ensure<uint32_t>(c, c->px_rng, n);
+    RT3_LAUNCH(c, k_probe_interpolate, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, p, gbuffer, depth, sh, (float4*)light, failed);
+    RT3_LAUNCH(c, k_probe_failed, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, (uint32_t)n, failed, (float4*)light);
 }
 
 void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h, const float* slab, float* frame,

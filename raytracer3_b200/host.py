@@ -264,6 +264,13 @@ class RenderGraph:
             self.resources[name] = torch.zeros(shape, dtype=getattr(torch, dt), device=f"cuda:{self.ctx.device}")
         return name
 
+    def buffer(self, name, shape, dtype="float32"):
+        """A resource that is not window sized (ImageSize::Custom / buffers of render_graph/mod.rs:440-483): probe atlas, SH records."""
+        torch = _torch()
+        if name not in self.resources or tuple(self.resources[name].shape) != tuple(shape):
+            self.resources[name] = torch.zeros(tuple(shape), dtype=getattr(torch, dtype), device=f"cuda:{self.ctx.device}")
+        return name
+
     def tensor(self, name):
         return self.resources[name]
 
@@ -323,8 +330,11 @@ class RayTracingPass(_PassBuilder):
         elif self._shader == "refrence_mode":
             st = ctx.L.rt3_pass_reference(ctx.h, p, rect, self._ptr("gbuffer"), self._ptr("gbuffer_depth"), self._ptr("PrevLight", False),
                                           self._ptr("Light"), ctx.stream())
+        elif self._shader == "trace_probes":                      # shaders/old/trace_probes.slang, launched over the probe atlas
+            st = ctx.L.rt3_pass_probe_trace(ctx.h, p, self._ptr("gbuffer"), self._ptr("gbuffer_depth"), self._ptr("directions", False),
+                                            self._ptr("prev_probe_atlas", False), self._ptr("probe_atlas"), ctx.stream())
         else:
-            raise ValueError(f"unknown ray-tracing shader '{self._shader}' (known: gbuffer, refrence_mode)")
+            raise ValueError(f"unknown ray-tracing shader '{self._shader}' (known: gbuffer, refrence_mode, trace_probes)")
         ctx.check(st)
         return self.name
 
@@ -337,10 +347,16 @@ class ComputePass(_PassBuilder):
     def dispatch(self, work=WorkSize2D.FullScreen()):
         ctx = self.rg.ctx
         x, y = work.size(self.rg.window)
-        if self._shader != "postprocess":
-            raise ValueError(f"unknown compute shader '{self._shader}' (known: postprocess)")
-        ctx.check(ctx.L.rt3_pass_postprocess(ctx.h, ptr(self._constants), Rect(0, 0, x, y), self._ptr("Depth"), self._ptr("In"), self._ptr("Out"),
-                                             ctx.stream()))
+        p = ptr(self._constants)
+        if self._shader == "postprocess":
+            ctx.check(ctx.L.rt3_pass_postprocess(ctx.h, p, Rect(0, 0, x, y), self._ptr("Depth"), self._ptr("In"), self._ptr("Out"), ctx.stream()))
+        elif self._shader == "spherical_harmonic_conversion":
+            ctx.check(ctx.L.rt3_pass_probe_sh(ctx.h, p, self._ptr("probe_atlas"), self._ptr("out"), ctx.stream()))
+        elif self._shader == "interpolate_probes":
+            ctx.check(ctx.L.rt3_pass_probe_interpolate(ctx.h, p, self._ptr("gbuffer"), self._ptr("gbuffer_depth"), self._ptr("sh_coeficents"),
+                                                       self._ptr("Light"), ctx.stream()))
+        else:
+            raise ValueError(f"unknown compute shader '{self._shader}' (known: postprocess, spherical_harmonic_conversion, interpolate_probes)")
         return self.name
 
 
@@ -371,6 +387,28 @@ class Renderer:
         self.cur = 1 - self.cur
         rg.frame_number += 1
         return rg.tensor(light)
+
+    def probe_frame(self, gconst):
+        """The screen-space probe path: gbuffer -> trace_probes -> spherical_harmonic_conversion -> interpolate_probes,
+        probe atlas ping-ponged for the temporal blend.  Returns the Light tensor."""
+        rg = self.rg
+        p = np.ascontiguousarray(gconst)
+        aw, ah, nsh = C.c_uint32(0), C.c_uint32(0), C.c_uint32(0)
+        self.ctx.check(self.ctx.L.rt3_probe_layout(ptr(p), C.byref(aw), C.byref(ah), C.byref(nsh)))
+        rg.buffer("probe_atlas0", (ah.value, aw.value, 4)); rg.buffer("probe_atlas1", (ah.value, aw.value, 4)); rg.buffer("probe_sh", (nsh.value, 9))
+        self.probe_cur = getattr(self, "probe_cur", 0)
+        atlas, prev = f"probe_atlas{self.probe_cur}", f"probe_atlas{1 - self.probe_cur}"
+        (RayTracingPass.new(rg, "gbuffer").shader("gbuffer").constants(gconst).write("gbuffer", "gbuffer").write("gbuffer_depth", "gbuffer_depth")
+         .launch(WorkSize2D.FullScreen()))
+        (RayTracingPass.new(rg, "trace_probes").shader("trace_probes").constants(gconst).read("gbuffer", "gbuffer").read("gbuffer_depth", "gbuffer_depth")
+         .read("prev_probe_atlas", prev).write("probe_atlas", atlas).launch(WorkSize2D.FractionalFullScreen(2, 2)))
+        (ComputePass.new(rg, "sh").shader("spherical_harmonic_conversion").constants(gconst).read("probe_atlas", atlas).write("out", "probe_sh")
+         .dispatch(WorkSize2D.FractionalFullScreen(2, 2)))
+        (ComputePass.new(rg, "interpolate").shader("interpolate_probes").constants(gconst).read("gbuffer", "gbuffer").read("gbuffer_depth", "gbuffer_depth")
+         .read("sh_coeficents", "probe_sh").write("Light", "light0").dispatch(WorkSize2D.FullScreen()))
+        self.probe_cur = 1 - self.probe_cur
+        rg.frame_number += 1
+        return rg.tensor("light0")
 
     def render_frame_host(self, gconst, light_host, prev_light_host=None):
         """End-to-end path with HOST buffers (params in, framebuffer out)."""
