@@ -25,6 +25,10 @@ sys.path.insert(0, ROOT)
 FRAME_DIMS = {1: (1920, 1080), 2: (3840, 1080), 4: (3840, 2160), 8: (7680, 2160)}
 BOUNCES, SAMPLES = 4, 1
 HBM_BYTES_PER_RAY = 48          # 32 B rt3_ray read + 16 B rt3_hit written
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_trace_dyn<closest> launch of this workload (1.8 M secondary rays), from the committed
+# `ncu --set full` capture; algorithmic bytes of that launch = 48 B x 1.8 M = 86 MB
+NCU_TRACE_DRAM_BYTES_PER_LAUNCH = 83.96e6 + 10.28e6
+NCU_TRACE_DRAM_SOURCE = "profiles/r1d_trace_summary.txt (ncu --set full, launch 1 of 3: 83.96 MB read + 10.28 MB written)"
 FALLBACK_HBM_GBS = 6650.0       # /opt/skills/guides/B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 
 
@@ -324,7 +328,7 @@ def run_cuda(args):
                     "sync_ms_per_step": sync_e2e_ms, "host_frame_verified": e2e_verified},
             "gpu_launches": int(launches_all),
             "roofline": {"kernel": "k_trace<closest> (secondary-ray queues)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "bytes_per_ray": HBM_BYTES_PER_RAY,
+                         "frac": achieved / peak, "traffic": NCU_TRACE_DRAM_BYTES_PER_LAUNCH, "traffic_source": NCU_TRACE_DRAM_SOURCE, "peak_source": peak_src, "bytes_per_ray": HBM_BYTES_PER_RAY,
                          "kernel_ms_per_launch": t_ms / t_n, "rays_per_launch": t_rays / t_n, "launches": int(t_n),
                          "kernel_share_of_step": t_ms / ms if ms > 0 else None,
                          "note": "traversal is L2-latency/issue bound, not HBM bound: the BVH is L2-resident, HBM only streams 48 B per ray (see roofline_l2)"},

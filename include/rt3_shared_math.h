@@ -506,6 +506,10 @@ struct SceneView {
     float env_total;                /* sum of env_func                                   */
     /* blue noise */
     const uint8_t* bn; uint32_t bn_w, bn_h;
+    /* optional per-triangle shading records (built by rt3_accel_build, NULL in the oracle): (global vertex index x 3, segment)
+     * indexed by the global triangle id — replaces the binary search + geometry + index fetches in front of the vertex fetch by
+     * one 16-byte load; the values fetched afterwards, and so the results, are the same */
+    const uint32_t* shade_rec;
 };
 
 RT3_HD uint32_t find_segment(const SceneView& s, uint32_t prim) {
@@ -583,12 +587,24 @@ RT3_HD vec3 sample_environment(const SceneView& s, vec3 dir) {
  * The per-vertex colour the old shader reads (hit_logic.slang:27) does not exist in the 32-byte
  * Vertex (assets/mod.rs:127-133) and is taken as (1,1,1). */
 RT3_HD GbufferData hit_info(const SceneView& s, uint32_t prim, float bu, float bv, uint32_t* out_geometry = nullptr) {
-    uint32_t seg = find_segment(s, prim);
+    uint32_t seg, i0, i1, i2;
+    if (s.shade_rec != nullptr) {
+        const uint32_t* r = s.shade_rec + 4u * (size_t)prim;
+#ifdef __CUDA_ARCH__
+        const uint4 q = __ldg((const uint4*)r);
+        i0 = q.x; i1 = q.y; i2 = q.z; seg = q.w;
+#else
+        i0 = r[0]; i1 = r[1]; i2 = r[2]; seg = r[3];
+#endif
+    } else {
+        seg = find_segment(s, prim);
+        const rt3_geometry_info& g0 = s.geometries[s.seg_geometry[seg]];
+        uint32_t io = g0.index_offset + 3u * (prim - s.seg_first_prim[seg]);
+        i0 = g0.vertex_offset + s.indices[io]; i1 = g0.vertex_offset + s.indices[io + 1]; i2 = g0.vertex_offset + s.indices[io + 2];
+    }
     uint32_t gi = s.seg_geometry[seg];
     if (out_geometry) *out_geometry = gi;
     const rt3_geometry_info& g = s.geometries[gi];
-    uint32_t io = g.index_offset + 3u * (prim - s.seg_first_prim[seg]);
-    uint32_t i0 = g.vertex_offset + s.indices[io], i1 = g.vertex_offset + s.indices[io + 1], i2 = g.vertex_offset + s.indices[io + 2];
     const rt3_vertex& a = s.vertices[i0];
     const rt3_vertex& b = s.vertices[i1];
     const rt3_vertex& c = s.vertices[i2];

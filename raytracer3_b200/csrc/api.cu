@@ -233,7 +233,7 @@ void rt3_destroy(rt3_context* c) {
     if (c->d_srgb_lut) cudaFree(c->d_srgb_lut);
     if (c->d_counters) cudaFree(c->d_counters);
     Scratch* all[] = {&c->d_geometries, &c->d_seg_first, &c->d_seg_geo, &c->d_seg_inst, &c->d_inst_xform, &c->d_tex_ptr, &c->d_tex_dim, &c->bvh_nodes,
-                      &c->bvh_tris, &c->d_insts, &c->q_rays[0], &c->q_rays[1], &c->q_hits, &c->q_thr[0], &c->q_thr[1], &c->q_pix[0], &c->q_pix[1], &c->q_pdf[0], &c->q_pdf[1], &c->q_srays, &c->q_scontrib, &c->q_sbits, &c->px_radiance,
+                      &c->bvh_tris, &c->d_insts, &c->d_shade_rec, &c->q_rays[0], &c->q_rays[1], &c->q_hits, &c->q_thr[0], &c->q_thr[1], &c->q_pix[0], &c->q_pix[1], &c->q_pdf[0], &c->q_pdf[1], &c->q_srays, &c->q_scontrib, &c->q_sbits, &c->px_radiance,
                       &c->px_rng, &c->d_counts, &c->d_rects, &c->d_untile_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();

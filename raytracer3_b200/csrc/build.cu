@@ -67,6 +67,16 @@ __global__ void __launch_bounds__(256) k_flatten(rt3m::SceneView s, uint32_t n, 
     }
 }
 
+/* Per-triangle shading records for rt3m::hit_info: (global vertex indices, segment) by global triangle id. */
+__global__ void __launch_bounds__(256) k_shade_records(rt3m::SceneView s, uint32_t n, uint4* rec) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t seg = rt3m::find_segment(s, i);
+    const rt3_geometry_info& g = s.geometries[s.seg_geometry[seg]];
+    const uint32_t io = g.index_offset + 3u * (i - s.seg_first_prim[seg]);
+    rec[i] = make_uint4(g.vertex_offset + s.indices[io], g.vertex_offset + s.indices[io + 1], g.vertex_offset + s.indices[io + 2], seg);
+}
+
 /* Bottom level of the two-level build: the triangles of one mesh (segments [seg0, ...) of its first instance, global ids
  * [prim0, prim0 + n)) in OBJECT space — geometry transform applied, instance transform not — stored as VERTICES with the
  * mesh-local id (REC_TRI_VERTS).  The vertex arithmetic is that of rt3m::world_triangle up to the instance transform. */
@@ -575,6 +585,14 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         RT3_LAUNCH(c, k_empty_root, 1, 32, 0, st, nodes);
         RT3_CUDA(c, cudaStreamSynchronize(st));
         c->n_wide_nodes = 1; c->n_leaf_records = 0; c->two_level = false; bs.wide_nodes = 1; bs.node_bytes = sizeof(WideNode);
+    }
+    c->view.shade_rec = nullptr;
+    if (n && !getenv("RT3_NO_SHADE_REC")) {
+        uint4* rec = ensure<uint4>(c, c->d_shade_rec, n);
+        RT3_LAUNCH(c, k_shade_records, div_up(n, 256), 256, 0, st, c->view, n, rec);
+        c->view.shade_rec = (const uint32_t*)rec;
+    }
+    if (n == 0) {
     } else if ((flags & RT3_BUILD_TWO_LEVEL) && !c->h_instances.empty()) {
         build_two_level(c, st, bs);
     } else {

@@ -95,7 +95,7 @@ struct rt3_context {
     rt3m::SceneView view;           /* device pointers */
 
     /* acceleration structure */
-    Scratch bvh_nodes, bvh_tris, d_insts;   /* d_insts: rt3b::InstRec table of the two-level structure */
+    Scratch bvh_nodes, bvh_tris, d_insts, d_shade_rec;   /* d_insts: rt3b::InstRec table of the two-level structure */
     uint32_t n_wide_nodes = 0, n_leaf_records = 0;
     bool two_level = false;
     bool accel_valid = false;

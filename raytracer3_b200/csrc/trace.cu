@@ -193,18 +193,22 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                 }
             }
             if (active && (found_any || (tg_hits == 0u && ng_hits <= 0x00FFFFFFu))) {
-                bool done = found_any;
-                while (!done && tg_hits == 0u && ng_hits <= 0x00FFFFFFu) {     /* pop; more than once only across a sentinel */
-                    if (sp == 0) { done = true; break; }
-                    uint32_t eb, eh;
-                    RT3_POP(eb, eh);
-                    if (TWO && eb == RT3_STACK_SENTINEL && eh == 0u) {
-                        cur_inst = RT3_STACK_SENTINEL;
-                        rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
-                        r = prepare_ray(wr, magic);
-                        continue;
+                bool done = found_any || sp == 0;
+                if (!TWO) {
+                    if (!done) RT3_POP(ng_base, ng_hits);
+                } else {
+                    while (!done && tg_hits == 0u && ng_hits <= 0x00FFFFFFu) {     /* pop; more than once only across a sentinel */
+                        if (sp == 0) { done = true; break; }
+                        uint32_t eb, eh;
+                        RT3_POP(eb, eh);
+                        if (eb == RT3_STACK_SENTINEL && eh == 0u) {
+                            cur_inst = RT3_STACK_SENTINEL;
+                            rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
+                            r = prepare_ray(wr, magic);
+                            continue;
+                        }
+                        if (eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; ng_hits = 0u; }
                     }
-                    if (!TWO || eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; ng_hits = 0u; }
                 }
                 if (done) {
                     if (ANY) { if (found_any) atomicOr(bits + (my_index >> 5), 1u << (my_index & 31u)); }
