@@ -27,8 +27,8 @@ BOUNCES, SAMPLES = 4, 1
 HBM_BYTES_PER_RAY = 48          # 32 B rt3_ray read + 16 B rt3_hit written
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_trace_dyn<closest> launch of this workload (1.8 M secondary rays), from the committed
 # `ncu --set full` capture; algorithmic bytes of that launch = 48 B x 1.8 M = 86 MB
-NCU_TRACE_DRAM_BYTES_PER_LAUNCH = 83.96e6 + 10.28e6
-NCU_TRACE_DRAM_SOURCE = "profiles/r1d_trace_summary.txt (ncu --set full, launch 1 of 3: 83.96 MB read + 10.28 MB written)"
+NCU_TRACE_DRAM_BYTES_PER_LAUNCH = (77.40e6 + 72.09e6 + 83.96e6 + 8.22e6 + 6.27e6 + 9.73e6) / 3
+NCU_TRACE_DRAM_SOURCE = "profiles/r1d_trace_summary.txt (ncu --set full, mean of the frame's 3 launches: 77.8 MB read + 8.1 MB written)"
 FALLBACK_HBM_GBS = 6650.0       # /opt/skills/guides/B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 
 
