@@ -32,10 +32,15 @@ NCU_TRACE_DRAM_SOURCE = "profiles/r1g_k_trace_dyn_summary.txt (ncu --set full, m
 FALLBACK_HBM_GBS = 6650.0       # /opt/skills/guides/B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 
 
-def make_scene():
+CAMERA = "cam0"                 # --workload cfg5 switches scene, camera and workload name (BASELINE configs[4]); the default is configs[1]
+
+
+def make_scene(workload="cfg2"):
     from raytracer3_b200 import scenes
     sc = scenes.synthetic_atrium(scenes.SPONZA_DETAIL)
     sc["bluenoise"] = scenes.blue_noise_tile()
+    if workload == "cfg5":
+        sc = scenes.instanced_grid(sc, 8)
     return sc
 
 
@@ -47,7 +52,7 @@ def frame_dims(n):
 
 def params_for(sc, W, H, frame, flags):
     from raytracer3_b200.camera import camera_for, make_params
-    return make_params(camera_for(sc, "cam0", W, H), W, H, frame=frame, bounces=BOUNCES, samples=SAMPLES, blendfactor=1.0, flags=flags)
+    return make_params(camera_for(sc, CAMERA, W, H), W, H, frame=frame, bounces=BOUNCES, samples=SAMPLES, blendfactor=1.0, flags=flags)
 
 
 def hbm_peak():
@@ -165,7 +170,7 @@ def run_cuda(args):
     import torch.distributed as dist
     from raytracer3_b200 import scenes
     from raytracer3_b200.host import RenderContext, Renderer, RenderWorld, TiledRenderer
-    from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, RAY
+    from raytracer3_b200.types import BUILD_TWO_LEVEL, FLAG_BLUENOISE, FLAG_ENV, RAY
 
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
@@ -180,11 +185,15 @@ def run_cuda(args):
     flags = FLAG_ENV | FLAG_BLUENOISE
     W, H = frame_dims(n_gpus)
 
-    sc = make_scene()
+    global CAMERA
+    cfg5 = args.workload == "cfg5"
+    if cfg5:
+        CAMERA, args.no_extras = "cam_grid", True
+    sc = make_scene(args.workload)
     ctx = RenderContext(local_rank)
     world = RenderWorld(ctx)
     world.load_scene(sc)
-    bs = world.create_acceleration_structure()
+    bs = world.create_acceleration_structure(1 | (BUILD_TWO_LEVEL if args.two_level else 0))
 
     tiled = n_gpus > 1
     if tiled:
@@ -316,7 +325,8 @@ def run_cuda(args):
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "spp_per_s": paths / (ms * 1e-3), "rays_per_step": rays / args.steps,
-            "config": {"workload": f"synthetic_atrium {W}x{H} path tracing, bounces={BOUNCES}, {SAMPLES} spp, env light + blue noise (BASELINE configs[1]"
+            "config": {"workload": ("8x8 instanced synthetic_atrium (" + ("two-level BLAS/TLAS" if args.two_level else "flattened") + ")" if cfg5 else "synthetic_atrium")
+                                   + f" {W}x{H} path tracing, bounces={BOUNCES}, {SAMPLES} spp, env light + blue noise (BASELINE configs[{4 if cfg5 else 1}]"
                                    + (f", weak-scaled to {n_gpus} x 1920x1080 pixels over 64x64 screen tiles + NCCL all_gather per frame)" if tiled else ")"),
                        "scene": "synthetic_atrium", "triangles": int(bs.triangles), "wide_nodes": int(bs.wide_nodes), "bvh_mb": (bs.node_bytes + bs.tri_bytes) / 1e6,
                        "build_ms": bs.ms_total, "flags": "ENV|BLUENOISE", "parallelism": f"tiles{n_gpus}",
@@ -397,6 +407,8 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg5"], help="cfg2 = BASELINE configs[1] (default, the headline); cfg5 = configs[4], 8x8 instanced grid")
+    ap.add_argument("--two-level", action="store_true", help="RT3_BUILD_TWO_LEVEL (BLAS per mesh + TLAS over the instances)")
     ap.add_argument("--no-extras", action="store_true", help="skip the microbench / L2 roofline / cpu_baseline legs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
