@@ -1,0 +1,182 @@
+"""GPU parity at the edges of the domain: window sizes that are not multiples of the 8x4 pixel block / 16-pixel probe cell / 64-pixel
+tile, one-pixel frames, sub-rect launches, tile lists with clipped and empty tiles, zero bounces, progressive accumulation.
+Every comparison is bit-for-bit against the CPU oracle (or against the full-frame GPU result where the oracle was already compared)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from raytracer3_b200 import scenes
+from raytracer3_b200.camera import camera_for, make_params
+from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV, FLAG_NEE, FLAG_SPECULAR, MISS, Rect, ptr
+
+pytestmark = pytest.mark.gpu
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def _world(gpu_ctx, sc):
+    from raytracer3_b200.host import RenderWorld
+    w = RenderWorld(gpu_ctx)
+    w.clear()
+    w.load_scene(sc)
+    w.create_acceleration_structure()
+    return w
+
+
+def _oracle(sc):
+    from oracle.oracle_py import OracleScene
+    return OracleScene(sc)
+
+
+@pytest.fixture(scope="module")
+def cornell():
+    sc = scenes.cornell_box()
+    sc["environment"] = scenes.analytic_sky(64, 32)
+    sc["bluenoise"] = scenes.blue_noise_tile(64, iters=2)
+    return sc, _oracle(sc)
+
+
+@pytest.mark.parametrize("W,H", [(1, 1), (7, 3), (9, 5), (33, 17), (65, 130), (333, 187)])
+def test_ragged_window_sizes(gpu_ctx, cornell, W, H):
+    """Frames smaller than / not divisible by the 8x4-pixel warp block: padding lanes must neither write nor count."""
+    from raytracer3_b200.host import Renderer
+    sc, orc = cornell
+    w = _world(gpu_ctx, sc)
+    flags = FLAG_ENV | FLAG_BLUENOISE | FLAG_NEE | FLAG_SPECULAR
+    p = make_params(camera_for(sc, "cam0", W, H), W, H, frame=3, bounces=3, samples=2, flags=flags)
+    r = Renderer(gpu_ctx, w, W, H)
+    gpu_ctx.counters(reset=True)
+    light = r.frame(p, debug_ids=True).cpu().numpy()
+    c = gpu_ctx.counters(reset=True)
+    gb, dp, ids, bary = orc.pass_gbuffer(p)
+    want, cnt = orc.pass_reference(p, gb, dp)
+    assert (r.rg.tensor("ids").cpu().numpy().view(np.uint32) == ids).all()
+    assert (_bits(r.rg.tensor("gbuffer_depth").cpu().numpy()) == _bits(dp)).all()
+    assert (_bits(r.rg.tensor("bary").cpu().numpy()) == _bits(bary)).all()
+    hit = ids[..., 0] != MISS
+    assert (r.rg.tensor("gbuffer").cpu().numpy().view(np.uint32)[hit] == gb[hit]).all()
+    assert (_bits(light) == _bits(want)).all()
+    assert c.rays_primary == W * H and c.rays_secondary == cnt.rays_secondary and c.rays_shadow == cnt.rays_shadow
+
+
+def test_sub_rect_launch_touches_only_its_rect(gpu_ctx, cornell):
+    """rt3_pass_gbuffer / rt3_pass_reference on a rect that starts off the block grid: inside == the full-frame result, outside untouched."""
+    import torch
+    sc, orc = cornell
+    w = _world(gpu_ctx, sc)
+    W, H = 200, 120
+    p = make_params(camera_for(sc, "cam0", W, H), W, H, frame=1, bounces=3, samples=1, flags=FLAG_ENV)
+    pp = np.ascontiguousarray(p)
+    gb_full, dp_full, _, _ = orc.pass_gbuffer(p)
+    want, _ = orc.pass_reference(p, gb_full, dp_full)
+    L, h, st = gpu_ctx.L, gpu_ctx.h, gpu_ctx.stream()
+    for (x0, y0, rw, rh) in ((13, 7, 50, 33), (0, 0, 1, 1), (199, 119, 1, 1), (64, 0, 136, 120)):
+        gb = torch.full((H, W, 4), 0x5A5A5A5A, dtype=torch.int32, device="cuda")
+        dp = torch.full((H, W), -7.0, dtype=torch.float32, device="cuda")
+        lt = torch.full((H, W, 4), -3.0, dtype=torch.float32, device="cuda")
+        rect = Rect(x0, y0, rw, rh)
+        gpu_ctx.check(L.rt3_pass_gbuffer(h, ptr(pp), rect, gb.data_ptr(), dp.data_ptr(), None, None, st))
+        gpu_ctx.check(L.rt3_pass_reference(h, ptr(pp), rect, gb.data_ptr(), dp.data_ptr(), None, lt.data_ptr(), st))
+        gbn, dpn, ltn = gb.cpu().numpy().view(np.uint32), dp.cpu().numpy(), lt.cpu().numpy()
+        inside = np.zeros((H, W), bool)
+        inside[y0:y0 + rh, x0:x0 + rw] = True
+        assert (dpn[~inside] == -7.0).all() and (gbn[~inside] == 0x5A5A5A5A).all() and (ltn[~inside] == -3.0).all()
+        assert (_bits(dpn[inside]) == _bits(dp_full[inside])).all()
+        hit = inside & (dp_full != np.float32(100000.0))
+        assert (gbn[hit] == gb_full[hit]).all()
+        assert (_bits(ltn[hit]) == _bits(want[hit])).all()
+        bg = inside & ~hit
+        assert (ltn[bg] == -3.0).all()                      # refrence_mode.slang:20-23: background pixels are left alone
+
+
+@pytest.mark.parametrize("W,H,N,tile", [(200, 130, 3, 64), (97, 61, 2, 32), (260, 200, 5, 64)])
+def test_tile_lists_with_clipped_and_empty_tiles(gpu_ctx, cornell, W, H, N, tile):
+    """N logical ranks on one GPU: slabs of clipped edge tiles and padding rects, gathered in rank order and un-tiled, equal the
+    full-frame render bit for bit (the multi-GPU path minus the NCCL call, which the gloo test and bench.py's verification cover)."""
+    import torch
+    from raytracer3_b200.host import Renderer, TiledRenderer
+    from raytracer3_b200.tiles import all_tiles
+    sc, orc = cornell
+    w = _world(gpu_ctx, sc)
+    flags = FLAG_ENV | FLAG_BLUENOISE
+    cam = camera_for(sc, "cam0", W, H)
+    full = Renderer(gpu_ctx, w, W, H)
+    ranks = []
+    for rk in range(N):
+        try:
+            ranks.append(TiledRenderer(gpu_ctx, w, W, H, rk, N, tile=tile))
+        except AssertionError:
+            pytest.skip("a rank without a full tile: not a configuration the tile renderer accepts")
+    for n in range(3):                                       # progressive accumulation, slabs stay rank-local
+        p = make_params(cam, W, H, frame=n, bounces=3, samples=1, blendfactor=1.0 / (n + 1), flags=flags)
+        want = full.frame(p)
+        slabs = [R.frame(p) for R in ranks]
+    gathered = torch.cat(slabs, 0).contiguous()
+    rects = np.ascontiguousarray(all_tiles(W, H, N, tile))
+    frame = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    gpu_ctx.check(gpu_ctx.L.rt3_untile_rgba32f(gpu_ctx.h, ptr(rects), len(rects), tile, tile, gathered.data_ptr(), frame.data_ptr(), W, H, gpu_ctx.stream()))
+    assert torch.equal(frame.view(torch.int32), want.view(torch.int32))
+    assert float(frame[..., :3].abs().sum()) > 0
+
+
+def test_zero_bounces_and_progressive_accumulation(gpu_ctx, cornell):
+    from raytracer3_b200.host import Renderer
+    sc, orc = cornell
+    w = _world(gpu_ctx, sc)
+    W, H = 96, 64
+    cam = camera_for(sc, "cam0", W, H)
+    r = Renderer(gpu_ctx, w, W, H)
+    p0 = make_params(cam, W, H, frame=0, bounces=0, samples=1)           # the bounce loop does not run: radiance 0 on every hit pixel
+    light = r.frame(p0).cpu().numpy()
+    gb, dp, _, _ = orc.pass_gbuffer(p0)
+    want, _ = orc.pass_reference(p0, gb, dp)
+    assert (_bits(light) == _bits(want)).all() and (light[..., :3] == 0).all()
+    prev = None
+    for n in range(6):                                                     # cfg3's schedule: blendfactor 1/(n+1), Light / PrevLight ping-pong
+        p = make_params(cam, W, H, frame=n, bounces=4, samples=1, blendfactor=1.0 / (n + 1), flags=FLAG_ENV)
+        light = r.frame(p).cpu().numpy()
+        want, _ = orc.pass_reference(p, gb, dp, prev_light=prev)
+        prev = want
+        assert (_bits(light) == _bits(want)).all(), f"accumulated frame {n} differs"
+
+
+@pytest.mark.parametrize("W,H", [(250, 130), (17, 16), (16, 33)])
+def test_probe_passes_at_ragged_sizes(gpu_ctx, cornell, W, H):
+    """Probe grid with a partial last row / column of 16x16 cells."""
+    from raytracer3_b200.host import Renderer
+    sc, orc = cornell
+    w = _world(gpu_ctx, sc)
+    p = make_params(camera_for(sc, "cam0", W, H), W, H, frame=2, bounces=1, samples=1, flags=FLAG_ENV)
+    gb, dp, _, _ = orc.pass_gbuffer(p)
+    r = Renderer(gpu_ctx, w, W, H)
+    light = r.probe_frame(p).cpu().numpy()
+    atlas = r.rg.tensor(f"probe_atlas{1 - r.probe_cur}").cpu().numpy()
+    sh = r.rg.tensor("probe_sh").cpu().numpy()
+    want_atlas = orc.pass_probe_trace(p, gb, dp)
+    want_sh = orc.pass_probe_sh(p, want_atlas)
+    want_light = orc.pass_probe_interpolate(p, gb, dp, want_sh)
+    assert (_bits(atlas) == _bits(want_atlas)).all()
+    used = np.abs(want_sh).sum(1) > 0
+    assert (_bits(sh[used]) == _bits(want_sh[used])).all()
+    assert (_bits(light) == _bits(want_light)).all()
+
+
+def test_invalid_arguments_are_status_codes(gpu_ctx, cornell):
+    from raytracer3_b200 import _lib
+    sc, _ = cornell
+    w = _world(gpu_ctx, sc)
+    W, H = 32, 16
+    p = np.ascontiguousarray(make_params(camera_for(sc, "cam0", W, H), W, H, bounces=1, samples=1))
+    L, h = gpu_ctx.L, gpu_ctx.h
+    bad = p.copy(); bad["samples"] = 0
+    assert L.rt3_pass_reference(h, ptr(bad), Rect(0, 0, W, H), None, None, None, None, None) != 0
+    assert b"samples" in L.rt3_last_error(h)
+    import torch
+    gb = torch.zeros((H, W + 1, 4), dtype=torch.int32, device="cuda"); dp = torch.zeros((H, W + 1), dtype=torch.float32, device="cuda")
+    assert L.rt3_pass_gbuffer(h, ptr(p), Rect(0, 0, W + 1, H), gb.data_ptr(), dp.data_ptr(), None, None, None) != 0      # rect outside the window
+    assert b"rect" in L.rt3_last_error(h)
+    with pytest.raises(_lib.Rt3Error):
+        gpu_ctx.check(L.rt3_pass_gbuffer(h, ptr(p), Rect(0, 0, W, H), None, None, None, None, None))  # NULL outputs
