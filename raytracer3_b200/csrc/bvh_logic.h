@@ -176,6 +176,7 @@ struct CollapseCtx {
     uint32_t* next_items;         /* pairs (bvh2 ref, wide index) for the next level */
     uint32_t* next_count;
     float* sah_accum;             /* [0] node term, [1] triangle term (area-weighted)   */
+    const struct DpNode* dp;      /* optional: cost-optimal child selection (dp_node); nullptr = greedy by surface area */
 };
 
 RT3_HD uint32_t bvh2_slot(const CollapseCtx& c, uint32_t ref) {
@@ -194,6 +195,58 @@ RT3_HD int quant_exponent(float extent) {
     return e;
 }
 
+/* ---- cost-optimal choice of the children of a wide node (Ylitie, Karras, Laine 2017, section 3.1) -----------------------------
+ * For every BVH2 node n and i = 1..7, C(n, i) = least SAH cost of representing the subtree of n by at most i wide-BVH children:
+ *   C(n, 1)      = leaf cost A(n) * P(n) * c_prim           if P(n) <= 3 (our leaf limit)
+ *                = A(n) * c_node + D(n, 8)                  otherwise (n becomes an inner wide node)
+ *   C(n, i)      = min(D(n, i), C(n, i - 1))                i = 2..7
+ *   D(n, j)      = min over 0 < k < j of C(left, k) + C(right, j - k)
+ * dec[i] records the argmin: 0 = "same as i - 1", else k = children given to the left subtree; dec[0] is the k of D(n, 8).
+ * Computed bottom-up (dp_node, after the refit), consumed top-down by collapse_one. */
+struct DpNode { float cost[7]; uint8_t dec[8]; uint32_t pad; };            /* 40 B per BVH2 internal node */
+#define RT3_DP_C_NODE 1.0f     /* cost of one wide-node test ...                                        */
+#define RT3_DP_C_PRIM 0.3f     /* ... and of one triangle test (the result is flat between 0.2 and 1.2) */
+RT3_HD void dp_leaf_costs(float area, float cost[7]) {
+    for (int i = 0; i < 7; ++i) cost[i] = area * RT3_DP_C_PRIM;
+}
+RT3_HD void dp_node(const float cl[7], const float cr[7], float area, uint32_t count, DpNode& out) {
+    /* D(n, j), j = 2..8 */
+    float D[9]; uint8_t K[9];
+    for (int j = 2; j <= 8; ++j) {
+        float best = 3.4e38f; int bk = 1;
+        for (int k = 1; k < j; ++k) {
+            if (k > 7 || j - k > 7) continue;
+            float v = cl[k - 1] + cr[j - k - 1];
+            if (v < best) { best = v; bk = k; }
+        }
+        D[j] = best; K[j] = (uint8_t)bk;
+    }
+    out.dec[0] = K[8];
+    out.cost[0] = count <= 3u ? area * (float)count * RT3_DP_C_PRIM : area * RT3_DP_C_NODE + D[8];
+    for (int i = 2; i <= 7; ++i) {
+        if (D[i] < out.cost[i - 2]) { out.cost[i - 1] = D[i]; out.dec[i] = K[i]; }
+        else { out.cost[i - 1] = out.cost[i - 2]; out.dec[i] = 0; }
+    }
+    out.dec[1] = 0; out.pad = 0;
+}
+/* children of the wide node rooted at BVH2 internal node `ref`, from the decisions */
+RT3_HD int dp_select_children(const Bvh2Node* nodes, const DpNode* dp, uint32_t ref, uint32_t ch[8]) {
+    uint32_t st_ref[8]; int st_i[8]; int sp = 0, nc = 0;
+    const int k8 = dp[ref].dec[0];
+    st_ref[sp] = nodes[ref].right; st_i[sp++] = 8 - k8;
+    st_ref[sp] = nodes[ref].left; st_i[sp++] = k8;
+    while (sp) {
+        uint32_t m = st_ref[--sp]; int i = st_i[sp];
+        if (m & LEAF_FLAG) { ch[nc++] = m; continue; }
+        while (i > 1 && dp[m].dec[i] == 0) --i;
+        if (i <= 1) { ch[nc++] = m; continue; }
+        const int k = dp[m].dec[i];
+        st_ref[sp] = nodes[m].right; st_i[sp++] = i - k;
+        st_ref[sp] = nodes[m].left; st_i[sp++] = k;
+    }
+    return nc;
+}
+
 /*
  * Node layout (20 words):
  *   w0..w2  p = node box min (float)            w3  ex | ey<<8 | ez<<16 | imask<<24   (e biased by 127)
@@ -208,9 +261,10 @@ RT3_HD void collapse_one(const CollapseCtx& c, uint32_t ref, uint32_t wide_index
     int nc;
     uint32_t self = bvh2_slot(c, ref);
     if (ref & LEAF_FLAG) { ch[0] = ref; nc = 1; }
+    else if (c.dp != nullptr && c.counts[ref] > 3u) nc = dp_select_children(c.nodes, c.dp, ref, ch);
     else { ch[0] = c.nodes[ref].left; ch[1] = c.nodes[ref].right; nc = 2; }
     /* greedy: open the inner child of largest surface area until 8 slots are used */
-    while (nc < 8) {
+    while (c.dp == nullptr && nc < 8) {
         int best = -1; float best_a = -1.0f;
         for (int k = 0; k < nc; ++k) {
             if (ch[k] & LEAF_FLAG) continue;

@@ -25,7 +25,7 @@ struct EmuBvh {
 
 extern "C" {
 
-EmuBvh* emu_build(const float* tris9, uint32_t n) {
+static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp) {
     EmuBvh* b = new EmuBvh();
     b->tris_in.resize(n);
     for (int a = 0; a < 3; ++a) { b->lo[a] = 3.4e38f; b->hi[a] = -3.4e38f; }
@@ -81,6 +81,25 @@ EmuBvh* emu_build(const float* tris9, uint32_t n) {
             cur = parent[cur];
         }
     }
+    /* optional: cost-optimal child selection (same per-node function the GPU runs bottom-up after the refit) */
+    std::vector<DpNode> dp;
+    if (use_dp && n > 1) {
+        dp.resize(n - 1);
+        std::vector<uint32_t> order_; order_.reserve(n - 1);
+        std::vector<uint32_t> stack_{0u};
+        while (!stack_.empty()) { uint32_t r = stack_.back(); stack_.pop_back(); order_.push_back(r);
+            if (!(n2[r].left & LEAF_FLAG)) stack_.push_back(n2[r].left); if (!(n2[r].right & LEAF_FLAG)) stack_.push_back(n2[r].right); }
+        for (size_t q = order_.size(); q-- > 0;) {          /* reverse pre-order: children before parents */
+            uint32_t r = order_[q];
+            float cl[7], cr[7];
+            auto child_costs = [&](uint32_t ref, float out[7]) {
+                if (ref & LEAF_FLAG) { const Bvh2Node& lf = n2[n - 1 + (ref & ~LEAF_FLAG)]; dp_leaf_costs(box_area(lf.lo, lf.hi), out); }
+                else for (int i = 0; i < 7; ++i) out[i] = dp[ref].cost[i];
+            };
+            child_costs(n2[r].left, cl); child_costs(n2[r].right, cr);
+            dp_node(cl, cr, box_area(n2[r].lo, n2[r].hi), counts[r], dp[r]);
+        }
+    }
     /* collapse, level by level */
     b->nodes.resize(n);  /* upper bound: every wide node has >= 2 children unless n == 1 */
     b->tris_out.resize(n);
@@ -90,7 +109,7 @@ EmuBvh* emu_build(const float* tris9, uint32_t n) {
     CollapseCtx c;
     c.nodes = n2.data(); c.counts = counts.data(); c.tris_sorted = b->tris_sorted.data(); c.n_leaves = n;
     c.out_nodes = b->nodes.data(); c.out_tris = b->tris_out.data(); c.node_counter = &node_counter; c.tri_counter = &tri_counter;
-    c.next_count = &next_count; c.sah_accum = b->sah;
+    c.next_count = &next_count; c.sah_accum = b->sah; c.dp = dp.empty() ? nullptr : dp.data();
     while (q_count) {
         next_count = 0; c.next_items = qn.data();
         for (uint32_t i = 0; i < q_count; ++i) collapse_one(c, q[2 * i], q[2 * i + 1]);
@@ -99,6 +118,8 @@ EmuBvh* emu_build(const float* tris9, uint32_t n) {
     b->n_nodes = node_counter; b->n_tris = tri_counter;
     return b;
 }
+EmuBvh* emu_build(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, false); }
+EmuBvh* emu_build_dp(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, true); }
 /* wrap an acceleration structure built elsewhere (downloaded from the GPU) so that it can be traversed here */
 EmuBvh* emu_wrap(const uint32_t* nodes20, uint32_t n_nodes, const uint32_t* tris12, uint32_t n_tris) {
     EmuBvh* b = new EmuBvh();
@@ -250,7 +271,7 @@ extern "C" EmuBvh* emu_build_sah(const float* tris9, uint32_t n) {
     uint32_t node_counter = 1, tri_counter = 0, q_count = 1, next_count = 0;
     q[0] = root; q[1] = 0;
     CollapseCtx c; c.nodes = n2.data(); c.counts = counts.data(); c.tris_sorted = b->tris_sorted.data(); c.n_leaves = n;
-    c.out_nodes = b->nodes.data(); c.out_tris = b->tris_out.data(); c.node_counter = &node_counter; c.tri_counter = &tri_counter; c.next_count = &next_count; c.sah_accum = b->sah;
+    c.out_nodes = b->nodes.data(); c.out_tris = b->tris_out.data(); c.node_counter = &node_counter; c.tri_counter = &tri_counter; c.next_count = &next_count; c.sah_accum = b->sah; c.dp = nullptr;
     while (q_count) { next_count = 0; c.next_items = qn.data(); for (uint32_t i = 0; i < q_count; ++i) collapse_one(c, q[2 * i], q[2 * i + 1]); q.swap(qn); q_count = next_count; b->levels++; }
     b->n_nodes = node_counter; b->n_tris = tri_counter;
     return b;

@@ -23,6 +23,8 @@ def lib():
         L = C.CDLL(_SO)
         L.emu_build.restype = C.c_void_p
         L.emu_build.argtypes = [C.c_void_p, C.c_uint32]
+        L.emu_build_dp.restype = C.c_void_p
+        L.emu_build_dp.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_wrap.restype = C.c_void_p
         L.emu_wrap.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
         L.emu_destroy.argtypes = [C.c_void_p]
@@ -36,11 +38,12 @@ def lib():
 
 
 class EmuBvh:
-    def __init__(self, tris=None, nodes=None, tri_records=None):
+    def __init__(self, tris=None, nodes=None, tri_records=None, optimal_collapse=True):
+        """optimal_collapse: children of the wide nodes by the cost dynamic programme (the device default) or greedily (RT3_BUILD_FAST_BUILD)"""
         self.L = lib()
         if tris is not None:
             t = np.ascontiguousarray(tris, np.float32)
-            self.h = self.L.emu_build(ptr(t), len(t))
+            self.h = (self.L.emu_build_dp if optimal_collapse else self.L.emu_build)(ptr(t), len(t))
         else:
             n, r = np.ascontiguousarray(nodes, np.uint32), np.ascontiguousarray(tri_records, np.uint32)
             self.h = self.L.emu_wrap(ptr(n), len(n), ptr(r), len(r))

@@ -16,11 +16,12 @@ CASES = {
 }
 
 
+@pytest.mark.parametrize("optimal", [True, False])
 @pytest.mark.parametrize("name", list(CASES))
-def test_wide_bvh_equals_brute_force(name):
+def test_wide_bvh_equals_brute_force(name, optimal):
     sc = CASES[name]()
     T = np.ascontiguousarray(scenes.world_triangles(sc), np.float32)
-    b = EmuBvh(tris=T)
+    b = EmuBvh(tris=T, optimal_collapse=optimal)
     info = b.info()
     assert info["tris"] == len(T) and b.check_triangles() == 0          # order-independent: every triangle kept exactly once, unmodified
     assert info["levels"] < 64
@@ -33,6 +34,19 @@ def test_wide_bvh_equals_brute_force(name):
     assert (b.trace_any(a) == b.trace_any(a, brute=True)).all()
 
 
+def test_cost_optimal_collapse_needs_fewer_nodes_and_less_work():
+    """The dynamic programme (bvh_logic.h dp_node / dp_select_children) against the greedy choice on the same binary tree."""
+    sc = scenes.synthetic_atrium(0.05, environment=False)
+    T = np.ascontiguousarray(scenes.world_triangles(sc), np.float32)
+    c, _ = scenes.incoherent_rays(sc, 4000, seed=5, tris=T.astype(np.float64))
+    greedy, best = EmuBvh(tris=T, optimal_collapse=False), EmuBvh(tris=T, optimal_collapse=True)
+    hg, sg = greedy.trace_closest(c)
+    hb, sb = best.trace_closest(c)
+    assert (hg == hb).all()                                                # hits do not depend on the topology
+    assert best.info()["nodes"] < 0.85 * greedy.info()["nodes"]
+    assert sb[0] + 0.4 * sb[1] < sg[0] + 0.4 * sg[1]                       # node tests + 0.4 x triangle tests per ray (measured cost ratio)
+
+
 def test_degenerate_inputs():
     # all triangles identical (duplicate Morton codes -> index tie-break in lbvh_delta), zero-area triangles, one triangle, none
     tri = np.array([[[0, 0, 0], [1, 0, 0], [0, 1, 0]]], np.float32)
@@ -40,8 +54,8 @@ def test_degenerate_inputs():
     rays["o"] = [0.2, 0.2, -1]
     rays["d"] = [0, 0, 1]
     rays["tmax"] = 10
-    for T in (np.repeat(tri, 37, 0), tri, np.concatenate([tri, np.zeros((5, 3, 3), np.float32)])):
-        b = EmuBvh(tris=T)
+    for T, optimal in [(t, o) for t in (np.repeat(tri, 37, 0), tri, np.concatenate([tri, np.zeros((5, 3, 3), np.float32)])) for o in (True, False)]:
+        b = EmuBvh(tris=T, optimal_collapse=optimal)
         assert b.check_triangles() == 0
         got, _ = b.trace_closest(rays)
         assert (got["prim"] == 0).all() and np.allclose(got["t"], 1.0)     # equal t resolves to the lowest triangle id

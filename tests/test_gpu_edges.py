@@ -180,3 +180,30 @@ def test_invalid_arguments_are_status_codes(gpu_ctx, cornell):
     assert b"rect" in L.rt3_last_error(h)
     with pytest.raises(_lib.Rt3Error):
         gpu_ctx.check(L.rt3_pass_gbuffer(h, ptr(p), Rect(0, 0, W, H), None, None, None, None, None))  # NULL outputs
+
+
+def test_collapse_policies_give_identical_hits(gpu_ctx):
+    """RT3_BUILD_FAST_TRACE (cost-optimal children, the default) vs RT3_BUILD_FAST_BUILD (greedy): same hits bit for bit, fewer nodes,
+    every triangle kept exactly once in both (order-independent check on the downloaded structure)."""
+    import sys, os, torch
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from emu_lib import EmuBvh
+    from raytracer3_b200.host import RenderWorld
+    from raytracer3_b200.types import BUILD_FAST_BUILD, BUILD_FAST_TRACE, BUILD_TWO_LEVEL
+    sc = scenes.instanced_grid(scenes.synthetic_atrium(0.05, environment=False), 2)
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc)
+    closest, anyr = scenes.incoherent_rays(sc, 200000, seed=9)
+    rays = torch.from_numpy(np.concatenate([closest, scenes.random_rays(sc, 50000, seed=10)]).view(np.float32).reshape(-1, 8)).cuda()
+    arays = torch.from_numpy(anyr.view(np.float32).reshape(-1, 8)).cuda()
+    results = {}
+    for name, flags in (("trace", BUILD_FAST_TRACE), ("build", BUILD_FAST_BUILD), ("trace2", BUILD_FAST_TRACE | BUILD_TWO_LEVEL), ("build2", BUILD_FAST_BUILD | BUILD_TWO_LEVEL)):
+        bs = w.create_acceleration_structure(flags)
+        results[name] = (bs.wide_nodes, w.trace_closest(rays).cpu().numpy().view(np.uint32), w.trace_any(arays).cpu().numpy())
+        if not flags & BUILD_TWO_LEVEL:
+            nodes, tris = w.download_accel()
+            assert EmuBvh(nodes=nodes, tri_records=tris).check_triangles() == 0
+    for name in ("build", "trace2", "build2"):
+        assert (results[name][1] == results["trace"][1]).all() and (results[name][2] == results["trace"][2]).all(), name
+    assert results["trace"][0] < 0.85 * results["build"][0] and results["trace2"][0] < 0.85 * results["build2"][0]
+    assert (results["trace"][1][:, 3] != MISS).mean() > 0.5
