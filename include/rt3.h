@@ -109,8 +109,9 @@ typedef struct { float t, u, v; uint32_t prim; } rt3_hit;           /* 16 B; pri
 /* RT3_BUILD_TWO_LEVEL: one bottom-level tree per distinct mesh (= distinct geometry range of rt3_scene_push_instance) and a
  * top-level tree over the instances — the BLAS / TLAS split of VK_KHR_acceleration_structure (raytracing.rs:88-148 builds
  * either level).  Default: instances are flattened into one world-space tree.  Hits are bit-identical in both modes. */
-/* RT3_BUILD_FAST_BUILD: the children of each wide node are chosen greedily by surface area; otherwise (RT3_BUILD_FAST_TRACE, the
- * reference's PREFER_FAST_TRACE, raytracing.rs:121) by the SAH dynamic programme of Ylitie et al. 2017 over the binary tree. */
+/* RT3_BUILD_FAST_BUILD: plain LBVH, the children of each wide node chosen greedily by surface area.  Otherwise (RT3_BUILD_FAST_TRACE,
+ * the reference's PREFER_FAST_TRACE, raytracing.rs:121): three bottom-up passes of SAH tree rotations over the binary tree and the
+ * children chosen by the SAH dynamic programme of Ylitie et al. 2017.  Hits are bit-identical either way. */
 enum { RT3_BUILD_FAST_TRACE = 1u, RT3_BUILD_FAST_BUILD = 2u, RT3_BUILD_TWO_LEVEL = 4u };
 
 typedef struct {

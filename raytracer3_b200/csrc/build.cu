@@ -229,44 +229,60 @@ __global__ void __launch_bounds__(256) k_lbvh_hierarchy(const uint64_t* keys, in
     if (i < n - 1) lbvh_build_node(keys, n, i, nodes, parent);
 }
 
+/* How refit_visit (bvh_logic.h) reads what OTHER threads of the same launch wrote: past the non-coherent L1 (ld.global.cg). */
+struct DevMem {
+    Bvh2Node* nodes; uint32_t* counts; DpNode* dp; uint32_t n;
+    __device__ uint32_t slot(uint32_t ref) const { return (ref & LEAF_FLAG) ? n - 1 + (ref & ~LEAF_FLAG) : ref; }
+    __device__ Bvh2Node node(uint32_t i) const {
+        const float4 a = __ldcg((const float4*)(nodes + i)), b = __ldcg((const float4*)(nodes + i) + 1);
+        Bvh2Node m;
+        m.lo[0] = a.x; m.lo[1] = a.y; m.lo[2] = a.z; m.left = __float_as_uint(a.w);
+        m.hi[0] = b.x; m.hi[1] = b.y; m.hi[2] = b.z; m.right = __float_as_uint(b.w);
+        return m;
+    }
+    __device__ void store_node(uint32_t i, const Bvh2Node& m) {
+        float4* p = (float4*)(nodes + i);
+        __stcg(p, make_float4(m.lo[0], m.lo[1], m.lo[2], __uint_as_float(m.left)));
+        __stcg(p + 1, make_float4(m.hi[0], m.hi[1], m.hi[2], __uint_as_float(m.right)));
+    }
+    __device__ uint32_t count(uint32_t ref) const { return (ref & LEAF_FLAG) ? 1u : __ldcg(counts + ref); }
+    __device__ void store_count(uint32_t i, uint32_t c) { __stcg(counts + i, c); }
+    __device__ void dp_costs(uint32_t ref, float out[7]) const { for (int i = 0; i < 7; ++i) out[i] = __ldcg(&dp[ref].cost[i]); }
+    __device__ void store_dp(uint32_t i, const DpNode& d) {
+        uint32_t* p = (uint32_t*)(dp + i); const uint32_t* q = (const uint32_t*)&d;
+        for (int k = 0; k < 10; ++k) __stcg(p + k, q[k]);
+    }
+};
+
+/* leaf boxes (first pass only), then the bottom-up walk: one atomic flag per node, the second arrival runs refit_visit */
 __global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_t n, int kind, float pad, Bvh2Node* nodes, const uint32_t* parent,
-                                               uint32_t* flags, uint32_t* counts, DpNode* dp) {
+                                               uint32_t* flags, uint32_t* counts, DpNode* dp, int first_pass, int rotate, int with_dp) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
-    Bvh2Node leaf;
-    tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi, kind);
-    leaf.left = leaf.right = 0;
-    nodes[n - 1 + k] = leaf;
+    DevMem mem{nodes, counts, dp, n};
+    if (first_pass) {
+        Bvh2Node leaf;
+        tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi, kind);
+        leaf.left = leaf.right = 0;
+        mem.store_node(n - 1 + k, leaf);
+    }
     uint32_t cur = parent[n - 1 + k];
     while (cur != 0xFFFFFFFFu) {
         __threadfence();
         if (atomicAdd(flags + cur, 1u) == 0u) return;   /* first arrival: the sibling subtree is not ready yet */
-        volatile Bvh2Node* nd = nodes + cur;
-        uint32_t l = nd->left, r = nd->right;
-        uint32_t li = (l & LEAF_FLAG) ? n - 1 + (l & ~LEAF_FLAG) : l, ri = (r & LEAF_FLAG) ? n - 1 + (r & ~LEAF_FLAG) : r;
-        volatile Bvh2Node* a = nodes + li;
-        volatile Bvh2Node* b = nodes + ri;
-        float lo[3], hi[3], alo[3], ahi[3], blo[3], bhi[3];
-        for (int ax = 0; ax < 3; ++ax) {
-            alo[ax] = a->lo[ax]; ahi[ax] = a->hi[ax]; blo[ax] = b->lo[ax]; bhi[ax] = b->hi[ax];
-            lo[ax] = fminf(alo[ax], blo[ax]); hi[ax] = fmaxf(ahi[ax], bhi[ax]);
-            nd->lo[ax] = lo[ax]; nd->hi[ax] = hi[ax];
-        }
-        volatile uint32_t* vc = counts;
-        const uint32_t cnt = ((l & LEAF_FLAG) ? 1u : vc[l]) + ((r & LEAF_FLAG) ? 1u : vc[r]);
-        vc[cur] = cnt;
-        if (dp != nullptr) {                             /* cost-optimal collapse: C(cur, 1..7) from the children's (bvh_logic.h) */
-            float cl[7], cr[7];
-            if (l & LEAF_FLAG) dp_leaf_costs(box_area(alo, ahi), cl);
-            else for (int i = 0; i < 7; ++i) cl[i] = __ldcg(&dp[l].cost[i]);
-            if (r & LEAF_FLAG) dp_leaf_costs(box_area(blo, bhi), cr);
-            else for (int i = 0; i < 7; ++i) cr[i] = __ldcg(&dp[r].cost[i]);
-            DpNode out;
-            dp_node(cl, cr, box_area(lo, hi), cnt, out);
-            dp[cur] = out;
-        }
+        __threadfence();
+        refit_visit(mem, n, cur, rotate != 0, with_dp != 0);
         cur = parent[cur];
     }
+}
+
+/* rotations moved subtrees: parent links for the next bottom-up pass */
+__global__ void __launch_bounds__(256) k_parents(const Bvh2Node* nodes, uint32_t n, uint32_t* parent) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 >= n) return;
+    const uint32_t l = nodes[i].left, r = nodes[i].right;
+    parent[(l & LEAF_FLAG) ? n - 1 + (l & ~LEAF_FLAG) : l] = i;
+    parent[(r & LEAF_FLAG) ? n - 1 + (r & ~LEAF_FLAG) : r] = i;
 }
 
 __global__ void __launch_bounds__(128) k_collapse(CollapseCtx c, const uint32_t* items, uint32_t count) {
@@ -387,7 +403,15 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         dbg_mark("hierarchy");
         tm.begin();
         DpNode* dp = io.optimal_collapse ? (DpNode*)(base + o_dp) : nullptr;
-        RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp);
+        const int passes = io.optimal_collapse ? RT3_REFIT_PASSES : 1;
+        for (int pass = 0; pass < passes; ++pass) {
+            if (pass) {
+                RT3_CUDA(c, cudaMemsetAsync(nflags, 0, sizeof(uint32_t) * n, st));
+                if (n > 1) RT3_LAUNCH(c, k_parents, div_up(n - 1, 256), 256, 0, st, nodes2, n, parent);
+            }
+            RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0,
+                       io.optimal_collapse ? 1 : 0, (io.optimal_collapse && pass == passes - 1) ? 1 : 0);
+        }
         bs.ms_refit += tm.end();
         dbg_mark("refit");
         /* collapse */

@@ -204,6 +204,7 @@ RT3_HD int quant_exponent(float extent) {
  * dec[i] records the argmin: 0 = "same as i - 1", else k = children given to the left subtree; dec[0] is the k of D(n, 8).
  * Computed bottom-up (dp_node, after the refit), consumed top-down by collapse_one. */
 struct DpNode { float cost[7]; uint8_t dec[8]; uint32_t pad; };            /* 40 B per BVH2 internal node */
+#define RT3_REFIT_PASSES 3      /* bottom-up passes of the default build (rotations in all, the programme in the last) */
 #define RT3_DP_C_NODE 1.0f     /* cost of one wide-node test ...                                        */
 #define RT3_DP_C_PRIM 0.3f     /* ... and of one triangle test (the result is flat between 0.2 and 1.2) */
 RT3_HD void dp_leaf_costs(float area, float cost[7]) {
@@ -245,6 +246,89 @@ RT3_HD int dp_select_children(const Bvh2Node* nodes, const DpNode* dp, uint32_t 
         st_ref[sp] = nodes[m].left; st_i[sp++] = k;
     }
     return nc;
+}
+
+/* ---- one step of the bottom-up pass over the BVH2 (the thread that arrives second at `cur` runs it; both subtrees are final) ------
+ * 1. optional tree rotations (Kensler 2008): exchange a child of `cur` with a grandchild on the other side, or two grandchildren of
+ *    different sides, when that shrinks the surface area of the rebuilt child(ren) — the SAH term those nodes contribute.  Only
+ *    nodes below `cur` change, so threads still walking elsewhere are not affected; the choice depends on the tree alone, not on
+ *    which thread got here, so the build stays deterministic.
+ * 2. bounds and triangle count of `cur`, 3. optionally its row of the collapse programme (dp_node).
+ * `Mem` hides how nodes written by OTHER threads of the same launch are read (device: ld.global.cg past the non-coherent L1;
+ * emulator: plain arrays).  Leaves are referenced as LEAF_FLAG | k and stored at slot n - 1 + k (box only). */
+RT3_HD void box_union(const Bvh2Node& a, const Bvh2Node& b, float lo[3], float hi[3]) {
+    for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(a.lo[q], b.lo[q]); hi[q] = rt3m::max_(a.hi[q], b.hi[q]); }
+}
+RT3_HD float union_area(const Bvh2Node& a, const Bvh2Node& b) { float lo[3], hi[3]; box_union(a, b, lo, hi); return box_area(lo, hi); }
+template <class Mem>
+RT3_HD void refit_visit(Mem& mem, uint32_t n, uint32_t cur, bool rotate, bool with_dp) {
+    Bvh2Node P = mem.node(cur);
+    uint32_t L = P.left, R = P.right;
+    Bvh2Node nl = mem.node(mem.slot(L)), nr = mem.node(mem.slot(R));
+    /* (re)build internal node `id` from two finished subtrees; ka / kb: programme rows of a / b when they were rebuilt by this very
+     * visit (otherwise they are read from memory), out: the row of `id` */
+    auto rebuild = [&](uint32_t id, uint32_t a_ref, const Bvh2Node& a, uint32_t na, const float* ka, uint32_t b_ref, const Bvh2Node& b, uint32_t nb, const float* kb,
+                       float* out) {
+        Bvh2Node m;
+        box_union(a, b, m.lo, m.hi);
+        m.left = a_ref; m.right = b_ref;
+        mem.store_node(id, m);
+        const uint32_t cnt = na + nb;
+        mem.store_count(id, cnt);
+        if (with_dp) {
+            float ca[7], cb[7];
+            if (a_ref & LEAF_FLAG) dp_leaf_costs(box_area(a.lo, a.hi), ca); else if (ka) { for (int i = 0; i < 7; ++i) ca[i] = ka[i]; } else mem.dp_costs(a_ref, ca);
+            if (b_ref & LEAF_FLAG) dp_leaf_costs(box_area(b.lo, b.hi), cb); else if (kb) { for (int i = 0; i < 7; ++i) cb[i] = kb[i]; } else mem.dp_costs(b_ref, cb);
+            DpNode d;
+            dp_node(ca, cb, box_area(m.lo, m.hi), cnt, d);
+            mem.store_dp(id, d);
+            if (out) for (int i = 0; i < 7; ++i) out[i] = d.cost[i];
+        }
+        return m;
+    };
+    float kl[7], kr[7];
+    const float *pkl = nullptr, *pkr = nullptr;
+    uint32_t cL = mem.count(L), cR = mem.count(R);
+    if (rotate) {
+        const bool li = !(L & LEAF_FLAG), ri = !(R & LEAF_FLAG);
+        Bvh2Node ll = nl, lr = nl, rl = nr, rr = nr;
+        if (li) { ll = mem.node(mem.slot(nl.left)); lr = mem.node(mem.slot(nl.right)); }
+        if (ri) { rl = mem.node(mem.slot(nr.left)); rr = mem.node(mem.slot(nr.right)); }
+        const float aL = box_area(nl.lo, nl.hi), aR = box_area(nr.lo, nr.hi);
+        float best = 0.0f; int opt = 0;
+        if (ri) {
+            const float g1 = aR - union_area(nl, rr);        /* L <-> R.left  : R' = (L, R.right)  */
+            const float g2 = aR - union_area(rl, nl);        /* L <-> R.right : R' = (R.left, L)   */
+            if (g1 > best) { best = g1; opt = 1; }
+            if (g2 > best) { best = g2; opt = 2; }
+        }
+        if (li) {
+            const float g3 = aL - union_area(nr, lr);        /* R <-> L.left  : L' = (R, L.right)  */
+            const float g4 = aL - union_area(ll, nr);        /* R <-> L.right : L' = (L.left, R)   */
+            if (g3 > best) { best = g3; opt = 3; }
+            if (g4 > best) { best = g4; opt = 4; }
+        }
+        if (li && ri) {
+            const float g5 = (aL + aR) - (union_area(rl, lr) + union_area(ll, rr));   /* L.left <-> R.left  */
+            const float g6 = (aL + aR) - (union_area(rr, lr) + union_area(rl, ll));   /* L.left <-> R.right */
+            if (g5 > best) { best = g5; opt = 5; }
+            if (g6 > best) { best = g6; opt = 6; }
+        }
+        const uint32_t ll_ref = nl.left, lr_ref = nl.right, rl_ref = nr.left, rr_ref = nr.right;
+        const uint32_t cll = li ? mem.count(ll_ref) : 0u, clr = li ? mem.count(lr_ref) : 0u, crl = ri ? mem.count(rl_ref) : 0u, crr = ri ? mem.count(rr_ref) : 0u;
+        if (opt == 1) { nr = rebuild(R, L, nl, cL, nullptr, rr_ref, rr, crr, nullptr, kr); pkr = kr; cR = cL + crr; nl = rl; L = rl_ref; cL = crl; }
+        else if (opt == 2) { nr = rebuild(R, rl_ref, rl, crl, nullptr, L, nl, cL, nullptr, kr); pkr = kr; cR = crl + cL; nl = rr; L = rr_ref; cL = crr; }
+        else if (opt == 3) { nl = rebuild(L, R, nr, cR, nullptr, lr_ref, lr, clr, nullptr, kl); pkl = kl; cL = cR + clr; nr = ll; R = ll_ref; cR = cll; }
+        else if (opt == 4) { nl = rebuild(L, ll_ref, ll, cll, nullptr, R, nr, cR, nullptr, kl); pkl = kl; cL = cll + cR; nr = lr; R = lr_ref; cR = clr; }
+        else if (opt == 5) {
+            nl = rebuild(L, rl_ref, rl, crl, nullptr, lr_ref, lr, clr, nullptr, kl); nr = rebuild(R, ll_ref, ll, cll, nullptr, rr_ref, rr, crr, nullptr, kr);
+            pkl = kl; pkr = kr; cL = crl + clr; cR = cll + crr;
+        } else if (opt == 6) {
+            nl = rebuild(L, rr_ref, rr, crr, nullptr, lr_ref, lr, clr, nullptr, kl); nr = rebuild(R, rl_ref, rl, crl, nullptr, ll_ref, ll, cll, nullptr, kr);
+            pkl = kl; pkr = kr; cL = crr + clr; cR = crl + cll;
+        }
+    }
+    rebuild(cur, L, nl, cL, pkl, R, nr, cR, pkr, nullptr);
 }
 
 /*

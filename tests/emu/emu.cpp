@@ -65,39 +65,36 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp) {
     std::vector<Bvh2Node> n2(2 * (size_t)n - 1);
     std::vector<uint32_t> parent(2 * (size_t)n - 1, 0xFFFFFFFFu), counts(n > 1 ? n - 1 : 1, 0), flags(n > 1 ? n - 1 : 1, 0);
     for (int i = 0; i + 1 < (int)n; ++i) lbvh_build_node(skeys.data(), (int)n, i, n2.data(), parent.data());
-    /* refit: the same walk the kernel does (second arrival computes the parent) */
+    /* bottom-up passes: the same walk the kernel does (the second arrival at a node runs refit_visit).  Greedy build: one pass,
+     * bounds and counts only.  Default build: REFIT_PASSES passes with tree rotations, the collapse programme in the last one. */
+    struct HostMem {
+        Bvh2Node* n2; uint32_t* counts; DpNode* dp; uint32_t n;
+        uint32_t slot(uint32_t ref) const { return (ref & LEAF_FLAG) ? n - 1 + (ref & ~LEAF_FLAG) : ref; }
+        Bvh2Node node(uint32_t i) const { return n2[i]; }
+        void store_node(uint32_t i, const Bvh2Node& m) { n2[i] = m; }
+        uint32_t count(uint32_t ref) const { return (ref & LEAF_FLAG) ? 1u : counts[ref]; }
+        void store_count(uint32_t i, uint32_t c) { counts[i] = c; }
+        void dp_costs(uint32_t ref, float out[7]) const { for (int i = 0; i < 7; ++i) out[i] = dp[ref].cost[i]; }
+        void store_dp(uint32_t i, const DpNode& d) { dp[i] = d; }
+    };
+    std::vector<DpNode> dp(use_dp && n > 1 ? n - 1 : 0);
     for (uint32_t k = 0; k < n; ++k) {
         Bvh2Node& leaf = n2[n - 1 + k];
         tri_bounds(b->tris_sorted[k], b->pad, leaf.lo, leaf.hi);
         leaf.left = leaf.right = 0;
-        uint32_t cur = parent[n - 1 + k];
-        while (cur != 0xFFFFFFFFu) {
-            if (flags[cur]++ == 0) break;
-            Bvh2Node& nd = n2[cur];
-            uint32_t l = (nd.left & LEAF_FLAG) ? n - 1 + (nd.left & ~LEAF_FLAG) : nd.left;
-            uint32_t r = (nd.right & LEAF_FLAG) ? n - 1 + (nd.right & ~LEAF_FLAG) : nd.right;
-            for (int a = 0; a < 3; ++a) { nd.lo[a] = std::min(n2[l].lo[a], n2[r].lo[a]); nd.hi[a] = std::max(n2[l].hi[a], n2[r].hi[a]); }
-            counts[cur] = ((nd.left & LEAF_FLAG) ? 1 : counts[nd.left]) + ((nd.right & LEAF_FLAG) ? 1 : counts[nd.right]);
-            cur = parent[cur];
-        }
     }
-    /* optional: cost-optimal child selection (same per-node function the GPU runs bottom-up after the refit) */
-    std::vector<DpNode> dp;
-    if (use_dp && n > 1) {
-        dp.resize(n - 1);
-        std::vector<uint32_t> order_; order_.reserve(n - 1);
-        std::vector<uint32_t> stack_{0u};
-        while (!stack_.empty()) { uint32_t r = stack_.back(); stack_.pop_back(); order_.push_back(r);
-            if (!(n2[r].left & LEAF_FLAG)) stack_.push_back(n2[r].left); if (!(n2[r].right & LEAF_FLAG)) stack_.push_back(n2[r].right); }
-        for (size_t q = order_.size(); q-- > 0;) {          /* reverse pre-order: children before parents */
-            uint32_t r = order_[q];
-            float cl[7], cr[7];
-            auto child_costs = [&](uint32_t ref, float out[7]) {
-                if (ref & LEAF_FLAG) { const Bvh2Node& lf = n2[n - 1 + (ref & ~LEAF_FLAG)]; dp_leaf_costs(box_area(lf.lo, lf.hi), out); }
-                else for (int i = 0; i < 7; ++i) out[i] = dp[ref].cost[i];
-            };
-            child_costs(n2[r].left, cl); child_costs(n2[r].right, cr);
-            dp_node(cl, cr, box_area(n2[r].lo, n2[r].hi), counts[r], dp[r]);
+    HostMem mem{n2.data(), counts.data(), dp.data(), n};
+    const int passes = use_dp ? RT3_REFIT_PASSES : 1;
+    for (int pass = 0; pass < passes; ++pass) {
+        std::fill(flags.begin(), flags.end(), 0u);
+        if (pass) for (uint32_t i = 0; i + 1 < n; ++i) { parent[mem.slot(n2[i].left)] = i; parent[mem.slot(n2[i].right)] = i; }   /* rotations moved subtrees */
+        for (uint32_t k = 0; k < n; ++k) {
+            uint32_t cur = parent[n - 1 + k];
+            while (cur != 0xFFFFFFFFu) {
+                if (flags[cur]++ == 0) break;
+                refit_visit(mem, n, cur, use_dp, use_dp && pass == passes - 1);
+                cur = parent[cur];
+            }
         }
     }
     /* collapse, level by level */
