@@ -27,8 +27,8 @@ BOUNCES, SAMPLES = 4, 1
 HBM_BYTES_PER_RAY = 48          # 32 B rt3_ray read + 16 B rt3_hit written
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_trace_dyn<closest> launch of this workload (1.8 M secondary rays), from the committed
 # `ncu --set full` capture; algorithmic bytes of that launch = 48 B x 1.8 M = 86 MB
-NCU_TRACE_DRAM_BYTES_PER_LAUNCH = (83.93e6 + 77.36e6 + 72.02e6 + 9.66e6 + 10.18e6 + 6.10e6) / 3
-NCU_TRACE_DRAM_SOURCE = "profiles/r1g_k_trace_dyn_summary.txt (ncu --set full, mean of the frame's 3 launches: 77.8 MB read + 8.6 MB written)"
+NCU_TRACE_DRAM_BYTES_PER_LAUNCH = (82.71e6 + 76.04e6 + 70.74e6 + 13.64e6 + 8.22e6 + 6.65e6) / 3
+NCU_TRACE_DRAM_SOURCE = "profiles/r1j_k_trace_dyn_summary.txt (ncu --set full, mean of the frame's 3 launches: 76.5 MB read + 9.5 MB written)"
 FALLBACK_HBM_GBS = 6650.0       # /opt/skills/guides/B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 
 
