@@ -55,6 +55,34 @@ def params_for(sc, W, H, frame, flags):
     return make_params(camera_for(sc, CAMERA, W, H), W, H, frame=frame, bounces=BOUNCES, samples=SAMPLES, blendfactor=1.0, flags=flags)
 
 
+def bind_to_gpu_numa_node(device_index):
+    """Host plumbing for the end-to-end path: run this rank's host thread on the CPUs of the NUMA node its GPU hangs off, so that the
+    page-locked frames it allocates / first-touches afterwards live in that node's memory (D2H then does not cross the socket link).
+    Returns the node, or None when the topology is not exposed.  RT3_BENCH_NO_NUMA=1 switches it off (A/B)."""
+    if os.environ.get("RT3_BENCH_NO_NUMA"):
+        return None
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device_index)
+        bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return node
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def hbm_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -178,6 +206,7 @@ def run_cuda(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
+    numa_node = bind_to_gpu_numa_node(local_rank)
     if world_size > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
@@ -256,10 +285,18 @@ def run_cuda(args):
                     f.truncate(nbytes)
             barrier()
             shared = torch.from_file(shm_path, shared=True, size=FRAMES_IN_FLIGHT * H * W * 4, dtype=torch.float32).view(FRAMES_IN_FLIGHT, H, W, 4)
+            band = H // world_size
+            # first touch: every rank writes ITS band of every frame of the (still sparse) file, from CPUs of its GPU's NUMA node, so the
+            # pages it will receive D2H traffic on are allocated there instead of all on the node of whichever rank pins the file first
+            for k in range(FRAMES_IN_FLIGHT):
+                shared[k][rank * band:(H if rank == world_size - 1 else (rank + 1) * band)].zero_()
+            barrier()
             err = torch.cuda.cudart().cudaHostRegister(shared.data_ptr(), nbytes, 0)
             assert int(err) == 0, f"cudaHostRegister failed: {err}"
-            band = H // world_size
             R.enable_host_output([shared[k] for k in range(FRAMES_IN_FLIGHT)], rank * band, H if rank == world_size - 1 else (rank + 1) * band)
+            diag_no_d2h = bool(os.environ.get("RT3_DIAG_NO_D2H"))      # diagnosis only (never a reported number): gather without the read-back
+            if diag_no_d2h:
+                R.row1 = R.row0
 
         def e2e_step(i):
             p = e2e_params[i]
@@ -292,7 +329,7 @@ def run_cuda(args):
         if tiled:
             # outside the timed region: the frame assembled in shared host memory from the ranks' bands == the gathered device frame
             k_last = (R.next_ticket - 1) % FRAMES_IN_FLIGHT
-            if rank == 0:
+            if rank == 0 and not diag_no_d2h:
                 e2e_verified = bool(torch.equal(shared[k_last], R.frame_ring[k_last].cpu()))
                 assert e2e_verified, "host frame assembled from the ranks' row bands differs from the gathered device frame"
             torch.cuda.cudart().cudaHostUnregister(shared.data_ptr())
@@ -340,7 +377,7 @@ def run_cuda(args):
                             "waited for inside the timed region)" if not tiled else
                             "rt3_pass_*_tiles + all_gather + rt3_untile, 3 frames in flight; every rank reads its band of rows of the gathered frame back "
                             "into one page-locked host frame shared by the ranks (POSIX shm), every frame waited for inside the timed region",
-                    "sync_ms_per_step": sync_e2e_ms, "host_frame_verified": e2e_verified},
+                    "sync_ms_per_step": sync_e2e_ms, "host_frame_verified": e2e_verified, "host_numa_node_rank0": numa_node},
             "gpu_launches": int(launches_all),
             "roofline": {"kernel": "k_trace<closest> (secondary-ray queues)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": NCU_TRACE_DRAM_BYTES_PER_LAUNCH, "traffic_source": NCU_TRACE_DRAM_SOURCE, "peak_source": peak_src, "bytes_per_ray": HBM_BYTES_PER_RAY,
