@@ -5,11 +5,15 @@
  * Stages (all on the device; the host only reads back 4-byte counters between collapse levels):
  *   k_flatten        scene buffers + instances -> world-space (v0,e1,e2,id) records, scene AABB
  *   k_morton         63-bit Morton code of each triangle's box centre
- *   radix sort       8 passes x 8 bits, stable: k_radix_hist -> k_radix_scan -> k_radix_scatter
+ *   radix sort       8 passes x 8 bits, stable: k_radix_hist -> k_radix_scan (one block per digit) -> k_radix_scatter
  *   k_gather_sorted  triangles into Morton order
  *   k_lbvh_hierarchy Karras 2012, one thread per internal node
- *   k_refit          bottom-up AABBs + subtree counts with one atomic flag per internal node
+ *   k_refit          bottom-up walk with one atomic flag per internal node: AABBs + subtree counts; unless RT3_BUILD_FAST_BUILD,
+ *                    three passes with SAH tree rotations (k_parents re-links in between) and, in the last one, the dynamic
+ *                    programme that picks the children of the wide nodes (refit_visit / dp_node in bvh_logic.h)
  *   k_collapse       BVH2 -> 8-wide quantised nodes, one thread per wide node, level by level
+ * Temporaries of one build live in a single arena from the stream-ordered pool.  One level (instances flattened to world space)
+ * or two (RT3_BUILD_TWO_LEVEL: one tree per distinct mesh + a tree over the instances).
  */
 #include "common.cuh"
 
