@@ -206,6 +206,7 @@ def run_cuda(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
+    all_cpus = os.sched_getaffinity(0)
     numa_node = bind_to_gpu_numa_node(local_rank)
     if world_size > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -342,6 +343,7 @@ def run_cuda(args):
             for i in range(e2e_steps):
                 R.render_frame_host(e2e_params[200 + i], host_light.data_ptr())
             sync_e2e_ms = 1e3 * (time.perf_counter() - t1) / e2e_steps
+    os.sched_setaffinity(0, all_cpus)      # the CPU legs below (cpu_baseline) use every host core again
     rays_local = cnt.rays_primary + cnt.rays_secondary
     stats = torch.tensor([ms, float(rays_local), float(cnt.paths_started), float(e2e_s), float(e2e_cnt.rays_primary + e2e_cnt.rays_secondary),
                           float(launches), float(cnt.rays_secondary), float(trace_ms), float(trace_launches)], dtype=torch.float64, device=f"cuda:{local_rank}")
