@@ -8,6 +8,7 @@ Mirrors /root/reference/src/assets/mod.rs:
   MeshSaver                               assets/mod.rs:298-314    write_mesh
   GltfMeshLoader (".glb")                 assets/mod.rs:180-201    load_glb (full scene: every mesh, primitive, node transform)
   MeshTransformer                         assets/mod.rs:208-284    process_primitive (vertex-fetch remap + meshlets 64 / 124)
+  skybox2.exr (image / exr crates)        main.rs:94 (commented)   read_exr / load_environment_exr (scanline OpenEXR: NONE, RLE, ZIPS, ZIP)
 
 Third-party arithmetic absent from /root/reference (parity unpinned, algorithms restated from their published descriptions):
 bincode 2.0.1 (Cargo.lock:814-815; format spec: github.com/bincode-org/bincode docs/spec.md), gltf 1.4.1 (Cargo.lock:1741-1742;
@@ -634,3 +635,181 @@ def import_glb_to_mesh(data):
     tex = None if int(g["base_color_tex"]) < 0 else int(g["base_color_tex"])
     mat = material_record(tuple(float(x) for x in g["base_color"][:3]), float(g["metallic"]), float(g["roughness"]), tex)
     return write_mesh(process_primitive(sc["vertices"], sc["indices"], mat))
+
+
+# ---------------------------------------------------------------------------------------------------------------- OpenEXR
+# resources/skybox2.exr (the environment light BASELINE.json names; absent from the mount) is an OpenEXR image, read by the reference
+# through the `image` / `exr 1.73.0` crates (Cargo.lock:1448-1449; only in a commented-out line, main.rs:94).  Restated from the
+# published file layout (openexr.com "OpenEXR File Layout"): single-part scanline images, channels HALF / FLOAT / UINT with any
+# sampling of 1, compression NONE / RLE / ZIPS / ZIP.  The lossy and wavelet codecs (PIZ, PXR24, B44, DWA) are not implemented and
+# fail loudly.  Parity unpinned: no EXR file ships with the reference; the tests pin the reader against a byte-level hand assembly of
+# the layout and against the writer below.
+EXR_MAGIC = 20000630
+_EXR_LINES_PER_BLOCK = {0: 1, 1: 1, 2: 1, 3: 16}           # NONE, RLE, ZIPS, ZIP
+_EXR_COMPRESSION_NAMES = {0: "NONE", 1: "RLE", 2: "ZIPS", 3: "ZIP", 4: "PIZ", 5: "PXR24", 6: "B44", 7: "B44A", 8: "DWAA", 9: "DWAB"}
+_EXR_PIXEL = {0: np.dtype("<u4"), 1: np.dtype("<f2"), 2: np.dtype("<f4")}
+
+
+def _exr_unfilter(buf):
+    """Inverse of the byte predictor + even/odd split both RLE and ZIP blocks go through."""
+    b = np.frombuffer(buf, np.uint8).astype(np.int64)
+    if len(b) == 0:
+        return b""
+    b[1:] -= 128
+    b = (np.cumsum(b) & 0xFF).astype(np.uint8)
+    half = (len(b) + 1) // 2
+    out = np.empty(len(b), np.uint8)
+    out[0::2] = b[:half]
+    out[1::2] = b[half:]
+    return out.tobytes()
+
+
+def _exr_filter(raw):
+    b = np.frombuffer(raw, np.uint8)
+    t = np.concatenate([b[0::2], b[1::2]]).astype(np.int64)
+    d = t.copy()
+    d[1:] = (t[1:] - t[:-1] + 128 + 256) & 0xFF
+    return d.astype(np.uint8).tobytes()
+
+
+def _exr_rle_decode(data, expect):
+    out, i = bytearray(), 0
+    while i < len(data):
+        c = data[i] - 256 if data[i] > 127 else data[i]
+        i += 1
+        if c < 0:
+            out += data[i:i - c]
+            i += -c
+        else:
+            out += bytes([data[i]]) * (c + 1)
+            i += 1
+    if len(out) != expect:
+        raise ValueError("EXR: RLE block decodes to the wrong size")
+    return bytes(out)
+
+
+def _exr_rle_encode(raw):
+    out, i, n = bytearray(), 0, len(raw)
+    while i < n:
+        j = i + 1
+        while j < n and raw[j] == raw[i] and j - i < 128:
+            j += 1
+        if j - i >= 3:
+            out += bytes([j - i - 1, raw[i]])
+            i = j
+        else:
+            k = i
+            while k < n and k - i < 127 and not (k + 2 < n and raw[k] == raw[k + 1] == raw[k + 2]):
+                k += 1
+            out += bytes([(256 - (k - i)) & 0xFF]) + raw[i:k]
+            i = k
+    return bytes(out)
+
+
+def read_exr(data):
+    """-> (pixels float32 [H, W, C], channel names in file order).  Scanline OpenEXR, see the section comment for the subset."""
+    if len(data) < 8 or struct.unpack_from("<i", data, 0)[0] != EXR_MAGIC:
+        raise ValueError("not an OpenEXR file")
+    version = struct.unpack_from("<i", data, 4)[0]
+    if version & 0xFF != 2 or version & (0x200 | 0x800 | 0x1000):
+        raise NotImplementedError("EXR: only version-2 single-part scanline images are supported")
+    o, attrs = 8, {}
+
+    def cstr(o):
+        e = data.index(b"\0", o)
+        return data[o:e].decode("latin-1"), e + 1
+    while data[o] != 0:
+        name, o = cstr(o)
+        typ, o = cstr(o)
+        size = struct.unpack_from("<i", data, o)[0]
+        attrs[name] = (typ, data[o + 4:o + 4 + size])
+        o += 4 + size
+    o += 1
+    for need in ("channels", "compression", "dataWindow"):
+        if need not in attrs:
+            raise ValueError(f"EXR: header lacks '{need}'")
+    channels, c = [], 0
+    cl = attrs["channels"][1]
+    while cl[c] != 0:
+        e = cl.index(b"\0", c)
+        name = cl[c:e].decode("latin-1")
+        ptype, _plinear, xs, ys = struct.unpack_from("<iB3xii", cl, e + 1)
+        if xs != 1 or ys != 1:
+            raise NotImplementedError("EXR: subsampled channels are not supported")
+        channels.append((name, _EXR_PIXEL[ptype]))
+        c = e + 1 + 16
+    comp = attrs["compression"][1][0]
+    if comp not in _EXR_LINES_PER_BLOCK:
+        raise NotImplementedError(f"EXR: compression {_EXR_COMPRESSION_NAMES.get(comp, comp)} is not implemented (NONE, RLE, ZIPS, ZIP are)")
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    W, H = x1 - x0 + 1, y1 - y0 + 1
+    lines = _EXR_LINES_PER_BLOCK[comp]
+    n_blocks = -(-H // lines)
+    offsets = struct.unpack_from(f"<{n_blocks}Q", data, o)
+    row_bytes = sum(W * dt.itemsize for _, dt in channels)
+    out = np.zeros((H, W, len(channels)), np.float32)
+    for off in offsets:
+        y, size = struct.unpack_from("<ii", data, off)
+        body = data[off + 8:off + 8 + size]
+        nl = min(lines, y1 - y + 1)
+        expect = nl * row_bytes
+        if size < expect:                                   # a block that did not shrink is stored raw
+            raw = zlib.decompress(body) if comp in (2, 3) else _exr_rle_decode(body, expect)
+            raw = _exr_unfilter(raw)
+        else:
+            raw = body
+        if len(raw) != expect:
+            raise ValueError("EXR: block decodes to the wrong size")
+        p = 0
+        for ln in range(nl):
+            for ci, (_, dt) in enumerate(channels):
+                out[y - y0 + ln, :, ci] = np.frombuffer(raw, dt, W, p).astype(np.float32)
+                p += W * dt.itemsize
+    return out, [n for n, _ in channels]
+
+
+def write_exr(rgb, compression="ZIP", half=False, data_window_origin=(0, 0)):
+    """float [H, W, 3] -> OpenEXR bytes, channels B, G, R (alphabetical, as the format requires), FLOAT or HALF."""
+    comp = {v: k for k, v in _EXR_COMPRESSION_NAMES.items()}[compression]
+    rgb = np.asarray(rgb)
+    H, W = rgb.shape[:2]
+    dt = np.dtype("<f2") if half else np.dtype("<f4")
+    x0, y0 = data_window_origin
+
+    def attr(name, typ, value):
+        return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<i", len(value)) + value
+    chl = b"".join(n.encode() + b"\0" + struct.pack("<iB3xii", 1 if half else 2, 0, 1, 1) for n in "BGR") + b"\0"
+    box = struct.pack("<4i", x0, y0, x0 + W - 1, y0 + H - 1)
+    hdr = (struct.pack("<ii", EXR_MAGIC, 2) + attr("channels", "chlist", chl) + attr("compression", "compression", bytes([comp]))
+           + attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box) + attr("lineOrder", "lineOrder", b"\0")
+           + attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) + attr("screenWindowCenter", "v2f", struct.pack("<ff", 0.0, 0.0))
+           + attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0")
+    lines = _EXR_LINES_PER_BLOCK[comp]
+    blocks = []
+    for b0 in range(0, H, lines):
+        raw = b"".join(np.ascontiguousarray(rgb[y, :, ch]).astype(dt).tobytes() for y in range(b0, min(H, b0 + lines)) for ch in (2, 1, 0))
+        body = raw
+        if comp:
+            f = _exr_filter(raw)
+            enc = zlib.compress(f, 6) if comp in (2, 3) else _exr_rle_encode(f)
+            if len(enc) < len(raw):
+                body = enc
+        blocks.append(struct.pack("<ii", y0 + b0, len(body)) + body)
+    table_at = len(hdr)
+    pos, table = table_at + 8 * len(blocks), []
+    for b in blocks:
+        table.append(pos)
+        pos += len(b)
+    return hdr + struct.pack(f"<{len(blocks)}Q", *table) + b"".join(blocks)
+
+
+def load_environment_exr(data):
+    """skybox2.exr role: equirect RGB float32 [H, W, 3] for rt3_scene_set_environment (missing colour channels read as 0)."""
+    px, names = read_exr(data)
+    out = np.zeros(px.shape[:2] + (3,), np.float32)
+    for k, n in enumerate("RGB"):
+        if n in names:
+            out[..., k] = px[..., names.index(n)]
+        elif "Y" in names:
+            out[..., k] = px[..., names.index("Y")]
+    return out

@@ -497,3 +497,41 @@ def random_rays(scene, n, seed=3):
     r["d"] = d
     r["tmin"], r["tmax"] = 0.0, 1e5
     return r
+
+
+# ------------------------------------------------------------------------------------------------ the real assets, when present
+def default_cameras(scene):
+    """SURVEY.md section 8d preset for a scene that brings no camera: eye at the AABB centre - 0.35 x the long-axis extent, at 0.25 x the
+    AABB height, looking down the long (horizontal) axis, up +Y, fov 65 degrees (main.rs:69-76)."""
+    t = world_triangles(scene).reshape(-1, 3)
+    lo, hi = t.min(0), t.max(0)
+    c, ext = 0.5 * (lo + hi), hi - lo
+    axis = 0 if ext[0] >= ext[2] else 2
+    eye = c.copy()
+    eye[axis] -= 0.35 * ext[axis]
+    eye[1] = lo[1] + 0.25 * ext[1]
+    d = np.zeros(3)
+    d[axis] = 1.0
+    return {"cam0": dict(position=tuple(float(x) for x in eye), direction=tuple(float(x) for x in d), fov_deg=65.0)}
+
+
+def load_real_assets(directory):
+    """The scene resolution rule of SURVEY.md section 8d: `sponza_scene.glb` (and `skybox2.exr`) from `directory` if the files are
+    there (they are not part of the reference mount, .MISSING_LARGE_BLOBS:2-3), else None.  Returns a scene dictionary named
+    'sponza_glb'; callers tag every number with scene['name']."""
+    import os
+    from . import assets
+    glb = os.path.join(directory, "sponza_scene.glb")
+    if not os.path.isfile(glb):
+        return None
+    with open(glb, "rb") as f:
+        sc = assets.load_glb(f.read(), name="sponza_glb")
+    exr = os.path.join(directory, "skybox2.exr")
+    if os.path.isfile(exr):
+        with open(exr, "rb") as f:
+            sc["environment"] = assets.load_environment_exr(f.read())
+    else:
+        sc["environment"] = analytic_sky()
+    if not sc.get("cameras"):
+        sc["cameras"] = default_cameras(sc)
+    return sc

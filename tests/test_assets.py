@@ -171,3 +171,80 @@ def test_reference_pipeline_glb_to_mesh():
     assert len(mesh.meshlets) == 1 and len(mesh.materials) == 1 and mesh.triangles().shape == (2, 3)
     sc = assets.mesh_to_scene(mesh)
     assert scenes.world_triangles(sc).shape == (2, 3, 3)
+
+
+# ---------------------------------------------------------------------------------------------------------------- OpenEXR (skybox2.exr role)
+@pytest.mark.parametrize("compression", ["NONE", "RLE", "ZIPS", "ZIP"])
+@pytest.mark.parametrize("half", [False, True])
+def test_exr_round_trip(compression, half):
+    rng = np.random.default_rng(3)
+    img = (rng.random((37, 53, 3)) * 40).astype(np.float32)
+    img[5:22, 10:31] = 2.5                                           # runs, so that RLE / ZIP blocks really shrink
+    img[30:] = 0
+    data = assets.write_exr(img, compression, half, data_window_origin=(3, -2))
+    px, names = assets.read_exr(data)
+    assert names == ["B", "G", "R"] and px.shape == (37, 53, 3)
+    want = img.astype(np.float16).astype(np.float32) if half else img
+    assert (assets.load_environment_exr(data) == want).all()
+    if compression != "NONE":
+        assert len(data) < len(assets.write_exr(img, "NONE", half))
+
+
+def test_exr_reader_against_hand_assembled_file():
+    """Bytes assembled here straight from the published layout (magic, version, attribute list, offset table, one chunk per scanline,
+    channels stored alphabetically row by row): independent of write_exr."""
+    import struct
+    W, H = 3, 2
+    r = np.array([[1.0, 2.0, 3.0], [4.0, 5.0, 6.0]], np.float16)
+    g = np.array([[0.5, 0.25, 0.125], [8.0, 16.0, 32.0]], np.float32)
+    z = np.array([[7, 8, 9], [10, 11, 4000000000]], np.uint32)
+
+    def attr(name, typ, val):
+        return name + b"\0" + typ + b"\0" + struct.pack("<i", len(val)) + val
+    ch = (b"G\0" + struct.pack("<iB3xii", 2, 0, 1, 1) + b"R\0" + struct.pack("<iB3xii", 1, 0, 1, 1) + b"Z\0" + struct.pack("<iB3xii", 0, 0, 1, 1) + b"\0")
+    hdr = (bytes([0x76, 0x2F, 0x31, 0x01]) + struct.pack("<i", 2) + attr(b"channels", b"chlist", ch) + attr(b"compression", b"compression", b"\0")
+           + attr(b"dataWindow", b"box2i", struct.pack("<4i", 0, 0, W - 1, H - 1)) + attr(b"displayWindow", b"box2i", struct.pack("<4i", 0, 0, W - 1, H - 1))
+           + attr(b"lineOrder", b"lineOrder", b"\0") + attr(b"pixelAspectRatio", b"float", struct.pack("<f", 1.0))
+           + attr(b"screenWindowCenter", b"v2f", struct.pack("<ff", 0, 0)) + attr(b"screenWindowWidth", b"float", struct.pack("<f", 1.0)) + b"\0")
+    rows = [g[y].tobytes() + r[y].tobytes() + z[y].tobytes() for y in range(H)]
+    chunks = [struct.pack("<ii", y, len(rows[y])) + rows[y] for y in range(H)]
+    t0 = len(hdr) + 8 * H
+    table = struct.pack("<2Q", t0 + len(chunks[1]), t0)               # file order: scanline 1 first (decreasing-y files exist)
+    data = hdr + table + chunks[1] + chunks[0]
+    px, names = assets.read_exr(data)
+    assert names == ["G", "R", "Z"]
+    assert (px[..., 0] == g).all() and (px[..., 1] == r.astype(np.float32)).all() and (px[..., 2] == z.astype(np.float32)).all()
+    env = assets.load_environment_exr(data)
+    assert (env[..., 0] == r.astype(np.float32)).all() and (env[..., 1] == g).all() and (env[..., 2] == 0).all()
+
+
+def test_exr_unsupported_and_malformed_inputs_fail_loudly():
+    img = np.ones((4, 4, 3), np.float32)
+    data = bytearray(assets.write_exr(img, "NONE"))
+    i = data.index(b"compression\0compression\0") + len(b"compression\0compression\0") + 4
+    data[i] = 4                                                      # PIZ
+    with pytest.raises(NotImplementedError, match="PIZ"):
+        assets.read_exr(bytes(data))
+    with pytest.raises(ValueError):
+        assets.read_exr(b"\x89PNG\r\n\x1a\n" + b"\0" * 32)
+    tiled = bytearray(assets.write_exr(img, "NONE"))
+    tiled[5] |= 0x02                                                 # version field bit 9: tiled
+    with pytest.raises(NotImplementedError):
+        assets.read_exr(bytes(tiled))
+
+
+def test_real_asset_hook_uses_files_when_present(tmp_path):
+    """SURVEY 8d scene rule: sponza_scene.glb / skybox2.exr are used if they exist, else the stand-in (None here)."""
+    assert scenes.load_real_assets(str(tmp_path)) is None
+    src = scenes.synthetic_atrium(0.01, environment=False)
+    (tmp_path / "sponza_scene.glb").write_bytes(assets.write_glb(src))
+    sky = scenes.analytic_sky(32, 16)
+    (tmp_path / "skybox2.exr").write_bytes(assets.write_exr(sky, "ZIP"))
+    sc = scenes.load_real_assets(str(tmp_path))
+    assert sc["name"] == "sponza_glb" and scenes.scene_num_triangles(sc) == scenes.scene_num_triangles(src)
+    assert (sc["environment"] == sky).all()
+    cam = sc["cameras"]["cam0"]
+    t = scenes.world_triangles(sc).reshape(-1, 3)
+    lo, hi = t.min(0), t.max(0)
+    assert lo[0] < cam["position"][0] < hi[0] and abs(cam["position"][1] - (lo[1] + 0.25 * (hi[1] - lo[1]))) < 1e-6   # inside, a quarter up
+    assert cam["direction"] == (1.0, 0.0, 0.0)                      # the atrium's long axis is x
