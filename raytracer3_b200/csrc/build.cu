@@ -259,8 +259,9 @@ struct DevMem {
 };
 
 /* leaf boxes (first pass only), then the bottom-up walk: one atomic flag per node, the second arrival runs refit_visit */
+template <bool ROTATE, bool WITH_DP>
 __global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_t n, int kind, float pad, Bvh2Node* nodes, const uint32_t* parent,
-                                               uint32_t* flags, uint32_t* counts, DpNode* dp, int first_pass, int rotate, int with_dp) {
+                                               uint32_t* flags, uint32_t* counts, DpNode* dp, int first_pass) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     DevMem mem{nodes, counts, dp, n};
@@ -275,7 +276,7 @@ __global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_
         __threadfence();
         if (atomicAdd(flags + cur, 1u) == 0u) return;   /* first arrival: the sibling subtree is not ready yet */
         __threadfence();
-        refit_visit(mem, n, cur, rotate != 0, with_dp != 0);
+        refit_visit(mem, n, cur, ROTATE, WITH_DP);
         cur = parent[cur];
     }
 }
@@ -413,8 +414,9 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
                 RT3_CUDA(c, cudaMemsetAsync(nflags, 0, sizeof(uint32_t) * n, st));
                 if (n > 1) RT3_LAUNCH(c, k_parents, div_up(n - 1, 256), 256, 0, st, nodes2, n, parent);
             }
-            RT3_LAUNCH(c, k_refit, div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0,
-                       io.optimal_collapse ? 1 : 0, (io.optimal_collapse && pass == passes - 1) ? 1 : 0);
+            if (!io.optimal_collapse) RT3_LAUNCH(c, (k_refit<false, false>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, 1);
+            else if (pass < passes - 1) RT3_LAUNCH(c, (k_refit<true, false>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
+            else RT3_LAUNCH(c, (k_refit<true, true>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
         }
         bs.ms_refit += tm.end();
         dbg_mark("refit");
