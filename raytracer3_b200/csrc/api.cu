@@ -143,7 +143,14 @@ PixelMap tiles_map(rt3_context* c, const rt3_params* p, const rt3_rect* tiles, u
         tw = std::max(tw, tiles[i].w); th = std::max(th, tiles[i].h);
     }
     rt3_rect* d = ensure<rt3_rect>(c, c->d_rects, n ? n : 1);
-    if (n) RT3_CUDA(c, cudaMemcpyAsync(d, tiles, n * sizeof(rt3_rect), cudaMemcpyHostToDevice, st));
+    /* the same list on the same stream as the last upload (every frame of a tiled renderer): the device copy is still valid, skip the
+     * pageable H2D copy, which costs a staging round trip per pass call */
+    const bool same = n && d == c->rects_dev && st == c->rects_stream && c->rects_host.size() == n &&
+                      memcmp(c->rects_host.data(), tiles, n * sizeof(rt3_rect)) == 0;
+    if (n && !same) {
+        RT3_CUDA(c, cudaMemcpyAsync(d, tiles, n * sizeof(rt3_rect), cudaMemcpyHostToDevice, st));
+        c->rects_host.assign(tiles, tiles + n); c->rects_dev = d; c->rects_stream = st;
+    }
     m.rects = d; m.n_tiles = n; m.tile_w = tw; m.tile_h = th;
     m.bw = (tw + 7) / 8; m.bh = (th + 3) / 4; m.pitch = W; m.slab = 1;
     if (n == 1) m.single = tiles[0];
@@ -437,7 +444,12 @@ rt3_status rt3_untile_rgba32f(rt3_context* c, const rt3_rect* tiles, uint32_t n,
     return guarded(c, [&]() {
         if ((n && !tiles) || !slab || !frame) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
         rt3_rect* d = ensure<rt3_rect>(c, c->d_untile_rects, n ? n : 1);
-        if (n) RT3_CUDA(c, cudaMemcpyAsync(d, tiles, n * sizeof(rt3_rect), cudaMemcpyHostToDevice, (cudaStream_t)st));
+        const bool same = n && d == c->urects_dev && (cudaStream_t)st == c->urects_stream && c->urects_host.size() == n &&
+                          memcmp(c->urects_host.data(), tiles, n * sizeof(rt3_rect)) == 0;       /* as in tiles_map */
+        if (n && !same) {
+            RT3_CUDA(c, cudaMemcpyAsync(d, tiles, n * sizeof(rt3_rect), cudaMemcpyHostToDevice, (cudaStream_t)st));
+            c->urects_host.assign(tiles, tiles + n); c->urects_dev = d; c->urects_stream = (cudaStream_t)st;
+        }
         rt3_launch_untile(c, d, n, tile_w, tile_h, slab, frame, frame_w, frame_h, (cudaStream_t)st);
     });
 }

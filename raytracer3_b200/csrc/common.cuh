@@ -106,6 +106,8 @@ struct rt3_context {
     Scratch f_gbuffer, f_depth, f_light, f_prev, f_rays, f_hits, f_bits, l2_buf;
     DeviceCounters* d_counters = nullptr;
     cudaEvent_t ev[8];
+    std::vector<rt3_rect> rects_host; const rt3_rect* rects_dev = nullptr; cudaStream_t rects_stream = nullptr;   /* tile list last uploaded to d_rects */
+    std::vector<rt3_rect> urects_host; const rt3_rect* urects_dev = nullptr; cudaStream_t urects_stream = nullptr;   /* ... and to d_untile_rects */
 
     /* frames in flight (rt3_frame_submit_host / rt3_frame_wait): FRAMES_IN_FLIGHT = 3 of the reference's swapchain.rs:8 */
     struct FrameSlot { Scratch gb, dp, lt, pv; cudaEvent_t rendered = nullptr, copied = nullptr; bool busy = false; };
