@@ -629,7 +629,9 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
             tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
         }
         bool found_any = false;
-        if (active && tg_hits) {
+        for (int rep = 0; rep < 2; ++rep) {   /* up to two record steps per node step, as in k_trace_dyn */
+        if (rep && !RT3_WARP_ANY(active && tg_hits != 0u && !found_any)) break;
+        if (active && tg_hits && !found_any) {
             const int bit = bfind32(tg_hits);
             tg_hits &= ~(1u << bit);
             const Tri48* tp = tris + (tg_base + (uint32_t)bit);
@@ -658,6 +660,7 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
                     else if (rt3m::closer_hit(t, prim, hit.t, hit.prim)) { hit.t = t; hit.u = u; hit.v = v; hit.prim = prim; }
                 }
             }
+        }
         }
         if (active && found_any) active = false;
         while (active && tg_hits == 0u && ng_hits <= 0x00FFFFFFu) {       /* nothing pending here: pop (more than once only across a sentinel) */
