@@ -83,7 +83,11 @@ def test_two_rank_gather_on_gloo(tmp_path):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1")
+    import socket
+    with socket.socket() as s:                       # a free port: a fixed one fails when two runs follow each other within TIME_WAIT
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-                        "--master-port", "29731", str(script), root], capture_output=True, text=True, env=env, timeout=300)
+                        "--master-port", str(port), str(script), root], capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "rank0ok" in r.stdout and "rank1ok" in r.stdout
