@@ -1,7 +1,7 @@
 # usage: tools/exp.sh "<nvcc extra flags>" ... : rebuild with each flag set on the GPU box and print bench numbers (experiments only)
 for flags in "$@"; do
   echo "== RT3_NVCC_EXTRA=$flags"
-  RT3_NVCC_EXTRA="$flags" python -c "from raytracer3_b200 import build as b; b.build(force=True, verbose=True)" 2>&1 | grep -A3 "k_trace_dynILb0ELi28ELi1" | grep "Used\|spill" 
+  RT3_NVCC_EXTRA="$flags" python -c "from raytracer3_b200 import build as b; b.build(force=True, verbose=True)" 2>&1 | grep -A3 "k_trace_dynILb0ELi28ELb0" | grep "Used\|spill"
   python -m pytest tests/test_gpu_parity.py -x -q -k "trace_closest or reference_pass" 2>&1 | tail -1
   python bench.py --steps 30 --warmup 5 2>&1 | python -c "
 import sys,json
