@@ -17,15 +17,18 @@ using namespace rt3b;
 struct EmuBvh {
     std::vector<Tri48> tris_in, tris_sorted, tris_out;
     std::vector<WideNode> nodes;
-    uint32_t n_nodes = 0, n_tris = 0, levels = 0;
+    uint32_t n_nodes = 0, n_tris = 0, levels = 0, n_refs = 0, ploc_rounds = 0;
     float sah[2] = {0, 0};
     float pad = 0;
     float lo[3], hi[3];
 };
 
+static inline uint32_t mem_slot(uint32_t n, uint32_t ref) { return (ref & LEAF_FLAG) ? n - 1 + (ref & ~LEAF_FLAG) : ref; }
+
 extern "C" {
 
-static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp) {
+/* split_beta > 0: triangle splitting (bvh_logic.h split_*): the hierarchy is built over references, n below is then their number */
+static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp, float split_beta = 0.0f, uint32_t ploc_radius = 0) {
     EmuBvh* b = new EmuBvh();
     b->tris_in.resize(n);
     for (int a = 0; a < 3; ++a) { b->lo[a] = 3.4e38f; b->hi[a] = -3.4e38f; }
@@ -46,12 +49,31 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp) {
         b->n_nodes = 1;
         return b;
     }
+    /* references: one per triangle, or several with clipped boxes */
+    std::vector<RefBox> refs;
+    if (split_beta > 0.0f) {
+        SplitGrid g;
+        for (int a = 0; a < 3; ++a) { g.lo[a] = b->lo[a]; g.ext[a] = b->hi[a] - b->lo[a]; }
+        std::vector<float> prio(n);
+        const float inv_norm = split_inv_norm(g);
+        uint64_t total = 0;                                    /* fixed point, as the device sums it with integer atomics */
+        for (uint32_t i = 0; i < n; ++i) { prio[i] = split_priority(b->tris_in[i], REC_TRI_EDGES, g); total += split_priority_fixed(prio[i], inv_norm); }
+        const float scale = split_scale(total, n, split_beta, inv_norm);
+        for (uint32_t i = 0; i < n; ++i) {
+            uint32_t s = split_count(prio[i], scale);
+            split_triangle(b->tris_in[i], REC_TRI_EDGES, g, s, [&](const float* lo, const float* hi) {
+                RefBox r; for (int a = 0; a < 3; ++a) { r.lo[a] = lo[a]; r.hi[a] = hi[a]; } r.tri = i; r.pad = 0; refs.push_back(r); });
+        }
+    } else {
+        refs.resize(n);
+        for (uint32_t i = 0; i < n; ++i) { tri_bounds(b->tris_in[i], 0.f, refs[i].lo, refs[i].hi); refs[i].tri = i; refs[i].pad = 0; }
+    }
+    b->n_refs = n = (uint32_t)refs.size();
     /* morton + sort */
     std::vector<uint64_t> keys(n);
     std::vector<uint32_t> order(n);
     for (uint32_t i = 0; i < n; ++i) {
-        float l[3], h[3];
-        tri_bounds(b->tris_in[i], 0.f, l, h);
+        const float *l = refs[i].lo, *h = refs[i].hi;
         float c[3];
         for (int a = 0; a < 3; ++a) { float e = b->hi[a] - b->lo[a]; c[a] = e > 0 ? (0.5f * (l[a] + h[a]) - b->lo[a]) / e : 0.f; }
         keys[i] = morton63(c[0], c[1], c[2]);
@@ -60,11 +82,36 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp) {
     std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return keys[x] < keys[y]; });
     std::vector<uint64_t> skeys(n);
     b->tris_sorted.resize(n);
-    for (uint32_t i = 0; i < n; ++i) { skeys[i] = keys[order[i]]; b->tris_sorted[i] = b->tris_in[order[i]]; }
+    for (uint32_t i = 0; i < n; ++i) { skeys[i] = keys[order[i]]; b->tris_sorted[i] = b->tris_in[refs[order[i]].tri]; }
     /* hierarchy */
     std::vector<Bvh2Node> n2(2 * (size_t)n - 1);
     std::vector<uint32_t> parent(2 * (size_t)n - 1, 0xFFFFFFFFu), counts(n > 1 ? n - 1 : 1, 0), flags(n > 1 ? n - 1 : 1, 0);
-    for (int i = 0; i + 1 < (int)n; ++i) lbvh_build_node(skeys.data(), (int)n, i, n2.data(), parent.data());
+    for (uint32_t k = 0; k < n; ++k) {
+        Bvh2Node& leaf = n2[n - 1 + k];
+        for (int a = 0; a < 3; ++a) { leaf.lo[a] = refs[order[k]].lo[a] - b->pad; leaf.hi[a] = refs[order[k]].hi[a] + b->pad; }
+        leaf.left = leaf.right = 0;
+    }
+    if (ploc_radius == 0 || n < 2) {
+        for (int i = 0; i + 1 < (int)n; ++i) lbvh_build_node(skeys.data(), (int)n, i, n2.data(), parent.data());
+    } else {
+        /* PLOC rounds, as the device runs them: nearest neighbours, roles, ids by the prefix sum of the merges (handed out downwards
+         * so that the last merge, the root, is node 0), compaction in order */
+        std::vector<Bvh2Node> cl(n), nx; std::vector<uint32_t> nn(n);
+        for (uint32_t k = 0; k < n; ++k) { cl[k] = n2[n - 1 + k]; cl[k].left = LEAF_FLAG | k; }
+        uint32_t m = n, next_id = n - 1;
+        while (m > 1) {
+            for (uint32_t i = 0; i < m; ++i) nn[i] = ploc_nearest(cl.data(), m, i, ploc_radius);
+            nx.clear(); uint32_t rank = 0;
+            for (uint32_t i = 0; i < m; ++i) {
+                const int role = ploc_role(nn.data(), i);
+                if (role == 0) nx.push_back(cl[i]);
+                else if (role == 1) { const uint32_t id = next_id - 1 - rank++; nx.push_back(ploc_merge(cl[i], cl[nn[i]], id, n2[id])); }
+            }
+            next_id -= rank; cl.swap(nx); m = (uint32_t)cl.size(); b->ploc_rounds++;
+        }
+        for (uint32_t i = 0; i + 1 < n; ++i) { parent[mem_slot(n, n2[i].left)] = i; parent[mem_slot(n, n2[i].right)] = i; }
+        parent[0] = 0xFFFFFFFFu;
+    }
     /* bottom-up passes: the same walk the kernel does (the second arrival at a node runs refit_visit).  Greedy build: one pass,
      * bounds and counts only.  Default build: REFIT_PASSES passes with tree rotations, the collapse programme in the last one. */
     struct HostMem {
@@ -78,11 +125,6 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp) {
         void store_dp(uint32_t i, const DpNode& d) { dp[i] = d; }
     };
     std::vector<DpNode> dp(use_dp && n > 1 ? n - 1 : 0);
-    for (uint32_t k = 0; k < n; ++k) {
-        Bvh2Node& leaf = n2[n - 1 + k];
-        tri_bounds(b->tris_sorted[k], b->pad, leaf.lo, leaf.hi);
-        leaf.left = leaf.right = 0;
-    }
     HostMem mem{n2.data(), counts.data(), dp.data(), n};
     const int passes = use_dp ? RT3_REFIT_PASSES : 1;
     for (int pass = 0; pass < passes; ++pass) {
@@ -117,6 +159,9 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp) {
 }
 EmuBvh* emu_build(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, false); }
 EmuBvh* emu_build_dp(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, true); }
+EmuBvh* emu_build_ploc(const float* tris9, uint32_t n, int use_dp, uint32_t radius) { return build_lbvh(tris9, n, use_dp != 0, 0.0f, radius); }
+uint32_t emu_ploc_rounds(const EmuBvh* b) { return b->ploc_rounds; }
+EmuBvh* emu_build_split(const float* tris9, uint32_t n, int use_dp, float beta) { return build_lbvh(tris9, n, use_dp != 0, beta); }
 /* wrap an acceleration structure built elsewhere (downloaded from the GPU) so that it can be traversed here */
 EmuBvh* emu_wrap(const uint32_t* nodes20, uint32_t n_nodes, const uint32_t* tris12, uint32_t n_tris) {
     EmuBvh* b = new EmuBvh();
@@ -144,7 +189,8 @@ uint32_t emu_check_triangles(const EmuBvh* b) {
         seen[t.prim]++;
         if (memcmp(&t, &b->tris_in[t.prim], sizeof(Tri48)) != 0) bad++;
     }
-    for (uint32_t s : seen) if (s != 1) bad++;
+    const bool split = b->n_refs > b->tris_in.size();      /* with triangle splitting a triangle is kept once per reference */
+    for (uint32_t s : seen) if (split ? s < 1 : s != 1) bad++;
     return bad;
 }
 void emu_trace_closest(const EmuBvh* b, const rt3_ray* rays, uint64_t n, rt3_hit* out, int brute, double* stats2) {

@@ -25,6 +25,12 @@ def lib():
         L.emu_build.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_build_dp.restype = C.c_void_p
         L.emu_build_dp.argtypes = [C.c_void_p, C.c_uint32]
+        L.emu_build_split.restype = C.c_void_p
+        L.emu_build_split.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_float]
+        L.emu_build_ploc.restype = C.c_void_p
+        L.emu_build_ploc.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_uint32]
+        L.emu_ploc_rounds.restype = C.c_uint32
+        L.emu_ploc_rounds.argtypes = [C.c_void_p]
         L.emu_wrap.restype = C.c_void_p
         L.emu_wrap.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
         L.emu_destroy.argtypes = [C.c_void_p]
@@ -38,12 +44,18 @@ def lib():
 
 
 class EmuBvh:
-    def __init__(self, tris=None, nodes=None, tri_records=None, optimal_collapse=True):
-        """optimal_collapse: children of the wide nodes by the cost dynamic programme (the device default) or greedily (RT3_BUILD_FAST_BUILD)"""
+    def __init__(self, tris=None, nodes=None, tri_records=None, optimal_collapse=True, split_beta=0.0, ploc_radius=0):
+        """optimal_collapse: children of the wide nodes by the cost dynamic programme (the device default) or greedily (RT3_BUILD_FAST_BUILD);
+        split_beta > 0: triangle splitting with a budget of split_beta x triangles extra references (RT3_BUILD_SPLIT)"""
         self.L = lib()
         if tris is not None:
             t = np.ascontiguousarray(tris, np.float32)
-            self.h = (self.L.emu_build_dp if optimal_collapse else self.L.emu_build)(ptr(t), len(t))
+            if ploc_radius > 0:
+                self.h = self.L.emu_build_ploc(ptr(t), len(t), 1 if optimal_collapse else 0, ploc_radius)
+            elif split_beta > 0:
+                self.h = self.L.emu_build_split(ptr(t), len(t), 1 if optimal_collapse else 0, split_beta)
+            else:
+                self.h = (self.L.emu_build_dp if optimal_collapse else self.L.emu_build)(ptr(t), len(t))
         else:
             n, r = np.ascontiguousarray(nodes, np.uint32), np.ascontiguousarray(tri_records, np.uint32)
             self.h = self.L.emu_wrap(ptr(n), len(n), ptr(r), len(r))
@@ -58,6 +70,9 @@ class EmuBvh:
         a, s = np.zeros(4, np.uint32), np.zeros(2, np.float32)
         self.L.emu_info(self.h, ptr(a), ptr(s))
         return dict(nodes=int(a[0]), tris=int(a[1]), levels=int(a[2]), input_tris=int(a[3]), sah_nodes=float(s[0]), sah_tris=float(s[1]))
+
+    def ploc_rounds(self):
+        return int(self.L.emu_ploc_rounds(self.h))
 
     def check_triangles(self):
         return self.L.emu_check_triangles(self.h)

@@ -77,3 +77,45 @@ def test_axis_parallel_rays_and_flat_boxes():
     got, _ = b.trace_closest(rays)
     want, _ = b.trace_closest(rays, brute=True)
     assert (got == want).all() and (got["prim"] != MISS).all()
+
+
+@pytest.mark.parametrize("name", ["cornell", "soup", "atrium"])
+def test_alternative_topologies_find_the_same_hits(name):
+    """Builder experiments kept in bvh_logic.h (neither is in the device build): PLOC instead of the Karras hierarchy,
+    and triangle splitting (several references with clipped boxes per triangle).  Topology must never change a hit."""
+    sc = CASES[name]()
+    T = np.ascontiguousarray(scenes.world_triangles(sc), np.float32)
+    c, a = scenes.incoherent_rays(sc, 2000, seed=41, tris=T.astype(np.float64))
+    rays = np.concatenate([c, scenes.random_rays(sc, 2000, seed=42)])
+    base = EmuBvh(tris=T)
+    want, _ = base.trace_closest(rays, brute=True)
+    want_any = base.trace_any(a, brute=True)
+    for kw in (dict(ploc_radius=4), dict(ploc_radius=25), dict(split_beta=0.5), dict(split_beta=4.0)):
+        b = EmuBvh(tris=T, **kw)
+        info = b.info()
+        assert b.check_triangles() == 0 and info["levels"] < 64
+        if "ploc_radius" in kw:
+            assert info["tris"] == len(T) and 1 <= b.ploc_rounds() < 200
+        else:
+            assert len(T) <= info["tris"] <= len(T) * (1 + kw["split_beta"]) + 1        # the split budget bounds the extra references
+        got, st = b.trace_closest(rays)
+        assert (got == want).all(), kw
+        assert (b.trace_any(a) == want_any).all(), kw
+        assert st[0] < 60 and st[1] < 40
+    assert EmuBvh(tris=T, split_beta=4.0).info()["tris"] > len(T)                      # and it does split something
+
+
+def test_ploc_and_split_degenerate_inputs():
+    tri = np.array([[[0, 0, 0], [1, 0, 0], [0, 1, 0]]], np.float32)
+    rays = np.zeros(8, RAY)
+    rays["o"] = [0.2, 0.2, -1]
+    rays["d"] = [0, 0, 1]
+    rays["tmax"] = 10
+    for T in (np.repeat(tri, 37, 0), tri, np.concatenate([tri, np.zeros((5, 3, 3), np.float32)]),
+              np.concatenate([tri, tri * 1000.0 + 5.0])):                              # identical, single, zero-area, one huge + one small
+        for kw in (dict(ploc_radius=3), dict(split_beta=8.0)):
+            b = EmuBvh(tris=T, **kw)
+            assert b.check_triangles() == 0
+            got, _ = b.trace_closest(rays)
+            want, _ = b.trace_closest(rays, brute=True)
+            assert (got == want).all() and (got["prim"] == 0).all()
