@@ -87,11 +87,20 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
 #ifndef RT3_TRI_REPS
 #define RT3_TRI_REPS 2
 #endif
+#ifndef RT3_TRI_BALANCE
+#define RT3_TRI_BALANCE 0
+#endif
+/* experiments only: -DRT3_TRACE_MIN_BLOCKS=8 caps the registers for 8 resident CTAs per SM (RT3_TRI_BALANCE needs 72 without it) */
+#ifdef RT3_TRACE_MIN_BLOCKS
+#define RT3_TRACE_BOUNDS __launch_bounds__(TRACE_THREADS, RT3_TRACE_MIN_BLOCKS)
+#else
+#define RT3_TRACE_BOUNDS __launch_bounds__(TRACE_THREADS)
+#endif
 /* TWO = two-level structure (RT3_BUILD_TWO_LEVEL): top-level leaf records are instances; see traverse_wide in bvh_logic.h for the
  * stack protocol (node group, record group, sentinel).  The world-space ray stays in registers for the triangle test, which
  * rebuilds the world-space triangle from the stored object-space vertices (bit-identical to the flattened build). */
 template <bool ANY, int KEEP, bool TWO>
-__global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
+__global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
                                                              const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
                                                              rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter, uint32_t magic,
                                                              const InstRec* __restrict__ insts) {
@@ -164,6 +173,63 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace_dyn(const WideNode* __r
                 tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
             }
             bool found_any = false;
+#if RT3_TRI_BALANCE
+            if (!TWO) {
+                /* EXPERIMENT (compile with -DRT3_TRI_BALANCE=1; not in the product build, not yet run on a GPU): the record phase spread over
+                 * the whole warp.  The pending triangles of all lanes are numbered by a warp prefix sum; lane k tests triangle k (up to 32 a
+                 * step) with the owner's ray fetched by shuffles, results go back through shared memory and the owner keeps the closest. */
+                __shared__ uint16_t s_src[TRACE_THREADS / 32][32];
+                __shared__ float4 s_res[TRACE_THREADS / 32][32];
+                const uint32_t wid = threadIdx.x >> 5;
+                uint32_t rest = active ? tg_hits : 0u;
+                const uint32_t cnt = (uint32_t)__popc(rest);
+                uint32_t incl = cnt;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, off); if ((int)lane >= off) incl += v; }
+                const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+                if (total) {
+                    const uint32_t first = incl - cnt;
+                    uint32_t pos = first, mine = 0;
+                    while (rest && pos < 32u) {
+                        const int bit = bfind32(rest);
+                        rest &= ~(1u << bit);
+                        s_src[wid][pos] = (uint16_t)(lane | ((uint32_t)bit << 8));
+                        pos++; mine++;
+                    }
+                    if (active) tg_hits = rest;                                   /* what did not fit into this step stays pending */
+                    __syncwarp();
+                    const uint32_t items = total < 32u ? total : 32u;
+                    const uint32_t e = lane < items ? (uint32_t)s_src[wid][lane] : lane;
+                    const uint32_t src = e & 31u, sbit = e >> 8;
+                    const uint32_t sbase = __shfl_sync(0xFFFFFFFFu, tg_base, src);
+                    const float sox = __shfl_sync(0xFFFFFFFFu, r.ox, src), soy = __shfl_sync(0xFFFFFFFFu, r.oy, src), soz = __shfl_sync(0xFFFFFFFFu, r.oz, src);
+                    const float sdx = __shfl_sync(0xFFFFFFFFu, r.dx, src), sdy = __shfl_sync(0xFFFFFFFFu, r.dy, src), sdz = __shfl_sync(0xFFFFFFFFu, r.dz, src);
+                    const float stmin = __shfl_sync(0xFFFFFFFFu, r.tmin, src), stmax = __shfl_sync(0xFFFFFFFFu, ray_tmax, src);
+                    float4 res = make_float4(0.f, 0.f, 0.f, __uint_as_float(RT3_MISS));
+                    if (lane < items) {
+                        const Tri48* tp = tris + (sbase + sbit);
+                        const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
+                        float t, u, v;
+                        const rt3m::vec3 v0 = rt3m::v3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
+                        const rt3m::vec3 e1 = rt3m::v3(__uint_as_float(b.x), __uint_as_float(b.y), __uint_as_float(b.z));
+                        const rt3m::vec3 e2 = rt3m::v3(__uint_as_float(c.x), __uint_as_float(c.y), __uint_as_float(c.z));
+                        if (rt3m::ray_triangle(rt3m::v3(sox, soy, soz), rt3m::v3(sdx, sdy, sdz), v0, e1, e2, t, u, v) && t > stmin && t < stmax)
+                            res = make_float4(t, u, v, __uint_as_float(a.w));
+                    }
+                    s_res[wid][lane] = res;
+                    __syncwarp();
+                    for (uint32_t j = 0; j < mine; ++j) {
+                        const float4 q = s_res[wid][first + j];
+                        const uint32_t prim = __float_as_uint(q.w);
+                        if (prim == RT3_MISS) continue;
+                        if (ANY) found_any = true;
+                        else if (rt3m::closer_hit(q.x, prim, h.t, h.prim)) { h.t = q.x; h.u = q.y; h.v = q.z; h.prim = prim; }
+                    }
+                    __syncwarp();                                                  /* the next step overwrites s_src / s_res */
+                    if (ANY && found_any) tg_hits = 0;
+                }
+            } else
+#endif
 #if RT3_TRI_REPS > 1
             for (int rep_ = 0; rep_ < RT3_TRI_REPS; ++rep_) {
             if (rep_ && __ballot_sync(0xFFFFFFFFu, active && tg_hits != 0u && !found_any) == 0u) break;
