@@ -174,6 +174,11 @@ EmuBvh* emu_wrap(const uint32_t* nodes20, uint32_t n_nodes, const uint32_t* tris
     b->n_nodes = n_nodes; b->n_tris = n_tris;
     return b;
 }
+/* the wide nodes and leaf records as the device holds them (for tests/emu/warp_emu.cpp) */
+void emu_export(const EmuBvh* b, uint32_t* nodes20, uint32_t* tris12) {
+    memcpy(nodes20, b->nodes.data(), (size_t)b->n_nodes * sizeof(WideNode));
+    memcpy(tris12, b->tris_out.data(), (size_t)b->n_tris * sizeof(Tri48));
+}
 void emu_destroy(EmuBvh* b) { delete b; }
 void emu_info(const EmuBvh* b, uint32_t* out4, float* sah2) {
     out4[0] = b->n_nodes; out4[1] = b->n_tris; out4[2] = b->levels; out4[3] = (uint32_t)b->tris_in.size();

@@ -10,6 +10,7 @@ from raytracer3_b200.types import HIT, ptr
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "emu", "libemu.so")
 _lib = None
+_wlibs = {}
 
 
 def lib():
@@ -34,6 +35,7 @@ def lib():
         L.emu_wrap.restype = C.c_void_p
         L.emu_wrap.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
         L.emu_destroy.argtypes = [C.c_void_p]
+        L.emu_export.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.emu_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.emu_check_triangles.restype = C.c_uint32
         L.emu_check_triangles.argtypes = [C.c_void_p]
@@ -41,6 +43,30 @@ def lib():
         L.emu_trace_any.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]
         _lib = L
     return _lib
+
+
+def warp_lib(balance=False, defines=()):
+    """tests/emu/warp_emu.cpp: the production kernel source (csrc/trace_kernel.cuh) over a lock-step warp emulation.
+    balance=True builds it with -DRT3_TRI_BALANCE=1 (the warp-balanced record phase, an experiment not in the product build)."""
+    defines = tuple(defines) + (("RT3_TRI_BALANCE=1",) if balance else ())
+    key = "_".join(d.replace("=", "") for d in defines)
+    if key not in _wlibs:
+        so = os.path.join(_HERE, "emu", f"libwemu_{key}.so" if key else "libwemu.so")
+        src = os.path.join(_HERE, "emu", "warp_emu.cpp")
+        csrc = os.path.join(_HERE, "..", "raytracer3_b200", "csrc")
+        deps = [src, os.path.join(csrc, "bvh_logic.h"), os.path.join(csrc, "trace_kernel.cuh"), os.path.join(_HERE, "..", "include", "rt3_shared_math.h")]
+        if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas"]
+                                  + ["-D" + d for d in defines]
+                                  + ["-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", so, src])
+        L = C.CDLL(so)
+        L.wemu_trace.restype = C.c_int
+        L.wemu_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.wemu_last_error.restype = C.c_char_p
+        L.wemu_tri_balance.restype = C.c_int
+        L.wemu_phase_stats.argtypes = [C.c_void_p]
+        _wlibs[key] = L
+    return _wlibs[key]
 
 
 class EmuBvh:
@@ -73,6 +99,27 @@ class EmuBvh:
 
     def ploc_rounds(self):
         return int(self.L.emu_ploc_rounds(self.h))
+
+    def export(self):
+        """(wide nodes [n, 20] u32, leaf records [m, 12] u32) as the device holds them"""
+        i = self.info()
+        nodes, recs = np.zeros((max(i["nodes"], 1), 20), np.uint32), np.zeros((max(i["tris"], 1), 12), np.uint32)
+        self.L.emu_export(self.h, ptr(nodes), ptr(recs))
+        return nodes, recs
+
+    def kernel_trace(self, rays, any_hit=False, blocks=2, d_count=False, balance=False, defines=()):
+        """the production kernel k_trace_dyn on the warp emulation: hits (closest) or result bits (any); also the number of warp collectives run"""
+        W = warp_lib(balance, defines)
+        nodes, recs = self.export()
+        rays = np.ascontiguousarray(rays)
+        hits, bits, coll = np.zeros(len(rays), HIT), np.zeros((len(rays) + 31) // 32 + 1, np.uint32), np.zeros(1, np.uint64)
+        rc = W.wemu_trace(ptr(nodes), ptr(recs), None, ptr(rays), len(rays), 1 if any_hit else 0, blocks, 1 if d_count else 0, ptr(hits), ptr(bits), ptr(coll))
+        if rc != 0:
+            raise RuntimeError("warp emulation: " + W.wemu_last_error().decode())
+        ph = np.zeros((8, 3), np.uint64)
+        W.wemu_phase_stats(ptr(ph))
+        self.phase_stats = ph          # [phase][warp executions with >= 1 lane, lanes taking part, times reached]; phases: see warp_emu.cpp
+        return (bits[:(len(rays) + 31) // 32] if any_hit else hits), int(coll[0])
 
     def check_triangles(self):
         return self.L.emu_check_triangles(self.h)
