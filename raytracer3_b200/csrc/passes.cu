@@ -159,8 +159,15 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_para
 }
 
 /* Loop iteration b >= 1 of refrence_mode.slang:36-57 for every path whose ray was traced at b-1. */
+/* experiments only: -DRT3_SHADE_MIN_BLOCKS=5 / 6 trades registers (64 -> 48 / 40, 92 / 160 bytes of spills) for resident warps; the kernel is
+ * latency bound at 50 % occupancy (profiles/r1j_k_ref_shade_summary.txt: 10 long-scoreboard stalls per issue) */
+#ifdef RT3_SHADE_MIN_BLOCKS
+#define RT3_SHADE_BOUNDS __launch_bounds__(PASS_THREADS, RT3_SHADE_MIN_BLOCKS)
+#else
+#define RT3_SHADE_BOUNDS __launch_bounds__(PASS_THREADS)
+#endif
 template <bool LAYERED>
-__global__ void __launch_bounds__(PASS_THREADS) k_ref_shade(SceneView s, rt3_params p, PixelMap m, uint32_t b, const rt3_ray* __restrict__ rays_in,
+__global__ void RT3_SHADE_BOUNDS k_ref_shade(SceneView s, rt3_params p, PixelMap m, uint32_t b, const rt3_ray* __restrict__ rays_in,
                                                             const rt3_hit* __restrict__ hits, const float4* __restrict__ thr_in,
                                                             const uint32_t* __restrict__ count_in, rt3_ray* __restrict__ rays_out,
                                                             float4* __restrict__ thr_out, uint32_t* count_out, float4* __restrict__ px_radiance,
