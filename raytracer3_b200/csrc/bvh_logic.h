@@ -803,10 +803,16 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
      * function; lanes without a ray pass active = false) so that both phases run converged. */
 #ifdef __CUDA_ARCH__
 #define RT3_WARP_ANY(x) __any_sync(0xFFFFFFFFu, (x))
+#elif defined(RT3_WARP_EMU)
+#define RT3_WARP_ANY(x) (__ballot_sync(0xFFFFFFFFu, (x)) != 0u)      /* tests/emu/warp_emu.cpp: 32 lanes in lock step on the CPU */
 #else
 #define RT3_WARP_ANY(x) (x)
 #endif
+#ifndef RT3_EMU_PHASE
+#define RT3_EMU_PHASE(id, pred) do { } while (0)                      /* phase statistics of the warp emulation; empty everywhere else */
+#endif
     while (RT3_WARP_ANY(active)) {
+        RT3_EMU_PHASE(5, active && tg_hits == 0u && ng_hits > 0x00FFFFFFu);
         if (active && tg_hits == 0u && ng_hits > 0x00FFFFFFu) {
             const int bit = bfind32(ng_hits);
             const uint32_t imask = ng_hits & 0xFFu;
@@ -824,6 +830,7 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
         bool found_any = false;
         for (int rep = 0; rep < 2; ++rep) {   /* up to two record steps per node step, as in k_trace_dyn */
         if (rep && !RT3_WARP_ANY(active && tg_hits != 0u && !found_any)) break;
+        RT3_EMU_PHASE(6, active && tg_hits && !found_any);
         if (active && tg_hits && !found_any) {
             const int bit = bfind32(tg_hits);
             tg_hits &= ~(1u << bit);

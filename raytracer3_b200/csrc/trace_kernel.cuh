@@ -12,10 +12,7 @@
 #define RT3_TRACE_KERNEL_CUH
 
 /* The warp emulation counts how often a warp runs each phase of the loop and with how many lanes (RT3_EMU_PHASE is a ballot there);
- * in the device build the hook is empty. */
-#ifndef RT3_EMU_PHASE
-#define RT3_EMU_PHASE(id, pred) do { } while (0)
-#endif
+ * in the device build the hook is empty (bvh_logic.h). */
 
 namespace {
 

@@ -21,6 +21,13 @@
 #include <cstring>
 #include <vector>
 
+#define RT3_WARP_EMU 1
+static inline uint32_t __ballot_sync(uint32_t mask, bool pred);
+struct EmuThreadIdx { unsigned x; };
+static EmuThreadIdx threadIdx;       /* set by the scheduler whenever a fiber is resumed */
+/* phase statistics: [id][0] = times a warp ran the phase with at least one lane, [id][1] = lanes that took part, [id][2] = times reached */
+static uint64_t g_phase[8][3];
+#define RT3_EMU_PHASE(id, pred) do { const uint32_t m_ = __ballot_sync(0xFFFFFFFFu, (pred)); if ((threadIdx.x & 31u) == 0u) { g_phase[id][0] += m_ != 0u; g_phase[id][1] += (uint64_t)__builtin_popcount(m_); g_phase[id][2]++; } } while (0)
 #include "../../raytracer3_b200/csrc/bvh_logic.h"
 
 /* ------------------------------------------------------------------ CUDA surface used by trace_kernel.cuh ---------------- */
@@ -94,9 +101,6 @@ static void gather(int kind, uint64_t v, uint64_t all[LANES]) {
 
 }  // namespace wemu
 
-struct EmuThreadIdx { unsigned x; };
-static EmuThreadIdx threadIdx;       /* set by the scheduler whenever a fiber is resumed */
-
 static inline uint32_t __ballot_sync(uint32_t mask, bool pred) {
     (void)mask;
     uint64_t all[wemu::LANES];
@@ -125,12 +129,30 @@ static inline uint32_t __shfl_up_sync(uint32_t, uint32_t v, int delta) {
     return r;
 }
 
-/* phase statistics: [id][0] = times a warp ran the phase with at least one lane, [id][1] = lanes that took part, [id][2] = times reached */
-static uint64_t g_phase[8][3];
-#define RT3_EMU_PHASE(id, pred) do { const uint32_t m_ = __ballot_sync(0xFFFFFFFFu, (pred)); if ((threadIdx.x & 31u) == 0u) { g_phase[id][0] += m_ != 0u; g_phase[id][1] += (uint64_t)__builtin_popcount(m_); g_phase[id][2]++; } } while (0)
-
 using namespace rt3b;
 #include "../../raytracer3_b200/csrc/trace_kernel.cuh"
+
+/* Static assignment, as k_gbuffer (passes.cu) and k_trace (trace.cu) use traverse_wide: a warp takes 32 consecutive rays and keeps them
+ * until the slowest lane is done.  Statistics only (phases 5 / 6 of traverse_wide). */
+namespace {
+void k_static(const WideNode* nodes, const Tri48* tris, const rt3_ray* rays, uint64_t n, rt3_hit* hits, unsigned long long* work_counter) {
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(work_counter, 32ull);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const uint64_t i = base + lane;
+        const bool valid = i < n;
+        rt3_ray r;
+        if (valid) r = rays[i];
+        else { r.o[0] = r.o[1] = r.o[2] = 0.f; r.d[0] = r.d[1] = 0.f; r.d[2] = 1.f; r.tmin = 0.f; r.tmax = 0.f; }
+        rt3_hit h; h.t = r.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+        traverse_wide<false>(nodes, tris, r, h, nullptr, valid, nullptr);
+        if (valid) hits[i] = h;
+    }
+}
+}  // namespace
 
 /* ------------------------------------------------------------------ block runner ---------------------------------------- */
 namespace wemu {
@@ -143,7 +165,8 @@ static LaunchArgs g_args;
 
 static void fiber_main() {
     const LaunchArgs& a = g_args;
-    if (a.any) {
+    if (a.any == 2) k_static(a.nodes, a.tris, a.rays, a.n, a.hits, a.work_counter);
+    else if (a.any) {
         if (a.two) k_trace_dyn<true, 28, true>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
         else k_trace_dyn<true, 28, false>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
     } else {
@@ -195,7 +218,8 @@ static int run_block() {
 
 extern "C" {
 
-/* Runs k_trace_dyn<ANY, 28, TWO> with `blocks` blocks of 128 threads over the ray queue.  d_count_mode != 0 passes the queue length
+/* any = 2: the static-assignment loop over traverse_wide (closest hit) instead of the production kernel.
+ * Runs k_trace_dyn<ANY, 28, TWO> with `blocks` blocks of 128 threads over the ray queue.  d_count_mode != 0 passes the queue length
  * through device memory (as the bounce loop does) instead of by value.  Returns 0, or -1 (message via wemu_last_error). */
 int wemu_trace(const uint32_t* nodes20, const uint32_t* tris12, const void* insts, const rt3_ray* rays, uint64_t n, int any, int blocks,
                int d_count_mode, rt3_hit* hits, uint32_t* bits, uint64_t* collectives) {
@@ -208,13 +232,14 @@ int wemu_trace(const uint32_t* nodes20, const uint32_t* tris12, const void* inst
     g_args.d_count = d_count_mode ? &count32 : nullptr; g_args.n = d_count_mode ? n + 1000 : n;   /* n_static is the capacity when d_count is given */
     g_args.hits = hits; g_args.bits = bits; g_args.work_counter = &counter; g_args.insts = (const InstRec*)insts;
     g_args.any = any; g_args.two = insts != nullptr;
-    if (any) memset(bits, 0, ((n + 31) / 32) * 4);        /* launch_dyn zeroes the result bits before the launch */
+    if (any == 1) memset(bits, 0, ((n + 31) / 32) * 4);        /* launch_dyn zeroes the result bits before the launch */
     for (int b = 0; b < blocks; ++b)
         if (run_block() != 0) return -1;
     if (collectives) *collectives = g_collectives;
     return 0;
 }
-/* out[id][3] for id = 0 node step, 1 record step (one per lane), 2 balanced record step: lanes holding triangles, 3 balanced: lanes testing, 4 refill */
+/* out[id][3] for id = 0 node step, 1 record step (one per lane), 2 balanced record step: lanes holding triangles, 3 balanced: lanes testing, 4 refill,
+ * 5 / 6 node / record step of traverse_wide (static assignment) */
 void wemu_phase_stats(uint64_t* out24) { memcpy(out24, g_phase, sizeof(g_phase)); }
 const char* wemu_last_error() { return wemu::g_error ? wemu::g_error : ""; }
 int wemu_tri_balance() { return RT3_TRI_BALANCE; }

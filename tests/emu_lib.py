@@ -107,13 +107,13 @@ class EmuBvh:
         self.L.emu_export(self.h, ptr(nodes), ptr(recs))
         return nodes, recs
 
-    def kernel_trace(self, rays, any_hit=False, blocks=2, d_count=False, balance=False, defines=()):
+    def kernel_trace(self, rays, any_hit=False, blocks=2, d_count=False, balance=False, defines=(), static=False):
         """the production kernel k_trace_dyn on the warp emulation: hits (closest) or result bits (any); also the number of warp collectives run"""
         W = warp_lib(balance, defines)
         nodes, recs = self.export()
         rays = np.ascontiguousarray(rays)
         hits, bits, coll = np.zeros(len(rays), HIT), np.zeros((len(rays) + 31) // 32 + 1, np.uint32), np.zeros(1, np.uint64)
-        rc = W.wemu_trace(ptr(nodes), ptr(recs), None, ptr(rays), len(rays), 1 if any_hit else 0, blocks, 1 if d_count else 0, ptr(hits), ptr(bits), ptr(coll))
+        rc = W.wemu_trace(ptr(nodes), ptr(recs), None, ptr(rays), len(rays), 2 if static else (1 if any_hit else 0), blocks, 1 if d_count else 0, ptr(hits), ptr(bits), ptr(coll))
         if rc != 0:
             raise RuntimeError("warp emulation: " + W.wemu_last_error().decode())
         ph = np.zeros((8, 3), np.uint64)
