@@ -281,6 +281,29 @@ __global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_
     }
 }
 
+/* RT3_BUILD_TREELET: the same walk with treelet_visit (bvh_logic.h) in place of the rotations */
+template <bool WITH_DP>
+__global__ void __launch_bounds__(128) k_refit_treelet(const Tri48* tris_sorted, uint32_t n, int kind, float pad, Bvh2Node* nodes, const uint32_t* parent,
+                                                       uint32_t* flags, uint32_t* counts, DpNode* dp, int first_pass) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    DevMem mem{nodes, counts, dp, n};
+    if (first_pass) {
+        Bvh2Node leaf;
+        tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi, kind);
+        leaf.left = leaf.right = 0;
+        mem.store_node(n - 1 + k, leaf);
+    }
+    uint32_t cur = parent[n - 1 + k];
+    while (cur != 0xFFFFFFFFu) {
+        __threadfence();
+        if (atomicAdd(flags + cur, 1u) == 0u) return;
+        __threadfence();
+        treelet_visit(mem, n, cur, WITH_DP);
+        cur = parent[cur];
+    }
+}
+
 /* rotations moved subtrees: parent links for the next bottom-up pass */
 __global__ void __launch_bounds__(256) k_parents(const Bvh2Node* nodes, uint32_t n, uint32_t* parent) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -331,6 +354,7 @@ struct WideBuild {
     WideNode* wide; uint32_t root_index, first_free_node;
     Tri48* out_recs; uint32_t first_free_rec;
     bool optimal_collapse = false;   /* choose the children of every wide node by the cost dynamic programme instead of greedily */
+    bool treelet = false;            /* with optimal_collapse: treelet restructuring instead of rotations (RT3_BUILD_TREELET) */
     uint32_t nodes_end = 0, recs_end = 0, levels = 0; float sah_nodes = 0.f, sah_recs = 0.f;   /* results */
 };
 
@@ -408,13 +432,17 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         dbg_mark("hierarchy");
         tm.begin();
         DpNode* dp = io.optimal_collapse ? (DpNode*)(base + o_dp) : nullptr;
-        const int passes = io.optimal_collapse ? RT3_REFIT_PASSES : 1;
+        const bool treelet = io.optimal_collapse && io.treelet;
+        const int passes = treelet ? RT3_TREELET_PASSES : (io.optimal_collapse ? RT3_REFIT_PASSES : 1);
         for (int pass = 0; pass < passes; ++pass) {
             if (pass) {
                 RT3_CUDA(c, cudaMemsetAsync(nflags, 0, sizeof(uint32_t) * n, st));
                 if (n > 1) RT3_LAUNCH(c, k_parents, div_up(n - 1, 256), 256, 0, st, nodes2, n, parent);
             }
-            if (!io.optimal_collapse) RT3_LAUNCH(c, (k_refit<false, false>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, 1);
+            if (treelet) {
+                if (pass < passes - 1) RT3_LAUNCH(c, (k_refit_treelet<false>), div_up(n, 128), 128, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
+                else RT3_LAUNCH(c, (k_refit_treelet<true>), div_up(n, 128), 128, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
+            } else if (!io.optimal_collapse) RT3_LAUNCH(c, (k_refit<false, false>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, 1);
             else if (pass < passes - 1) RT3_LAUNCH(c, (k_refit<true, false>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
             else RT3_LAUNCH(c, (k_refit<true, true>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
         }
@@ -482,7 +510,7 @@ static bool invert_affine(const float m[12], float out[12]) {
 }
 
 /* ---- single level: every instance flattened to world space (the default) -------------------------------------------- */
-static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal) {
+static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal, bool treelet) {
     const uint32_t n = c->n_triangles;
     StageTimer tm(c, st);
     dbg_mark("enter single");
@@ -501,7 +529,7 @@ static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats&
         dbg_mark("flatten");
         for (int k = 0; k < 3; ++k) { bs.scene_lo[k] = lo[k]; bs.scene_hi[k] = hi[k]; }
         WideBuild io;
-        io.optimal_collapse = optimal;
+        io.optimal_collapse = optimal; io.treelet = treelet;
         io.recs = &s_tris; io.n = n; io.kind = REC_TRI_EDGES; io.pad = max_extent(lo, hi) * (1.0f / 65536.0f);
         memcpy(io.lo, lo, sizeof(lo)); memcpy(io.hi, hi, sizeof(hi));
         io.wide = ensure<WideNode>(c, c->bvh_nodes, n); io.root_index = 0; io.first_free_node = 1;
@@ -520,7 +548,7 @@ static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats&
 }
 
 /* ---- two levels (RT3_BUILD_TWO_LEVEL): one bottom-level tree per distinct mesh, one top-level tree over the instances ---- */
-static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal) {
+static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal, bool treelet) {
     StageTimer tm(c, st);
     const std::vector<InstanceRec>& inst = c->h_instances;
     const uint32_t ni = (uint32_t)inst.size();
@@ -596,7 +624,7 @@ static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs
             mi.root = next_node;
             if (mi.n == 0) { RT3_LAUNCH(c, k_empty_root, 1, 32, 0, st, wide + mi.root); next_node++; continue; }
             WideBuild io;
-            io.optimal_collapse = optimal;
+            io.optimal_collapse = optimal; io.treelet = treelet;
             io.recs = &mesh_tris[m]; io.n = mi.n; io.kind = REC_TRI_VERTS;
             /* padding covers the intersection slop and node quantisation (object extent / 65536, as in the single-level build) AND the
              * rounding of the world -> object ray transform, which grows with the distance of the ray origin in object units */
@@ -623,7 +651,7 @@ static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs
         Tri48* d_boxes = palloc<Tri48>(c, s_recs, ni, st);
         RT3_CUDA(c, cudaMemcpyAsync(d_boxes, boxes.data(), ni * sizeof(Tri48), cudaMemcpyHostToDevice, st));
         WideBuild top;
-        top.optimal_collapse = optimal;
+        top.optimal_collapse = optimal; top.treelet = treelet;
         top.recs = &s_recs; top.n = ni; top.kind = REC_BOX; top.pad = top_pad;
         memcpy(top.lo, wlo, sizeof(wlo)); memcpy(top.hi, whi, sizeof(whi));
         top.wide = wide; top.root_index = 0; top.first_free_node = next_node;
@@ -667,11 +695,12 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
      * the fastest build, then greedy by surface area.  Measured: 36 % fewer nodes, +2 % path-tracing and +2..6 % incoherent-ray
      * throughput, build 1.37 -> 1.49 ms at 263 k triangles. */
     const bool optimal = !(flags & RT3_BUILD_FAST_BUILD);
+    const bool treelet = optimal && ((flags & RT3_BUILD_TREELET) || getenv("RT3_FORCE_TREELET") != nullptr);   /* the env switch: A/B of whole benchmarks */
     if (n == 0) {
     } else if ((flags & RT3_BUILD_TWO_LEVEL) && !c->h_instances.empty()) {
-        build_two_level(c, st, bs, optimal);
+        build_two_level(c, st, bs, optimal, treelet);
     } else {
-        build_single_level(c, st, bs, optimal);
+        build_single_level(c, st, bs, optimal, treelet);
     }
     cudaEventRecord(total_b, st); cudaEventSynchronize(total_b);
     float ms = 0; cudaEventElapsedTime(&ms, total_a, total_b); bs.ms_total = ms;

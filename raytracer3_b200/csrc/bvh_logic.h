@@ -524,6 +524,121 @@ RT3_HD void refit_visit(Mem& mem, uint32_t n, uint32_t cur, bool rotate, bool wi
     rebuild(cur, L, nl, cL, pkl, R, nr, cR, pkr, nullptr);
 }
 
+/* ---- treelet restructuring (Karras & Aila 2013, section 3) as an alternative to the rotations of refit_visit ---------------------
+ * The second thread to arrive at `cur` grows a treelet below it — up to RT3_TREELET_LEAVES subtrees, always opening the subtree of
+ * largest surface area — and finds, by dynamic programming over the subsets of those subtrees, the binary topology of least summed
+ * surface area:  copt(S) = A(S) + min over partitions P of S of copt(P) + copt(S \ P),  copt({l}) = 0.  The treelet's internal nodes
+ * (cur and the nodes that were opened) are re-linked in place when that beats the topology found; subtrees below the treelet's leaves
+ * are untouched, so, as with the rotations, only nodes below `cur` change and the result depends on the tree alone.
+ * Rotations are the special case of 3- and 4-leaf treelets. */
+#ifndef RT3_TREELET_LEAVES
+#define RT3_TREELET_LEAVES 7      /* 5 / 7 / 9 leaves: 8.82 / 8.53 / 8.54 work units per incoherent ray on the bench scene (rotations: 9.12) */
+#endif
+#define RT3_TREELET_PASSES 2       /* 1 / 2 / 3 / 5 passes: 8.92 / 8.55 / 8.53 / 8.52 */
+template <class Mem>
+RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
+    const int K = RT3_TREELET_LEAVES;
+    uint32_t leaf_ref[K], inner_id[K];
+    Bvh2Node leaf_box[K];
+    float leaf_area[K];
+    int nl = 0, ni = 0;
+    {
+        const Bvh2Node P = mem.node(cur);
+        leaf_ref[0] = P.left; leaf_ref[1] = P.right; nl = 2;
+        inner_id[ni++] = cur;
+        for (int k = 0; k < 2; ++k) { leaf_box[k] = mem.node(mem.slot(leaf_ref[k])); leaf_area[k] = box_area(leaf_box[k].lo, leaf_box[k].hi); }
+    }
+    float found_cost = 0.0f;                       /* summed area of the internal nodes below cur as they are now */
+    while (nl < K) {
+        int best = -1; float ba = -1.0f;
+        for (int k = 0; k < nl; ++k) if (!(leaf_ref[k] & LEAF_FLAG) && leaf_area[k] > ba) { ba = leaf_area[k]; best = k; }
+        if (best < 0) break;
+        const Bvh2Node open = leaf_box[best];
+        found_cost += ba;
+        inner_id[ni++] = leaf_ref[best];
+        leaf_ref[best] = open.left; leaf_ref[nl] = open.right;
+        leaf_box[best] = mem.node(mem.slot(open.left)); leaf_box[nl] = mem.node(mem.slot(open.right));
+        leaf_area[best] = box_area(leaf_box[best].lo, leaf_box[best].hi); leaf_area[nl] = box_area(leaf_box[nl].lo, leaf_box[nl].hi);
+        nl++;
+    }
+    const uint32_t full = (1u << nl) - 1u;
+    float area[1 << K], copt[1 << K];
+    uint16_t part[1 << K];
+    for (uint32_t sset = 1; sset <= full; ++sset) {
+        float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+        for (int k = 0; k < nl; ++k) if (sset & (1u << k)) for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(lo[q], leaf_box[k].lo[q]); hi[q] = rt3m::max_(hi[q], leaf_box[k].hi[q]); }
+        area[sset] = box_area(lo, hi);
+        copt[sset] = 0.0f; part[sset] = 0;
+    }
+    /* subsets in increasing numeric order: every proper subset of S is smaller than S, so its copt is final when S is reached */
+    for (uint32_t sset = 3; sset <= full; ++sset) {
+        if ((sset & (sset - 1u)) == 0u) continue;                                  /* singleton */
+        float bc = 3.4e38f; uint32_t bp = 0;
+        const uint32_t low = sset & (0u - sset);                                    /* the partition holding the lowest member is P: halves the search */
+        const uint32_t rest = sset ^ low;
+        for (uint32_t sub = (rest - 1u) & rest;; sub = (sub - 1u) & rest) {        /* P = low | sub for every proper subset sub of rest (incl. empty) */
+            const uint32_t pp = low | sub;
+            const float c = copt[pp] + copt[sset ^ pp];
+            if (c < bc) { bc = c; bp = pp; }
+            if (sub == 0u) break;
+        }
+        copt[sset] = (sset == full ? 0.0f : area[sset]) + bc;                       /* the root's own area is the same for every topology */
+        part[sset] = (uint16_t)bp;
+    }
+    const bool restructure = nl > 2 && copt[full] < found_cost * 0.99999f;
+    /* the topology to write: node list in pre-order (set, id), children resolved after; written in reverse (children first) */
+    uint32_t t_set[K], t_id[K]; int t_n = 0;
+    uint16_t t_l[K], t_r[K];                                                        /* child sets */
+    if (restructure) {
+        uint32_t st[K]; int sp = 0, next_inner = 1;
+        st[sp++] = full; t_id[0] = cur;
+        /* pre-order with explicit stack; ids handed out in visit order (inner_id[0] = cur is the root) */
+        int idx_of_set[1 << K];
+        while (sp) {
+            const uint32_t sset = st[--sp];
+            const int me = t_n++;
+            t_set[me] = sset;
+            if (me > 0) t_id[me] = inner_id[next_inner++];
+            idx_of_set[sset] = me;
+            const uint32_t pl = part[sset], pr = sset ^ pl;
+            t_l[me] = (uint16_t)pl; t_r[me] = (uint16_t)pr;
+            if (pr & (pr - 1u)) st[sp++] = pr;
+            if (pl & (pl - 1u)) st[sp++] = pl;
+        }
+        /* children first: a node's children that are treelet-internal come later in pre-order, so walk backwards */
+        Bvh2Node nb[K]; uint32_t ncount[K]; float nrow[K][7];
+        for (int me = t_n - 1; me >= 0; --me) {
+            Bvh2Node cb[2]; uint32_t cref[2], cc[2]; float crow[2][7];
+            for (int side = 0; side < 2; ++side) {
+                const uint32_t cs = side ? t_r[me] : t_l[me];
+                if ((cs & (cs - 1u)) == 0u) {
+                    const int k = bfind32(cs);
+                    cref[side] = leaf_ref[k]; cb[side] = leaf_box[k]; cc[side] = mem.count(leaf_ref[k]);
+                    if (with_dp) { if (leaf_ref[k] & LEAF_FLAG) dp_leaf_costs(leaf_area[k], crow[side]); else mem.dp_costs(leaf_ref[k], crow[side]); }
+                } else {
+                    const int ci = idx_of_set[cs];
+                    cref[side] = t_id[ci]; cb[side] = nb[ci]; cc[side] = ncount[ci];
+                    if (with_dp) for (int i = 0; i < 7; ++i) crow[side][i] = nrow[ci][i];
+                }
+            }
+            Bvh2Node m;
+            box_union(cb[0], cb[1], m.lo, m.hi);
+            m.left = cref[0]; m.right = cref[1];
+            mem.store_node(t_id[me], m);
+            mem.store_count(t_id[me], cc[0] + cc[1]);
+            nb[me] = m; ncount[me] = cc[0] + cc[1];
+            if (with_dp) {
+                DpNode d;
+                dp_node(crow[0], crow[1], box_area(m.lo, m.hi), cc[0] + cc[1], d);
+                mem.store_dp(t_id[me], d);
+                for (int i = 0; i < 7; ++i) nrow[me][i] = d.cost[i];
+            }
+        }
+    } else {
+        refit_visit(mem, n, cur, false, with_dp);                                   /* topology kept: bounds, count and programme row of cur */
+    }
+}
+
 /*
  * Node layout (20 words):
  *   w0..w2  p = node box min (float)            w3  ex | ey<<8 | ez<<16 | imask<<24   (e biased by 127)

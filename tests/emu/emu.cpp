@@ -28,7 +28,7 @@ static inline uint32_t mem_slot(uint32_t n, uint32_t ref) { return (ref & LEAF_F
 extern "C" {
 
 /* split_beta > 0: triangle splitting (bvh_logic.h split_*): the hierarchy is built over references, n below is then their number */
-static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp, float split_beta = 0.0f, uint32_t ploc_radius = 0) {
+static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp, float split_beta = 0.0f, uint32_t ploc_radius = 0, int treelet_passes = 0) {
     EmuBvh* b = new EmuBvh();
     b->tris_in.resize(n);
     for (int a = 0; a < 3; ++a) { b->lo[a] = 3.4e38f; b->hi[a] = -3.4e38f; }
@@ -126,7 +126,7 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp, float spl
     };
     std::vector<DpNode> dp(use_dp && n > 1 ? n - 1 : 0);
     HostMem mem{n2.data(), counts.data(), dp.data(), n};
-    const int passes = use_dp ? RT3_REFIT_PASSES : 1;
+    const int passes = treelet_passes > 0 ? treelet_passes : (use_dp ? RT3_REFIT_PASSES : 1);
     for (int pass = 0; pass < passes; ++pass) {
         std::fill(flags.begin(), flags.end(), 0u);
         if (pass) for (uint32_t i = 0; i + 1 < n; ++i) { parent[mem.slot(n2[i].left)] = i; parent[mem.slot(n2[i].right)] = i; }   /* rotations moved subtrees */
@@ -134,7 +134,8 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp, float spl
             uint32_t cur = parent[n - 1 + k];
             while (cur != 0xFFFFFFFFu) {
                 if (flags[cur]++ == 0) break;
-                refit_visit(mem, n, cur, use_dp, use_dp && pass == passes - 1);
+                if (treelet_passes > 0) treelet_visit(mem, n, cur, use_dp && pass == passes - 1);
+                else refit_visit(mem, n, cur, use_dp, use_dp && pass == passes - 1);
                 cur = parent[cur];
             }
         }
@@ -161,6 +162,7 @@ EmuBvh* emu_build(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, 
 EmuBvh* emu_build_dp(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, true); }
 EmuBvh* emu_build_ploc(const float* tris9, uint32_t n, int use_dp, uint32_t radius) { return build_lbvh(tris9, n, use_dp != 0, 0.0f, radius); }
 uint32_t emu_ploc_rounds(const EmuBvh* b) { return b->ploc_rounds; }
+EmuBvh* emu_build_treelet(const float* tris9, uint32_t n, int passes) { return build_lbvh(tris9, n, true, 0.0f, 0, passes); }
 EmuBvh* emu_build_split(const float* tris9, uint32_t n, int use_dp, float beta) { return build_lbvh(tris9, n, use_dp != 0, beta); }
 /* wrap an acceleration structure built elsewhere (downloaded from the GPU) so that it can be traversed here */
 EmuBvh* emu_wrap(const uint32_t* nodes20, uint32_t n_nodes, const uint32_t* tris12, uint32_t n_tris) {

@@ -19,8 +19,9 @@ def lib():
         src = os.path.join(_HERE, "emu", "emu.cpp")
         hdr = os.path.join(_HERE, "..", "raytracer3_b200", "csrc", "bvh_logic.h")
         if not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
-            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas",
-                                   "-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", _SO, src])
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas"]
+                                  + os.environ.get("RT3_EMU_DEFINES", "").split()          # experiments only (e.g. -DRT3_TREELET_LEAVES=9)
+                                  + ["-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", _SO, src])
         L = C.CDLL(_SO)
         L.emu_build.restype = C.c_void_p
         L.emu_build.argtypes = [C.c_void_p, C.c_uint32]
@@ -28,6 +29,8 @@ def lib():
         L.emu_build_dp.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_build_split.restype = C.c_void_p
         L.emu_build_split.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_float]
+        L.emu_build_treelet.restype = C.c_void_p
+        L.emu_build_treelet.argtypes = [C.c_void_p, C.c_uint32, C.c_int]
         L.emu_build_ploc.restype = C.c_void_p
         L.emu_build_ploc.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_uint32]
         L.emu_ploc_rounds.restype = C.c_uint32
@@ -70,13 +73,15 @@ def warp_lib(balance=False, defines=()):
 
 
 class EmuBvh:
-    def __init__(self, tris=None, nodes=None, tri_records=None, optimal_collapse=True, split_beta=0.0, ploc_radius=0):
+    def __init__(self, tris=None, nodes=None, tri_records=None, optimal_collapse=True, split_beta=0.0, ploc_radius=0, treelet_passes=0):
         """optimal_collapse: children of the wide nodes by the cost dynamic programme (the device default) or greedily (RT3_BUILD_FAST_BUILD);
         split_beta > 0: triangle splitting with a budget of split_beta x triangles extra references (RT3_BUILD_SPLIT)"""
         self.L = lib()
         if tris is not None:
             t = np.ascontiguousarray(tris, np.float32)
-            if ploc_radius > 0:
+            if treelet_passes > 0:
+                self.h = self.L.emu_build_treelet(ptr(t), len(t), treelet_passes)
+            elif ploc_radius > 0:
                 self.h = self.L.emu_build_ploc(ptr(t), len(t), 1 if optimal_collapse else 0, ploc_radius)
             elif split_beta > 0:
                 self.h = self.L.emu_build_split(ptr(t), len(t), 1 if optimal_collapse else 0, split_beta)

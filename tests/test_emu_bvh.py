@@ -81,8 +81,9 @@ def test_axis_parallel_rays_and_flat_boxes():
 
 @pytest.mark.parametrize("name", ["cornell", "soup", "atrium"])
 def test_alternative_topologies_find_the_same_hits(name):
-    """Builder experiments kept in bvh_logic.h (neither is in the device build): PLOC instead of the Karras hierarchy,
-    and triangle splitting (several references with clipped boxes per triangle).  Topology must never change a hit."""
+    """Other topologies from bvh_logic.h: treelet restructuring (RT3_BUILD_TREELET, opt-in on the device), and two experiments that are not
+    in the device build: PLOC instead of the Karras hierarchy, triangle splitting (several references with clipped boxes
+    per triangle).  Topology must never change a hit."""
     sc = CASES[name]()
     T = np.ascontiguousarray(scenes.world_triangles(sc), np.float32)
     c, a = scenes.incoherent_rays(sc, 2000, seed=41, tris=T.astype(np.float64))
@@ -90,11 +91,13 @@ def test_alternative_topologies_find_the_same_hits(name):
     base = EmuBvh(tris=T)
     want, _ = base.trace_closest(rays, brute=True)
     want_any = base.trace_any(a, brute=True)
-    for kw in (dict(ploc_radius=4), dict(ploc_radius=25), dict(split_beta=0.5), dict(split_beta=4.0)):
+    for kw in (dict(treelet_passes=1), dict(treelet_passes=2), dict(ploc_radius=4), dict(ploc_radius=25), dict(split_beta=0.5), dict(split_beta=4.0)):
         b = EmuBvh(tris=T, **kw)
         info = b.info()
         assert b.check_triangles() == 0 and info["levels"] < 64
-        if "ploc_radius" in kw:
+        if "treelet_passes" in kw:
+            assert info["tris"] == len(T)
+        elif "ploc_radius" in kw:
             assert info["tris"] == len(T) and 1 <= b.ploc_rounds() < 200
         else:
             assert len(T) <= info["tris"] <= len(T) * (1 + kw["split_beta"]) + 1        # the split budget bounds the extra references
@@ -113,9 +116,25 @@ def test_ploc_and_split_degenerate_inputs():
     rays["tmax"] = 10
     for T in (np.repeat(tri, 37, 0), tri, np.concatenate([tri, np.zeros((5, 3, 3), np.float32)]),
               np.concatenate([tri, tri * 1000.0 + 5.0])):                              # identical, single, zero-area, one huge + one small
-        for kw in (dict(ploc_radius=3), dict(split_beta=8.0)):
+        for kw in (dict(treelet_passes=2), dict(ploc_radius=3), dict(split_beta=8.0)):
             b = EmuBvh(tris=T, **kw)
             assert b.check_triangles() == 0
             got, _ = b.trace_closest(rays)
             want, _ = b.trace_closest(rays, brute=True)
             assert (got == want).all() and (got["prim"] == 0).all()
+
+
+def test_treelet_restructuring_beats_rotations():
+    """RT3_BUILD_TREELET (treelet_visit) against the default rotations (refit_visit) on the same Karras hierarchy: same hits, less work."""
+    sc = scenes.synthetic_atrium(0.05, environment=False)
+    T = np.ascontiguousarray(scenes.world_triangles(sc), np.float32)
+    c, _ = scenes.incoherent_rays(sc, 4000, seed=5, tris=T.astype(np.float64))
+    rot, tre = EmuBvh(tris=T), EmuBvh(tris=T, treelet_passes=2)
+    hr, sr = rot.trace_closest(c)
+    ht, stt = tre.trace_closest(c)
+    assert (hr == ht).all()
+    assert stt[0] + 0.4 * stt[1] < 0.99 * (sr[0] + 0.4 * sr[1])
+    assert tre.info()["sah_nodes"] < rot.info()["sah_nodes"]
+    tiny = np.array([[[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[2, 0, 0], [3, 0, 0], [2, 1, 0]], [[0, 2, 0], [1, 2, 0], [0, 3, 0]]], np.float32)
+    for k in (1, 2, 3):                                                    # treelets smaller than 7 leaves
+        assert EmuBvh(tris=tiny[:k], treelet_passes=2).check_triangles() == 0

@@ -1,6 +1,6 @@
 """Traversal work per incoherent ray in the CPU emulator of the device builder / traversal (tests/emu), for builder variants.
 Work = node visits + 0.4 x triangle tests (the cost ratio measured on B200).  No GPU needed:
-    python tools/emu_topology.py [detail] [rays] [lbvh,split:BETA,ploc:RADIUS,...]"""
+    python tools/emu_topology.py [detail] [rays] [lbvh,split:BETA,ploc:RADIUS,treelet:PASSES,...]"""
 import os
 import sys
 import time
@@ -25,7 +25,8 @@ def main():
     for var in variants:
         kind, _, arg = var.partition(":")
         t0 = time.time()
-        b = EmuBvh(tris=T, split_beta=float(arg) if kind == "split" else 0.0, ploc_radius=int(arg) if kind == "ploc" else 0)
+        b = EmuBvh(tris=T, split_beta=float(arg) if kind == "split" else 0.0, ploc_radius=int(arg) if kind == "ploc" else 0,
+                   treelet_passes=int(arg) if kind == "treelet" else 0)
         tb = time.time() - t0
         info = b.info()
         hits, st = b.trace_closest(c)
