@@ -162,6 +162,9 @@ EmuBvh* emu_build(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, 
 EmuBvh* emu_build_dp(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, true); }
 EmuBvh* emu_build_ploc(const float* tris9, uint32_t n, int use_dp, uint32_t radius) { return build_lbvh(tris9, n, use_dp != 0, 0.0f, radius); }
 uint32_t emu_ploc_rounds(const EmuBvh* b) { return b->ploc_rounds; }
+EmuBvh* emu_build_ex(const float* tris9, uint32_t n, int use_dp, float split_beta, uint32_t ploc_radius, int treelet_passes) {
+    return build_lbvh(tris9, n, use_dp != 0, split_beta, ploc_radius, treelet_passes);
+}
 EmuBvh* emu_build_treelet(const float* tris9, uint32_t n, int passes) { return build_lbvh(tris9, n, true, 0.0f, 0, passes); }
 EmuBvh* emu_build_split(const float* tris9, uint32_t n, int use_dp, float beta) { return build_lbvh(tris9, n, use_dp != 0, beta); }
 /* wrap an acceleration structure built elsewhere (downloaded from the GPU) so that it can be traversed here */

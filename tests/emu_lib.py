@@ -29,6 +29,8 @@ def lib():
         L.emu_build_dp.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_build_split.restype = C.c_void_p
         L.emu_build_split.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_float]
+        L.emu_build_ex.restype = C.c_void_p
+        L.emu_build_ex.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_float, C.c_uint32, C.c_int]
         L.emu_build_treelet.restype = C.c_void_p
         L.emu_build_treelet.argtypes = [C.c_void_p, C.c_uint32, C.c_int]
         L.emu_build_ploc.restype = C.c_void_p
@@ -79,7 +81,9 @@ class EmuBvh:
         self.L = lib()
         if tris is not None:
             t = np.ascontiguousarray(tris, np.float32)
-            if treelet_passes > 0:
+            if (treelet_passes > 0) + (ploc_radius > 0) + (split_beta > 0) > 1:                  # combinations (experiments)
+                self.h = self.L.emu_build_ex(ptr(t), len(t), 1 if optimal_collapse else 0, split_beta, ploc_radius, treelet_passes)
+            elif treelet_passes > 0:
                 self.h = self.L.emu_build_treelet(ptr(t), len(t), treelet_passes)
             elif ploc_radius > 0:
                 self.h = self.L.emu_build_ploc(ptr(t), len(t), 1 if optimal_collapse else 0, ploc_radius)

@@ -23,10 +23,17 @@ def main():
     c, a = scenes.incoherent_rays(sc, n_rays, seed=0x5EED0004, tris=T.astype(np.float64))
     base = None
     for var in variants:
-        kind, _, arg = var.partition(":")
+        opts = dict(split_beta=0.0, ploc_radius=0, treelet_passes=0)
+        for part in var.split("+"):                                     # e.g. ploc:4+treelet:2
+            kind, _, arg = part.partition(":")
+            if kind == "split":
+                opts["split_beta"] = float(arg)
+            elif kind == "ploc":
+                opts["ploc_radius"] = int(arg)
+            elif kind == "treelet":
+                opts["treelet_passes"] = int(arg)
         t0 = time.time()
-        b = EmuBvh(tris=T, split_beta=float(arg) if kind == "split" else 0.0, ploc_radius=int(arg) if kind == "ploc" else 0,
-                   treelet_passes=int(arg) if kind == "treelet" else 0)
+        b = EmuBvh(tris=T, **opts)
         tb = time.time() - t0
         info = b.info()
         hits, st = b.trace_closest(c)
@@ -34,7 +41,7 @@ def main():
             base = hits
         same = bool((hits == base).all())
         work = st[0] + 0.4 * st[1]
-        print(f"{var:10s} rounds={b.ploc_rounds():3d} tris={len(T)} refs={info['tris']} (+{info['tris'] / len(T) - 1:.1%}) wide_nodes={info['nodes']} "
+        print(f"{var:22s} rounds={b.ploc_rounds():3d} tris={len(T)} refs={info['tris']} (+{info['tris'] / len(T) - 1:.1%}) wide_nodes={info['nodes']} "
               f"nodes/ray={st[0]:.3f} tris/ray={st[1]:.3f} work={work:.3f} sah_nodes={info['sah_nodes']:.0f} sah_tris={info['sah_tris']:.0f} hits_identical={same} build_s={tb:.1f}", flush=True)
 
 
