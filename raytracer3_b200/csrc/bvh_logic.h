@@ -593,13 +593,13 @@ RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
         uint32_t st[K]; int sp = 0, next_inner = 1;
         st[sp++] = full; t_id[0] = cur;
         /* pre-order with explicit stack; ids handed out in visit order (inner_id[0] = cur is the root) */
-        int idx_of_set[1 << K];
+        uint8_t idx_of_set[1 << K];
         while (sp) {
             const uint32_t sset = st[--sp];
             const int me = t_n++;
             t_set[me] = sset;
             if (me > 0) t_id[me] = inner_id[next_inner++];
-            idx_of_set[sset] = me;
+            idx_of_set[sset] = (uint8_t)me;
             const uint32_t pl = part[sset], pr = sset ^ pl;
             t_l[me] = (uint16_t)pl; t_r[me] = (uint16_t)pr;
             if (pr & (pr - 1u)) st[sp++] = pr;
