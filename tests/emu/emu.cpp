@@ -10,7 +10,7 @@
 #include <cstring>
 #include <numeric>
 #include <vector>
-#include "../../raytracer3_b200/csrc/bvh_logic.h"
+#include "bvh_experiments.h"
 
 using namespace rt3b;
 

@@ -18,7 +18,8 @@ def lib():
     if _lib is None:
         src = os.path.join(_HERE, "emu", "emu.cpp")
         hdr = os.path.join(_HERE, "..", "raytracer3_b200", "csrc", "bvh_logic.h")
-        if not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        hdr2 = os.path.join(_HERE, "emu", "bvh_experiments.h")
+        if not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(src), os.path.getmtime(hdr), os.path.getmtime(hdr2)):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas"]
                                   + os.environ.get("RT3_EMU_DEFINES", "").split()          # experiments only (e.g. -DRT3_TREELET_LEAVES=9)
                                   + ["-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", _SO, src])

@@ -81,7 +81,7 @@ def test_axis_parallel_rays_and_flat_boxes():
 
 @pytest.mark.parametrize("name", ["cornell", "soup", "atrium"])
 def test_alternative_topologies_find_the_same_hits(name):
-    """Other topologies from bvh_logic.h: treelet restructuring (RT3_BUILD_TREELET, opt-in on the device), and two experiments that are not
+    """Other topologies: treelet restructuring (bvh_logic.h, RT3_BUILD_TREELET, opt-in on the device), and two experiments (tests/emu/bvh_experiments.h) that are not
     in the device build: PLOC instead of the Karras hierarchy, triangle splitting (several references with clipped boxes
     per triangle).  Topology must never change a hit."""
     sc = CASES[name]()
