@@ -14,14 +14,6 @@ from raytracer3_b200.types import MISS
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not os.environ.get("RT3_TEST_UNVERIFIED"), reason="not yet run on hardware; set RT3_TEST_UNVERIFIED=1")]
 
 
-@pytest.fixture(scope="module")
-def gpu_ctx():
-    from raytracer3_b200.host import RenderContext
-    ctx = RenderContext(0)
-    yield ctx
-    ctx.close()
-
-
 def test_treelet_build_gives_identical_hits_and_the_emulators_tree(gpu_ctx):
     """RT3_BUILD_TREELET: same hits bit for bit as the default build, every triangle kept once, and exactly the tree the CPU emulation of
     the builder produces (node count and visit statistics), with less traversal work than the rotations."""
