@@ -29,6 +29,9 @@ HBM_BYTES_PER_RAY = 48          # 32 B rt3_ray read + 16 B rt3_hit written (SURV
 # `ncu --set full` capture; algorithmic bytes of that launch = 48 B x 1.8 M = 86 MB
 NCU_TRACE_DRAM_BYTES_PER_LAUNCH = (82.71e6 + 76.04e6 + 70.74e6 + 13.64e6 + 8.22e6 + 6.65e6) / 3
 NCU_TRACE_DRAM_SOURCE = "profiles/r1j_k_trace_dyn_summary.txt (ncu --set full, mean of the frame's 3 launches: 76.5 MB read + 9.5 MB written)"
+# smsp__inst_executed.sum of the frame's three k_trace_dyn<closest> launches in the same capture (439.6 M + 378.4 M + 335.1 M warp instructions)
+# over the 5.40 M rays they traced: the instruction-issue view of the kernel (148 SMs x 4 schedulers x 1 warp instruction per clock)
+NCU_TRACE_WARP_INST_PER_RAY = (439578051 + 378415418 + 335107758) / (3 * 1.7993e6)
 FALLBACK_HBM_GBS = 6650.0       # /opt/skills/guides/B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 
 
@@ -390,6 +393,16 @@ def run_cuda(args):
                          "kernel_share_of_step": t_ms / ms if ms > 0 else None,
                          "note": "traversal is L2-latency/issue bound, not HBM bound: the BVH is L2-resident, HBM only streams 48 B per ray (see roofline_l2)"},
         }
+        try:    # supplementary: the bound the traversal kernel actually runs against; never allowed to break the line
+            sm_mhz = float((line["clocks"] or {}).get("sm_mhz") or 1965.0)
+            issue_peak = 148 * 4 * sm_mhz * 1e6 / 1e9                                   # G warp instructions / s
+            issue_ach = NCU_TRACE_WARP_INST_PER_RAY * (t_rays / (t_ms * 1e-3)) / 1e9 if t_ms > 0 else None
+            line["roofline_issue"] = {"kernel": "k_trace<closest> (secondary-ray queues)", "bound": "warp-instruction issue", "achieved": issue_ach, "peak": issue_peak,
+                                      "unit": "G warp-inst/s", "frac": issue_ach / issue_peak if issue_ach else None, "warp_inst_per_ray": NCU_TRACE_WARP_INST_PER_RAY,
+                                      "source": "instructions per ray from " + NCU_TRACE_DRAM_SOURCE.split(" (")[0] + " (smsp__inst_executed.sum), rays/s measured live; "
+                                                "18.6 of 32 lanes active per instruction in that capture"}
+        except Exception:  # noqa: BLE001
+            pass
         if not args.no_extras:
             line.update(extras(ctx, world, sc, bs, t_rays / (t_ms * 1e-3) if t_ms > 0 else 0.0))
             line["cpu_baseline"] = cpu_baseline(sc, flags)
