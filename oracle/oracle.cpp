@@ -394,6 +394,11 @@ void orc_pass_gbuffer(const orc_scene* s, const rt3_params* p, rt3_rect rc, uint
     });
 }
 
+/* Optional capture of the secondary rays of orc_pass_reference (for tools/emu_warp_stats.py --frame: the warp emulation of the product's
+ * traversal kernel is then fed the frame's own bounce rays): rays[b * pixels + px] = the ray traced after loop index b, valid[...] = 1. */
+static rt3_ray* g_cap_rays = nullptr; static uint8_t* g_cap_valid = nullptr; static uint64_t g_cap_pixels = 0; static uint32_t g_cap_bounces = 0;
+void orc_set_ray_capture(rt3_ray* rays, uint8_t* valid, uint64_t pixels, uint32_t bounces) { g_cap_rays = rays; g_cap_valid = valid; g_cap_pixels = pixels; g_cap_bounces = bounces; }
+
 /* shaders/old/refrence_mode.slang:14-66 */
 void orc_pass_reference(const orc_scene* s, const rt3_params* p, rt3_rect rc, const uint32_t* gbuffer, const float* depth, const float* prev_light,
                         float* light, int threads, rt3_counters* opt_counters) {
@@ -445,6 +450,7 @@ void orc_pass_reference(const orc_scene* s, const rt3_params* p, rt3_rect rc, co
                         }
                         if (b != p->bounces - 1) {                                      /* :53-56 */
                             rt3_hit h = closest_bvh(*s, make_ray(ro, rd, tmin, tmax));
+                            if (g_cap_rays && b < g_cap_bounces && px < g_cap_pixels) { g_cap_rays[b * g_cap_pixels + px] = make_ray(ro, rd, tmin, tmax); g_cap_valid[b * g_cap_pixels + px] = 1; }
                             secondary++;
                             if (h.prim == RT3_MISS) { missed = true; escaped++; }
                             else { surface = hit_info(sv, h.prim, h.u, h.v); hit_t = h.t; }

@@ -43,6 +43,7 @@ void orc_trace_any(const orc_scene*, const rt3_ray* rays, uint64_t n, uint32_t* 
 
 void orc_pass_gbuffer(const orc_scene*, const rt3_params*, rt3_rect, uint32_t* gbuffer, float* depth, uint32_t* opt_ids, float* opt_bary,
                       int threads);
+void orc_set_ray_capture(rt3_ray* rays, uint8_t* valid, uint64_t pixels, uint32_t bounces);   /* see oracle.cpp; NULL switches it off */
 void orc_pass_reference(const orc_scene*, const rt3_params*, rt3_rect, const uint32_t* gbuffer, const float* depth, const float* prev_light,
                         float* light, int threads, rt3_counters* opt_counters);
 void orc_pass_postprocess(const orc_scene*, const rt3_params*, rt3_rect, const float* depth, const float* in, float* out, int threads);

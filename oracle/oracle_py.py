@@ -50,6 +50,7 @@ def lib():
         L.orc_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int, C.c_int]
         L.orc_trace_any.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int, C.c_int]
         L.orc_pass_gbuffer.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_set_ray_capture.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]
         L.orc_pass_reference.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_pass_postprocess.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_probe_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]

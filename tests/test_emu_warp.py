@@ -77,3 +77,30 @@ def test_degenerate_scene_and_rays():
         assert (got == want).all()
         if len(T):
             assert (got["prim"][1::3] == 0).all() and (got["prim"][::3] == MISS).all()
+
+
+def test_kernel_on_the_frames_own_bounce_rays():
+    """The oracle can hand out the secondary rays of a frame (orc_set_ray_capture); the production kernel must answer them like brute force,
+    and there must be exactly as many as the oracle counts."""
+    from oracle.oracle_py import OracleScene
+    from raytracer3_b200.camera import camera_for, make_params
+    from raytracer3_b200.types import ptr
+    sc = scenes.synthetic_atrium(0.02)
+    sc["bluenoise"] = scenes.blue_noise_tile(64)
+    W, H = 64, 36
+    orc = OracleScene(sc)
+    p = make_params(camera_for(sc, "cam0", W, H), W, H, frame=1, bounces=4, samples=1, flags=3)
+    gb, dp, _, _ = orc.pass_gbuffer(p)
+    rays, valid = np.zeros((3, W * H), RAY), np.zeros((3, W * H), np.uint8)
+    orc.L.orc_set_ray_capture(ptr(rays), ptr(valid), W * H, 3)
+    try:
+        _, cnt = orc.pass_reference(p, gb, dp)
+    finally:
+        orc.L.orc_set_ray_capture(None, None, 0, 0)
+    assert int(valid.sum()) == cnt.rays_secondary and (valid.sum(1)[:-1] >= valid.sum(1)[1:]).all()      # queues only shrink from bounce to bounce
+    queue = np.ascontiguousarray(rays[valid != 0])
+    b = EmuBvh(tris=np.ascontiguousarray(scenes.world_triangles(sc), np.float32))
+    want, _ = b.trace_closest(queue, brute=True)
+    for defines in ((), ("RT3_TRI_WAIT=8",)):
+        got, _ = b.kernel_trace(queue, defines=defines)
+        assert (got == want).all()

@@ -11,4 +11,5 @@ python -c "import __graft_entry__ as g; g.build()"
 echo "== unverified GPU tests"; RT3_TEST_UNVERIFIED=1 python -m pytest tests/test_gpu_unverified.py -m gpu -x -q 2>&1 | tail -3
 echo "== default";              python bench.py --steps 30 --warmup 5 2>&1 | line
 echo "== RT3_FORCE_TREELET=1";  RT3_FORCE_TREELET=1 python bench.py --steps 30 --warmup 5 2>&1 | line
-bash tools/exp.sh "-DRT3_TRI_WAIT=8" "-DRT3_TRI_BALANCE=1 -DRT3_TRACE_MIN_BLOCKS=8" "-DRT3_TRI_BALANCE=1 -DRT3_TRI_WAIT=16 -DRT3_TRACE_MIN_BLOCKS=8" "-DRT3_SHADE_MIN_BLOCKS=5" "-DRT3_SHADE_MIN_BLOCKS=6"
+bash tools/exp.sh "-DRT3_TRI_WAIT=8" "-DRT3_TRI_WAIT=6" "-DRT3_TRI_WAIT=10" "-DRT3_TRI_BALANCE=1 -DRT3_TRI_WAIT=16 -DRT3_TRACE_MIN_BLOCKS=8" "-DRT3_SHADE_MIN_BLOCKS=5" "-DRT3_SHADE_MIN_BLOCKS=6"
+echo "== RT3_TRI_WAIT=8 + treelet"; RT3_NVCC_EXTRA="-DRT3_TRI_WAIT=8" python -c "from raytracer3_b200 import build as b; b.build(force=True)"; RT3_FORCE_TREELET=1 python bench.py --steps 30 --warmup 5 2>&1 | line
