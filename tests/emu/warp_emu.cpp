@@ -163,15 +163,18 @@ struct LaunchArgs {
 };
 static LaunchArgs g_args;
 
+#ifndef RT3_EMU_KEEP
+#define RT3_EMU_KEEP 28          /* the product's KEEP (launch_dyn in trace.cu); other values for tools/emu_warp_stats.py experiments */
+#endif
 static void fiber_main() {
     const LaunchArgs& a = g_args;
     if (a.any == 2) k_static(a.nodes, a.tris, a.rays, a.n, a.hits, a.work_counter);
     else if (a.any) {
-        if (a.two) k_trace_dyn<true, 28, true>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
-        else k_trace_dyn<true, 28, false>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
+        if (a.two) k_trace_dyn<true, RT3_EMU_KEEP, true>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
+        else k_trace_dyn<true, RT3_EMU_KEEP, false>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
     } else {
-        if (a.two) k_trace_dyn<false, 28, true>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
-        else k_trace_dyn<false, 28, false>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
+        if (a.two) k_trace_dyn<false, RT3_EMU_KEEP, true>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
+        else k_trace_dyn<false, RT3_EMU_KEEP, false>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
     }
     g_cur->done = true;
     g_cur->warp->live--;
