@@ -372,11 +372,27 @@ RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
     const uint32_t full = (1u << nl) - 1u;
     float area[1 << K], copt[1 << K];
     uint16_t part[1 << K];
-    for (uint32_t sset = 1; sset <= full; ++sset) {
-        float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
-        for (int k = 0; k < nl; ++k) if (sset & (1u << k)) for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(lo[q], leaf_box[k].lo[q]); hi[q] = rt3m::max_(hi[q], leaf_box[k].hi[q]); }
-        area[sset] = box_area(lo, hi);
-        copt[sset] = 0.0f; part[sset] = 0;
+    /* box of a subset = union of the boxes of its members in the low three and in the remaining places: 8 + 2^(K-3) partial unions,
+     * then one union per subset (min / max are exact, so the order of the unions does not matter) */
+    {
+        const int KH = K > 3 ? K - 3 : 0;
+        float plo[8][3], phi[8][3], qlo[1 << KH][3], qhi[1 << KH][3];
+        for (int g = 0; g < 2; ++g) {
+            const int first = g ? 3 : 0, cnt = g ? KH : 3;
+            for (uint32_t sub = 0; sub < (1u << cnt); ++sub) {
+                float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+                for (int k = 0; k < cnt; ++k)
+                    if ((sub & (1u << k)) && first + k < nl)
+                        for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(lo[q], leaf_box[first + k].lo[q]); hi[q] = rt3m::max_(hi[q], leaf_box[first + k].hi[q]); }
+                for (int q = 0; q < 3; ++q) { if (g) { qlo[sub][q] = lo[q]; qhi[sub][q] = hi[q]; } else { plo[sub][q] = lo[q]; phi[sub][q] = hi[q]; } }
+            }
+        }
+        for (uint32_t sset = 1; sset <= full; ++sset) {
+            float lo[3], hi[3];
+            for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(plo[sset & 7u][q], qlo[sset >> 3][q]); hi[q] = rt3m::max_(phi[sset & 7u][q], qhi[sset >> 3][q]); }
+            area[sset] = box_area(lo, hi);
+            copt[sset] = 0.0f; part[sset] = 0;
+        }
     }
     /* subsets in increasing numeric order: every proper subset of S is smaller than S, so its copt is final when S is reached */
     for (uint32_t sset = 3; sset <= full; ++sset) {
