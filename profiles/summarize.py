@@ -1,4 +1,4 @@
-"""Summaries of ncu outputs: `python profiles/summarize.py launches <csv>` or `... raw <ncu-rep> [kernel-substring]`."""
+"""Summaries of ncu outputs: `python profiles/summarize.py launches <csv>`, `... raw <ncu-rep> [kernel-substring]` or `... source <ncu-rep> [kernel-substring]`."""
 import collections
 import csv
 import subprocess
@@ -50,8 +50,41 @@ def raw(path, sub=None):
             print(f"{k:80s} {units[i]:14s}", [r[i] for r in data])
 
 
+def source(path, sub=None, top=40):
+    """`... source <ncu-rep> [kernel-substring]`: executed warp instructions per SOURCE LINE of the first matching kernel (needs -lineinfo and
+    `--import-source on`), heaviest lines first — where a kernel spends its instructions, e.g. the attribute half of k_gbuffer."""
+    hdr = rows = None
+    for extra in (['--print-source', 'cuda'], []):                 # CUDA-C lines if the report carries the source, else SASS lines
+        args = ['ncu', '-i', path, '--page', 'source', '--csv'] + extra + (['-k', 'regex:' + sub] if sub else [])
+        out = subprocess.run(args, capture_output=True, text=True).stdout
+        rows = [r for r in csv.reader(out.splitlines()) if len(r) > 3]
+        hdr = next((r for r in rows if any(c.strip() == 'Source' for c in r) and any('Instructions Executed' in c for c in r)), None)
+        if hdr is not None:
+            break
+    if hdr is None:
+        print('no source page in', path, '(column names differ? look at: ncu -i', path, '--page source --csv | head)')
+        return
+    si = next(i for i, c in enumerate(hdr) if c.strip() == 'Source')
+    ii = next((i for i, c in enumerate(hdr) if c.strip() == 'Instructions Executed'), None)
+    if ii is None:
+        ii = next(i for i, c in enumerate(hdr) if 'Instructions Executed' in c)
+    agg = collections.defaultdict(float)
+    for r in rows[rows.index(hdr) + 1:]:
+        try:
+            agg[r[si].strip()[:150]] += float(r[ii].replace(',', ''))
+        except (ValueError, IndexError):
+            continue
+    tot = sum(agg.values()) or 1.0
+    print(f"# {path} {sub or ''}: {tot / 1e6:.1f} M warp instructions")
+    for k, v in sorted(agg.items(), key=lambda kv: -kv[1])[:top]:
+        print(f"{100 * v / tot:5.1f}%  {k}")
+
+
 if __name__ == '__main__':
     if sys.argv[1] == 'launches':
         launches(sys.argv[2])
+    elif sys.argv[1] == 'source':
+        source(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
     else:
         raw(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
+
