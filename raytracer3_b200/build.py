@@ -7,7 +7,7 @@ CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(HERE, "..", "include")
 SO = os.path.join(HERE, "librt3.so")
 SOURCES = ["api.cu", "build.cu", "trace.cu", "passes.cu"]
-HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "bvh_logic.h"), os.path.join(CSRC, "trace_kernel.cuh"), os.path.join(INCLUDE, "rt3.h"),
+HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "bvh_logic.h"), os.path.join(CSRC, "trace_kernel.cuh"), os.path.join(CSRC, "pass_kernels.cuh"), os.path.join(CSRC, "pass_types.h"), os.path.join(INCLUDE, "rt3.h"),
            os.path.join(INCLUDE, "rt3_shared_math.h")]
 
 # -fmad=false: the determinism contract of include/rt3_shared_math.h (explicit fmaf still compiles to FFMA).

@@ -54,21 +54,8 @@ struct Scratch {
 struct InstanceRec { uint32_t first_geometry, geometry_count; float xform[12]; };
 struct TextureRec { uint8_t* data = nullptr; uint32_t w = 0, h = 0; };
 
-/* Pixel work list: one or many rects, frame-pitch or tile-slab addressing (see rt3.h). */
-struct PixelMap {
-    rt3_rect single;          /* used when n_tiles == 1          */
-    const rt3_rect* rects;    /* device array when n_tiles > 1   */
-    uint32_t n_tiles;
-    uint32_t tile_w, tile_h;  /* max rect size; slab stride      */
-    uint32_t bw, bh;          /* 8x4-pixel blocks per tile       */
-    uint32_t pitch;           /* frame width (frame addressing)  */
-    uint32_t slab;            /* 1 = tile-major slab addressing  */
-    uint32_t work;            /* n_tiles * bw * bh * 32          */
-};
+#include "pass_types.h"
 
-struct DeviceCounters {
-    unsigned long long rays_primary, rays_secondary, rays_shadow, paths_started, paths_escaped;
-};
 
 struct rt3_context {
     int device = 0;
@@ -143,20 +130,6 @@ static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1
         (ctx)->launches++;                                                              \
         RT3_CUDA(ctx, cudaGetLastError());                                              \
     } while (0)
-
-/* work index -> pixel.  Returns false for padding lanes. */
-__device__ __forceinline__ bool pixel_of(const PixelMap& m, uint32_t idx, uint32_t& x, uint32_t& y, size_t& out_index) {
-    const uint32_t per_tile = m.bw * m.bh * 32u;
-    const uint32_t k = idx / per_tile, rem = idx - k * per_tile;
-    const uint32_t blk = rem >> 5, lane = rem & 31u;
-    const uint32_t lx = (blk % m.bw) * 8u + (lane & 7u), ly = (blk / m.bw) * 4u + (lane >> 3);
-    rt3_rect r;
-    if (m.n_tiles == 1) r = m.single; else r = m.rects[k];
-    if (lx >= r.w || ly >= r.h) return false;
-    x = r.x0 + lx; y = r.y0 + ly;
-    out_index = m.slab ? ((size_t)k * m.tile_w * m.tile_h + (size_t)ly * m.tile_w + lx) : ((size_t)y * m.pitch + x);
-    return true;
-}
 
 /* implemented in build.cu / trace.cu / passes.cu */
 void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out);

@@ -1,133 +1,9 @@
 /*
- * warp_emu.cpp — TEST INFRASTRUCTURE: runs the production traversal kernel (raytracer3_b200/csrc/trace_kernel.cuh, the very source
- * nvcc compiles into librt3.so) on the CPU over a lock-step warp emulation, so the `-m "not gpu"` suite can check the kernel's control
- * flow — dynamic ray fetch, the two-phase loop, the stack protocol, the optional warp-balanced record phase — against a brute-force
- * loop on a machine without a GPU.  It is not a fallback: librt3.so neither contains nor calls this code.
- *
- * Model: one CUDA block = 4 warps x 32 lanes, every lane a fiber (ucontext) running the kernel function on its own stack.  A warp
- * collective (__ballot_sync, __shfl_sync, __shfl_up_sync, __syncwarp — always with the full mask in this kernel) is a rendezvous: the lane
- * deposits its operand and yields until all 32 lanes of its warp have arrived; a lane that returns from the kernel while its warp
- * waits at a collective is reported as a divergence error (on hardware that is a hang).  Fibers are resumed round-robin over all
- * lanes of all warps of the block, so warps interleave at collective granularity and share the global work counter like resident
- * warps do; blocks run one after the other.  __shared__ becomes a static array (one block at a time), atomics are plain operations
- * (one OS thread).  Arithmetic goes through the host branches of bvh_logic.h / rt3_shared_math.h, which the determinism contract
- * makes bit-identical to the device branches.
+ * warp_emu.cpp — TEST INFRASTRUCTURE: the production traversal kernel (raytracer3_b200/csrc/trace_kernel.cuh) on the CPU warp emulation of
+ * warp_emu.h, compared with brute force by tests/test_emu_warp.py; phase statistics for tools/emu_warp_stats.py.  Not a fallback:
+ * librt3.so neither contains nor calls this code.
  */
-#include <ucontext.h>
-
-#include <cstdint>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <vector>
-
-#define RT3_WARP_EMU 1
-static inline uint32_t __ballot_sync(uint32_t mask, bool pred);
-struct EmuThreadIdx { unsigned x; };
-static EmuThreadIdx threadIdx;       /* set by the scheduler whenever a fiber is resumed */
-/* phase statistics: [id][0] = times a warp ran the phase with at least one lane, [id][1] = lanes that took part, [id][2] = times reached */
-static uint64_t g_phase[8][3];
-#define RT3_EMU_PHASE(id, pred) do { const uint32_t m_ = __ballot_sync(0xFFFFFFFFu, (pred)); if ((threadIdx.x & 31u) == 0u) { g_phase[id][0] += m_ != 0u; g_phase[id][1] += (uint64_t)__builtin_popcount(m_); g_phase[id][2]++; } } while (0)
-#include "../../raytracer3_b200/csrc/bvh_logic.h"
-
-/* ------------------------------------------------------------------ CUDA surface used by trace_kernel.cuh ---------------- */
-struct float4 { float x, y, z, w; };
-struct uint2 { uint32_t x, y; };
-static inline float4 make_float4(float x, float y, float z, float w) { float4 r = {x, y, z, w}; return r; }
-static inline uint2 make_uint2(uint32_t x, uint32_t y) { uint2 r = {x, y}; return r; }
-#define __global__
-#define __device__
-#define __forceinline__ inline
-#define __launch_bounds__(...)
-#define __shared__ static
-static inline float4 __ldcs(const float4* p) { return *p; }
-static inline void __stcs(float4* p, float4 v) { *p = v; }
-static inline float __uint_as_float(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
-static inline uint32_t __float_as_uint(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
-static inline int __popc(uint32_t x) { return __builtin_popcount(x); }
-static inline int __ffs(uint32_t x) { return __builtin_ffs((int)x); }
-static inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { unsigned long long o = *p; *p += v; return o; }
-static inline uint32_t atomicOr(uint32_t* p, uint32_t v) { uint32_t o = *p; *p |= v; return o; }
-
-namespace wemu {
-
-constexpr int LANES = 32;
-constexpr size_t FIBER_STACK = 256 * 1024;
-
-struct Warp {
-    uint64_t slot[2][LANES];
-    uint64_t slot_gen[2] = {~0ull, ~0ull};
-    int kind[2] = {0, 0};
-    int arrived[2] = {0, 0};
-    uint64_t lane_gen[LANES];
-    int live = LANES;                 /* lanes that have not returned from the kernel */
-    int waiting = 0;                  /* lanes parked at a collective                 */
-};
-struct Fiber {
-    ucontext_t ctx;
-    std::vector<char> stack;
-    Warp* warp = nullptr;
-    int lane = 0, tid = 0;
-    bool done = false;
-};
-
-static ucontext_t g_sched;
-static Fiber* g_cur = nullptr;
-static const char* g_error = nullptr;
-static uint64_t g_collectives = 0;
-
-static void yield() { swapcontext(&g_cur->ctx, &g_sched); }
-
-/* every lane of the warp contributes v; returns after all have, with all[] = the 32 contributions */
-enum { K_BALLOT = 1, K_SHFL32, K_SHFL64, K_SHFL_UP, K_SYNCWARP };
-static void gather(int kind, uint64_t v, uint64_t all[LANES]) {
-    Fiber* f = g_cur;
-    Warp* w = f->warp;
-    const uint64_t g = w->lane_gen[f->lane]++;
-    const int b = (int)(g & 1u);
-    if (w->slot_gen[b] != g) { w->slot_gen[b] = g; w->arrived[b] = 0; w->kind[b] = kind; }     /* first lane of this generation: the buffer was last used by g - 2 */
-    else if (w->kind[b] != kind) g_error = "lanes of one warp met at different collectives (divergent code around a *_sync)";
-    w->slot[b][f->lane] = v;
-    w->arrived[b]++;
-    w->waiting++;
-    while (!(w->slot_gen[b] == g && w->arrived[b] == LANES)) {
-        if (w->live < LANES) { g_error = "a lane left the kernel while its warp waits at a collective"; }
-        yield();
-    }
-    w->waiting--;
-    memcpy(all, w->slot[b], sizeof(uint64_t) * LANES);
-    if (f->lane == 0) g_collectives++;
-}
-
-}  // namespace wemu
-
-static inline uint32_t __ballot_sync(uint32_t mask, bool pred) {
-    (void)mask;
-    uint64_t all[wemu::LANES];
-    wemu::gather(wemu::K_BALLOT, pred ? 1u : 0u, all);
-    uint32_t r = 0;
-    for (int i = 0; i < wemu::LANES; ++i) if (all[i]) r |= 1u << i;
-    return r;
-}
-static inline void __syncwarp() { uint64_t all[wemu::LANES]; wemu::gather(wemu::K_SYNCWARP, 0, all); }
-template <class T>
-static inline T emu_shfl(T v, int src, int kind = 0) {
-    static_assert(sizeof(T) <= 8, "shuffle operand");
-    uint64_t bits = 0, all[wemu::LANES];
-    memcpy(&bits, &v, sizeof(T));
-    wemu::gather(kind ? kind : (sizeof(T) == 8 ? wemu::K_SHFL64 : wemu::K_SHFL32), bits, all);
-    T r;
-    memcpy(&r, &all[src & 31], sizeof(T));
-    return r;
-}
-static inline unsigned long long __shfl_sync(uint32_t, unsigned long long v, int src) { return emu_shfl(v, src); }
-static inline uint32_t __shfl_sync(uint32_t, uint32_t v, int src) { return emu_shfl(v, src); }
-static inline float __shfl_sync(uint32_t, float v, int src) { return emu_shfl(v, src); }
-static inline uint32_t __shfl_up_sync(uint32_t, uint32_t v, int delta) {
-    const int lane = (int)(threadIdx.x & 31u);
-    const uint32_t r = emu_shfl(v, lane >= delta ? lane - delta : lane, wemu::K_SHFL_UP);     /* lanes below delta keep their own value */
-    return r;
-}
+#include "warp_emu.h"
 
 using namespace rt3b;
 #include "../../raytracer3_b200/csrc/trace_kernel.cuh"
@@ -154,7 +30,6 @@ void k_static(const WideNode* nodes, const Tri48* tris, const rt3_ray* rays, uin
 }
 }  // namespace
 
-/* ------------------------------------------------------------------ block runner ---------------------------------------- */
 namespace wemu {
 
 struct LaunchArgs {
@@ -166,7 +41,7 @@ static LaunchArgs g_args;
 #ifndef RT3_EMU_KEEP
 #define RT3_EMU_KEEP 28          /* the product's KEEP (launch_dyn in trace.cu); other values for tools/emu_warp_stats.py experiments */
 #endif
-static void fiber_main() {
+static void trace_body() {
     const LaunchArgs& a = g_args;
     if (a.any == 2) k_static(a.nodes, a.tris, a.rays, a.n, a.hits, a.work_counter);
     else if (a.any) {
@@ -176,45 +51,6 @@ static void fiber_main() {
         if (a.two) k_trace_dyn<false, RT3_EMU_KEEP, true>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
         else k_trace_dyn<false, RT3_EMU_KEEP, false>(a.nodes, a.tris, a.rays, a.d_count, a.n, a.hits, a.bits, a.work_counter, 0x47000000u, a.insts);
     }
-    g_cur->done = true;
-    g_cur->warp->live--;
-    swapcontext(&g_cur->ctx, &g_sched);
-}
-
-/* one block of TRACE_THREADS threads; returns 0, or -1 with g_error set */
-static int run_block() {
-    const int n_warps = TRACE_THREADS / LANES;
-    std::vector<Warp> warps(n_warps);
-    std::vector<Fiber> fibers(TRACE_THREADS);
-    for (int t = 0; t < TRACE_THREADS; ++t) {
-        Fiber& f = fibers[t];
-        f.warp = &warps[t / LANES]; f.lane = t % LANES; f.tid = t; f.done = false;
-        f.warp->lane_gen[f.lane] = 0;
-        f.stack.resize(FIBER_STACK);
-        getcontext(&f.ctx);
-        f.ctx.uc_stack.ss_sp = f.stack.data();
-        f.ctx.uc_stack.ss_size = f.stack.size();
-        f.ctx.uc_link = &g_sched;
-        makecontext(&f.ctx, fiber_main, 0);
-    }
-    int remaining = TRACE_THREADS;
-    uint64_t idle_rounds = 0;
-    while (remaining && !g_error) {
-        const uint64_t before = g_collectives;
-        int finished_now = 0;
-        for (int t = 0; t < TRACE_THREADS && !g_error; ++t) {
-            Fiber& f = fibers[t];
-            if (f.done) continue;
-            g_cur = &f;
-            threadIdx.x = (unsigned)f.tid;
-            swapcontext(&g_sched, &f.ctx);
-            if (f.done) { remaining--; finished_now++; }
-        }
-        /* a full round in which no collective completed and no lane finished means the warps can make no progress */
-        if (g_collectives == before && finished_now == 0) { if (++idle_rounds > 4) g_error = "deadlock: lanes of a warp wait at different collectives"; }
-        else idle_rounds = 0;
-    }
-    return g_error ? -1 : 0;
 }
 
 }  // namespace wemu
@@ -236,8 +72,7 @@ int wemu_trace(const uint32_t* nodes20, const uint32_t* tris12, const void* inst
     g_args.hits = hits; g_args.bits = bits; g_args.work_counter = &counter; g_args.insts = (const InstRec*)insts;
     g_args.any = any; g_args.two = insts != nullptr;
     if (any == 1) memset(bits, 0, ((n + 31) / 32) * 4);        /* launch_dyn zeroes the result bits before the launch */
-    for (int b = 0; b < blocks; ++b)
-        if (run_block() != 0) return -1;
+    if (run_grid(trace_body, (unsigned)blocks, TRACE_THREADS) != 0) return -1;
     if (collectives) *collectives = g_collectives;
     return 0;
 }

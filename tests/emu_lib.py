@@ -60,7 +60,8 @@ def warp_lib(balance=False, defines=()):
         so = os.path.join(_HERE, "emu", f"libwemu_{key}.so" if key else "libwemu.so")
         src = os.path.join(_HERE, "emu", "warp_emu.cpp")
         csrc = os.path.join(_HERE, "..", "raytracer3_b200", "csrc")
-        deps = [src, os.path.join(csrc, "bvh_logic.h"), os.path.join(csrc, "trace_kernel.cuh"), os.path.join(_HERE, "..", "include", "rt3_shared_math.h")]
+        deps = [src, os.path.join(_HERE, "emu", "warp_emu.h"), os.path.join(csrc, "bvh_logic.h"), os.path.join(csrc, "trace_kernel.cuh"),
+                os.path.join(_HERE, "..", "include", "rt3_shared_math.h")]
         if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas"]
                                   + ["-D" + d for d in defines]
