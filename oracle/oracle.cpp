@@ -341,6 +341,20 @@ void orc_resolve_prim(const orc_scene* s, uint32_t prim, uint32_t* instance, uin
     uint32_t seg = find_segment(sv, prim);
     *instance = s->seg_instance[seg]; *geometry = s->seg_geometry[seg]; *primitive = prim - s->seg_first_prim[seg];
 }
+/* the records the traversal tests: (v0, e1, e2) of every triangle in global id order, and the oracle's scene view (host pointers, valid
+ * while the scene lives) — for tests/emu/pass_emu.cpp, which runs the product's kernels on the CPU against this oracle */
+void orc_world_edges(const orc_scene* s, float* out9) {
+    for (size_t i = 0; i < s->tris.size(); ++i) {
+        const WorldTri& t = s->tris[i];
+        float* o = out9 + 9 * i;
+        o[0] = t.v0.x; o[1] = t.v0.y; o[2] = t.v0.z; o[3] = t.e1.x; o[4] = t.e1.y; o[5] = t.e1.z; o[6] = t.e2.x; o[7] = t.e2.y; o[8] = t.e2.z;
+    }
+}
+uint64_t orc_scene_view(const orc_scene* s, void* out, uint64_t capacity) {
+    SceneView v = s->view();
+    if (capacity >= sizeof(v)) memcpy(out, &v, sizeof(v));
+    return sizeof(v);
+}
 void orc_world_triangles(const orc_scene* s, float* out9) {
     for (size_t i = 0; i < s->tris.size(); ++i) {
         const WorldTri& t = s->tris[i];

@@ -36,6 +36,8 @@ void orc_scene_bounds(const orc_scene*, float lo[3], float hi[3]);
 void orc_resolve_prim(const orc_scene*, uint32_t prim, uint32_t* instance, uint32_t* geometry, uint32_t* primitive);
 /* World-space triangles in global id order: 9 floats each (v0, v1, v2). */
 void orc_world_triangles(const orc_scene*, float* out9);
+void orc_world_edges(const orc_scene*, float* out9);                       /* (v0, e1, e2) per triangle */
+uint64_t orc_scene_view(const orc_scene*, void* out, uint64_t capacity);   /* rt3m::SceneView of host pointers; returns its size */
 
 /* mode 0 = brute force over all triangles, 1 = BVH2 */
 void orc_trace_closest(const orc_scene*, const rt3_ray* rays, uint64_t n, rt3_hit* out, int mode, int threads);

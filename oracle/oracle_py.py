@@ -47,6 +47,9 @@ def lib():
         L.orc_scene_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_resolve_prim.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_world_triangles.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_world_edges.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_scene_view.restype = C.c_uint64
+        L.orc_scene_view.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
         L.orc_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int, C.c_int]
         L.orc_trace_any.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int, C.c_int]
         L.orc_pass_gbuffer.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
@@ -137,6 +140,12 @@ class OracleScene:
     def world_triangles(self):
         out = np.zeros((self.num_triangles, 3, 3), np.float32)
         self.L.orc_world_triangles(self.h, ptr(out))
+        return out
+
+    def world_edges(self):
+        """(v0, e1, e2) of every triangle in global id order: the records the traversal tests"""
+        out = np.zeros((self.num_triangles, 3, 3), np.float32)
+        self.L.orc_world_edges(self.h, ptr(out))
         return out
 
     def trace_closest(self, rays, brute=False):

@@ -23,6 +23,7 @@ struct EmuBvh {
     float lo[3], hi[3];
 };
 
+static int g_input_edges = 0;
 static inline uint32_t mem_slot(uint32_t n, uint32_t ref) { return (ref & LEAF_FLAG) ? n - 1 + (ref & ~LEAF_FLAG) : ref; }
 
 extern "C" {
@@ -36,6 +37,12 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp, float spl
         const float* p = tris9 + 9 * (size_t)i;
         Tri48& t = b->tris_in[i];
         for (int a = 0; a < 3; ++a) {
+            if (g_input_edges) {           /* input is (v0, e1, e2) already: the records of another builder, bit for bit */
+                t.v0[a] = p[a]; t.e1[a] = p[3 + a]; t.e2[a] = p[6 + a];
+                const float q[3] = {p[a], p[a] + p[3 + a], p[a] + p[6 + a]};
+                for (int k = 0; k < 3; ++k) { b->lo[a] = std::min(b->lo[a], q[k]); b->hi[a] = std::max(b->hi[a], q[k]); }
+                continue;
+            }
             t.v0[a] = p[a]; t.e1[a] = p[3 + a] - p[a]; t.e2[a] = p[6 + a] - p[a];
             for (int k = 0; k < 3; ++k) { b->lo[a] = std::min(b->lo[a], p[3 * k + a]); b->hi[a] = std::max(b->hi[a], p[3 * k + a]); }
         }
@@ -162,6 +169,7 @@ EmuBvh* emu_build(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, 
 EmuBvh* emu_build_dp(const float* tris9, uint32_t n) { return build_lbvh(tris9, n, true); }
 EmuBvh* emu_build_ploc(const float* tris9, uint32_t n, int use_dp, uint32_t radius) { return build_lbvh(tris9, n, use_dp != 0, 0.0f, radius); }
 uint32_t emu_ploc_rounds(const EmuBvh* b) { return b->ploc_rounds; }
+void emu_set_input_edges(int on) { g_input_edges = on; }
 EmuBvh* emu_build_ex(const float* tris9, uint32_t n, int use_dp, float split_beta, uint32_t ploc_radius, int treelet_passes) {
     return build_lbvh(tris9, n, use_dp != 0, split_beta, ploc_radius, treelet_passes);
 }

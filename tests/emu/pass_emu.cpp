@@ -1,0 +1,141 @@
+/*
+ * pass_emu.cpp — TEST INFRASTRUCTURE: whole frames of the product's pass kernels (raytracer3_b200/csrc/pass_kernels.cuh: k_gbuffer,
+ * k_ref_init / k_ref_shade / k_ref_shadow / k_ref_finish, k_postprocess) and of its traversal kernel (trace_kernel.cuh) on the CPU warp
+ * emulation of warp_emu.h.  The launch sequences below restate rt3_launch_gbuffer / rt3_launch_reference / rt3_launch_postprocess
+ * (passes.cu) and launch_dyn (trace.cu) with host memory in place of device memory; tests/test_emu_passes.py compares the frames bit for
+ * bit with the oracle.  Not a fallback: librt3.so neither contains nor calls this code.
+ */
+#include "warp_emu.h"
+
+#include <algorithm>
+#include <functional>
+
+#include "../../raytracer3_b200/csrc/pass_types.h"
+
+using namespace rt3b;
+using namespace rt3m;
+#include "../../raytracer3_b200/csrc/trace_kernel.cuh"
+#include "../../raytracer3_b200/csrc/pass_kernels.cuh"
+
+namespace {
+
+std::function<void()> g_call;
+void call_body() { g_call(); }
+
+/* kernel<<<grid, block>>>(...) */
+int launch(unsigned grid, unsigned block, std::function<void()> f) {
+    g_call = std::move(f);
+    return wemu::run_grid(call_body, grid, block);
+}
+unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+const int SM_COUNT = 148;
+
+/* launch_dyn (trace.cu): persistent warps over a queue whose length lives in memory */
+int trace_closest(const WideNode* nodes, const Tri48* tris, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits) {
+    if (n_max == 0) return 0;
+    unsigned long long counter = 0;
+    const unsigned grid = (unsigned)std::min<uint64_t>(4, (n_max + TRACE_THREADS - 1) / TRACE_THREADS);      /* a few resident blocks are enough here */
+    return launch(grid, TRACE_THREADS, [&]() { k_trace_dyn<false, 28, false>(nodes, tris, rays, d_count, n_max, hits, nullptr, &counter, 0x47000000u, nullptr); });
+}
+int trace_any(const WideNode* nodes, const Tri48* tris, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits) {
+    if (n_max == 0) return 0;
+    unsigned long long counter = 0;
+    memset(bits, 0, ((n_max + 31) / 32) * 4);
+    const unsigned grid = (unsigned)std::min<uint64_t>(4, (n_max + TRACE_THREADS - 1) / TRACE_THREADS);
+    return launch(grid, TRACE_THREADS, [&]() { k_trace_dyn<true, 28, false>(nodes, tris, rays, d_count, n_max, nullptr, bits, &counter, 0x47000000u, nullptr); });
+}
+
+PixelMap full_frame(const rt3_params& p) {
+    const uint32_t W = (uint32_t)p.window_size[0], H = (uint32_t)p.window_size[1];
+    PixelMap m;
+    memset(&m, 0, sizeof(m));
+    m.single.x0 = 0; m.single.y0 = 0; m.single.w = W; m.single.h = H;
+    m.rects = nullptr; m.n_tiles = 1; m.tile_w = W; m.tile_h = H;
+    m.bw = (W + 7) / 8; m.bh = (H + 3) / 4; m.pitch = W; m.slab = 0;
+    m.work = m.bw * m.bh * 32u;
+    return m;
+}
+
+}  // namespace
+
+extern "C" {
+
+/* SceneView with the per-triangle shading records the device build adds (k_shade_records, build.cu) */
+void pemu_shade_records(const void* scene_view, uint32_t n_prims, uint32_t* rec4) {
+    const SceneView& s = *(const SceneView*)scene_view;
+    for (uint32_t i = 0; i < n_prims; ++i) {
+        const uint32_t seg = find_segment(s, i);
+        const rt3_geometry_info& g = s.geometries[s.seg_geometry[seg]];
+        const uint32_t io = g.index_offset + 3u * (i - s.seg_first_prim[seg]);
+        rec4[4 * i] = g.vertex_offset + s.indices[io]; rec4[4 * i + 1] = g.vertex_offset + s.indices[io + 1];
+        rec4[4 * i + 2] = g.vertex_offset + s.indices[io + 2]; rec4[4 * i + 3] = seg;
+    }
+}
+
+/* rt3_launch_gbuffer + rt3_launch_reference (+ rt3_launch_postprocess when post != NULL) for one full frame.
+ * counters5: rays_primary, rays_secondary, rays_shadow, paths_started, paths_escaped.  Returns 0, or -1 (wemu::g_error). */
+int pemu_frame(const void* scene_view, const uint32_t* shade_rec, const uint32_t* nodes20, const uint32_t* tris12, const rt3_params* pp,
+               uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary, const float* prev, float* light, float* post, uint64_t* counters5) {
+    wemu::g_error = nullptr; wemu::g_collectives = 0;
+    SceneView view = *(const SceneView*)scene_view;
+    view.shade_rec = shade_rec;
+    const rt3_params p = *pp;
+    const WideNode* nodes = (const WideNode*)nodes20;
+    const Tri48* tris = (const Tri48*)tris12;
+    const PixelMap m = full_frame(p);
+    DeviceCounters dc;
+    memset(&dc, 0, sizeof(dc));
+    if (!m.work) return 0;
+    /* ---- rt3_launch_gbuffer */
+    if (launch(div_up(m.work, 128), 128, [&]() { k_gbuffer(view, nodes, tris, p, m, gbuffer, depth, ids, bary, &dc, nullptr); })) return -1;
+    /* ---- rt3_launch_reference */
+    const size_t W = m.work;
+    const bool nee = nee_enabled(p.flags), layered = (p.flags & RT3_FLAG_SPECULAR) != 0;
+    std::vector<rt3_ray> q_rays[2] = {std::vector<rt3_ray>(W), std::vector<rt3_ray>(W)}, srays(nee ? W : 1);
+    std::vector<float4> q_thr[2] = {std::vector<float4>(W), std::vector<float4>(W)}, px_radiance(W), scontrib(nee ? W : 1);
+    std::vector<rt3_hit> q_hits(W);
+    std::vector<uint32_t> px_rng(W), sbits((W + 31) / 32 + 1);
+    std::vector<float> q_pdf[2] = {std::vector<float>(nee ? W : 1), std::vector<float>(nee ? W : 1)};
+    uint32_t counts[4] = {0, 0, 0, 0};
+    NeeQueues nq = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (nee) { nq.srays = srays.data(); nq.scontrib = scontrib.data(); nq.scount = counts + 2; }
+    const unsigned grid = std::min<unsigned>(div_up(W, PASS_THREADS), (unsigned)SM_COUNT * 8u);
+    auto resolve_shadows = [&]() -> int {
+        if (trace_any(nodes, tris, nq.srays, nq.scount, W, sbits.data())) return -1;
+        return launch(grid, PASS_THREADS, [&]() { k_ref_shadow(nq.scontrib, sbits.data(), nq.scount, px_radiance.data()); });
+    };
+    for (uint32_t sidx = 0; sidx < p.samples; ++sidx) {
+        counts[0] = counts[1] = counts[2] = 0;
+        nq.pdf_in = nullptr; nq.pdf_out = nee ? q_pdf[0].data() : nullptr;
+        const int first = sidx == 0 ? 1 : 0;
+        if (launch(grid, PASS_THREADS, [&]() {
+                if (layered) k_ref_init<true>(view, p, m, gbuffer, depth, px_radiance.data(), px_rng.data(), first, q_rays[0].data(), q_thr[0].data(), counts, nq, &dc);
+                else k_ref_init<false>(view, p, m, gbuffer, depth, px_radiance.data(), px_rng.data(), first, q_rays[0].data(), q_thr[0].data(), counts, nq, &dc);
+            })) return -1;
+        if (nee && p.bounces > 1 && resolve_shadows()) return -1;
+        int cur = 0;
+        for (uint32_t b = 1; b < p.bounces; ++b) {
+            if (trace_closest(nodes, tris, q_rays[cur].data(), counts + cur, W, q_hits.data())) return -1;
+            counts[1 - cur] = 0;
+            if (nee) counts[2] = 0;
+            nq.pdf_in = nee ? q_pdf[cur].data() : nullptr; nq.pdf_out = nee ? q_pdf[1 - cur].data() : nullptr;
+            if (launch(grid, PASS_THREADS, [&]() {
+                    if (layered) k_ref_shade<true>(view, p, m, b, q_rays[cur].data(), q_hits.data(), q_thr[cur].data(), counts + cur, q_rays[1 - cur].data(),
+                                                   q_thr[1 - cur].data(), counts + (1 - cur), px_radiance.data(), px_rng.data(), nq, &dc);
+                    else k_ref_shade<false>(view, p, m, b, q_rays[cur].data(), q_hits.data(), q_thr[cur].data(), counts + cur, q_rays[1 - cur].data(),
+                                            q_thr[1 - cur].data(), counts + (1 - cur), px_radiance.data(), px_rng.data(), nq, &dc);
+                })) return -1;
+            if (nee && b != p.bounces - 1 && resolve_shadows()) return -1;
+            cur = 1 - cur;
+        }
+    }
+    if (launch(div_up(W, PASS_THREADS), PASS_THREADS, [&]() { k_ref_finish(p, m, px_radiance.data(), prev, light); })) return -1;
+    /* ---- rt3_launch_postprocess */
+    if (post && launch(div_up(W, PASS_THREADS), PASS_THREADS, [&]() { k_postprocess(view, p, m, depth, light, post); })) return -1;
+    if (counters5) { counters5[0] = dc.rays_primary; counters5[1] = dc.rays_secondary; counters5[2] = dc.rays_shadow; counters5[3] = dc.paths_started; counters5[4] = dc.paths_escaped; }
+    return 0;
+}
+const char* pemu_last_error() { return wemu::g_error ? wemu::g_error : ""; }
+
+}

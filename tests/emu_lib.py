@@ -40,6 +40,7 @@ def lib():
         L.emu_ploc_rounds.argtypes = [C.c_void_p]
         L.emu_wrap.restype = C.c_void_p
         L.emu_wrap.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
+        L.emu_set_input_edges.argtypes = [C.c_int]
         L.emu_destroy.argtypes = [C.c_void_p]
         L.emu_export.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.emu_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -76,11 +77,62 @@ def warp_lib(balance=False, defines=()):
     return _wlibs[key]
 
 
+def pass_lib():
+    """tests/emu/pass_emu.cpp: the product's pass kernels (csrc/pass_kernels.cuh) + traversal kernel over the warp emulation."""
+    if "pass" not in _wlibs:
+        so = os.path.join(_HERE, "emu", "libpemu.so")
+        src = os.path.join(_HERE, "emu", "pass_emu.cpp")
+        csrc = os.path.join(_HERE, "..", "raytracer3_b200", "csrc")
+        deps = [src, os.path.join(_HERE, "emu", "warp_emu.h"), os.path.join(_HERE, "..", "include", "rt3_shared_math.h")] + [
+            os.path.join(csrc, f) for f in ("bvh_logic.h", "trace_kernel.cuh", "pass_kernels.cuh", "pass_types.h")]
+        if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas",
+                                   "-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", so, src])
+        L = C.CDLL(so)
+        L.pemu_shade_records.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.pemu_frame.restype = C.c_int
+        L.pemu_frame.argtypes = [C.c_void_p] * 13
+        L.pemu_last_error.restype = C.c_char_p
+        _wlibs["pass"] = L
+    return _wlibs["pass"]
+
+
+class PassEmu:
+    """Whole frames of the product's kernels on the CPU: scene tables from the oracle's scene, acceleration structure from the CPU
+    emulation of the device builder over the oracle's (v0, e1, e2) records."""
+
+    def __init__(self, oracle_scene, **build_options):
+        self.P = pass_lib()
+        self.orc = oracle_scene
+        self.view = np.zeros(int(oracle_scene.L.orc_scene_view(oracle_scene.h, None, 0)), np.uint8)
+        oracle_scene.L.orc_scene_view(oracle_scene.h, ptr(self.view), len(self.view))
+        edges = oracle_scene.world_edges()
+        self.bvh = EmuBvh(tris=edges, edges=True, **build_options)
+        self.nodes, self.recs = self.bvh.export()
+        self.shade_rec = np.zeros((max(len(edges), 1), 4), np.uint32)
+        self.P.pemu_shade_records(ptr(self.view), len(edges), ptr(self.shade_rec))
+
+    def frame(self, params, prev_light=None, postprocess=False):
+        w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])
+        out = dict(gbuffer=np.zeros((h, w, 4), np.uint32), depth=np.zeros((h, w), np.float32), ids=np.zeros((h, w, 2), np.uint32),
+                   bary=np.zeros((h, w, 2), np.float32), light=np.zeros((h, w, 4), np.float32), counters=np.zeros(5, np.uint64))
+        post = np.zeros((h, w, 4), np.float32) if postprocess else None
+        rc = self.P.pemu_frame(ptr(self.view), ptr(self.shade_rec), ptr(self.nodes), ptr(self.recs), ptr(params), ptr(out["gbuffer"]), ptr(out["depth"]),
+                               ptr(out["ids"]), ptr(out["bary"]), None if prev_light is None else ptr(prev_light), ptr(out["light"]),
+                               None if post is None else ptr(post), ptr(out["counters"]))
+        if rc != 0:
+            raise RuntimeError("warp emulation: " + self.P.pemu_last_error().decode())
+        out["post"] = post
+        return out
+
+
 class EmuBvh:
-    def __init__(self, tris=None, nodes=None, tri_records=None, optimal_collapse=True, split_beta=0.0, ploc_radius=0, treelet_passes=0):
+    def __init__(self, tris=None, nodes=None, tri_records=None, optimal_collapse=True, split_beta=0.0, ploc_radius=0, treelet_passes=0, edges=False):
         """optimal_collapse: children of the wide nodes by the cost dynamic programme (the device default) or greedily (RT3_BUILD_FAST_BUILD);
-        split_beta > 0: triangle splitting with a budget of split_beta x triangles extra references (RT3_BUILD_SPLIT)"""
+        split_beta > 0: triangle splitting with a budget of split_beta x triangles extra references (RT3_BUILD_SPLIT);
+        edges: `tris` holds (v0, e1, e2) records (e.g. the oracle's, OracleScene.world_edges) instead of three vertices"""
         self.L = lib()
+        self.L.emu_set_input_edges(1 if edges else 0)
         if tris is not None:
             t = np.ascontiguousarray(tris, np.float32)
             if (treelet_passes > 0) + (ploc_radius > 0) + (split_beta > 0) > 1:                  # combinations (experiments)
