@@ -674,6 +674,9 @@ static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs
 void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out) {
     rt3_build_stats bs;
     memset(&bs, 0, sizeof(bs));
+    /* a build that fails midway (out of memory, a depth guard) must not leave the previous structure marked usable: its buffers are being
+     * overwritten.  Valid again only after the final synchronisation below. */
+    c->accel_valid = false;
     const uint32_t n = c->n_triangles;
     bs.triangles = n;
     cudaEvent_t total_a = c->ev[2], total_b = c->ev[3];
@@ -695,7 +698,10 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
      * the fastest build, then greedy by surface area.  Measured: 36 % fewer nodes, +2 % path-tracing and +2..6 % incoherent-ray
      * throughput, build 1.37 -> 1.49 ms at 263 k triangles. */
     const bool optimal = !(flags & RT3_BUILD_FAST_BUILD);
-    const bool treelet = optimal && ((flags & RT3_BUILD_TREELET) || getenv("RT3_FORCE_TREELET") != nullptr);   /* the env switch: A/B of whole benchmarks */
+    /* FAST_TRACE (the default, the reference's PREFER_FAST_TRACE) = treelet restructuring; RT3_BUILD_ROTATIONS keeps round 1's cheaper
+     * optimisation (tree rotations).  Measured on B200, bench scene (profiles/r2a_ab_experiments.log): traversal launch 0.497 -> 0.477 ms,
+     * incoherent closest 5.37 -> 5.68 Grays/s, frame 3011 -> 3063 Mrays/s, for a 1.9 -> 10.8 ms build. */
+    const bool treelet = optimal && !(flags & RT3_BUILD_ROTATIONS);
     if (n == 0) {
     } else if ((flags & RT3_BUILD_TWO_LEVEL) && !c->h_instances.empty()) {
         build_two_level(c, st, bs, optimal, treelet);

@@ -217,6 +217,22 @@ def blue_noise_tile(size=256, seed=7, iters=12):
     return out
 
 
+def reference_blue_noise(directory=None):
+    """The reference's own sampler input: resources/bluenoise.png (256x256 RGBA8, /root/reference/resources/bluenoise.png; committed
+    under <repo>/resources as a data fixture, byte-identical).  Looked up in `directory`, $RT3_ASSET_DIR, then <repo>/resources.
+    Returns (tile, source); falls back to the generated stand-in `blue_noise_tile()` (source says so) only if the file is nowhere."""
+    import os
+    from . import assets
+    here = os.path.dirname(os.path.abspath(__file__))
+    for d in (directory, os.environ.get("RT3_ASSET_DIR"), os.path.join(here, "..", "resources")):
+        if d and os.path.isfile(os.path.join(d, "bluenoise.png")):
+            with open(os.path.join(d, "bluenoise.png"), "rb") as f:
+                tile = assets.decode_image(f.read())
+            assert tile.shape == (256, 256, 4) and tile.dtype == np.uint8
+            return np.ascontiguousarray(tile), "resources/bluenoise.png (the reference's tile)"
+    return blue_noise_tile(), "generated stand-in (scenes.blue_noise_tile)"
+
+
 # ----------------------------------------------------------------------------- scenes
 
 
@@ -237,12 +253,14 @@ def cornell_box(light_emission=1.4):
     mb.add(*quad((1, -1, -1), (0, 0, 2), (0, 2, 0)), base_color=red)                # wall x=+1 (screen left: red, as in refrence.png), normal -x
     mb.add(*quad((-0.35, 0.998, -0.3), (0.7, 0, 0), (0, 0, 0.6)), base_color=grey, emission=(light_emission,) * 3)
     c, s = np.cos(0.3), np.sin(0.3)
-    rot = np.array([c, 0, s, -0.35, 0, 1, 0, 0, -s, 0, c, 0.35], np.float32)
-    mb.add(*box((-0.3, -1, -0.3), (0.3, 0.2, 0.3)), base_color=(0.5, 0.5, 0.5), xform=rot)      # tall box (geometry transform)
+    rot = np.array([c, 0, s, 0.35, 0, 1, 0, 0, -s, 0, c, 0.35], np.float32)
+    mb.add(*box((-0.3, -1, -0.3), (0.3, 0.2, 0.3)), base_color=(0.5, 0.5, 0.5), xform=rot)      # tall box (geometry transform), near the red wall as in refrence.png
     c, s = np.cos(-0.3), np.sin(-0.3)
-    rot2 = np.array([c, 0, s, 0.4, 0, 1, 0, 0, -s, 0, c, -0.3], np.float32)
+    rot2 = np.array([c, 0, s, -0.4, 0, 1, 0, 0, -s, 0, c, -0.3], np.float32)
     mb.add(*box((-0.28, -1, -0.28), (0.28, -0.44, 0.28)), base_color=(0.02, 0.02, 0.02), roughness=0.5, xform=rot2)
-    cams = {"cam0": dict(position=(0, 0, -3.6), direction=(0, 0, 1), fov_deg=40.0)}
+    # cam_ref: the framing of /root/reference/resources/refrence.png (front opening = 79 % of the image height, back wall = 75 % of the opening)
+    cams = {"cam0": dict(position=(0, 0, -3.6), direction=(0, 0, 1), fov_deg=40.0),
+            "cam_ref": dict(position=(0, 0, -7.0), direction=(0, 0, 1), fov_deg=23.8)}
     return _scene(mb, cams, name="cornell_box")
 
 

@@ -57,7 +57,7 @@ FLAG_ENV = 1
 FLAG_BLUENOISE = 2
 FLAG_NEE = 4
 FLAG_SPECULAR = 8
-BUILD_FAST_TRACE, BUILD_FAST_BUILD, BUILD_TWO_LEVEL, BUILD_TREELET = 1, 2, 4, 8
+BUILD_FAST_TRACE, BUILD_FAST_BUILD, BUILD_TWO_LEVEL, BUILD_TREELET, BUILD_ROTATIONS = 1, 2, 4, 8, 16
 
 IDENTITY_3X4 = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], dtype=np.float32)
 

@@ -52,7 +52,7 @@ def lib():
     return _lib
 
 
-def warp_lib(balance=False, defines=()):
+def warp_lib(balance=False, defines=(), load=True):
     """tests/emu/warp_emu.cpp: the production kernel source (csrc/trace_kernel.cuh) over a lock-step warp emulation.
     balance=True builds it with -DRT3_TRI_BALANCE=1 (the warp-balanced record phase, an experiment not in the product build)."""
     defines = tuple(defines) + (("RT3_TRI_BALANCE=1",) if balance else ())
@@ -67,6 +67,8 @@ def warp_lib(balance=False, defines=()):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas"]
                                   + ["-D" + d for d in defines]
                                   + ["-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", so, src])
+        if not load:                                              # __graft_entry__.build(): compile the checker, do not open it
+            return so
         L = C.CDLL(so)
         L.wemu_trace.restype = C.c_int
         L.wemu_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -77,7 +79,7 @@ def warp_lib(balance=False, defines=()):
     return _wlibs[key]
 
 
-def pass_lib():
+def pass_lib(load=True):
     """tests/emu/pass_emu.cpp: the product's pass kernels (csrc/pass_kernels.cuh) + traversal kernel over the warp emulation."""
     if "pass" not in _wlibs:
         so = os.path.join(_HERE, "emu", "libpemu.so")
@@ -88,6 +90,8 @@ def pass_lib():
         if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-march=x86-64-v3", "-Wno-unknown-pragmas",
                                    "-I", os.path.join(_HERE, "..", "include"), "-shared", "-o", so, src])
+        if not load:
+            return so
         L = C.CDLL(so)
         L.pemu_shade_records.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
         L.pemu_frame.restype = C.c_int

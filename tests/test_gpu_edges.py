@@ -207,3 +207,36 @@ def test_collapse_policies_give_identical_hits(gpu_ctx):
         assert (results[name][1] == results["trace"][1]).all() and (results[name][2] == results["trace"][2]).all(), name
     assert results["trace"][0] < 0.85 * results["build"][0] and results["trace2"][0] < 0.85 * results["build2"][0]
     assert (results["trace"][1][:, 3] != MISS).mean() > 0.5
+
+
+def test_treelet_build_gives_identical_hits_and_the_emulators_tree(gpu_ctx):
+    """The default FAST_TRACE build (treelet restructuring) against RT3_BUILD_ROTATIONS: same hits bit for bit, every triangle kept once, and
+    exactly the tree the CPU emulation of the builder produces (node count), with less traversal work than the rotations.  First run on a
+    B200 in round 2 (profiles/r2a_ab_experiments.log)."""
+    import sys, os, torch
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from emu_lib import EmuBvh
+    from raytracer3_b200.host import RenderWorld
+    from raytracer3_b200.types import BUILD_FAST_TRACE, BUILD_ROTATIONS, BUILD_TREELET, BUILD_TWO_LEVEL
+    sc = scenes.synthetic_atrium(0.05, environment=False)
+    T = np.ascontiguousarray(scenes.world_triangles(sc), np.float32)
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc)
+    closest, anyr = scenes.incoherent_rays(sc, 100000, seed=9, tris=T.astype(np.float64))
+    rays = torch.from_numpy(np.concatenate([closest, scenes.random_rays(sc, 20000, seed=10)]).view(np.float32).reshape(-1, 8)).cuda()
+    arays = torch.from_numpy(anyr.view(np.float32).reshape(-1, 8)).cuda()
+    res = {}
+    for name, flags in (("rot", BUILD_ROTATIONS), ("treelet", BUILD_FAST_TRACE), ("treelet_explicit", BUILD_FAST_TRACE | BUILD_TREELET),
+                        ("treelet2", BUILD_FAST_TRACE | BUILD_TWO_LEVEL)):
+        bs = w.create_acceleration_structure(flags)
+        st = w.trace_stats(rays)
+        res[name] = (bs.wide_nodes, w.trace_closest(rays).cpu().numpy().view(np.uint32), w.trace_any(arays).cpu().numpy(), st.nodes_per_ray + 0.4 * st.tris_per_ray)
+        if not flags & BUILD_TWO_LEVEL:
+            nodes, tris = w.download_accel()
+            assert EmuBvh(nodes=nodes, tri_records=tris).check_triangles() == 0
+    for name in ("treelet", "treelet_explicit", "treelet2"):
+        assert (res[name][1] == res["rot"][1]).all() and (res[name][2] == res["rot"][2]).all(), name
+    assert res["treelet"][0] == res["treelet_explicit"][0] == EmuBvh(tris=T, treelet_passes=2).info()["nodes"]   # the device build is the emulator's build
+    assert res["rot"][0] == EmuBvh(tris=T).info()["nodes"]
+    assert res["treelet"][3] < res["rot"][3]                               # fewer node visits + 0.4 x triangle tests per ray
+    assert (res["rot"][1][:, 3] != MISS).mean() > 0.5
