@@ -6,9 +6,11 @@ tracer at 1920x1080, 1 spp, environment light + blue-noise sampling (BASELINE.js
   python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU under torchrun for N > 1)
   python bench.py --impl reference --gpus N --steps K ...  # the CPU restatement of the reference's shader passes (oracle/), all host threads
 
-A step = one frame: G-buffer pass + reference-mode pass (+ for N > 1 the NCCL gather of the finished tiles).
-N > 1 is WEAK scaling over screen tiles: every rank owns 1920x1080 pixels' worth of 64x64 tiles of an N-times larger frame
-(N=2: 3840x1080, N=4: 3840x2160, N=8: 7680x2160), scene and BVH replicated, one all_gather of the framebuffer slabs per frame.
+N = 1: a step = one frame (G-buffer pass + reference-mode pass) of configs[1].
+N > 1: STRONG scaling of BASELINE configs[2] — a fixed 3840x2160 frame, 64 spp progressive accumulation, 64x64 screen tiles sharded over the
+ranks, scene and BVH replicated, no communication while samples accumulate, one delivery of the finished tiles per image; a step = one
+64-sample image.  The N = 1 line carries the same workload on one GPU as `strong_base`; the N > 1 lines carry round 1's weak-scaled
+workload (N x 1080p per-frame delivery) as `weak`.
 """
 import argparse
 import json
@@ -25,13 +27,8 @@ sys.path.insert(0, ROOT)
 FRAME_DIMS = {1: (1920, 1080), 2: (3840, 1080), 4: (3840, 2160), 8: (7680, 2160)}
 BOUNCES, SAMPLES = 4, 1
 HBM_BYTES_PER_RAY = 48          # 32 B rt3_ray read + 16 B rt3_hit written
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_trace_dyn<closest> launch of this workload (1.8 M secondary rays), from the committed
-# `ncu --set full` capture; algorithmic bytes of that launch = 48 B x 1.8 M = 86 MB
-NCU_TRACE_DRAM_BYTES_PER_LAUNCH = (82.71e6 + 76.04e6 + 70.74e6 + 13.64e6 + 8.22e6 + 6.65e6) / 3
-NCU_TRACE_DRAM_SOURCE = "profiles/r1j_k_trace_dyn_summary.txt (ncu --set full, mean of the frame's 3 launches: 76.5 MB read + 9.5 MB written)"
-# smsp__inst_executed.sum of the frame's three k_trace_dyn<closest> launches in the same capture (439.6 M + 378.4 M + 335.1 M warp instructions)
-# over the 5.40 M rays they traced: the instruction-issue view of the kernel (148 SMs x 4 schedulers x 1 warp instruction per clock)
-NCU_TRACE_WARP_INST_PER_RAY = (439578051 + 378415418 + 335107758) / (3 * 1.7993e6)
+# ncu counters of the dominant kernel (DRAM bytes and warp instructions per launch / per ray) are NOT literals here: they are read from
+# profiles/r2_trace_counters.json, which profiles/summarize.py writes from the committed `ncu --set full` capture of the current kernel
 FALLBACK_HBM_GBS = 6650.0       # /opt/skills/guides/B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 
 
@@ -201,13 +198,30 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ CUDA arm
-def run_cuda(args):
+CFG3_W, CFG3_H, CFG3_SPP = 3840, 2160, 64      # BASELINE configs[2]: one step = a 64-sample progressive 4K image
+
+
+def cfg3_params(sc, flags):
+    """configs[2] as written: 64 spp progressive accumulation = 64 frames x 1 spp, blendfactor 1/(n+1), Light / PrevLight ping-pong."""
+    from raytracer3_b200.camera import camera_for, make_params
+    cam = camera_for(sc, CAMERA, CFG3_W, CFG3_H)
+    return [make_params(cam, CFG3_W, CFG3_H, frame=n, bounces=BOUNCES, samples=1, blendfactor=1.0 / (n + 1), flags=flags) for n in range(CFG3_SPP)]
+
+
+def cfg3_step(R, params, slot):
+    """One step of configs[2] on this rank: 64 frames into the rank-local slabs (no communication), then ONE delivery of the finished tiles."""
+    R.cur = 0
+    light = None
+    for p in params:
+        light = R.frame(p)
+    return R.exchange(light, slot)
+
+
+def setup_cuda(args):
     import torch
     import torch.distributed as dist
-    from raytracer3_b200 import scenes
-    from raytracer3_b200.host import RenderContext, Renderer, RenderWorld, TiledRenderer
-    from raytracer3_b200.types import BUILD_TWO_LEVEL, FLAG_BLUENOISE, FLAG_ENV, RAY
-
+    from raytracer3_b200.host import RenderContext, RenderWorld
+    from raytracer3_b200.types import BUILD_ROTATIONS, BUILD_TWO_LEVEL
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -219,38 +233,89 @@ def run_cuda(args):
     if world_size > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
-    n_gpus = world_size
-    flags = FLAG_ENV | FLAG_BLUENOISE
-    W, H = frame_dims(n_gpus)
-
     global CAMERA
-    cfg5 = args.workload == "cfg5"
-    if cfg5:
+    if args.workload == "cfg5":
         CAMERA, args.no_extras = "cam_grid", True
     sc = make_scene(args.workload)
-    base_name = sc["name"].split("_grid")[0]
     ctx = RenderContext(local_rank)
     world = RenderWorld(ctx)
     world.load_scene(sc)
-    bs_first = world.create_acceleration_structure(1 | (BUILD_TWO_LEVEL if args.two_level else 0))     # first call: pool growth, allocations
-    bs = world.create_acceleration_structure(1 | (BUILD_TWO_LEVEL if args.two_level else 0))
-
-    tiled = n_gpus > 1
-    if tiled:
-        R = TiledRenderer(ctx, world, W, H, rank, world_size, tile=64)
-    else:
-        R = Renderer(ctx, world, W, H)
-
-    def step(i):
-        p = params_for(sc, W, H, i, flags)
-        if tiled:
-            return R.frame_gather_overlapped(p)     # the NCCL gather + un-tile of frame i overlap the tracing of frame i+1
-        return R.frame(p)
+    bflags = 1 | (BUILD_TWO_LEVEL if args.two_level else 0) | (BUILD_ROTATIONS if args.build == "rotations" else 0)
+    bs_first = world.create_acceleration_structure(bflags)     # first call: pool growth, allocations
+    bs = world.create_acceleration_structure(bflags)
 
     def barrier():
         if world_size > 1:
             dist.barrier()
         torch.cuda.synchronize()
+    return dict(rank=rank, world_size=world_size, local_rank=local_rank, all_cpus=all_cpus, numa_node=numa_node, sc=sc, ctx=ctx, world=world, bs=bs,
+                bs_first=bs_first, barrier=barrier, base_name=sc["name"].split("_grid")[0])
+
+
+def scene_config(S, args):
+    bs, bs_first = S["bs"], S["bs_first"]
+    return {"scene": S["base_name"], "triangles": int(bs.triangles), "wide_nodes": int(bs.wide_nodes), "bvh_mb": (bs.node_bytes + bs.tri_bytes) / 1e6,
+            "build": args.build + (" two-level" if args.two_level else ""), "build_ms": bs.ms_total, "build_first_call_ms": bs_first.ms_total,
+            "flags": "ENV|BLUENOISE", "bluenoise": S["sc"].get("bluenoise_source"), "strips": int(os.environ.get("RT3_STRIPS", "2"))}
+
+
+def roofline_objects(t_rays, t_ms, t_n, step_ms, prof_steps, clocks):
+    """`roofline` (HBM view, the contract's) and `roofline_issue` (the bound the kernel runs against) of the dominant kernel, the closest-hit
+    traversal over the secondary-ray queues, from its launches timed with CUDA events in the profiling pass."""
+    peak, peak_src = hbm_peak()
+    t_n = max(1.0, t_n)
+    achieved = (HBM_BYTES_PER_RAY * t_rays / t_n) / (t_ms / t_n * 1e-3) / 1e9 if t_ms > 0 else 0.0
+    cnt = trace_counters()
+    out = {"roofline": {"kernel": "k_trace_dyn<closest> (secondary-ray queues)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak, "traffic": cnt.get("dram_bytes_per_launch"), "traffic_source": cnt.get("source"), "peak_source": peak_src,
+                        "bytes_per_ray": HBM_BYTES_PER_RAY, "kernel_ms_per_launch": t_ms / t_n, "rays_per_launch": t_rays / t_n, "launches": int(t_n),
+                        "kernel_share_of_step": (t_ms / prof_steps) / step_ms if step_ms > 0 else None,
+                        "timing": f"CUDA events around every launch on its own stream, a second pass of {prof_steps} step(s) over the timed workload (the timed loop runs without them)",
+                        "note": "traversal is issue / L2-latency bound, not HBM bound: the BVH is L2-resident, HBM only streams 48 B per ray (roofline_issue, roofline_l2)"}}
+    try:
+        sm_mhz = float((clocks or {}).get("sm_mhz") or 1965.0)
+        issue_peak = 148 * 4 * sm_mhz * 1e6 / 1e9                                   # G warp instructions / s
+        wipr = cnt.get("warp_inst_per_ray")
+        issue_ach = wipr * (t_rays / (t_ms * 1e-3)) / 1e9 if (t_ms > 0 and wipr) else None
+        out["roofline_issue"] = {"kernel": "k_trace_dyn<closest> (secondary-ray queues)", "bound": "warp-instruction issue", "achieved": issue_ach, "peak": issue_peak,
+                                 "unit": "G warp-inst/s", "frac": issue_ach / issue_peak if issue_ach else None, "warp_inst_per_ray": wipr,
+                                 "active_lanes_per_inst": cnt.get("active_lanes_per_inst"), "source": cnt.get("source")}
+    except Exception:  # noqa: BLE001
+        pass
+    return out
+
+
+def trace_counters():
+    """ncu counters of the traversal kernel per launch, read from the committed capture of the CURRENT kernel (profiles/r2_trace_counters.json,
+    written by profiles/summarize.py counters from an `ncu --set full` report; the file names the commit it was taken at)."""
+    p = os.path.join(ROOT, "profiles", "r2_trace_counters.json")
+    try:
+        with open(p) as f:
+            return json.load(f)
+    except Exception:  # noqa: BLE001
+        return {"source": "profiles/r2_trace_counters.json missing"}
+
+
+def run_cuda(args):
+    S = setup_cuda(args)
+    if S["world_size"] > 1:
+        return run_multi(args, S)
+    return run_single(args, S)
+
+
+def run_single(args, S):
+    """N = 1: BASELINE configs[1] — 1920x1080, 4 bounces, 1 spp, environment light + blue-noise sampling; a step = one frame of both passes."""
+    import torch
+    from raytracer3_b200.host import Renderer, TiledRenderer
+    from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV
+    ctx, world, sc, bs, barrier, local_rank = S["ctx"], S["world"], S["sc"], S["bs"], S["barrier"], S["local_rank"]
+    flags = FLAG_ENV | FLAG_BLUENOISE
+    W, H = frame_dims(1)
+    cfg5 = args.workload == "cfg5"
+    R = Renderer(ctx, world, W, H)
+
+    def step(i):
+        return R.frame(params_for(sc, W, H, i, flags))
 
     for i in range(args.warmup):
         step(i)
@@ -263,8 +328,6 @@ def run_cuda(args):
         ev0.record()
         for i in range(args.steps):
             step(args.warmup + i)
-        if tiled:
-            R.drain()                                # the last frame's gather must be inside the timed region
         ev1.record()
         barrier()
         ms = ev0.elapsed_time(ev1)
@@ -276,58 +339,25 @@ def run_cuda(args):
         ctx.profile_enable(True)
         for i in range(prof_steps):
             step(args.warmup + i)
-        if tiled:
-            R.drain()
         barrier()
         trace_ms, trace_launches = ctx.profile_read()
         ctx.profile_enable(False)
         prof_cnt = ctx.counters(reset=True)
         # the NVML polling thread belongs to the device-timed region above and stops here: its driver queries contend with the launches
-        # and event waits of the host loop below (with it running, single runs of this loop came out up to 2x slower: 4.36 / 7.8 ms a frame)
+        # and event waits of the host loop below (with it running, single runs of this loop came out up to 2x slower)
         clocks.__exit__()
 
-        # ---- end to end through the host-buffer C ABI call (N = 1) / tile path + gather + D2H (N > 1)
-        host_light = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
-        e2e_steps = max(3, min(2 * args.steps, 60))
-        e2e_params = {i: params_for(sc, W, H, i, flags) for i in list(range(2)) + list(range(100, 100 + e2e_steps)) + list(range(200, 200 + e2e_steps))}   # GConst blocks of the frames, built ahead (host memory)
+        # ---- end to end through the host-buffer C ABI call: rt3_frame_submit_host / rt3_frame_wait, 3 frames in flight
         FRAMES_IN_FLIGHT = 3                                   # the reference's swapchain.rs:8
-        host_ring = [host_light] + [torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() for _ in range(FRAMES_IN_FLIGHT - 1)] if not tiled else []
+        e2e_steps = max(3, min(2 * args.steps, 60))
+        e2e_params = {i: params_for(sc, W, H, i, flags) for i in list(range(2)) + list(range(100, 100 + e2e_steps)) + list(range(200, 200 + e2e_steps))}
+        host_ring = [torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() for _ in range(FRAMES_IN_FLIGHT)]
         tickets = []
-        shm_path = None
-        if tiled:
-            # one host framebuffer ring shared by the ranks of the node (POSIX shared memory, page-locked in every process): each
-            # rank reads back its own band of rows of the gathered frame, so D2H per GPU stays at 1920x1080x16 B for every N
-            shm_path = f"/dev/shm/rt3_bench_{os.environ.get('MASTER_PORT', '0')}_{W}x{H}"
-            nbytes = FRAMES_IN_FLIGHT * H * W * 16
-            if rank == 0:
-                with open(shm_path, "wb") as f:
-                    f.truncate(nbytes)
-            barrier()
-            shared = torch.from_file(shm_path, shared=True, size=FRAMES_IN_FLIGHT * H * W * 4, dtype=torch.float32).view(FRAMES_IN_FLIGHT, H, W, 4)
-            band = H // world_size
-            # first touch: every rank writes ITS band of every frame of the (still sparse) file, from CPUs of its GPU's NUMA node, so the
-            # pages it will receive D2H traffic on are allocated there instead of all on the node of whichever rank pins the file first
-            for k in range(FRAMES_IN_FLIGHT):
-                shared[k][rank * band:(H if rank == world_size - 1 else (rank + 1) * band)].zero_()
-            barrier()
-            err = torch.cuda.cudart().cudaHostRegister(shared.data_ptr(), nbytes, 0)
-            assert int(err) == 0, f"cudaHostRegister failed: {err}"
-            R.enable_host_output([shared[k] for k in range(FRAMES_IN_FLIGHT)], rank * band, H if rank == world_size - 1 else (rank + 1) * band)
-            diag_no_d2h = bool(os.environ.get("RT3_DIAG_NO_D2H"))      # diagnosis only (never a reported number): gather without the read-back
-            if diag_no_d2h:
-                R.row1 = R.row0
 
-        def e2e_step(i):
-            p = e2e_params[i]
-            if tiled:                                           # params go H2D inside the pass calls
-                tickets.append(R.submit_frame_host(p))
-                if len(tickets) >= FRAMES_IN_FLIGHT:
-                    R.wait_frame(tickets.pop(0))
-            else:
-                # frames in flight: frame i renders while frame i-1 is read back; a frame's host buffer is handed back after its wait
-                tickets.append(R.submit_frame_host(p, host_ring[i % FRAMES_IN_FLIGHT].data_ptr()))
-                if len(tickets) >= FRAMES_IN_FLIGHT:
-                    R.wait_frame(tickets.pop(0))
+        def e2e_step(i):    # frame i renders while frame i-1 is read back; a frame's host buffer is handed back after its wait
+            tickets.append(R.submit_frame_host(e2e_params[i], host_ring[i % FRAMES_IN_FLIGHT].data_ptr()))
+            if len(tickets) >= FRAMES_IN_FLIGHT:
+                R.wait_frame(tickets.pop(0))
 
         def e2e_drain():
             while tickets:
@@ -344,95 +374,248 @@ def run_cuda(args):
         barrier()
         e2e_s = time.perf_counter() - t0
         e2e_cnt = ctx.counters(reset=True)
-        e2e_verified = None
         e2e_last = 100 + e2e_steps - 1                          # frame index of the last end-to-end frame: the parity leg re-renders it on the CPU
-        e2e_last_host = host_ring[e2e_last % FRAMES_IN_FLIGHT].numpy().copy() if not tiled else None
-        if tiled:
-            # outside the timed region: the frame assembled in shared host memory from the ranks' bands == the gathered device frame
-            k_last = (R.next_ticket - 1) % FRAMES_IN_FLIGHT
-            if rank == 0 and not diag_no_d2h:
-                e2e_verified = bool(torch.equal(shared[k_last], R.frame_ring[k_last].cpu()))
-                assert e2e_verified, "host frame assembled from the ranks' row bands differs from the gathered device frame"
-            torch.cuda.cudart().cudaHostUnregister(shared.data_ptr())
-            barrier()
-            if rank == 0:
-                os.unlink(shm_path)
-        sync_e2e_ms = None
-        if not tiled:                                          # also the synchronous single-call path, for comparison
-            t1 = time.perf_counter()
-            for i in range(e2e_steps):
-                R.render_frame_host(e2e_params[200 + i], host_light.data_ptr())
-            sync_e2e_ms = 1e3 * (time.perf_counter() - t1) / e2e_steps
-    os.sched_setaffinity(0, all_cpus)      # the CPU legs below (cpu_baseline) use every host core again
-    rays_local = cnt.rays_primary + cnt.rays_secondary
-    stats = torch.tensor([ms, float(rays_local), float(cnt.paths_started), float(e2e_s), float(e2e_cnt.rays_primary + e2e_cnt.rays_secondary),
-                          float(launches), float(prof_cnt.rays_secondary), float(trace_ms), float(trace_launches)], dtype=torch.float64, device=f"cuda:{local_rank}")
-    if world_size > 1:
-        mx = stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms, e2e_s = float(mx[0]), float(mx[3])
-        rays, paths, e2e_rays, launches_all = float(sm[1]), float(sm[2]), float(sm[4]), float(sm[5])
-    else:
-        rays, paths, e2e_rays, launches_all = float(stats[1]), float(stats[2]), float(stats[4]), float(stats[5])
-
-    if rank == 0:
-        value = rays / (ms * 1e-3) / 1e6
-        peak, peak_src = hbm_peak()
-        # dominant kernel: k_trace (closest hit over the secondary-ray queues); algorithmic HBM bytes = 48 B per ray
-        t_rays, t_ms, t_n = float(stats[6]), float(stats[7]), max(1.0, float(stats[8]))
-        achieved = (HBM_BYTES_PER_RAY * t_rays / t_n) / (t_ms / t_n * 1e-3) / 1e9 if t_ms > 0 else 0.0
-        line = {
-            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "spp_per_s": paths / (ms * 1e-3), "rays_per_step": rays / args.steps,
-            "config": {"workload": (f"8x8 instanced {base_name} (" + ("two-level BLAS/TLAS" if args.two_level else "flattened") + ")" if cfg5 else base_name)
-                                   + f" {W}x{H} path tracing, bounces={BOUNCES}, {SAMPLES} spp, env light + blue noise (BASELINE configs[{4 if cfg5 else 1}]"
-                                   + (f", weak-scaled to {n_gpus} x 1920x1080 pixels over 64x64 screen tiles + NCCL all_gather per frame)" if tiled else ")"),
-                       "scene": base_name, "triangles": int(bs.triangles), "wide_nodes": int(bs.wide_nodes), "bvh_mb": (bs.node_bytes + bs.tri_bytes) / 1e6,
-                       "build_ms": bs.ms_total, "build_first_call_ms": bs_first.ms_total, "flags": "ENV|BLUENOISE", "parallelism": f"tiles{n_gpus}",
-                       "l2_policy": "per-frame buffers (G-buffer, depth, Light, ray/hit/path queues: ~%d MB) exceed the 126 MB L2 between steps; the "
-                                    "scene + BVH stay L2-resident across frames by design (static scene)" % int(W * H / n_gpus * (16 + 4 + 16 + 2 * 32 + 16 + 2 * 16 + 20) / 1e6)},
-            "clocks": clocks.summary(),
-            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 304 * (n_gpus if tiled else 1),
-                    "d2h_bytes_per_step": W * H * 16, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
-                    "path": "rt3_frame_submit_host / rt3_frame_wait, 3 frames in flight (params H2D, RGBA32F frame D2H to pinned memory, every frame "
-                            "waited for inside the timed region)" if not tiled else
-                            "rt3_pass_*_tiles + all_gather + rt3_untile, 3 frames in flight; every rank reads its band of rows of the gathered frame back "
-                            "into one page-locked host frame shared by the ranks (POSIX shm), every frame waited for inside the timed region",
-                    "sync_ms_per_step": sync_e2e_ms, "host_frame_verified": e2e_verified, "host_numa_node_rank0": numa_node},
-            "gpu_launches": int(launches_all),
-            "roofline": {"kernel": "k_trace<closest> (secondary-ray queues)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": NCU_TRACE_DRAM_BYTES_PER_LAUNCH, "traffic_source": NCU_TRACE_DRAM_SOURCE, "peak_source": peak_src, "bytes_per_ray": HBM_BYTES_PER_RAY,
-                         "kernel_ms_per_launch": t_ms / t_n, "rays_per_launch": t_rays / t_n, "launches": int(t_n),
-                         "kernel_share_of_step": (t_ms / prof_steps) / (ms / args.steps) if ms > 0 else None,
-                         "timing": f"CUDA events around every launch on its own stream, second pass of {prof_steps} steps over the timed frames (the timed loop itself runs without them)",
-                         "note": "traversal is L2-latency/issue bound, not HBM bound: the BVH is L2-resident, HBM only streams 48 B per ray (see roofline_l2)"},
-        }
-        try:    # supplementary: the bound the traversal kernel actually runs against; never allowed to break the line
-            sm_mhz = float((line["clocks"] or {}).get("sm_mhz") or 1965.0)
-            issue_peak = 148 * 4 * sm_mhz * 1e6 / 1e9                                   # G warp instructions / s
-            issue_ach = NCU_TRACE_WARP_INST_PER_RAY * (t_rays / (t_ms * 1e-3)) / 1e9 if t_ms > 0 else None
-            line["roofline_issue"] = {"kernel": "k_trace<closest> (secondary-ray queues)", "bound": "warp-instruction issue", "achieved": issue_ach, "peak": issue_peak,
-                                      "unit": "G warp-inst/s", "frac": issue_ach / issue_peak if issue_ach else None, "warp_inst_per_ray": NCU_TRACE_WARP_INST_PER_RAY,
-                                      "source": "instructions per ray from " + NCU_TRACE_DRAM_SOURCE.split(" (")[0] + " (smsp__inst_executed.sum), rays/s measured live; "
-                                                "18.6 of 32 lanes active per instruction in that capture"}
+        e2e_last_host = host_ring[e2e_last % FRAMES_IN_FLIGHT].numpy().copy()
+        t1 = time.perf_counter()                               # also the synchronous single-call path, for comparison
+        for i in range(e2e_steps):
+            R.render_frame_host(e2e_params[200 + i], host_ring[0].data_ptr())
+        sync_e2e_ms = 1e3 * (time.perf_counter() - t1) / e2e_steps
+    os.sched_setaffinity(0, S["all_cpus"])      # the CPU legs below (cpu_baseline) use every host core again
+    rays = float(cnt.rays_primary + cnt.rays_secondary)
+    e2e_rays = float(e2e_cnt.rays_primary + e2e_cnt.rays_secondary)
+    value = rays / (ms * 1e-3) / 1e6
+    cfg = scene_config(S, args)
+    cfg.update({"workload": (f"8x8 instanced {S['base_name']} (" + ("two-level BLAS/TLAS" if args.two_level else "flattened") + ")" if cfg5 else S["base_name"])
+                            + f" {W}x{H} path tracing, bounces={BOUNCES}, {SAMPLES} spp, env light + blue noise (BASELINE configs[{4 if cfg5 else 1}])",
+                "parallelism": "tiles1",
+                "l2_policy": "per-frame buffers (G-buffer, depth, Light, ray/hit/path queues: ~%d MB) exceed the 126 MB L2 between steps; the scene + BVH "
+                             "stay L2-resident across frames by design (static scene)" % int(W * H * (16 + 4 + 16 + 2 * 32 + 16 + 2 * 16 + 24) / 1e6)})
+    line = {
+        "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "spp_per_s": float(cnt.paths_started) / (ms * 1e-3), "rays_per_step": rays / args.steps,
+        "config": cfg, "clocks": clocks.summary(),
+        "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 304, "d2h_bytes_per_step": W * H * 16, "steps": e2e_steps,
+                "ms_per_step": 1e3 * e2e_s / e2e_steps,
+                "path": "rt3_frame_submit_host / rt3_frame_wait, 3 frames in flight (params H2D, RGBA32F frame D2H to pinned memory, every frame waited "
+                        "for inside the timed region)",
+                "sync_ms_per_step": sync_e2e_ms, "host_frame_verified": None, "host_numa_node_rank0": S["numa_node"]},
+        "gpu_launches": int(launches),
+    }
+    line.update(roofline_objects(float(prof_cnt.rays_secondary), float(trace_ms), float(trace_launches), ms / args.steps, prof_steps, line["clocks"]))
+    failed = None
+    if not args.no_extras:
+        line.update(extras(ctx, world, sc, bs, 0.0))
+        try:    # the L2 view of the TIMED kernel: ncu's lts__t_sectors per ray of the in-frame launches x the rays/s measured live
+            tc, rl = trace_counters(), line["roofline"]
+            rays_s = rl["rays_per_launch"] / (rl["kernel_ms_per_launch"] * 1e-3)
+            ach = tc["l2_bytes_per_ray"] * rays_s / 1e9
+            line["roofline_l2_inframe"] = {"kernel": "k_trace_dyn<closest> (secondary-ray queues of the timed frames)", "bound": "l2", "achieved": ach,
+                                           "peak": line["roofline_l2"]["peak"], "unit": "GB/s", "frac": ach / line["roofline_l2"]["peak"],
+                                           "bytes_per_ray": tc["l2_bytes_per_ray"], "source": tc["source"] + " (lts__t_sectors.sum x 32 B: all L2 traffic of the kernel)"}
         except Exception:  # noqa: BLE001
             pass
-        line["config"]["bluenoise"] = sc.get("bluenoise_source")
-        failed = None
-        if not args.no_extras:
-            line.update(extras(ctx, world, sc, bs, t_rays / (t_ms * 1e-3) if t_ms > 0 else 0.0))
-            keep = {}
-            line["cpu_baseline"] = cpu_baseline(sc, flags, frame=e2e_last if not tiled else 1, keep=keep)
-            if not tiled:
-                line["parity"], failed = parity_check(R, sc, W, H, flags, keep, e2e_last_host)
-                line["e2e"]["host_frame_verified"] = line["parity"]["host_frame_bit_identical"]
+        # the strong-scaling workload of --gpus N > 1 (configs[2]) on this one GPU, through the same tile path: the N = 1 point of that curve
+        Rt = TiledRenderer(ctx, world, CFG3_W, CFG3_H, 0, 1, tile=64)
+        Rt.setup_exchange()
+        p3 = cfg3_params(sc, flags)
+        cfg3_step(Rt, p3[:4], 0)
+        barrier()
+        ctx.counters(reset=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        cfg3_step(Rt, p3, 1)
+        e1.record()
+        barrier()
+        c3 = ctx.counters(reset=True)
+        ms3 = e0.elapsed_time(e1)
+        line["strong_base"] = {"workload": f"{CFG3_W}x{CFG3_H}, {CFG3_SPP} spp progressive (BASELINE configs[2]), one step on this GPU through the tile path",
+                               "value": (c3.rays_primary + c3.rays_secondary) / (ms3 * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms3,
+                               "note": "what bench.py --gpus N > 1 reports as `value` is this workload sharded over N GPUs"}
+        del Rt
+        keep = {}
+        line["cpu_baseline"] = cpu_baseline(sc, flags, frame=e2e_last, keep=keep)
+        line["parity"], failed = parity_check(R, sc, W, H, flags, keep, e2e_last_host)
+        line["e2e"]["host_frame_verified"] = line["parity"]["host_frame_bit_identical"]
+    print(json.dumps(line), flush=True)
+    if failed:
+        raise SystemExit("PARITY FAILURE: " + failed)
+
+
+def measure_steps(step_fn, steps, barrier, torch):
+    """K steps bracketed by barrier + synchronize on both sides, timed with CUDA events on the current stream."""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for k in range(steps):
+        step_fn(k)
+    e1.record()
+    barrier()
+    return e0.elapsed_time(e1)
+
+
+def run_multi(args, S):
+    """N > 1: STRONG scaling of BASELINE configs[2] — a fixed 3840x2160 frame, 64 spp progressive accumulation, 64x64 screen tiles sharded over
+    the ranks, scene and BVH replicated, no communication while samples accumulate and ONE delivery of the finished tiles per image (each
+    rank ends up with the band of rows it presents).  A step = one 64-sample image.  Extra key `weak`: round 1's weak-scaled workload
+    (N x 1080p, 1 spp, one delivery per frame)."""
+    import torch
+    import torch.distributed as dist
+    from raytracer3_b200.host import Renderer, TiledRenderer
+    from raytracer3_b200.types import FLAG_BLUENOISE, FLAG_ENV
+    ctx, world, sc, barrier = S["ctx"], S["world"], S["sc"], S["barrier"]
+    rank, N, local_rank = S["rank"], S["world_size"], S["local_rank"]
+    dev = f"cuda:{local_rank}"
+    flags = FLAG_ENV | FLAG_BLUENOISE
+    W, H = CFG3_W, CFG3_H
+    R = TiledRenderer(ctx, world, W, H, rank, N, tile=args.tile)
+    mode = R.setup_exchange(args.exchange, slots=2)
+    p3 = cfg3_params(sc, flags)
+
+    def step(k):
+        return cfg3_step(R, p3, k % 2)
+
+    for k in range(args.warmup):
+        step(k)
+    barrier()
+    ctx.counters(reset=True)
+    launches0 = ctx.kernel_launches()
+    with ClockSampler(local_rank) as clocks:
+        ms = measure_steps(step, args.steps, barrier, torch)
+        launches = ctx.kernel_launches() - launches0
+        cnt = ctx.counters(reset=True)
+        ctx.profile_enable(True)                               # second, untimed pass: per-launch times of the traversal kernel
+        step(0)
+        barrier()
+        trace_ms, trace_launches = ctx.profile_read()
+        ctx.profile_enable(False)
+        prof_cnt = ctx.counters(reset=True)
+        clocks.__exit__()
+
+    # ---- end to end: the same steps, every image read back into ONE page-locked host frame shared by the ranks (POSIX shm); each rank
+    # reads back its own band of rows over its own PCIe link; wall clock, every image in host memory before the clock stops
+    shm_path = f"/dev/shm/rt3_bench_{os.environ.get('MASTER_PORT', '0')}_{W}x{H}"
+    SLOTS = 2
+    nbytes = SLOTS * H * W * 16
+    if rank == 0:
+        with open(shm_path, "wb") as f:
+            f.truncate(nbytes)
+    barrier()
+    shared = torch.from_file(shm_path, shared=True, size=SLOTS * H * W * 4, dtype=torch.float32).view(SLOTS, H, W, 4)
+    for k in range(SLOTS):                                     # first touch from the CPUs of this GPU's NUMA node
+        shared[k][R.row0:R.row1].zero_()
+    barrier()
+    err = torch.cuda.cudart().cudaHostRegister(shared.data_ptr(), nbytes, 0)
+    assert int(err) == 0, f"cudaHostRegister failed: {err}"
+    copied = [torch.cuda.Event() for _ in range(SLOTS)]
+
+    def e2e_step(k):
+        copied[k % SLOTS].synchronize()                        # the host frame of image k - 2 has been handed over
+        band = step(k)
+        R.read_back(band, shared[k % SLOTS])
+        copied[k % SLOTS].record()
+
+    e2e_steps = max(2, min(args.steps, 10))
+    for k in range(2):
+        e2e_step(k)
+    barrier()
+    ctx.counters(reset=True)
+    t0 = time.perf_counter()
+    for k in range(e2e_steps):
+        e2e_step(k)
+    for e in copied:
+        e.synchronize()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    e2e_cnt = ctx.counters(reset=True)
+    last_slot = (e2e_steps - 1) % SLOTS
+
+    # ---- weak scaling (round 1's --gpus N workload), kept as an extra key: N x 1080p pixels, 1 spp, one delivery per frame overlapped with
+    # the next frame's tracing
+    Ww, Hw = frame_dims(N)
+    Rw = TiledRenderer(ctx, world, Ww, Hw, rank, N, tile=args.tile)
+    Rw.setup_exchange(mode, slots=2)
+    wsteps = max(3, min(args.steps * 4, 40))
+    wparams = [params_for(sc, Ww, Hw, i, flags) for i in range(wsteps + 3)]
+
+    def wstep(k):
+        Rw.frame_exchange_overlapped(wparams[k % len(wparams)], k % 2)
+    for k in range(3):
+        wstep(k)
+    Rw.drain()
+    barrier()
+    ctx.counters(reset=True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for k in range(wsteps):
+        wstep(k)
+    Rw.drain()
+    e1.record()
+    barrier()
+    wms = e0.elapsed_time(e1)
+    wcnt = ctx.counters(reset=True)
+
+    # ---- verification, outside every timed region: rank 0 renders the whole 64-sample image ALONE, un-tiled, and compares it bit for bit
+    # with the image the ranks assembled in host memory; the same run is the single-GPU point of the strong-scaling curve
+    verified, single = None, None
+    if rank == 0:
+        r1 = Renderer(ctx, world, W, H)
+        torch.cuda.synchronize()
+        e0.record()
+        alone = None
+        for p in p3:
+            alone = r1.frame(p)
+        e1.record()
+        torch.cuda.synchronize()
+        single_ms = e0.elapsed_time(e1)
+        c1 = ctx.counters(reset=True)
+        verified = bool(torch.equal(shared[last_slot].view(torch.int32), alone.cpu().view(torch.int32)))
+        single = {"value": (c1.rays_primary + c1.rays_secondary) / (single_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": single_ms,
+                  "note": "the same 64-sample image rendered by rank 0 alone (full-frame passes, first run: includes its allocations) while the other ranks wait"}
+    barrier()
+    torch.cuda.cudart().cudaHostUnregister(shared.data_ptr())
+    barrier()
+    if rank == 0:
+        os.unlink(shm_path)
+
+    rays_local = float(cnt.rays_primary + cnt.rays_secondary)
+    stats = torch.tensor([ms, rays_local, float(cnt.paths_started), e2e_s, float(e2e_cnt.rays_primary + e2e_cnt.rays_secondary), float(launches),
+                          float(prof_cnt.rays_secondary), float(trace_ms), float(trace_launches), wms, float(wcnt.rays_primary + wcnt.rays_secondary)],
+                         dtype=torch.float64, device=dev)
+    mx = stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        ms, e2e_s, wms = float(mx[0]), float(mx[3]), float(mx[9])
+        rays, paths, e2e_rays, launches_all, wrays = float(sm[1]), float(sm[2]), float(sm[4]), float(sm[5]), float(sm[10])
+        cfg = scene_config(S, args)
+        cfg.update({"workload": f"{S['base_name']} {W}x{H} path tracing, bounces={BOUNCES}, {CFG3_SPP} spp progressive accumulation (64 frames x 1 spp, "
+                                f"blendfactor 1/(n+1)), env light + blue noise, {args.tile}x{args.tile} screen tiles sharded over {N} GPUs, one delivery of "
+                                "the finished tiles per image (BASELINE configs[2])",
+                    "parallelism": f"tiles{N}", "tile": args.tile, "delivery": mode, "delivery_note": R.exchange_note,
+                    "tiles_per_rank": int(R.n_real), "rays_max_over_mean": float(mx[1]) / (float(sm[1]) / N),
+                    "l2_policy": "per-frame buffers of a rank (slabs, queues) exceed the 126 MB L2 between steps at N <= 4; scene + BVH L2-resident by design"})
+        line = {
+            "metric": "Mrays/s", "value": rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "spp_per_s": paths / (ms * 1e-3), "rays_per_step": rays / args.steps, "config": cfg, "clocks": clocks.summary(),
+            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 304 * CFG3_SPP * N, "d2h_bytes_per_step": W * H * 16,
+                    "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
+                    "path": "rt3_pass_*_tiles x 64 frames + one delivery (" + mode + ") per image; every rank reads its band of rows back into one page-locked "
+                            "host frame shared by the ranks (POSIX shm); every image in host memory before the clock stops",
+                    "host_frame_verified": verified, "host_numa_node_rank0": S["numa_node"]},
+            "gpu_launches": int(launches_all),
+            "gathered_equals_single_gpu_image": verified,
+            "single_gpu_same_workload": single,
+            "weak": {"value": wrays / (wms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": wms / wsteps, "steps": wsteps,
+                     "workload": f"{Ww}x{Hw} (N x 1920x1080 pixels), 1 spp, one delivery per frame overlapped with the next frame (round 1's --gpus N workload)"},
+        }
+        line.update(roofline_objects(float(stats[6]), float(stats[7]), float(stats[8]), ms / args.steps, 1, line["clocks"]))
         print(json.dumps(line), flush=True)
-        if failed:
-            raise SystemExit("PARITY FAILURE: " + failed)
-    if world_size > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    dist.barrier()
+    dist.destroy_process_group()
+    if rank == 0 and verified is False:
+        raise SystemExit("PARITY FAILURE: the image assembled from the ranks' bands differs from the single-GPU image")
 
 
 def extras(ctx, world, sc, bs, trace_rays_per_s):
@@ -516,6 +699,9 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg5"], help="cfg2 = BASELINE configs[1] (default, the headline); cfg5 = configs[4], 8x8 instanced grid")
     ap.add_argument("--two-level", action="store_true", help="RT3_BUILD_TWO_LEVEL (BLAS per mesh + TLAS over the instances)")
     ap.add_argument("--no-extras", action="store_true", help="skip the microbench / L2 roofline / cpu_baseline legs")
+    ap.add_argument("--build", default="treelet", choices=["treelet", "rotations"], help="FAST_TRACE quality level (rt3.h): treelet restructuring (default) or tree rotations")
+    ap.add_argument("--tile", type=int, default=64, help="screen-tile size of the multi-GPU path")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "a2a"], help="delivery of the finished tiles: peer-memory stores, NCCL all_to_all, or p2p when available")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":

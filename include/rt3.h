@@ -26,7 +26,12 @@
  *     the internal wavefront queues.  `*_host` variants take HOST pointers and do the copies
  *     themselves (the end-to-end path a non-CUDA host such as the Rust renderer would use).
  *   - Pass calls are asynchronous on `cuda_stream` (a cudaStream_t cast to void*, NULL = default
- *     stream): the analogue of recording into the reference's command buffer.
+ *     stream): the analogue of recording into the reference's command buffer.  The pass / trace calls
+ *     of ONE context share its internal queues, so they execute in CALL ORDER whatever streams they are
+ *     given: a call on another stream than the previous call's first waits, on the device, for the
+ *     previous call's work (one event per call; no host synchronisation).  Use one context per stream
+ *     for work that is meant to overlap.  Internally rt3_pass_reference splits the frame into strips that
+ *     run as concurrent wavefronts on the context's own streams and joins them back into `cuda_stream`.
  *   - A context is bound to one CUDA device; it is thread-compatible, not thread-safe.
  *   - There is NO CPU fallback: without a CUDA device rt3_create fails with RT3_ERR_NO_DEVICE.
  */
@@ -82,7 +87,7 @@ typedef struct {
     float    window_size[2];
     uint32_t frame;
     float    blendfactor;
-    uint32_t bounces, samples;
+    uint32_t bounces, samples;          /* limits of this implementation: bounces <= 255, 1 <= samples < 2^24 */
     uint32_t proberng;
     float    cell_size;
     uint32_t mouse[2];
@@ -177,11 +182,15 @@ RT3_API rt3_status rt3_pass_postprocess(rt3_context*, const rt3_params*, rt3_rec
 /* Screen-space probe GI: shaders/old/trace_probes.slang, spherical_harmonic_conversion.slang,
  * interpolate_probes.slang.  One probe per 16x16 pixels, 8x8 octahedral directions per probe.
  *   atlas       (W/16*8) x (H/16*8) RGBA32F: rgb = radiance along the direction (blended with prev_atlas by blendfactor), a = hit distance
- *   directions  optional u16 per atlas texel (structured_importance_sampling.slang:55-69: bit 15 = mip, low bits = direction index);
- *               NULL = the uniform assignment (texel k of a probe traces octahedral cell k)
+ *   directions  optional u16 per atlas texel (structured_importance_sampling.slang:55-69: bit 15 = mip, low bits = direction index), as written
+ *               by rt3_pass_probe_sis; NULL = the uniform assignment (texel k of a probe traces octahedral cell k)
  *   sh          rt3_probe_layout().sh_records records of 9 floats (float3x3 = SH L2), Z-curve indexed by (probe.x * 3 + channel, probe.y)
  * The probe shaders of the reference are in a debug state; include/rt3_shared_math.h documents line by line what is restated. */
 RT3_API rt3_status rt3_probe_layout(const rt3_params*, uint32_t* atlas_w, uint32_t* atlas_h, uint32_t* sh_records);
+/* shaders/old/structured_importance_sampling.slang:19-72: one u16 direction word per atlas texel from the probe's 16x16 G-buffer normals
+ * (64 threads per probe, shared-memory bitonic sort; the LIVE lines of the shader, include/rt3_shared_math.h).  The G-buffer image must be
+ * defined on every pixel the probes cover (background pixels keep whatever the image held: clear it once). */
+RT3_API rt3_status rt3_pass_probe_sis(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, uint16_t* directions_r16ui, void* cuda_stream);
 RT3_API rt3_status rt3_pass_probe_trace(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, const float* depth_r32f,
                                         const uint16_t* opt_directions_r16ui, const float* prev_atlas_rgba32f, float* atlas_rgba32f, void* cuda_stream);
 RT3_API rt3_status rt3_pass_probe_sh(rt3_context*, const rt3_params*, const float* atlas_rgba32f, float* sh, void* cuda_stream);
@@ -200,6 +209,13 @@ RT3_API rt3_status rt3_pass_reference_tiles(rt3_context*, const rt3_params*, con
 /* Scatter a gathered slab (n_tiles tiles of tile_w x tile_h RGBA32F) into a full frame of pitch frame_w. */
 RT3_API rt3_status rt3_untile_rgba32f(rt3_context*, const rt3_rect* tiles, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h,
                                       const float* slab, float* frame, uint32_t frame_w, uint32_t frame_h, void* cuda_stream);
+
+/* Peer-memory delivery (multi-GPU): tile k of `slab` is stored at dst_top_left[k], the DEVICE address of the tile's top-left pixel in the
+ * frame (or band of rows) of whoever presents it — this GPU's memory or a peer's mapped over NVLink (cudaIpc / VMM / torch symmetric
+ * memory) — rows dst_pitch_px pixels apart.  Empty rects are skipped.  Both arrays are HOST arrays of n_tiles entries.  The caller
+ * synchronises with the destination's owner afterwards (a barrier); see raytracer3_b200/host.py TiledRenderer.exchange. */
+RT3_API rt3_status rt3_scatter_tiles_rgba32f(rt3_context*, const rt3_rect* tiles, const uint64_t* dst_top_left, uint32_t n_tiles, uint32_t tile_w,
+                                             uint32_t tile_h, const float* slab, uint32_t dst_pitch_px, void* cuda_stream);
 
 /* ---- raw queries == trace() / TraceRay ------------------------------------------------------ */
 RT3_API rt3_status rt3_trace_closest(rt3_context*, const rt3_ray* rays, uint64_t n, rt3_hit* out, void* cuda_stream);

@@ -1065,9 +1065,42 @@ RT3_HD vec3 sh3_unproject_cos_lobe(const sh3& r, const sh3& g, const sh3& b, vec
 RT3_HD uint32_t probe_count_x(const rt3_params& p) { return (uint32_t)p.window_size[0] / 16u; }
 RT3_HD uint32_t probe_count_y(const rt3_params& p) { return (uint32_t)p.window_size[1] / 16u; }
 /* Direction word of an atlas texel (structured_importance_sampling.slang:55-69): bit 15 = mip, low 15 bits = direction index on
- * a grid of (8 << mip)^2 cells.  The reference's refinement never triggers (see above), leaving the uniform assignment of its
- * else-branch (:67): mip 0, index = thread index inside the probe. */
+ * a grid of (8 << mip)^2 cells.  probe_uniform_direction is the assignment of the shader's else-branch (:69): mip 0, index = thread
+ * index inside the probe; rt3_pass_probe_trace uses it when no direction image is bound. */
 RT3_HD uint32_t probe_uniform_direction(uint32_t ax, uint32_t ay) { return (ay & 7u) * 8u + (ax & 7u); }
+/* ---- structured_importance_sampling.slang:19-72, the LIVE lines --------------------------------------------------------------------
+ * One 8x8 thread group per probe; thread ti = ly * 8 + lx owns octahedral cell ti and 2x2 of the probe's 16x16 pixels.
+ *   :25-32  normals[ti * 4 + y * 2 + x] = unpack_normal(gbuffer[(probe * 8 + (lx, ly)) * 2 + (x, y)])
+ *   :35-41  brdf_pdf = sum_{i < 256, in index order} max(dot(normals[i], dir(ti)), 0) / 256,  dir(ti) = octa_decode((cell + 0.5) / 8)
+ *   :44-47  pdf = brdf_pdf (the `* light_pdf` factor is commented out); pdfs[ti] = pdf; bitonic sort of pdfs, ASCENDING (math.slang:142-163)
+ *   :49-52  `brdf_pdf < 0` never holds (a sum of max(., 0)): index stays -1, culled_rays stays 0
+ *   :55     the test is therefore `pdfs[0] < pdf`, pdfs[0] being the MINIMUM of the probe's 64 pdfs
+ *   :57-66  true (every thread whose pdf exceeds the minimum): out = 0x8000 | ti * 4   (mip 1: cell ti * 4 of the 16x16 grid)
+ *   :68-70  false (the minimum-pdf thread(s)):                 out = ti              (mip 0: the thread's own cell)
+ * The index array passed to the sort (pdf_directions, never initialised) is only read in the branch that cannot be taken.  What the
+ * shader seems to INTEND (refine where the pdf is high, `+ index % 3 + 1`) is commented out in the reference and is not restated. */
+RT3_HD vec3 probe_sis_direction(uint32_t ti) {
+    vec2 f; f.x = (float(ti % 8u) + 0.5f) / 8.0f; f.y = (float(ti / 8u) + 0.5f) / 8.0f;     /* :34-35 */
+    return octa_decode(f);
+}
+RT3_HD float probe_sis_pdf(const vec3* normals256, vec3 dir) {                             /* :37-40 */
+    float pdf = 0.0f;
+    for (int i = 0; i < 256; ++i) pdf = pdf + max_(dot(normals256[i], dir), 0.0f) / 256.0f;
+    return pdf;
+}
+RT3_HD uint32_t probe_sis_word(float pdf, float min_pdf, uint32_t ti) {                    /* :55-70 with index == -1, culled_rays == 0 */
+    return (min_pdf < pdf) ? (0x8000u | (ti * 4u)) : ti;
+}
+/* pixel whose G-buffer normal lands in normals[ti * 4 + y * 2 + x] (:25-31) */
+RT3_HD void probe_sis_pixel(uint32_t pcx, uint32_t pcy, uint32_t ti, uint32_t x, uint32_t y, uint32_t& px, uint32_t& py) {
+    px = (pcx * 8u + ti % 8u) * 2u + x; py = (pcy * 8u + ti / 8u) * 2u + y;
+}
+/* One step (k, j) of the bitonic network of math.slang:142-163 for element i of a 64-element array: returns true when i and l = i ^ j
+ * are to be exchanged by the thread that owns the smaller index. */
+RT3_HD bool bitonic_exchange(uint32_t i, uint32_t k, uint32_t j, float a_i, float a_l) {
+    return ((i & k) == 0u) ? (a_i > a_l) : (a_i < a_l);
+}
+
 struct ProbeRay { rt3_ray ray; uint32_t target_x, target_y; bool background; };
 /* trace_probes.slang:16-56: the ray of atlas texel (ax, ay). */
 RT3_HD ProbeRay probe_setup_ray(const rt3_params& p, uint32_t ax, uint32_t ay, float probe_pixel_depth, uint32_t direction_word) {
@@ -1089,6 +1122,10 @@ RT3_HD ProbeRay probe_setup_ray(const rt3_params& p, uint32_t ax, uint32_t ay, f
     o.target_y = pcy * 8u + (uint32_t)(dy / float(size) * 8.0f);
     return o;
 }
+/* Order of the atlas writes.  Every thread first clears ITS texel (:28-32) and later writes the texel its direction word points at (:75);
+ * with mip-1 words several threads of a probe aim at the same texel and others are aimed at by nobody — the shader races.  DEFINED here
+ * as if the threads of a probe ran in index order: all clears first, then the target writes, the highest thread index winning.  With the
+ * uniform assignment every thread writes its own texel and none of this matters. */
 /* trace_probes.slang:58-75: the texel value.  :75 writes the direction as a debug colour; restated is the expression
  * commented beside it: float4(lerp(prev.xyz, radiance, blendfactor), probe_depth) with radiance = the hit's emission (:63).
  * A miss (the reference reads hit_info of an unwritten payload there: undefined) is DEFINED as radiance 0, or the sky with

@@ -515,12 +515,44 @@ void orc_pass_probe_trace(const orc_scene* s, const rt3_params* p, const uint32_
                 const uint32_t word = directions ? directions[ai] : probe_uniform_direction(ax, ay);
                 ProbeRay pr = probe_setup_ray(*p, ax, ay, pd, word);
                 if (pr.background) { atlas[4 * ai] = 0.f; atlas[4 * ai + 1] = 0.f; atlas[4 * ai + 2] = 0.f; atlas[4 * ai + 3] = RT3_BACKGROUND_DEPTH; continue; }   /* :28-31 */
+                if (directions && (ay & 7u) == 0u && (ax & 7u) == 0u)                  /* :32, all clears of the probe before its first target write */
+                    for (uint32_t k = 0; k < 64u; ++k) {
+                        float* c = atlas + 4 * ((size_t)(ay + k / 8u) * aw + ax + k % 8u);
+                        c[0] = c[1] = c[2] = c[3] = 0.f;
+                    }
                 rt3_hit h = closest_bvh(*s, pr.ray);
                 const size_t ti = (size_t)pr.target_y * aw + pr.target_x;
                 vec3 prev = v3(0.f, 0.f, 0.f);
                 if (p->blendfactor < 1.0f && prev_atlas) prev = v3(prev_atlas[4 * ai], prev_atlas[4 * ai + 1], prev_atlas[4 * ai + 2]);
                 vec4 t = probe_texel(sv, *p, pr.ray, h, prev);
                 atlas[4 * ti] = t.x; atlas[4 * ti + 1] = t.y; atlas[4 * ti + 2] = t.z; atlas[4 * ti + 3] = t.w;
+            }
+    });
+}
+/* shaders/old/structured_importance_sampling.slang:19-72 (the live lines; see rt3_shared_math.h): one direction word per atlas texel */
+void orc_pass_probe_sis(const rt3_params* p, const uint32_t* gbuffer, uint16_t* out, int threads) {
+    const uint32_t W = (uint32_t)p->window_size[0], pw = probe_count_x(*p), ph = probe_count_y(*p), aw = pw * 8u;
+    parallel_for(ph, threads, 1, [&](uint64_t y0, uint64_t y1) {
+        for (uint32_t pcy = (uint32_t)y0; pcy < (uint32_t)y1; ++pcy)
+            for (uint32_t pcx = 0; pcx < pw; ++pcx) {
+                vec3 normals[256];
+                float pdf[64], sorted[64];
+                for (uint32_t ti = 0; ti < 64u; ++ti)                                  /* :25-31 */
+                    for (uint32_t y = 0; y < 2u; ++y)
+                        for (uint32_t x = 0; x < 2u; ++x) {
+                            uint32_t px, py;
+                            probe_sis_pixel(pcx, pcy, ti, x, y, px, py);
+                            normals[ti * 4u + y * 2u + x] = unpack_normal_11_10_11(gbuffer[4u * ((size_t)py * W + px) + 1u]);
+                        }
+                for (uint32_t ti = 0; ti < 64u; ++ti) sorted[ti] = pdf[ti] = probe_sis_pdf(normals, probe_sis_direction(ti));   /* :34-46 */
+                for (uint32_t k = 2; k <= 64u; k *= 2u)                                /* math.slang:142-163, the steps in lock step */
+                    for (uint32_t j = k / 2u; j > 0u; j /= 2u)
+                        for (uint32_t i = 0; i < 64u; ++i) {
+                            const uint32_t l = i ^ j;
+                            if (l > i && bitonic_exchange(i, k, j, sorted[i], sorted[l])) { const float t = sorted[i]; sorted[i] = sorted[l]; sorted[l] = t; }
+                        }
+                for (uint32_t ti = 0; ti < 64u; ++ti)                                  /* :55-70 */
+                    out[(size_t)(pcy * 8u + ti / 8u) * aw + pcx * 8u + ti % 8u] = (uint16_t)probe_sis_word(pdf[ti], sorted[0], ti);
             }
     });
 }

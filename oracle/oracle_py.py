@@ -58,6 +58,7 @@ def lib():
         L.orc_pass_postprocess.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_probe_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_probe_sh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_pass_probe_sis.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_probe_interpolate.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         # KAT hooks
         u32, f32, vp = C.c_uint32, C.c_float, C.c_void_p
@@ -187,6 +188,13 @@ class OracleScene:
         self.L.orc_pass_probe_trace(self.h, ptr(params), ptr(gbuffer), ptr(depth), None if directions is None else ptr(directions),
                                     None if prev_atlas is None else ptr(prev_atlas), ptr(atlas), self.threads)
         return atlas
+
+    def pass_probe_sis(self, params, gbuffer):
+        """structured_importance_sampling.slang -> u16 direction words [(H/16)*8, (W/16)*8]."""
+        w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])
+        out = np.zeros((h // 16 * 8, w // 16 * 8), np.uint16)
+        self.L.orc_pass_probe_sis(ptr(params), ptr(gbuffer), ptr(out), self.threads)
+        return out
 
     def pass_probe_sh(self, params, atlas):
         """spherical_harmonic_conversion.slang -> [capacity, 9] SH-L2 records, Z-curve indexed by (probe.x * 3 + channel, probe.y)."""

@@ -7,7 +7,7 @@ import sys
 KEYS = ['gpu__time_duration.sum', 'launch__registers_per_thread', 'launch__grid_size', 'launch__block_size', 'sm__warps_active.avg.pct_of_peak_sustained_active',
         'smsp__issue_active.avg.pct_of_peak_sustained_active', 'smsp__thread_inst_executed_per_inst_executed.ratio', 'smsp__inst_executed.sum',
         'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
-        'lts__t_bytes.sum', 'lts__t_sector_hit_rate.pct', 'l1tex__t_sector_hit_rate.pct', 'l1tex__t_bytes.sum', 'smsp__sass_average_branch_targets_threads_uniform.pct',
+        'lts__t_bytes.sum', 'lts__t_sectors.sum', 'lts__t_sector_hit_rate.pct', 'l1tex__t_sector_hit_rate.pct', 'l1tex__t_bytes.sum', 'smsp__sass_average_branch_targets_threads_uniform.pct',
         'smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio',
         'smsp__average_warps_issue_stalled_wait_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio',
         'smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio',
@@ -80,9 +80,45 @@ def source(path, sub=None, top=40):
         print(f"{100 * v / tot:5.1f}%  {k}")
 
 
+def counters(path, sub, out_json, note="", rays_total=None):
+    """`... counters <ncu-rep> <kernel-substring> <out.json> [note]`: per-launch ncu counters of a kernel as JSON for bench.py's roofline objects
+    (DRAM bytes, L2 bytes, warp instructions, active lanes; means over the captured launches of the kernel)."""
+    import json
+    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    data = [r for r in rows[2:] if sub in r[hdr.index('Kernel Name')]]
+
+    def col(name, scale_by_unit=True):
+        if name not in hdr:
+            return None
+        i = hdr.index(name)
+        mult = {'Mbyte': 1e6, 'Gbyte': 1e9, 'Kbyte': 1e3, 'byte': 1.0, 'us': 1e-6, 'ms': 1e-3, 'ns': 1e-9}.get(units[i], 1.0) if scale_by_unit else 1.0
+        return [float(r[i].replace(',', '')) * mult for r in data]
+    n = len(data)
+    mean = lambda v: sum(v) / len(v) if v else None
+    lts = col('lts__t_sectors.sum', False)                                   # 32-byte sectors at the L2 (all sources); lts__t_bytes is not in `--set full`
+    dr, dw, lt, inst, lanes, dur = col('dram__bytes_read.sum'), col('dram__bytes_write.sum'), col('lts__t_bytes.sum') or ([32.0 * x for x in lts] if lts else None), col('smsp__inst_executed.sum'), \
+        col('smsp__thread_inst_executed_per_inst_executed.ratio'), col('gpu__time_duration.sum')
+    git = subprocess.run(['git', 'rev-parse', '--short', 'HEAD'], capture_output=True, text=True).stdout.strip()
+    rec = {"source": f"{out_json.split('/')[-1]} <- ncu --set full capture {path.split('/')[-1]} of kernel '{sub}', {n} launches, summarised at commit {git}" + (f"; {note}" if note else ""),
+           "launches": n, "dram_bytes_per_launch": mean([a + b for a, b in zip(dr, dw)]) if dr and dw else None,
+           "dram_read_bytes": dr, "dram_write_bytes": dw, "l2_bytes_per_launch": mean(lt) if lt else None,
+           "warp_inst_per_launch": mean(inst) if inst else None, "warp_inst": inst, "active_lanes_per_inst": mean(lanes) if lanes else None,
+           "ncu_duration_s": dur,
+           "rays_in_captured_launches": rays_total, "warp_inst_per_ray": (sum(inst) / rays_total) if (inst and rays_total) else None,
+           "dram_bytes_per_ray": (sum(dr) + sum(dw)) / rays_total if (dr and dw and rays_total) else None,
+           "l2_bytes_per_ray": sum(lt) / rays_total if (lt and rays_total) else None}
+    with open(out_json, 'w') as f:
+        json.dump(rec, f, indent=1)
+    print(json.dumps(rec, indent=1))
+
+
 if __name__ == '__main__':
     if sys.argv[1] == 'launches':
         launches(sys.argv[2])
+    elif sys.argv[1] == 'counters':
+        counters(sys.argv[2], sys.argv[3], sys.argv[4], sys.argv[5] if len(sys.argv) > 5 else "", float(sys.argv[6]) if len(sys.argv) > 6 else None)
     elif sys.argv[1] == 'source':
         source(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
     else:

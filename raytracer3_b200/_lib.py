@@ -59,11 +59,13 @@ def load():
         "rt3_pass_postprocess": (i32, [vp, vp, Rect, vp, vp, vp, vp]),
         "rt3_probe_layout": (i32, [vp, P(u32), P(u32), P(u32)]),
         "rt3_pass_probe_trace": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
+        "rt3_pass_probe_sis": (i32, [vp, vp, vp, vp, vp]),
         "rt3_pass_probe_sh": (i32, [vp, vp, vp, vp, vp]),
         "rt3_pass_probe_interpolate": (i32, [vp, vp, vp, vp, vp, vp, vp]),
         "rt3_pass_gbuffer_tiles": (i32, [vp, vp, vp, u32, vp, vp, vp]),
         "rt3_pass_reference_tiles": (i32, [vp, vp, vp, u32, vp, vp, vp, vp, vp]),
         "rt3_untile_rgba32f": (i32, [vp, vp, u32, u32, u32, vp, vp, u32, u32, vp]),
+        "rt3_scatter_tiles_rgba32f": (i32, [vp, vp, vp, u32, u32, u32, vp, u32, vp]),
         "rt3_trace_closest": (i32, [vp, vp, u64, vp, vp]),
         "rt3_trace_any": (i32, [vp, vp, u64, vp, vp]),
         "rt3_render_frame_host": (i32, [vp, vp, vp, vp, vp, vp]),

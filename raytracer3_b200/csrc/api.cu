@@ -160,9 +160,23 @@ PixelMap tiles_map(rt3_context* c, const rt3_params* p, const rt3_rect* tiles, u
     return m;
 }
 
+/* All pass / trace calls of one context share its scratch (wavefront queues, per-pixel path state, counters, tile lists), so they must
+ * execute in call order even when the caller records them on different streams: a call whose stream differs from the previous call's first
+ * waits (on the device, cudaStreamWaitEvent) for the event recorded at the end of the previous call.  Same stream: stream order suffices. */
+struct CallOrder {
+    rt3_context* c; cudaStream_t st;
+    CallOrder(rt3_context* c_, cudaStream_t st_) : c(c_), st(st_) {
+        if (c->have_last && c->last_stream != st) RT3_CUDA(c, cudaStreamWaitEvent(st, c->ev_last, 0));
+    }
+    ~CallOrder() {
+        if (cudaEventRecord(c->ev_last, st) == cudaSuccess) { c->last_stream = st; c->have_last = true; }
+    }
+};
+
 void check_params(rt3_context* c, const rt3_params* p) {
     if (!p) RT3_FAIL(c, RT3_ERR_INVALID, "params is NULL");
     if (p->samples == 0) RT3_FAIL(c, RT3_ERR_INVALID, "samples must be >= 1");
+    if (p->samples >= (1u << 24) || p->bounces > 255u) RT3_FAIL(c, RT3_ERR_INVALID, "samples must be < 2^24 and bounces <= 255 (per-pixel path state is one 32-bit word)");
     if ((p->flags & (RT3_FLAG_ENV | RT3_FLAG_NEE)) && !c->d_env) RT3_FAIL(c, RT3_ERR_STATE, "RT3_FLAG_ENV / RT3_FLAG_NEE without rt3_scene_set_environment");
     if ((p->flags & RT3_FLAG_NEE) && !(p->flags & RT3_FLAG_ENV)) RT3_FAIL(c, RT3_ERR_INVALID, "RT3_FLAG_NEE requires RT3_FLAG_ENV");
     if ((p->flags & RT3_FLAG_BLUENOISE) && !c->d_bn) RT3_FAIL(c, RT3_ERR_STATE, "RT3_FLAG_BLUENOISE without rt3_scene_set_bluenoise");
@@ -209,6 +223,8 @@ rt3_status rt3_create(int cuda_device, rt3_context** out) {
         uint64_t keep_all = UINT64_MAX;
         RT3_CUDA(c, cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep_all));
         for (int i = 0; i < 8; ++i) RT3_CUDA(c, cudaEventCreate(&c->ev[i]));
+        RT3_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+        RT3_CUDA(c, cudaEventCreateWithFlags(&c->ev_last, cudaEventDisableTiming));
         RT3_CUDA(c, cudaMalloc(&c->d_counters, sizeof(DeviceCounters)));
         RT3_CUDA(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
         float lut[256];
@@ -240,10 +256,17 @@ void rt3_destroy(rt3_context* c) {
     if (c->d_srgb_lut) cudaFree(c->d_srgb_lut);
     if (c->d_counters) cudaFree(c->d_counters);
     Scratch* all[] = {&c->d_geometries, &c->d_seg_first, &c->d_seg_geo, &c->d_seg_inst, &c->d_inst_xform, &c->d_tex_ptr, &c->d_tex_dim, &c->bvh_nodes,
-                      &c->bvh_tris, &c->d_insts, &c->d_shade_rec, &c->q_rays[0], &c->q_rays[1], &c->q_hits, &c->q_thr[0], &c->q_thr[1], &c->q_pix[0], &c->q_pix[1], &c->q_pdf[0], &c->q_pdf[1], &c->q_srays, &c->q_scontrib, &c->q_sbits, &c->px_radiance,
-                      &c->px_rng, &c->d_counts, &c->d_rects, &c->d_untile_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
+                      &c->bvh_tris, &c->d_insts, &c->d_shade_rec, &c->px_radiance, &c->px_path, &c->px_failed, &c->d_counts, &c->d_rects, &c->d_untile_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();
+    for (RefLane& ln : c->lanes) {
+        Scratch* q[] = {&ln.q_rays[0], &ln.q_rays[1], &ln.q_hits, &ln.q_thr[0], &ln.q_thr[1], &ln.q_pdf[0], &ln.q_pdf[1], &ln.q_srays, &ln.q_scontrib, &ln.q_sbits, &ln.counts};
+        for (Scratch* s : q) s->release();
+        if (ln.stream) cudaStreamDestroy(ln.stream);
+        if (ln.done) cudaEventDestroy(ln.done);
+    }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_last) cudaEventDestroy(c->ev_last);
     for (auto& fs : c->slots) {
         fs.gb.release(); fs.dp.release(); fs.lt.release(); fs.pv.release();
         if (fs.rendered) cudaEventDestroy(fs.rendered);
@@ -370,6 +393,7 @@ rt3_status rt3_pass_gbuffer(rt3_context* c, const rt3_params* p, rt3_rect r, uin
         check_params(c, p); require_accel(c);
         if (!gbuffer || !depth) RT3_FAIL(c, RT3_ERR_INVALID, "gbuffer/depth is NULL");
         if (c->scene_dirty) refresh_scene_tables(c);
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_gbuffer(c, *p, single_rect_map(c, p, r), gbuffer, depth, ids, bary, (cudaStream_t)st);
     });
 }
@@ -380,6 +404,7 @@ rt3_status rt3_pass_reference(rt3_context* c, const rt3_params* p, rt3_rect r, c
         if (!gbuffer || !depth || !light) RT3_FAIL(c, RT3_ERR_INVALID, "gbuffer/depth/light is NULL");
         if (p->blendfactor < 1.0f && !prev) RT3_FAIL(c, RT3_ERR_INVALID, "prev_light is NULL with blendfactor < 1");
         if (c->scene_dirty) refresh_scene_tables(c);
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_reference(c, *p, single_rect_map(c, p, r), gbuffer, depth, prev, light, (cudaStream_t)st);
     });
 }
@@ -387,6 +412,7 @@ rt3_status rt3_pass_postprocess(rt3_context* c, const rt3_params* p, rt3_rect r,
     return guarded(c, [&]() {
         if (!p || !depth || !in || !out) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
         if (c->scene_dirty) refresh_scene_tables(c);
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_postprocess(c, *p, single_rect_map(c, p, r), depth, in, out, (cudaStream_t)st);
     });
 }
@@ -406,18 +432,28 @@ rt3_status rt3_pass_probe_trace(rt3_context* c, const rt3_params* p, const uint3
         if (!depth || !atlas) RT3_FAIL(c, RT3_ERR_INVALID, "depth/atlas is NULL");
         if (p->blendfactor < 1.0f && !prev_atlas) RT3_FAIL(c, RT3_ERR_INVALID, "prev_atlas is NULL with blendfactor < 1");
         if (c->scene_dirty) refresh_scene_tables(c);
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_probe_trace(c, *p, depth, directions, prev_atlas, atlas, (cudaStream_t)st);
+    });
+}
+rt3_status rt3_pass_probe_sis(rt3_context* c, const rt3_params* p, const uint32_t* gbuffer, uint16_t* directions, void* st) {
+    return guarded(c, [&]() {
+        if (!p || !gbuffer || !directions) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        CallOrder order(c, (cudaStream_t)st);
+        rt3_launch_probe_sis(c, *p, gbuffer, directions, (cudaStream_t)st);
     });
 }
 rt3_status rt3_pass_probe_sh(rt3_context* c, const rt3_params* p, const float* atlas, float* sh, void* st) {
     return guarded(c, [&]() {
         if (!p || !atlas || !sh) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_probe_sh(c, *p, atlas, sh, (cudaStream_t)st);
     });
 }
 rt3_status rt3_pass_probe_interpolate(rt3_context* c, const rt3_params* p, const uint32_t* gbuffer, const float* depth, const float* sh, float* light, void* st) {
     return guarded(c, [&]() {
         if (!p || !gbuffer || !depth || !sh || !light) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_probe_interpolate(c, *p, gbuffer, depth, sh, light, (cudaStream_t)st);
     });
 }
@@ -426,6 +462,7 @@ rt3_status rt3_pass_gbuffer_tiles(rt3_context* c, const rt3_params* p, const rt3
         check_params(c, p); require_accel(c);
         if ((n && !tiles) || !gbuffer || !depth) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
         if (c->scene_dirty) refresh_scene_tables(c);
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_gbuffer(c, *p, tiles_map(c, p, tiles, n, (cudaStream_t)st), gbuffer, depth, nullptr, nullptr, (cudaStream_t)st);
     });
 }
@@ -436,6 +473,7 @@ rt3_status rt3_pass_reference_tiles(rt3_context* c, const rt3_params* p, const r
         if ((n && !tiles) || !gbuffer || !depth || !light) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
         if (p->blendfactor < 1.0f && !prev) RT3_FAIL(c, RT3_ERR_INVALID, "prev_light is NULL with blendfactor < 1");
         if (c->scene_dirty) refresh_scene_tables(c);
+        CallOrder order(c, (cudaStream_t)st);
         rt3_launch_reference(c, *p, tiles_map(c, p, tiles, n, (cudaStream_t)st), gbuffer, depth, prev, light, (cudaStream_t)st);
     });
 }
@@ -454,19 +492,42 @@ rt3_status rt3_untile_rgba32f(rt3_context* c, const rt3_rect* tiles, uint32_t n,
     });
 }
 
+rt3_status rt3_scatter_tiles_rgba32f(rt3_context* c, const rt3_rect* tiles, const uint64_t* dst_top_left, uint32_t n, uint32_t tile_w, uint32_t tile_h,
+                                     const float* slab, uint32_t dst_pitch_px, void* st) {
+    return guarded(c, [&]() {
+        if ((n && (!tiles || !dst_top_left)) || !slab) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        if (!n) return;
+        for (uint32_t i = 0; i < n; ++i)
+            if (tiles[i].w && tiles[i].h && (!dst_top_left[i] || (dst_top_left[i] & 15u))) RT3_FAIL(c, RT3_ERR_INVALID, "tile destination is NULL or not 16-byte aligned");
+        /* one device buffer: n rects (16 B each) followed by n destination addresses; re-uploaded only when the lists change */
+        std::vector<uint64_t> packed(3 * (size_t)n);
+        memcpy(packed.data(), tiles, (size_t)n * sizeof(rt3_rect));
+        memcpy(packed.data() + 2 * (size_t)n, dst_top_left, (size_t)n * sizeof(uint64_t));
+        uint64_t* d = ensure<uint64_t>(c, c->d_scatter, packed.size());
+        if (packed != c->scatter_host || (cudaStream_t)st != c->scatter_stream) {
+            RT3_CUDA(c, cudaMemcpyAsync(d, packed.data(), packed.size() * 8, cudaMemcpyHostToDevice, (cudaStream_t)st));
+            RT3_CUDA(c, cudaStreamSynchronize((cudaStream_t)st));          /* `packed` is pageable and local: the copy must have left it */
+            c->scatter_host = packed; c->scatter_stream = (cudaStream_t)st;
+        }
+        rt3_launch_scatter_tiles(c, (const rt3_rect*)d, (const unsigned long long*)(d + 2 * (size_t)n), n, tile_w, tile_h, slab, dst_pitch_px, (cudaStream_t)st);
+    });
+}
+
 /* ---- raw queries ------------------------------------------------------------------------------ */
 rt3_status rt3_trace_closest(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_hit* out, void* st) {
     return guarded(c, [&]() {
         require_accel(c);
         if (n && (!rays || !out)) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
-        rt3_launch_trace_closest(c, rays, nullptr, n, out, (cudaStream_t)st);
+        CallOrder order(c, (cudaStream_t)st);
+        rt3_launch_trace_closest(c, rays, nullptr, n, out, nullptr, (cudaStream_t)st);
     });
 }
 rt3_status rt3_trace_any(rt3_context* c, const rt3_ray* rays, uint64_t n, uint32_t* out_bits, void* st) {
     return guarded(c, [&]() {
         require_accel(c);
         if (n && (!rays || !out_bits)) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
-        rt3_launch_trace_any(c, rays, nullptr, n, out_bits, (cudaStream_t)st);
+        CallOrder order(c, (cudaStream_t)st);
+        rt3_launch_trace_any(c, rays, nullptr, n, out_bits, nullptr, (cudaStream_t)st);
     });
 }
 
@@ -487,6 +548,7 @@ rt3_status rt3_render_frame_host(rt3_context* c, const rt3_params* p, const floa
         float* lt = ensure<float>(c, c->f_light, 4 * px);
         float* pv = nullptr;
         cudaStream_t st = 0;
+        CallOrder order(c, st);
         if (p->blendfactor < 1.0f) {
             pv = ensure<float>(c, c->f_prev, 4 * px);
             RT3_CUDA(c, cudaMemcpyAsync(pv, prev_light_host, 16 * px, cudaMemcpyHostToDevice, st));
@@ -520,6 +582,7 @@ rt3_status rt3_frame_submit_host(rt3_context* c, const rt3_params* p, const floa
         float* lt = ensure<float>(c, fs.lt, 4 * px);
         float* pv = nullptr;
         cudaStream_t st = c->s_compute;
+        CallOrder order(c, st);
         if (p->blendfactor < 1.0f) {
             pv = ensure<float>(c, fs.pv, 4 * px);
             RT3_CUDA(c, cudaMemcpyAsync(pv, prev_light_host, 16 * px, cudaMemcpyHostToDevice, st));
@@ -564,8 +627,9 @@ rt3_status rt3_trace_closest_host(rt3_context* c, const rt3_ray* rays_host, uint
         if (!n) return;
         rt3_ray* r = ensure<rt3_ray>(c, c->f_rays, n);
         rt3_hit* h = ensure<rt3_hit>(c, c->f_hits, n);
+        CallOrder order(c, 0);
         RT3_CUDA(c, cudaMemcpyAsync(r, rays_host, n * sizeof(rt3_ray), cudaMemcpyHostToDevice, 0));
-        rt3_launch_trace_closest(c, r, nullptr, n, h, 0);
+        rt3_launch_trace_closest(c, r, nullptr, n, h, nullptr, 0);
         RT3_CUDA(c, cudaMemcpyAsync(out_host, h, n * sizeof(rt3_hit), cudaMemcpyDeviceToHost, 0));
         RT3_CUDA(c, cudaStreamSynchronize(0));
     });
@@ -578,8 +642,9 @@ rt3_status rt3_trace_any_host(rt3_context* c, const rt3_ray* rays_host, uint64_t
         const size_t words = (n + 31) / 32;
         rt3_ray* r = ensure<rt3_ray>(c, c->f_rays, n);
         uint32_t* b = ensure<uint32_t>(c, c->f_bits, words);
+        CallOrder order(c, 0);
         RT3_CUDA(c, cudaMemcpyAsync(r, rays_host, n * sizeof(rt3_ray), cudaMemcpyHostToDevice, 0));
-        rt3_launch_trace_any(c, r, nullptr, n, b, 0);
+        rt3_launch_trace_any(c, r, nullptr, n, b, nullptr, 0);
         RT3_CUDA(c, cudaMemcpyAsync(out_bits_host, b, words * 4, cudaMemcpyDeviceToHost, 0));
         RT3_CUDA(c, cudaStreamSynchronize(0));
     });
@@ -608,6 +673,7 @@ rt3_status rt3_trace_closest_stats(rt3_context* c, const rt3_ray* rays, uint64_t
     return guarded(c, [&]() {
         require_accel(c);
         if (!out || (n && !rays)) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        CallOrder order(c, 0);
         rt3_launch_trace_stats(c, rays, n, out);
     });
 }

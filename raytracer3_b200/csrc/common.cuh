@@ -57,6 +57,15 @@ struct TextureRec { uint8_t* data = nullptr; uint32_t w = 0, h = 0; };
 #include "pass_types.h"
 
 
+/* One wavefront pipeline of the reference pass: its queues, its queue / work counters and (lanes > 0) its stream.  rt3_launch_reference
+ * runs one strip of the frame per lane (passes.cu). */
+constexpr int RT3_MAX_LANES = 4;
+struct RefLane {
+    Scratch q_rays[2], q_hits, q_thr[2], q_pdf[2], q_srays, q_scontrib, q_sbits, counts;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+};
+
 struct rt3_context {
     int device = 0;
     int sm_count = 148;
@@ -89,12 +98,18 @@ struct rt3_context {
     rt3_build_stats last_build;
 
     /* pass scratch */
-    Scratch q_rays[2], q_hits, q_thr[2], q_pix[2], q_pdf[2], q_srays, q_scontrib, q_sbits, px_radiance, px_rng, d_counts, d_rects, d_untile_rects, d_params;   /* d_untile_rects: un-tiling may run on another stream than the passes */
+    RefLane lanes[RT3_MAX_LANES];
+    Scratch px_radiance, px_path, px_failed, d_counts, d_rects, d_untile_rects, d_params;   /* d_untile_rects: un-tiling may run on another stream than the passes */
+    cudaEvent_t ev_fork = nullptr;
+    /* Stream ordering between calls: all pass / trace calls of one context share the scratch above, so a call on another stream than
+     * the previous one first waits for the previous call's work (order_call_begin / order_call_end, api.cu). */
+    cudaEvent_t ev_last = nullptr; cudaStream_t last_stream = nullptr; bool have_last = false;
     Scratch f_gbuffer, f_depth, f_light, f_prev, f_rays, f_hits, f_bits, l2_buf;
     DeviceCounters* d_counters = nullptr;
     cudaEvent_t ev[8];
     std::vector<rt3_rect> rects_host; const rt3_rect* rects_dev = nullptr; cudaStream_t rects_stream = nullptr;   /* tile list last uploaded to d_rects */
     std::vector<rt3_rect> urects_host; const rt3_rect* urects_dev = nullptr; cudaStream_t urects_stream = nullptr;   /* ... and to d_untile_rects */
+    Scratch d_scatter; std::vector<uint64_t> scatter_host; cudaStream_t scatter_stream = nullptr;                    /* rt3_scatter_tiles_rgba32f: rects + destinations last uploaded */
 
     /* frames in flight (rt3_frame_submit_host / rt3_frame_wait): FRAMES_IN_FLIGHT = 3 of the reference's swapchain.rs:8 */
     struct FrameSlot { Scratch gb, dp, lt, pv; cudaEvent_t rendered = nullptr, copied = nullptr; bool busy = false; };
@@ -133,8 +148,11 @@ static inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1
 
 /* implemented in build.cu / trace.cu / passes.cu */
 void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_stats* out);
-void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, cudaStream_t st);
-void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits, cudaStream_t st);
+/* work_counter: 4 x u64 of scratch for the persistent kernel's ray counter (zeroed by the launcher); NULL = the context's own (d_counts) */
+void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, unsigned long long* work_counter,
+                              cudaStream_t st);
+void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits, unsigned long long* work_counter,
+                          cudaStream_t st);
 void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out);
 void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary,
                         cudaStream_t st);
@@ -145,7 +163,10 @@ void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles
                        uint32_t frame_w, uint32_t frame_h, cudaStream_t st);
 void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,
                             cudaStream_t st);
+void rt3_launch_probe_sis(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, uint16_t* directions, cudaStream_t st);
 void rt3_launch_probe_sh(rt3_context* c, const rt3_params& p, const float* atlas, float* sh, cudaStream_t st);
 void rt3_launch_probe_interpolate(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, const float* depth, const float* sh, float* light,
                                   cudaStream_t st);
+void rt3_launch_scatter_tiles(rt3_context* c, const rt3_rect* d_rects, const unsigned long long* d_dst, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h,
+                              const float* slab, uint32_t dst_pitch, cudaStream_t st);
 double rt3_run_l2_sweep(rt3_context* c, size_t bytes, int iters);

@@ -21,6 +21,25 @@ struct PixelMap {
     uint32_t work;            /* n_tiles * bw * bh * 32          */
 };
 
+/* A frame's work indices are dealt to S strips in units of STRIP_UNIT indices (unit u goes to strip u mod S): every strip sees the whole
+ * image at a coarser grain, so the strips carry equal work.  The reference pass runs one wavefront per strip, each on its own stream
+ * (passes.cu): the tail of one strip's traversal launch overlaps the other strips' kernels, and a strip's queues are S times smaller. */
+constexpr uint32_t STRIP_UNIT = 2048u;
+struct StripMap {
+    uint32_t strip, n_strips;
+    uint32_t local_work;      /* number of local indices j of this strip (a multiple of STRIP_UNIT; indices that map past `work` are padding) */
+};
+__host__ __device__ __forceinline__ uint32_t strip_to_work(const StripMap& sm, uint32_t j) {
+    return ((j / STRIP_UNIT) * sm.n_strips + sm.strip) * STRIP_UNIT + (j % STRIP_UNIT);
+}
+static inline StripMap make_strip(uint32_t work, uint32_t strip, uint32_t n_strips) {
+    const uint32_t units = (work + STRIP_UNIT - 1) / STRIP_UNIT;
+    StripMap sm;
+    sm.strip = strip; sm.n_strips = n_strips;
+    sm.local_work = ((units + n_strips - 1 - strip) / n_strips) * STRIP_UNIT;
+    return sm;
+}
+
 struct DeviceCounters {
     unsigned long long rays_primary, rays_secondary, rays_shadow, paths_started, paths_escaped;
 };

@@ -22,6 +22,9 @@ using namespace rt3m;
 
 #include "pass_kernels.cuh"
 
+#include <cstdlib>
+static int env_int_passes(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
+
 void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary,
                         cudaStream_t st) {
     if (!m.work) return;
@@ -29,58 +32,88 @@ void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, 
                c->d_counters, c->two_level ? c->d_insts.as<InstRec>() : (const InstRec*)nullptr);
 }
 
-void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m, const uint32_t* gbuffer, const float* depth, const float* prev,
-                          float* light, cudaStream_t st) {
-    if (!m.work) return;
-    const size_t W = m.work;
+/* One wavefront (a strip of the frame, pass_types.h) on stream `st` with the lane's own queues and counters. */
+static void run_reference_strip(rt3_context* c, RefLane& ln, const rt3_params& p, const PixelMap& m, const StripMap& sm, const uint32_t* gbuffer, const float* depth,
+                                const float* prev, float* light, float4* px_radiance, uint2* px_path, cudaStream_t st) {
+    const size_t W = sm.local_work;                      /* at most one path per pixel of the strip is in flight */
     const bool nee = nee_enabled(p.flags);
     const bool layered = (p.flags & RT3_FLAG_SPECULAR) != 0;
-    rt3_ray* q_rays[2] = {ensure<rt3_ray>(c, c->q_rays[0], W), ensure<rt3_ray>(c, c->q_rays[1], W)};
-    float4* q_thr[2] = {ensure<float4>(c, c->q_thr[0], W), ensure<float4>(c, c->q_thr[1], W)};
-    rt3_hit* q_hits = ensure<rt3_hit>(c, c->q_hits, W);
-    float4* px_radiance = ensure<float4>(c, c->px_radiance, W);
-    uint32_t* px_rng = ensure<uint32_t>(c, c->px_rng, W);
-    uint32_t* counts = (uint32_t*)ensure<unsigned long long>(c, c->d_counts, 64);   /* [0],[1] path queues, [2] shadow queue */
+    rt3_ray* q_rays[2] = {ensure<rt3_ray>(c, ln.q_rays[0], W), ensure<rt3_ray>(c, ln.q_rays[1], W)};
+    float4* q_thr[2] = {ensure<float4>(c, ln.q_thr[0], W), ensure<float4>(c, ln.q_thr[1], W)};
+    rt3_hit* q_hits = ensure<rt3_hit>(c, ln.q_hits, W);
+    unsigned long long* cnt64 = ensure<unsigned long long>(c, ln.counts, 64);
+    uint32_t* counts = (uint32_t*)cnt64;                  /* [0],[1] path queues, [2] shadow queue; cnt64[32..] the traversal kernel's work counter */
     float* q_pdf[2] = {nullptr, nullptr};
     NeeQueues nq = {nullptr, nullptr, nullptr, nullptr, nullptr};
     uint32_t* sbits = nullptr;
     if (nee) {
-        q_pdf[0] = ensure<float>(c, c->q_pdf[0], W); q_pdf[1] = ensure<float>(c, c->q_pdf[1], W);
-        nq.srays = ensure<rt3_ray>(c, c->q_srays, W); nq.scontrib = ensure<float4>(c, c->q_scontrib, W); nq.scount = counts + 2;
-        sbits = ensure<uint32_t>(c, c->q_sbits, (W + 31) / 32);
+        q_pdf[0] = ensure<float>(c, ln.q_pdf[0], W); q_pdf[1] = ensure<float>(c, ln.q_pdf[1], W);
+        nq.srays = ensure<rt3_ray>(c, ln.q_srays, W); nq.scontrib = ensure<float4>(c, ln.q_scontrib, W); nq.scount = counts + 2;
+        sbits = ensure<uint32_t>(c, ln.q_sbits, (W + 31) / 32);
     }
     const unsigned grid = std::min<unsigned>(div_up(W, PASS_THREADS), (unsigned)c->sm_count * 8u);
+    const RegenInputs gin = {gbuffer, depth};
+    const bool regen = p.samples > 1;
     auto resolve_shadows = [&]() {                      /* any-hit pass over the shadow queue, then add the unoccluded contributions */
-        rt3_launch_trace_any(c, nq.srays, nq.scount, W, sbits, st);
+        rt3_launch_trace_any(c, nq.srays, nq.scount, W, sbits, cnt64 + 32, st);
         RT3_LAUNCH(c, k_ref_shadow, grid, PASS_THREADS, 0, st, nq.scontrib, sbits, nq.scount, px_radiance);
     };
-    for (uint32_t sidx = 0; sidx < p.samples; ++sidx) {
-        RT3_CUDA(c, cudaMemsetAsync(counts, 0, 12, st));
-        nq.pdf_in = nullptr; nq.pdf_out = q_pdf[0];
-        if (layered)
-            RT3_LAUNCH(c, k_ref_init<true>, grid, PASS_THREADS, 0, st, c->view, p, m, gbuffer, depth, px_radiance, px_rng, sidx == 0 ? 1 : 0, q_rays[0], q_thr[0],
-                       counts, nq, c->d_counters);
-        else
-            RT3_LAUNCH(c, k_ref_init<false>, grid, PASS_THREADS, 0, st, c->view, p, m, gbuffer, depth, px_radiance, px_rng, sidx == 0 ? 1 : 0, q_rays[0], q_thr[0],
-                       counts, nq, c->d_counters);
-        if (nee && p.bounces > 1) resolve_shadows();
-        int cur = 0;
-        for (uint32_t b = 1; b < p.bounces; ++b) {
-            rt3_launch_trace_closest(c, q_rays[cur], counts + cur, W, q_hits, st);
-            RT3_CUDA(c, cudaMemsetAsync(counts + (1 - cur), 0, 4, st));
-            if (nee) RT3_CUDA(c, cudaMemsetAsync(counts + 2, 0, 4, st));
-            nq.pdf_in = q_pdf[cur]; nq.pdf_out = q_pdf[1 - cur];
-            if (layered)
-                RT3_LAUNCH(c, k_ref_shade<true>, grid, PASS_THREADS, 0, st, c->view, p, m, b, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur],
-                           q_thr[1 - cur], counts + (1 - cur), px_radiance, px_rng, nq, c->d_counters);
-            else
-                RT3_LAUNCH(c, k_ref_shade<false>, grid, PASS_THREADS, 0, st, c->view, p, m, b, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur],
-                           q_thr[1 - cur], counts + (1 - cur), px_radiance, px_rng, nq, c->d_counters);
-            if (nee && b != p.bounces - 1) resolve_shadows();
-            cur = 1 - cur;
-        }
+    RT3_CUDA(c, cudaMemsetAsync(counts, 0, 12, st));
+    nq.pdf_in = nullptr; nq.pdf_out = q_pdf[0];
+    if (layered)
+        RT3_LAUNCH(c, k_ref_init<true>, grid, PASS_THREADS, 0, st, c->view, p, m, sm, gbuffer, depth, px_radiance, px_path, q_rays[0], q_thr[0], counts, nq, c->d_counters);
+    else
+        RT3_LAUNCH(c, k_ref_init<false>, grid, PASS_THREADS, 0, st, c->view, p, m, sm, gbuffer, depth, px_radiance, px_path, q_rays[0], q_thr[0], counts, nq, c->d_counters);
+    /* Rounds: every unfinished pixel advances by one traced ray per round, and a pixel traces at most bounces - 1 rays per sample.  The
+     * queue lengths live on the device, so the host enqueues the worst case; rounds past the last live path see an empty queue. */
+    const uint64_t rounds = p.bounces > 1 ? (uint64_t)p.samples * (p.bounces - 1) : 0;
+    if (nee && rounds) resolve_shadows();
+    int cur = 0;
+    for (uint64_t r = 0; r < rounds; ++r) {
+        rt3_launch_trace_closest(c, q_rays[cur], counts + cur, W, q_hits, cnt64 + 32, st);
+        RT3_CUDA(c, cudaMemsetAsync(counts + (1 - cur), 0, 4, st));
+        if (nee) RT3_CUDA(c, cudaMemsetAsync(counts + 2, 0, 4, st));
+        nq.pdf_in = q_pdf[cur]; nq.pdf_out = q_pdf[1 - cur];
+#define RT3_SHADE(L, R) RT3_LAUNCH(c, (k_ref_shade<L, R>), grid, PASS_THREADS, 0, st, c->view, p, m, gin, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur], \
+                                   q_thr[1 - cur], counts + (1 - cur), px_radiance, px_path, nq, c->d_counters)
+        if (layered) { if (regen) RT3_SHADE(true, true); else RT3_SHADE(true, false); }
+        else { if (regen) RT3_SHADE(false, true); else RT3_SHADE(false, false); }
+#undef RT3_SHADE
+        if (nee && r + 1 != rounds) resolve_shadows();
+        cur = 1 - cur;
     }
-    RT3_LAUNCH(c, k_ref_finish, div_up(W, PASS_THREADS), PASS_THREADS, 0, st, p, m, px_radiance, prev, light);
+    RT3_LAUNCH(c, k_ref_finish, div_up(W, PASS_THREADS), PASS_THREADS, 0, st, p, m, sm, px_radiance, prev, light);
+}
+
+/* The reference pass: S strips (pass_types.h), each a wavefront of its own on its own stream, forked from and joined back into the caller's
+ * stream with events.  Why: a persistent traversal launch ends with a tail in which the last long rays keep a shrinking number of warps
+ * busy, and the small kernels between the launches (shade, memsets) leave the GPU half empty; with two or more strips in flight the tail
+ * of one strip's launch is filled by the other strips' kernels.  The strips touch disjoint pixels, so the image does not depend on S. */
+void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m, const uint32_t* gbuffer, const float* depth, const float* prev,
+                          float* light, cudaStream_t st) {
+    if (!m.work) return;
+    static const int env_strips = env_int_passes("RT3_STRIPS", 2);
+    uint32_t S = (uint32_t)std::max(1, std::min(env_strips, RT3_MAX_LANES));
+    while (S > 1 && (m.work + STRIP_UNIT - 1) / STRIP_UNIT < 16u * S) --S;        /* small frames: one wavefront */
+    float4* px_radiance = ensure<float4>(c, c->px_radiance, m.work);
+    uint2* px_path = ensure<uint2>(c, c->px_path, m.work);
+    if (S == 1) {
+        run_reference_strip(c, c->lanes[0], p, m, make_strip(m.work, 0, 1), gbuffer, depth, prev, light, px_radiance, px_path, st);
+        return;
+    }
+    for (uint32_t k = 0; k < S; ++k)                                               /* allocate before forking: ensure() may cudaFree (synchronising) */
+        if (!c->lanes[k].stream) {
+            RT3_CUDA(c, cudaStreamCreateWithFlags(&c->lanes[k].stream, cudaStreamNonBlocking));
+            RT3_CUDA(c, cudaEventCreateWithFlags(&c->lanes[k].done, cudaEventDisableTiming));
+        }
+    RT3_CUDA(c, cudaEventRecord(c->ev_fork, st));
+    for (uint32_t k = 0; k < S; ++k) {
+        RefLane& ln = c->lanes[k];
+        RT3_CUDA(c, cudaStreamWaitEvent(ln.stream, c->ev_fork, 0));
+        run_reference_strip(c, ln, p, m, make_strip(m.work, k, S), gbuffer, depth, prev, light, px_radiance, px_path, ln.stream);
+        RT3_CUDA(c, cudaEventRecord(ln.done, ln.stream));
+    }
+    for (uint32_t k = 0; k < S; ++k) RT3_CUDA(c, cudaStreamWaitEvent(st, c->lanes[k].done, 0));
 }
 
 void rt3_launch_postprocess(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, float* out, cudaStream_t st) {
@@ -93,12 +126,23 @@ void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* de
     const uint32_t aw = probe_count_x(p) * 8u, ah = probe_count_y(p) * 8u;
     const size_t n = (size_t)aw * ah;
     if (!n) return;
-    rt3_ray* rays = ensure<rt3_ray>(c, c->q_rays[0], std::max<size_t>(n, 1));
-    rt3_hit* hits = ensure<rt3_hit>(c, c->q_hits, std::max<size_t>(n, 1));
+    rt3_ray* rays = ensure<rt3_ray>(c, c->lanes[0].q_rays[0], std::max<size_t>(n, 1));
+    rt3_hit* hits = ensure<rt3_hit>(c, c->lanes[0].q_hits, std::max<size_t>(n, 1));
     RT3_LAUNCH(c, k_probe_raygen, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, p, aw, ah, depth, directions, rays);
-    rt3_launch_trace_closest(c, rays, nullptr, n, hits, st);
+    rt3_launch_trace_closest(c, rays, nullptr, n, hits, nullptr, st);
+    float4* staged = nullptr; uint32_t* staged_target = nullptr;
+    if (directions) {                                   /* several texels of a probe may aim at one target: staged, then resolved in the defined order */
+        staged = ensure<float4>(c, c->lanes[0].q_thr[0], n);
+        staged_target = ensure<uint32_t>(c, c->lanes[0].q_sbits, n);
+    }
     RT3_LAUNCH(c, k_probe_texel, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, c->view, p, aw, ah, depth, directions, rays, hits, (const float4*)prev_atlas,
-               (float4*)atlas, c->d_counters);
+               (float4*)atlas, staged, staged_target, c->d_counters);
+    if (directions) RT3_LAUNCH(c, k_probe_resolve, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, aw, ah, staged, staged_target, (float4*)atlas);
+}
+void rt3_launch_probe_sis(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, uint16_t* directions, cudaStream_t st) {
+    const uint32_t probes = probe_count_x(p) * probe_count_y(p);
+    if (!probes) return;
+    RT3_LAUNCH(c, k_probe_sis, probes, 64, 0, st, p, gbuffer, directions);
 }
 void rt3_launch_probe_sh(rt3_context* c, const rt3_params& p, const float* atlas, float* sh, cudaStream_t st) {
     const size_t n = (size_t)probe_count_x(p) * probe_count_y(p) * 3u;
@@ -109,7 +153,7 @@ void rt3_launch_probe_interpolate(rt3_context* c, const rt3_params& p, const uin
                                   cudaStream_t st) {
     const size_t n = (size_t)p.window_size[0] * (size_t)p.window_size[1];
     if (!n) return;
-    uint32_t* failed = ensure<uint32_t>(c, c->px_rng, n);
+    uint32_t* failed = ensure<uint32_t>(c, c->px_failed, n);
     RT3_LAUNCH(c, k_probe_interpolate, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, p, gbuffer, depth, sh, (float4*)light, failed);
     RT3_LAUNCH(c, k_probe_failed, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, (uint32_t)n, failed, (float4*)light);
 }
@@ -120,4 +164,11 @@ void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles
     if (!total) return;
     RT3_LAUNCH(c, k_untile, div_up(total, PASS_THREADS), PASS_THREADS, 0, st, d_rects, n_tiles, tile_w, tile_h, (const float4*)slab, (float4*)frame, frame_w,
                frame_h);
+}
+
+void rt3_launch_scatter_tiles(rt3_context* c, const rt3_rect* d_rects, const unsigned long long* d_dst, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h,
+                              const float* slab, uint32_t dst_pitch, cudaStream_t st) {
+    size_t total = (size_t)n_tiles * tile_w * tile_h;
+    if (!total) return;
+    RT3_LAUNCH(c, k_scatter_tiles, div_up(total, PASS_THREADS), PASS_THREADS, 0, st, d_rects, d_dst, n_tiles, tile_w, tile_h, (const float4*)slab, dst_pitch);
 }

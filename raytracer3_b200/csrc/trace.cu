@@ -73,8 +73,8 @@ __global__ void __launch_bounds__(256) k_l2_sweep(const uint4* __restrict__ buf,
     if (acc.x == 0x12345678u && acc.y == 0x9ABCDEFu) sink[0] = acc;   /* keep the loads alive */
 }
 
-unsigned long long* work_counter(rt3_context* c, cudaStream_t st) {
-    unsigned long long* w = (unsigned long long*)ensure<unsigned long long>(c, c->d_counts, 64) + 32;
+unsigned long long* work_counter(rt3_context* c, unsigned long long* given, cudaStream_t st) {
+    unsigned long long* w = given ? given : (unsigned long long*)ensure<unsigned long long>(c, c->d_counts, 64) + 32;
     RT3_CUDA(c, cudaMemsetAsync(w, 0, 8 * 4, st));
     return w;
 }
@@ -93,11 +93,11 @@ cudaEvent_t prof_event(rt3_context* c) {
 int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
 
 template <bool ANY>
-void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, uint32_t* bits, cudaStream_t st) {
+void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, uint32_t* bits, unsigned long long* wc, cudaStream_t st) {
     static const int keep = env_int("RT3_TRACE_KEEP", 28);
     static const int waves = env_int("RT3_TRACE_BLOCKS_PER_SM", 8);
     static const int legacy = env_int("RT3_TRACE_STATIC", 0);
-    unsigned long long* w = work_counter(c, st);
+    unsigned long long* w = work_counter(c, wc, st);
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * waves, (n_max + TRACE_THREADS - 1) / TRACE_THREADS);
     const WideNode* nodes = c->bvh_nodes.as<WideNode>();
     const Tri48* tris = c->bvh_tris.as<Tri48>();
@@ -118,23 +118,25 @@ void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, ui
 
 }  // namespace
 
-void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, cudaStream_t st) {
+void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, unsigned long long* wc,
+                              cudaStream_t st) {
     if (n_max == 0) return;
     if (c->prof_on) RT3_CUDA(c, cudaEventRecord(prof_event(c), st));
-    launch_dyn<false>(c, rays, d_count, n_max, hits, nullptr, st);
+    launch_dyn<false>(c, rays, d_count, n_max, hits, nullptr, wc, st);
     if (c->prof_on) RT3_CUDA(c, cudaEventRecord(prof_event(c), st));
 }
 
-void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits, cudaStream_t st) {
+void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits, unsigned long long* wc,
+                          cudaStream_t st) {
     if (n_max == 0) return;
-    launch_dyn<true>(c, rays, d_count, n_max, nullptr, bits, st);
+    launch_dyn<true>(c, rays, d_count, n_max, nullptr, bits, wc, st);
 }
 
 void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out) {
     memset(out, 0, sizeof(*out));
     if (n == 0) return;
     cudaStream_t st = 0;
-    unsigned long long* w = work_counter(c, st);
+    unsigned long long* w = work_counter(c, nullptr, st);
     rt3_hit* hits = ensure<rt3_hit>(c, c->f_hits, n);
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * 12, (n + TRACE_THREADS - 1) / TRACE_THREADS);
     RT3_LAUNCH(c, (k_trace<false, true>), grid, TRACE_THREADS, 0, st, c->bvh_nodes.as<WideNode>(), c->bvh_tris.as<Tri48>(), rays, (const uint32_t*)nullptr, n, hits,

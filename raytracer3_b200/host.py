@@ -242,7 +242,7 @@ class WorkSize2D:
         return self.x, self.y
 
 
-_FORMATS = {"RGBA32UI": ("int32", 4), "R32F": ("float32", 1), "RGBA32F": ("float32", 4), "RG32UI": ("int32", 2), "RG32F": ("float32", 2)}
+_FORMATS = {"RGBA32UI": ("int32", 4), "R32F": ("float32", 1), "RGBA32F": ("float32", 4), "RG32UI": ("int32", 2), "RG32F": ("float32", 2), "R16UI": ("int16", 1)}
 
 
 class RenderGraph:
@@ -350,13 +350,16 @@ class ComputePass(_PassBuilder):
         p = ptr(self._constants)
         if self._shader == "postprocess":
             ctx.check(ctx.L.rt3_pass_postprocess(ctx.h, p, Rect(0, 0, x, y), self._ptr("Depth"), self._ptr("In"), self._ptr("Out"), ctx.stream()))
+        elif self._shader == "structured_importance_sampling":     # shaders/old/structured_importance_sampling.slang, 8x8 threads per probe
+            ctx.check(ctx.L.rt3_pass_probe_sis(ctx.h, p, self._ptr("gbuffer"), self._ptr("out"), ctx.stream()))
         elif self._shader == "spherical_harmonic_conversion":
             ctx.check(ctx.L.rt3_pass_probe_sh(ctx.h, p, self._ptr("probe_atlas"), self._ptr("out"), ctx.stream()))
         elif self._shader == "interpolate_probes":
             ctx.check(ctx.L.rt3_pass_probe_interpolate(ctx.h, p, self._ptr("gbuffer"), self._ptr("gbuffer_depth"), self._ptr("sh_coeficents"),
                                                        self._ptr("Light"), ctx.stream()))
         else:
-            raise ValueError(f"unknown compute shader '{self._shader}' (known: postprocess, spherical_harmonic_conversion, interpolate_probes)")
+            raise ValueError(f"unknown compute shader '{self._shader}' (known: postprocess, structured_importance_sampling, "
+                             "spherical_harmonic_conversion, interpolate_probes)")
         return self.name
 
 
@@ -388,9 +391,10 @@ class Renderer:
         rg.frame_number += 1
         return rg.tensor(light)
 
-    def probe_frame(self, gconst):
-        """The screen-space probe path: gbuffer -> trace_probes -> spherical_harmonic_conversion -> interpolate_probes,
-        probe atlas ping-ponged for the temporal blend.  Returns the Light tensor."""
+    def probe_frame(self, gconst, sis=False):
+        """The screen-space probe path: gbuffer -> [structured_importance_sampling ->] trace_probes ->
+        spherical_harmonic_conversion -> interpolate_probes, probe atlas ping-ponged for the temporal blend.  Returns the Light tensor.
+        sis=True runs the direction-selection pass and binds its u16 image to trace_probes; otherwise the uniform assignment."""
         rg = self.rg
         p = np.ascontiguousarray(gconst)
         aw, ah, nsh = C.c_uint32(0), C.c_uint32(0), C.c_uint32(0)
@@ -400,8 +404,14 @@ class Renderer:
         atlas, prev = f"probe_atlas{self.probe_cur}", f"probe_atlas{1 - self.probe_cur}"
         (RayTracingPass.new(rg, "gbuffer").shader("gbuffer").constants(gconst).write("gbuffer", "gbuffer").write("gbuffer_depth", "gbuffer_depth")
          .launch(WorkSize2D.FullScreen()))
-        (RayTracingPass.new(rg, "trace_probes").shader("trace_probes").constants(gconst).read("gbuffer", "gbuffer").read("gbuffer_depth", "gbuffer_depth")
-         .read("prev_probe_atlas", prev).write("probe_atlas", atlas).launch(WorkSize2D.FractionalFullScreen(2, 2)))
+        tp = (RayTracingPass.new(rg, "trace_probes").shader("trace_probes").constants(gconst).read("gbuffer", "gbuffer").read("gbuffer_depth", "gbuffer_depth")
+              .read("prev_probe_atlas", prev).write("probe_atlas", atlas))
+        if sis:
+            rg.buffer("probe_directions", (ah.value, aw.value), "int16")
+            (ComputePass.new(rg, "sis").shader("structured_importance_sampling").constants(gconst).read("gbuffer", "gbuffer").write("out", "probe_directions")
+             .dispatch(WorkSize2D.FractionalFullScreen(2, 2)))
+            tp.read("directions", "probe_directions")
+        tp.launch(WorkSize2D.FractionalFullScreen(2, 2))
         (ComputePass.new(rg, "sh").shader("spherical_harmonic_conversion").constants(gconst).read("probe_atlas", atlas).write("out", "probe_sh")
          .dispatch(WorkSize2D.FractionalFullScreen(2, 2)))
         (ComputePass.new(rg, "interpolate").shader("interpolate_probes").constants(gconst).read("gbuffer", "gbuffer").read("gbuffer_depth", "gbuffer_depth")
@@ -430,34 +440,49 @@ class Renderer:
 
 
 class TiledRenderer:
-    """Rank-local renderer for screen-tile sharding: this rank's tiles of a W x H frame are rendered
-    into tile-major slabs; `gather` all-gathers the Light slabs over NCCL (torch.distributed) and un-tiles them."""
+    """Rank-local renderer for screen-tile sharding (tiles.py): this rank's tiles of a W x H frame are rendered into
+    tile-major slabs with no communication while samples accumulate; the finished image is DELIVERED in bands of rows — rank r ends up with
+    rows tiles.band_rows()[r], the part it presents or reads back — by `exchange`:
+
+      p2p   rt3_scatter_tiles_rgba32f: one kernel of ours stores every tile straight into its owner's band buffer over NVLink peer memory
+            (torch symmetric memory provides the mapping and the barrier that follows); no collective library on the data path
+      a2a   one NCCL all_to_all_single (every rank sends (N-1)/N of its slab, receives its band) + rt3_untile_rgba32f
+
+    `gather` (all_gather of the slabs to EVERY rank + full-frame un-tile) is kept for callers that need the whole image on each GPU; it
+    moves N times the bytes."""
 
     def __init__(self, ctx, world, width, height, rank, world_size, tile=64):
-        import ctypes as C
         torch = _torch()
-        from .tiles import all_tiles, rank_tiles
+        from . import tiles as T
         self.ctx, self.world = ctx, world
         self.W, self.H, self.rank, self.world_size, self.tile = width, height, rank, world_size, tile
-        self.rects = np.ascontiguousarray(rank_tiles(width, height, rank, world_size, tile))
-        self.all_rects = np.ascontiguousarray(all_tiles(width, height, world_size, tile))
+        self.rects = np.ascontiguousarray(T.rank_tiles(width, height, rank, world_size, tile))
+        self.all_rects = np.ascontiguousarray(T.all_tiles(width, height, world_size, tile))
         assert self.rects["w"].max() == tile and self.rects["h"].max() == tile, "every rank needs at least one full tile"
         n = len(self.rects)
         dev = f"cuda:{ctx.device}"
+        self.dev = dev
         self.gbuffer = torch.zeros((n, tile, tile, 4), dtype=torch.int32, device=dev)
         self.depth = torch.zeros((n, tile, tile), dtype=torch.float32, device=dev)
         self.light = [torch.zeros((n, tile, tile, 4), dtype=torch.float32, device=dev) for _ in range(2)]
-        self.gathered = torch.zeros((world_size * n, tile, tile, 4), dtype=torch.float32, device=dev) if world_size > 1 else None
-        self.frame_buf = torch.zeros((height, width, 4), dtype=torch.float32, device=dev)
-        self.frame_ring = [self.frame_buf]      # grown to FRAMES_IN_FLIGHT by enable_host_output
         self.cur = 0
-        # the gather of frame i (side stream) overlaps the rendering of frame i+1 (caller's stream)
-        self.side = torch.cuda.Stream(device=dev)
-        self.ev_rendered_slab = [torch.cuda.Event(), torch.cuda.Event()]
-        self.ev_gathered_slab = [None, None]
-        self.ev_last_gather = None
         self.pixels = int((self.rects["w"].astype(np.int64) * self.rects["h"]).sum())
+        # delivery in bands
+        self.bands = T.band_rows(height, world_size, tile)
+        self.row0, self.row1 = self.bands[rank]
+        self.band_h_max = max(1, max(b - a for a, b in self.bands))
+        self.counts = T.exchange_plan(width, height, world_size, tile)           # counts[s][d]: tiles of rank s inside the band of rank d
+        self.n_real = int(self.counts[rank].sum())
+        self.band_rects = np.ascontiguousarray(T.band_tiles(width, height, rank, world_size, tile))
+        self.exchange_mode, self.exchange_note = None, ""
+        self.side = torch.cuda.Stream(device=dev)                                 # delivery of frame i overlaps the rendering of frame i + 1
+        self.ev_rendered_slab = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ev_delivered_slab = [None, None]
+        self.ev_last_delivery = None
+        self.gathered = None
+        self.frame_buf = None
 
+    # ---- rendering -------------------------------------------------------------------------------------------------------
     def frame(self, gconst):
         L, h, st = self.ctx.L, self.ctx.h, self.ctx.stream()
         p = np.ascontiguousarray(gconst)
@@ -468,72 +493,119 @@ class TiledRenderer:
         self.cur = 1 - self.cur
         return light
 
-    def frame_gather_overlapped(self, gconst):
-        """frame() on the current stream, gather() + un-tile on the side stream: NCCL traffic and the un-tile of frame i run while
-        frame i+1 is traced.  The Light slab a frame writes is the one gathered two frames earlier, so the current stream first
-        waits for that gather.  Call drain() before reading frame_buf or stopping a clock."""
+    # ---- delivery --------------------------------------------------------------------------------------------------------
+    def setup_exchange(self, mode="auto", slots=2):
+        """Allocate `slots` band buffers ([band rows, W, 4] RGBA32F each) and choose the delivery path ('p2p', 'a2a' or 'auto' = p2p when
+        torch symmetric memory can map the peers' buffers, agreed on by all ranks)."""
+        torch = _torch()
+        W, bh, N = self.W, self.band_h_max, self.world_size
+        self.slots = slots
+        per = bh * W * 4
+        buf = None
+        if N == 1:
+            mode = "local"
+        if mode in ("auto", "p2p"):
+            import torch.distributed as dist
+            ok, hdl = 1, None
+            try:
+                import torch.distributed._symmetric_memory as symm
+                buf = symm.empty(slots * per, dtype=torch.float32, device=self.dev)
+                hdl = symm.rendezvous(buf, dist.group.WORLD)
+                ptrs = [int(x) for x in hdl.buffer_ptrs]
+                assert len(ptrs) == N and all(ptrs)
+            except Exception as e:  # noqa: BLE001
+                ok, self.exchange_note = 0, f"symmetric memory unavailable: {type(e).__name__}: {e}"[:200]
+            flag = torch.tensor([ok], dtype=torch.int32, device=self.dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)                           # every rank takes the same path
+            if int(flag.item()) == 1:
+                self.hdl, self.peer_ptrs = hdl, ptrs
+                from . import tiles as T
+                real = self.rects[: self.n_real]
+                self.dst = []
+                for k in range(slots):
+                    d = np.zeros(self.n_real, np.uint64)
+                    for i, r in enumerate(real):
+                        owner = T.band_of_row(int(r["y0"]), self.H, N, self.tile)
+                        d[i] = ptrs[owner] + 4 * (k * per + ((int(r["y0"]) - self.bands[owner][0]) * W + int(r["x0"])) * 4)
+                    self.dst.append(d)
+                mode = "p2p"
+            elif mode == "p2p":
+                raise RuntimeError("peer-memory delivery requested but " + (self.exchange_note or "another rank could not map it"))
+            else:
+                mode, buf = "a2a", None
+        if buf is None:
+            buf = torch.zeros(slots * per, dtype=torch.float32, device=self.dev)
+        self.band_store = buf
+        self.band = [buf[k * per:(k + 1) * per].view(bh, W, 4) for k in range(slots)]
+        if mode == "a2a":
+            T2 = self.tile * self.tile * 4
+            self.in_splits = [int(c) * T2 for c in self.counts[self.rank]]
+            self.out_splits = [int(self.counts[s][self.rank]) * T2 for s in range(N)]
+            self.recv = torch.zeros(max(1, sum(self.out_splits)), dtype=torch.float32, device=self.dev)
+        self.exchange_mode = mode
+        return mode
+
+    def exchange(self, light, slot=0):
+        """Deliver the finished slab: afterwards (in stream order) band[slot][: row1 - row0] holds this rank's rows of the frame."""
+        L, h = self.ctx.L, self.ctx.h
+        T = self.tile
+        if self.exchange_mode == "p2p":
+            self.ctx.check(L.rt3_scatter_tiles_rgba32f(h, ptr(self.rects), ptr(self.dst[slot]), self.n_real, T, T, light.data_ptr(), self.W, self.ctx.stream()))
+            self.hdl.barrier(channel=0)                                           # every rank's stores have landed before anyone reads its band
+        elif self.exchange_mode == "a2a":
+            import torch.distributed as dist
+            send = light.view(-1)[: self.n_real * T * T * 4]
+            dist.all_to_all_single(self.recv[: sum(self.out_splits)], send, self.out_splits, self.in_splits)
+            self.ctx.check(L.rt3_untile_rgba32f(h, ptr(self.band_rects), len(self.band_rects), T, T, self.recv.data_ptr(), self.band[slot].data_ptr(),
+                                                self.W, self.row1 - self.row0, self.ctx.stream()))
+        elif self.exchange_mode == "local":
+            self.ctx.check(L.rt3_untile_rgba32f(h, ptr(self.rects), len(self.rects), T, T, light.data_ptr(), self.band[slot].data_ptr(), self.W, self.H,
+                                                self.ctx.stream()))
+        else:
+            raise RuntimeError("setup_exchange() has not been called")
+        return self.band[slot][: self.row1 - self.row0]
+
+    def frame_exchange_overlapped(self, gconst, slot):
+        """frame() on the current stream, exchange() on the side stream: the delivery of frame i runs while frame i + 1 is traced.  The Light
+        slab a frame writes is the one delivered two frames earlier, so the current stream first waits for that delivery.  Call drain()
+        before reading a band or stopping a clock."""
         torch = _torch()
         cur = torch.cuda.current_stream()
         c = self.cur
-        if self.ev_gathered_slab[c] is not None:
-            cur.wait_event(self.ev_gathered_slab[c])
+        if self.ev_delivered_slab[c] is not None:
+            cur.wait_event(self.ev_delivered_slab[c])
         light = self.frame(gconst)
         self.ev_rendered_slab[c].record(cur)
         with torch.cuda.stream(self.side):
             self.side.wait_event(self.ev_rendered_slab[c])
-            fb = self.gather(light)
+            band = self.exchange(light, slot)
             ev = torch.cuda.Event()
             ev.record(self.side)
-        self.ev_gathered_slab[c] = ev
-        self.ev_last_gather = ev
-        return fb
+        self.ev_delivered_slab[c] = ev
+        self.ev_last_delivery = ev
+        return band
 
     def drain(self):
-        if self.ev_last_gather is not None:
-            _torch().cuda.current_stream().wait_event(self.ev_last_gather)
+        if self.ev_last_delivery is not None:
+            _torch().cuda.current_stream().wait_event(self.ev_last_delivery)
 
-    # ---- end-to-end host output, frames in flight (swapchain.rs:8) ------------------------------------------------------
-    def enable_host_output(self, host_frames, row0, row1):
-        """`host_frames`: FRAMES_IN_FLIGHT pinned host tensors [H, W, 4] (shared between the ranks of a node: every rank reads
-        back ITS band of rows [row0, row1) of the gathered frame over its own PCIe link, so the read-back does not grow with
-        the number of GPUs)."""
-        torch = _torch()
-        self.host_frames, self.row0, self.row1 = host_frames, row0, row1
-        n = len(host_frames)
-        self.frame_ring = [self.frame_buf] + [torch.zeros_like(self.frame_buf) for _ in range(n - 1)]
-        self.ev_copied = [torch.cuda.Event() for _ in range(n)]
-        self.busy = [False] * n
-        self.next_ticket = 0
+    def read_back(self, band, host_frame):
+        """This rank's band -> rows [row0, row1) of a page-locked host frame [H, W, 4] (shared by the ranks of the node: every rank reads back
+        its own rows over its own PCIe link).  Asynchronous on the current stream."""
+        if self.row1 > self.row0:
+            host_frame[self.row0:self.row1].copy_(band, non_blocking=True)
 
-    def submit_frame_host(self, gconst):
-        torch = _torch()
-        t = self.next_ticket
-        k = t % len(self.host_frames)
-        if self.busy[k]:
-            self.ev_copied[k].synchronize()
-            self.busy[k] = False
-        self.frame_buf = self.frame_ring[k]
-        fb = self.frame_gather_overlapped(gconst)            # gather + un-tile on the side stream ...
-        with torch.cuda.stream(self.side):                    # ... followed there by this rank's band of the read-back
-            self.host_frames[k][self.row0:self.row1].copy_(fb[self.row0:self.row1], non_blocking=True)
-            self.ev_copied[k].record(self.side)
-        self.busy[k] = True
-        self.next_ticket = t + 1
-        return t
-
-    def wait_frame(self, ticket):
-        lo = max(0, self.next_ticket - len(self.host_frames))
-        for t in range(lo, ticket + 1):
-            k = t % len(self.host_frames)
-            if self.busy[k]:
-                self.ev_copied[k].synchronize()
-                self.busy[k] = False
-
+    # ---- the whole image on every rank (N times the traffic of exchange) --------------------------------------------------
     def gather(self, light):
         """One all_gather of the rank-local slabs + un-tile into the full frame (every rank gets the image)."""
         torch = _torch()
+        n = len(self.rects)
+        if self.frame_buf is None:
+            self.frame_buf = torch.zeros((self.H, self.W, 4), dtype=torch.float32, device=self.dev)
         if self.world_size > 1:
             import torch.distributed as dist
+            if self.gathered is None:
+                self.gathered = torch.zeros((self.world_size * n, self.tile, self.tile, 4), dtype=torch.float32, device=self.dev)
             dist.all_gather_into_tensor(self.gathered, light)
             slab, rects = self.gathered, self.all_rects
         else:

@@ -30,6 +30,8 @@ int launch(unsigned grid, unsigned block, std::function<void()> f) {
 unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
 const int SM_COUNT = 148;
+int g_strips = 1;                         /* pemu_set_strips: how many strips rt3_launch_reference would use */
+uint64_t* g_round_lengths = nullptr;      /* pemu_set_round_lengths: queue length at the start of every round (regeneration statistics) */
 
 /* launch_dyn (trace.cu): persistent warps over a queue whose length lives in memory */
 int trace_closest(const WideNode* nodes, const Tri48* tris, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits) {
@@ -89,53 +91,63 @@ int pemu_frame(const void* scene_view, const uint32_t* shade_rec, const uint32_t
     if (!m.work) return 0;
     /* ---- rt3_launch_gbuffer */
     if (launch(div_up(m.work, 128), 128, [&]() { k_gbuffer(view, nodes, tris, p, m, gbuffer, depth, ids, bary, &dc, nullptr); })) return -1;
-    /* ---- rt3_launch_reference */
-    const size_t W = m.work;
+    /* ---- rt3_launch_reference: n_strips wavefronts (run one after the other here; on the device they run on streams of their own) */
     const bool nee = nee_enabled(p.flags), layered = (p.flags & RT3_FLAG_SPECULAR) != 0;
-    std::vector<rt3_ray> q_rays[2] = {std::vector<rt3_ray>(W), std::vector<rt3_ray>(W)}, srays(nee ? W : 1);
-    std::vector<float4> q_thr[2] = {std::vector<float4>(W), std::vector<float4>(W)}, px_radiance(W), scontrib(nee ? W : 1);
-    std::vector<rt3_hit> q_hits(W);
-    std::vector<uint32_t> px_rng(W), sbits((W + 31) / 32 + 1);
-    std::vector<float> q_pdf[2] = {std::vector<float>(nee ? W : 1), std::vector<float>(nee ? W : 1)};
-    uint32_t counts[4] = {0, 0, 0, 0};
-    NeeQueues nq = {nullptr, nullptr, nullptr, nullptr, nullptr};
-    if (nee) { nq.srays = srays.data(); nq.scontrib = scontrib.data(); nq.scount = counts + 2; }
-    const unsigned grid = std::min<unsigned>(div_up(W, PASS_THREADS), (unsigned)SM_COUNT * 8u);
-    auto resolve_shadows = [&]() -> int {
-        if (trace_any(nodes, tris, nq.srays, nq.scount, W, sbits.data())) return -1;
-        return launch(grid, PASS_THREADS, [&]() { k_ref_shadow(nq.scontrib, sbits.data(), nq.scount, px_radiance.data()); });
-    };
-    for (uint32_t sidx = 0; sidx < p.samples; ++sidx) {
-        counts[0] = counts[1] = counts[2] = 0;
+    std::vector<float4> px_radiance(m.work);
+    std::vector<uint2> px_path(m.work);
+    uint32_t S = g_strips < 1 ? 1u : (uint32_t)g_strips;
+    for (uint32_t strip = 0; strip < S; ++strip) {
+        const StripMap sm = make_strip(m.work, strip, S);
+        const size_t W = sm.local_work;
+        if (!W) continue;
+        std::vector<rt3_ray> q_rays[2] = {std::vector<rt3_ray>(W), std::vector<rt3_ray>(W)}, srays(nee ? W : 1);
+        std::vector<float4> q_thr[2] = {std::vector<float4>(W), std::vector<float4>(W)}, scontrib(nee ? W : 1);
+        std::vector<rt3_hit> q_hits(W);
+        std::vector<uint32_t> sbits((W + 31) / 32 + 1);
+        std::vector<float> q_pdf[2] = {std::vector<float>(nee ? W : 1), std::vector<float>(nee ? W : 1)};
+        uint32_t counts[4] = {0, 0, 0, 0};
+        NeeQueues nq = {nullptr, nullptr, nullptr, nullptr, nullptr};
+        if (nee) { nq.srays = srays.data(); nq.scontrib = scontrib.data(); nq.scount = counts + 2; }
+        const unsigned grid = std::min<unsigned>(div_up(W, PASS_THREADS), (unsigned)SM_COUNT * 8u);
+        const RegenInputs gin = {gbuffer, depth};
+        auto resolve_shadows = [&]() -> int {
+            if (trace_any(nodes, tris, nq.srays, nq.scount, W, sbits.data())) return -1;
+            return launch(grid, PASS_THREADS, [&]() { k_ref_shadow(nq.scontrib, sbits.data(), nq.scount, px_radiance.data()); });
+        };
         nq.pdf_in = nullptr; nq.pdf_out = nee ? q_pdf[0].data() : nullptr;
-        const int first = sidx == 0 ? 1 : 0;
         if (launch(grid, PASS_THREADS, [&]() {
-                if (layered) k_ref_init<true>(view, p, m, gbuffer, depth, px_radiance.data(), px_rng.data(), first, q_rays[0].data(), q_thr[0].data(), counts, nq, &dc);
-                else k_ref_init<false>(view, p, m, gbuffer, depth, px_radiance.data(), px_rng.data(), first, q_rays[0].data(), q_thr[0].data(), counts, nq, &dc);
+                if (layered) k_ref_init<true>(view, p, m, sm, gbuffer, depth, px_radiance.data(), px_path.data(), q_rays[0].data(), q_thr[0].data(), counts, nq, &dc);
+                else k_ref_init<false>(view, p, m, sm, gbuffer, depth, px_radiance.data(), px_path.data(), q_rays[0].data(), q_thr[0].data(), counts, nq, &dc);
             })) return -1;
-        if (nee && p.bounces > 1 && resolve_shadows()) return -1;
+        const uint64_t rounds = p.bounces > 1 ? (uint64_t)p.samples * (p.bounces - 1) : 0;
+        if (nee && rounds && resolve_shadows()) return -1;
         int cur = 0;
-        for (uint32_t b = 1; b < p.bounces; ++b) {
+        for (uint64_t r = 0; r < rounds; ++r) {
+            if (g_round_lengths && r < 4096) g_round_lengths[r] += counts[cur];
             if (trace_closest(nodes, tris, q_rays[cur].data(), counts + cur, W, q_hits.data())) return -1;
             counts[1 - cur] = 0;
             if (nee) counts[2] = 0;
             nq.pdf_in = nee ? q_pdf[cur].data() : nullptr; nq.pdf_out = nee ? q_pdf[1 - cur].data() : nullptr;
             if (launch(grid, PASS_THREADS, [&]() {
-                    if (layered) k_ref_shade<true>(view, p, m, b, q_rays[cur].data(), q_hits.data(), q_thr[cur].data(), counts + cur, q_rays[1 - cur].data(),
-                                                   q_thr[1 - cur].data(), counts + (1 - cur), px_radiance.data(), px_rng.data(), nq, &dc);
-                    else k_ref_shade<false>(view, p, m, b, q_rays[cur].data(), q_hits.data(), q_thr[cur].data(), counts + cur, q_rays[1 - cur].data(),
-                                            q_thr[1 - cur].data(), counts + (1 - cur), px_radiance.data(), px_rng.data(), nq, &dc);
+#define PEMU_SHADE(L, R) k_ref_shade<L, R>(view, p, m, gin, q_rays[cur].data(), q_hits.data(), q_thr[cur].data(), counts + cur, q_rays[1 - cur].data(), \
+                                           q_thr[1 - cur].data(), counts + (1 - cur), px_radiance.data(), px_path.data(), nq, &dc)
+                    if (layered) { if (p.samples > 1) PEMU_SHADE(true, true); else PEMU_SHADE(true, false); }
+                    else { if (p.samples > 1) PEMU_SHADE(false, true); else PEMU_SHADE(false, false); }
+#undef PEMU_SHADE
                 })) return -1;
-            if (nee && b != p.bounces - 1 && resolve_shadows()) return -1;
+            if (nee && r + 1 != rounds && resolve_shadows()) return -1;
             cur = 1 - cur;
         }
+        if (launch(div_up(W, PASS_THREADS), PASS_THREADS, [&]() { k_ref_finish(p, m, sm, px_radiance.data(), prev, light); })) return -1;
     }
-    if (launch(div_up(W, PASS_THREADS), PASS_THREADS, [&]() { k_ref_finish(p, m, px_radiance.data(), prev, light); })) return -1;
+    const size_t W = m.work;
     /* ---- rt3_launch_postprocess */
     if (post && launch(div_up(W, PASS_THREADS), PASS_THREADS, [&]() { k_postprocess(view, p, m, depth, light, post); })) return -1;
     if (counters5) { counters5[0] = dc.rays_primary; counters5[1] = dc.rays_secondary; counters5[2] = dc.rays_shadow; counters5[3] = dc.paths_started; counters5[4] = dc.paths_escaped; }
     return 0;
 }
+void pemu_set_strips(int n) { g_strips = n; }
+void pemu_set_round_lengths(uint64_t* out4096) { g_round_lengths = out4096; }
 const char* pemu_last_error() { return wemu::g_error ? wemu::g_error : ""; }
 
 }

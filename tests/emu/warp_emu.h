@@ -43,6 +43,7 @@ static inline float4 make_float4(float x, float y, float z, float w) { float4 r 
 static inline uint2 make_uint2(uint32_t x, uint32_t y) { uint2 r = {x, y}; return r; }
 #define __global__
 #define __device__
+#define __host__
 #define __forceinline__ inline
 #define __launch_bounds__(...)
 #define __shared__ static

@@ -12,7 +12,7 @@ from raytracer3_b200 import scenes, types
 from raytracer3_b200.camera import camera_for, make_params
 
 
-def _check(sc, W, H, flags, frames=1, samples=1, bounces=4, postprocess=False, **build):
+def _check(sc, W, H, flags, frames=1, samples=1, bounces=4, postprocess=False, strips=1, round_lengths=None, **build):
     orc = OracleScene(sc)
     emu = PassEmu(orc, **build)
     prev_o = prev_e = None
@@ -20,7 +20,7 @@ def _check(sc, W, H, flags, frames=1, samples=1, bounces=4, postprocess=False, *
         p = make_params(camera_for(sc, "cam0", W, H), W, H, frame=frame, bounces=bounces, samples=samples, blendfactor=1.0 if frame == 0 else 0.5, flags=flags)
         gb, dp, ids, bary = orc.pass_gbuffer(p)
         want, cnt = orc.pass_reference(p, gb, dp, prev_light=prev_o)
-        got = emu.frame(p, prev_light=prev_e, postprocess=postprocess)
+        got = emu.frame(p, prev_light=prev_e, postprocess=postprocess, strips=strips, round_lengths=round_lengths)
         assert (got["ids"] == ids).all()                                                      # primary-hit ids: bit-exact
         assert (got["depth"].view(np.uint32) == dp.view(np.uint32)).all()
         assert (got["bary"].view(np.uint32) == bary.view(np.uint32)).all()
@@ -55,3 +55,38 @@ def test_treelet_build_under_the_product_kernels():
     sc = scenes.synthetic_atrium(0.02)
     sc["bluenoise"] = scenes.blue_noise_tile(64)
     _check(sc, 48, 27, types.FLAG_ENV | types.FLAG_BLUENOISE, treelet_passes=2)
+
+
+def test_regeneration_keeps_the_queue_full_and_the_image_identical():
+    """Ray regeneration between bounces (north_star; the loop being turned inside out is refrence_mode.slang:28-57): with samples > 1 a path
+    that ends is replaced, in the same shade thread, by the first bounce of its pixel's next sample.  The image stays bit-identical to the
+    per-pixel loop of the oracle (_check), and the queue of round r holds every unfinished pixel instead of shrinking bounce by bounce:
+    its length stays above 90 % of the first round's for the first (samples - 1) * 2 rounds."""
+    sc = scenes.synthetic_atrium(0.02)
+    sc["bluenoise"] = scenes.blue_noise_tile(64)
+    samples, bounces = 6, 4
+    lengths = np.zeros(4096, np.uint64)
+    cnt = _check(sc, 64, 36, types.FLAG_ENV | types.FLAG_BLUENOISE, samples=samples, bounces=bounces, round_lengths=lengths)
+    rounds = samples * (bounces - 1)
+    assert int(lengths[:rounds].sum()) == cnt.rays_secondary and lengths[rounds:].sum() == 0
+    assert lengths[0] > 0 and (lengths[:(samples - 1) * 2] > 0.9 * lengths[0]).all(), lengths[:rounds]
+    assert lengths[rounds - 1] < 0.5 * lengths[0]                                               # the tail: only the longest pixel chains are left
+
+
+@pytest.mark.parametrize("samples,bounces,flag_names", [(5, 3, ("ENV",)), (3, 1, ()), (2, 0, ()), (4, 2, ("ENV", "NEE")), (3, 4, ("ENV", "SPECULAR", "NEE"))])
+def test_regeneration_sample_and_bounce_counts(samples, bounces, flag_names):
+    flags = 0
+    for n in flag_names:
+        flags |= getattr(types, "FLAG_" + n)
+    sc = scenes.metal_cornell_box() if "SPECULAR" in flag_names else scenes.cornell_box()
+    if flags & types.FLAG_ENV:
+        sc["environment"] = scenes.analytic_sky(64, 32)
+    _check(sc, 40, 24, flags, samples=samples, bounces=bounces, frames=2)
+
+
+@pytest.mark.parametrize("strips", [2, 3])
+def test_strips_do_not_change_the_image(strips):
+    """rt3_launch_reference runs the frame as `strips` concurrent wavefronts (units of 2048 work indices dealt round-robin): same image."""
+    sc = scenes.synthetic_atrium(0.02)
+    sc["bluenoise"] = scenes.blue_noise_tile(64)
+    _check(sc, 200, 120, types.FLAG_ENV | types.FLAG_BLUENOISE | types.FLAG_NEE, samples=2, bounces=3, strips=strips)

@@ -120,6 +120,28 @@ def test_tile_lists_with_clipped_and_empty_tiles(gpu_ctx, cornell, W, H, N, tile
     gpu_ctx.check(gpu_ctx.L.rt3_untile_rgba32f(gpu_ctx.h, ptr(rects), len(rects), tile, tile, gathered.data_ptr(), frame.data_ptr(), W, H, gpu_ctx.stream()))
     assert torch.equal(frame.view(torch.int32), want.view(torch.int32))
     assert float(frame[..., :3].abs().sum()) > 0
+    # delivery in bands by peer-memory stores (rt3_scatter_tiles_rgba32f), the "peers" being buffers on this GPU: every logical rank stores
+    # its tiles straight into the band of rows of the rank that presents them; each band must equal those rows of the full-frame render
+    from raytracer3_b200 import tiles as T
+    bands = T.band_rows(H, N, tile)
+    bh = max(1, max(b - a for a, b in bands))
+    band_buf = [torch.full((bh, W, 4), -1.0, dtype=torch.float32, device="cuda") for _ in range(N)]
+    for rk, R in enumerate(ranks):
+        real = R.rects[: R.n_real]
+        dst = np.zeros(R.n_real, np.uint64)
+        for i, t in enumerate(real):
+            o = T.band_of_row(int(t["y0"]), H, N, tile)
+            dst[i] = band_buf[o].data_ptr() + 16 * ((int(t["y0"]) - bands[o][0]) * W + int(t["x0"]))
+        gpu_ctx.check(gpu_ctx.L.rt3_scatter_tiles_rgba32f(gpu_ctx.h, ptr(R.rects), ptr(dst), R.n_real, tile, tile, slabs[rk].data_ptr(), W, gpu_ctx.stream()))
+    for rk, (a, b) in enumerate(bands):
+        assert torch.equal(band_buf[rk][: b - a].view(torch.int32), want[a:b].view(torch.int32)), rk
+    # ... and the single-process form of TiledRenderer.exchange
+    one = TiledRenderer(gpu_ctx, w, W, H, 0, 1, tile=tile)
+    assert one.setup_exchange() == "local"
+    for n in range(3):
+        p = make_params(cam, W, H, frame=n, bounces=3, samples=1, blendfactor=1.0 / (n + 1), flags=flags)
+        light = one.frame(p)
+    assert torch.equal(one.exchange(light, 1).view(torch.int32), want.view(torch.int32))
 
 
 def test_zero_bounces_and_progressive_accumulation(gpu_ctx, cornell):
@@ -240,3 +262,56 @@ def test_treelet_build_gives_identical_hits_and_the_emulators_tree(gpu_ctx):
     assert res["rot"][0] == EmuBvh(tris=T).info()["nodes"]
     assert res["treelet"][3] < res["rot"][3]                               # fewer node visits + 0.4 x triangle tests per ray
     assert (res["rot"][1][:, 3] != MISS).mean() > 0.5
+
+
+def test_calls_on_different_streams_are_ordered_by_the_context(gpu_ctx):
+    """All pass / trace calls of one context share its wavefront queues and counters (rt3.h conventions): a call recorded on another stream
+    than the previous one must wait, on the device, for the previous call.  Frames and ray queries are issued alternately on two streams
+    with no host synchronisation in between; every result must equal the one computed alone."""
+    import torch
+    from raytracer3_b200.host import Renderer, RenderWorld
+    sc = scenes.synthetic_atrium(0.03, environment=False)
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc); w.create_acceleration_structure()
+    W, H = 640, 360
+    r = Renderer(gpu_ctx, w, W, H)
+    closest, _ = scenes.incoherent_rays(sc, 300000, seed=3)
+    rays = torch.from_numpy(closest.view(np.float32).reshape(-1, 8)).cuda()
+    ps = [make_params(camera_for(sc, "cam0", W, H), W, H, frame=f, bounces=4, samples=2) for f in range(4)]
+    want_frames = []
+    for p in ps:
+        want_frames.append(r.frame(p).clone())
+    want_hits = w.trace_closest(rays).clone()
+    torch.cuda.synchronize()
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    got_frames, got_hits = [], []
+    for k, p in enumerate(ps):
+        with torch.cuda.stream(sa if k % 2 == 0 else sb):
+            got_frames.append(r.frame(p).clone())
+        with torch.cuda.stream(sb if k % 2 == 0 else sa):
+            got_hits.append(w.trace_closest(rays, torch.empty((rays.shape[0], 4), dtype=torch.float32, device="cuda")))
+    torch.cuda.synchronize()
+    for k in range(len(ps)):
+        assert torch.equal(got_frames[k].view(torch.int32), want_frames[k].view(torch.int32)), k
+        assert torch.equal(got_hits[k].view(torch.int32), want_hits.view(torch.int32)), k
+
+
+def test_failed_rebuild_invalidates_the_acceleration_structure(gpu_ctx):
+    """A build that fails must not leave the previous structure usable (its buffers are being overwritten): the next pass is RT3_ERR_STATE."""
+    from raytracer3_b200 import _lib
+    from raytracer3_b200.host import RenderWorld
+    from raytracer3_b200.types import BUILD_TWO_LEVEL
+    sc = scenes.instanced_grid(scenes.cornell_box(), 2)
+    f, n, m = sc["instances"][0]
+    sc["instances"][0] = (f, n, np.zeros(12, np.float32))                        # singular transform: fine when flattened, rejected by the two-level build
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc); w.create_acceleration_structure()
+    rays = scenes.random_rays(sc, 100)
+    assert len(w.trace_closest_host(rays)) == 100
+    with pytest.raises(_lib.Rt3Error):                                           # same scene, other flags: the re-build fails midway
+        w.create_acceleration_structure(1 | BUILD_TWO_LEVEL)
+    with pytest.raises(_lib.Rt3Error) as e:
+        w.trace_closest_host(rays)
+    assert e.value.status == _lib.ERR_STATE
+    w.create_acceleration_structure()                                            # and a good build makes it usable again
+    assert len(w.trace_closest_host(rays)) == 100

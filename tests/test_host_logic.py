@@ -51,6 +51,16 @@ def test_tiles_partition_the_frame(W, H, N):
     assert (cover == 1).all()                                                  # every pixel owned exactly once
     assert len({len(tiles.rank_tiles(W, H, r, N, 64)) for r in range(N)}) == 1  # equal (padded) slab sizes
     assert max(counts) - min(counts) <= 0.05 * max(counts) + 64 * 64 * 2       # balanced
+    counts = tiles.exchange_plan(W, H, N, 64)
+    bands = tiles.band_rows(H, N, 64)
+    assert bands[0][0] == 0 and bands[-1][1] == H and all(bands[i][1] == bands[i + 1][0] for i in range(N - 1))
+    for r in range(N):
+        bt = tiles.band_tiles(W, H, r, N, 64)
+        assert int((bt["w"].astype(np.int64) * bt["h"]).sum()) == (bands[r][1] - bands[r][0]) * W          # a band is covered exactly once
+        assert int(counts[:, r].sum()) == len(bt)
+        mine = tiles.rank_tiles(W, H, r, N, 64)
+        dest = [tiles.band_of_row(int(t["y0"]), H, N, 64) for t in mine if t["w"] and t["h"]]
+        assert dest == sorted(dest)                                                                        # what a rank owes a band is one contiguous run
     allr = tiles.all_tiles(W, H, N, 64)
     frame = np.arange(H * W * 4, dtype=np.float32).reshape(H, W, 4)
     back = tiles.untile_host(tiles.tile_host(frame, allr, 64), allr, 64, np.zeros_like(frame))
@@ -72,13 +82,27 @@ out = torch.zeros((world * len(mine), T, T, 4))
 dist.all_gather_into_tensor(out, slab)                                          # the one collective of the path
 got = tiles.untile_host(out.numpy(), tiles.all_tiles(W, H, world, T), T, np.zeros_like(frame))
 assert (got == frame).all(), "gathered frame differs from the single-rank frame"
+# delivery in bands (TiledRenderer.exchange, 'a2a' path): ONE all_to_all in which every rank sends what it owes each band and receives its own
+counts = tiles.exchange_plan(W, H, world, T)
+n_real = int(counts[rank].sum())
+per = T * T * 4
+send = slab.reshape(-1)[: n_real * per].contiguous()
+in_splits = [int(c) * per for c in counts[rank]]
+out_splits = [int(counts[s][rank]) * per for s in range(world)]
+recv = torch.zeros(sum(out_splits))
+dist.all_to_all_single(recv, send, out_splits, in_splits)
+row0, row1 = tiles.band_rows(H, world, T)[rank]
+band = tiles.untile_host(recv.numpy(), tiles.band_tiles(W, H, rank, world, T), T, np.zeros((row1 - row0, W, 4), np.float32))
+assert (band == frame[row0:row1]).all(), "band assembled from the all_to_all differs from the single-rank frame's rows"
+assert sum(b - a for a, b in tiles.band_rows(H, world, T)) == H
 dist.barrier()
 sys.stdout.write("rank%dok\n" % rank); sys.stdout.flush()
 '''
 
 
 def test_two_rank_gather_on_gloo(tmp_path):
-    """N > 1 host path with the gloo backend: each rank fills its slab, one all_gather, un-tile == single-rank frame."""
+    """N > 1 host path with the gloo backend: each rank fills its slab; (a) one all_gather + un-tile == the single-rank frame on every rank,
+    (b) one all_to_all + un-tile == the rank's band of rows of that frame (the delivery bench.py uses)."""
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     script = tmp_path / "worker.py"
     script.write_text(WORKER)

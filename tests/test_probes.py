@@ -178,6 +178,83 @@ def test_probe_furnace_constant_sky():
         pytest.skip("camera does not cover the triangle at every probe anchor")
 
 
+def test_structured_importance_sampling_live_lines():
+    """structured_importance_sampling.slang:19-72 as it runs today: the pdf of a direction is the mean clamped cosine against the probe's 256
+    G-buffer normals; `brdf_pdf < 0` never holds, the sort is ascending, so the test at :55 is `min pdf < pdf`: every thread whose pdf exceeds
+    the probe's minimum writes 0x8000 | ti * 4 (mip 1), the minimum-pdf thread(s) write ti (mip 0).  Checked against a float64 restatement."""
+    sc, orc, p, gb, dp, ids = _setup()
+    W, H = 320, 192
+    words = orc.pass_probe_sis(p, gb)
+    assert words.shape == (H // 16 * 8, W // 16 * 8) and words.dtype == np.uint16
+    o3 = np.zeros(3, np.float32)
+    dirs = np.array([octa_decode64(np.float32([(k % 8 + 0.5) / 8.0, (k // 8 + 0.5) / 8.0])) for k in range(64)])
+    n_min_total = 0
+    for pcy in range(H // 16):
+        for pcx in range(W // 16):
+            normals = np.zeros((256, 3))
+            for ti in range(64):
+                for y in range(2):
+                    for x in range(2):
+                        px, py = (pcx * 8 + ti % 8) * 2 + x, (pcy * 8 + ti // 8) * 2 + y
+                        L.orc_unpack_normal(int(gb[py, px, 1]), ptr(o3))
+                        normals[ti * 4 + y * 2 + x] = o3
+            pdf = np.maximum(normals @ dirs.T, 0.0).sum(0) / 256.0
+            blk = words[pcy * 8:pcy * 8 + 8, pcx * 8:pcx * 8 + 8].reshape(64).astype(np.int64)
+            ti = np.arange(64)
+            is_min = blk == ti                                                    # ti == 0 writes 0 in the else-branch and 0x8000 otherwise
+            assert (blk[~is_min] == (0x8000 | (ti[~is_min] * 4))).all()
+            assert is_min.any() and (pdf[is_min] <= pdf.min() + 1e-6).all()
+            assert (pdf[~is_min] >= pdf.min() - 1e-6).all()
+            n_min_total += int(is_min.sum())
+    # every direction in the hemisphere behind all 256 normals has pdf == 0 == the minimum: on flat surfaces about half of the threads tie at
+    # the minimum and keep their own cell (mip 0), the other half — every direction the surface can see — takes the mip-1 branch
+    frac_mip1 = 1.0 - n_min_total / words.size
+    assert 0.3 < frac_mip1 < 0.8, frac_mip1
+    # what trace_probes makes of these words: texels that no thread aims at hold the clear value (trace_probes.slang:32), the others a hit
+    atlas = orc.pass_probe_trace(p, gb, dp, directions=words)
+    for pcy in range(H // 16):
+        for pcx in range(W // 16):
+            if dp[pcy * 16, pcx * 16] == 100000.0:
+                continue
+            blk = words[pcy * 8:pcy * 8 + 8, pcx * 8:pcx * 8 + 8].reshape(64).astype(np.int64)
+            aimed = np.zeros(64, bool)
+            for ti in range(64):
+                idx, size = blk[ti] & 0x7FFF, 16 if blk[ti] >> 15 else 8
+                aimed[int((idx // size) / size * 8) * 8 + int((idx % size) / size * 8)] = True
+            a = atlas[pcy * 8:pcy * 8 + 8, pcx * 8:pcx * 8 + 8].reshape(64, 4)
+            assert (a[~aimed] == 0).all() and (a[aimed][:, 3] > 0.0005).all()
+            assert 16 <= aimed.sum() <= 64
+
+
+@pytest.mark.gpu
+def test_gpu_structured_importance_sampling_matches_oracle(gpu_ctx):
+    """rt3_pass_probe_sis (64 threads per probe, shared-memory bitonic sort) against the oracle, and the probe frame driven by its words."""
+    from raytracer3_b200.host import Renderer, RenderWorld
+    W, H = 320, 192
+    sc, orc, p, gb, dp, ids = _setup(W, H, flags=FLAG_ENV)
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc); w.create_acceleration_structure()
+    r = Renderer(gpu_ctx, w, W, H)
+    prev = prev_light = None
+    bits = lambda a: np.ascontiguousarray(a).view(np.uint32)
+    for frame in range(2):
+        p["frame"] = frame
+        p["blendfactor"] = 1.0 if frame == 0 else 0.5
+        light = r.probe_frame(p, sis=True).cpu().numpy()
+        cur = 1 - r.probe_cur
+        words = r.rg.tensor("probe_directions").cpu().numpy().view(np.uint16)
+        want_words = orc.pass_probe_sis(p, gb)
+        assert (words == want_words).all(), f"{(words != want_words).sum()} direction words differ"
+        assert 0.3 < ((want_words >> 15) == 1).mean() < 0.8
+        atlas = r.rg.tensor(f"probe_atlas{cur}").cpu().numpy()
+        want_atlas = orc.pass_probe_trace(p, gb, dp, prev_atlas=prev, directions=want_words)
+        want_sh = orc.pass_probe_sh(p, want_atlas)
+        want_light = orc.pass_probe_interpolate(p, gb, dp, want_sh, light=prev_light)
+        prev, prev_light = want_atlas, want_light
+        assert (bits(atlas) == bits(want_atlas)).all(), f"atlas differs, frame {frame}"
+        assert (bits(light) == bits(want_light)).all(), f"interpolated radiance differs, frame {frame}"
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("flags,blend", [(0, 1.0), (FLAG_ENV, 0.5)])
 def test_gpu_probe_passes_match_oracle(gpu_ctx, flags, blend):
