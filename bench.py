@@ -270,7 +270,8 @@ def roofline_objects(t_rays, t_ms, t_n, step_ms, prof_steps, clocks):
                         "frac": achieved / peak, "traffic": cnt.get("dram_bytes_per_launch"), "traffic_source": cnt.get("source"), "peak_source": peak_src,
                         "bytes_per_ray": HBM_BYTES_PER_RAY, "kernel_ms_per_launch": t_ms / t_n, "rays_per_launch": t_rays / t_n, "launches": int(t_n),
                         "kernel_share_of_step": (t_ms / prof_steps) / step_ms if step_ms > 0 else None,
-                        "timing": f"CUDA events around every launch on its own stream, a second pass of {prof_steps} step(s) over the timed workload (the timed loop runs without them)",
+                        "timing": f"CUDA events around every launch on its own stream, a second pass of {prof_steps} step(s) over the timed workload with RT3_OPT_STRIPS = 1 "
+                                  "(the timed loop runs without events and with the frame split into concurrent strips, whose kernels overlap)",
                         "note": "traversal is issue / L2-latency bound, not HBM bound: the BVH is L2-resident, HBM only streams 48 B per ray (roofline_issue, roofline_l2)"}}
     try:
         sm_mhz = float((clocks or {}).get("sm_mhz") or 1965.0)
@@ -336,12 +337,14 @@ def run_single(args, S):
         # per-kernel times of the dominant kernel (roofline): a SECOND pass over the same frames, not part of `value`, in which every
         # closest-hit traversal launch is bracketed by CUDA events on its own stream (rt3_profile_enable)
         prof_steps = min(args.steps, 30)
+        ctx.set_strips(1)                                      # one wavefront: kernels of concurrent strips would overlap and could not be timed singly
         ctx.profile_enable(True)
         for i in range(prof_steps):
             step(args.warmup + i)
         barrier()
         trace_ms, trace_launches = ctx.profile_read()
         ctx.profile_enable(False)
+        ctx.set_strips(0)
         prof_cnt = ctx.counters(reset=True)
         # the NVML polling thread belongs to the device-timed region above and stops here: its driver queries contend with the launches
         # and event waits of the host loop below (with it running, single runs of this loop came out up to 2x slower)
@@ -484,11 +487,13 @@ def run_multi(args, S):
         ms = measure_steps(step, args.steps, barrier, torch)
         launches = ctx.kernel_launches() - launches0
         cnt = ctx.counters(reset=True)
-        ctx.profile_enable(True)                               # second, untimed pass: per-launch times of the traversal kernel
+        ctx.set_strips(1)                                      # second, untimed pass: per-launch times of the traversal kernel, one wavefront at a time
+        ctx.profile_enable(True)
         step(0)
         barrier()
         trace_ms, trace_launches = ctx.profile_read()
         ctx.profile_enable(False)
+        ctx.set_strips(0)
         prof_cnt = ctx.counters(reset=True)
         clocks.__exit__()
 

@@ -241,6 +241,12 @@ RT3_API rt3_status rt3_host_free(rt3_context*, void* p);
 RT3_API rt3_status rt3_trace_closest_host(rt3_context*, const rt3_ray* rays_host, uint64_t n, rt3_hit* out_host);
 RT3_API rt3_status rt3_trace_any_host(rt3_context*, const rt3_ray* rays_host, uint64_t n, uint32_t* out_bits_host);
 
+/* ---- tuning ------------------------------------------------------------------------------------ */
+/* RT3_OPT_STRIPS: number of concurrent wavefronts rt3_pass_reference splits a frame into (1..4; default 2, or $RT3_STRIPS).  The image does
+ * not depend on it.  bench.py sets 1 for the pass in which single kernels are timed (kernels of concurrent strips overlap). */
+enum { RT3_OPT_STRIPS = 1 };
+RT3_API rt3_status rt3_set_option(rt3_context*, int option, int value);
+
 /* ---- instrumentation ------------------------------------------------------------------------ */
 RT3_API rt3_status rt3_counters_read(rt3_context*, rt3_counters* out, int reset);   /* synchronises the device */
 RT3_API uint64_t   rt3_kernel_launches(const rt3_context*);                          /* kernels launched by this context so far */

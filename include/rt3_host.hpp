@@ -261,11 +261,13 @@ class ComputePass : public PassBuilder<ComputePass> {
                       "rt3_pass_postprocess");
         else if (shader_ == "spherical_harmonic_conversion")
             ctx.check(rt3_pass_probe_sh(ctx.handle(), params(), (const float*)ptr("probe_atlas"), (float*)ptr("out"), ctx.stream()), "rt3_pass_probe_sh");
+        else if (shader_ == "structured_importance_sampling")       /* shaders/old/structured_importance_sampling.slang, 8x8 threads per probe */
+            ctx.check(rt3_pass_probe_sis(ctx.handle(), params(), (const uint32_t*)ptr("gbuffer"), (uint16_t*)ptr("out"), ctx.stream()), "rt3_pass_probe_sis");
         else if (shader_ == "interpolate_probes")
             ctx.check(rt3_pass_probe_interpolate(ctx.handle(), params(), (const uint32_t*)ptr("gbuffer"), (const float*)ptr("gbuffer_depth"),
                                                  (const float*)ptr("sh_coeficents"), (float*)ptr("Light"), ctx.stream()), "rt3_pass_probe_interpolate");
         else
-            throw Error(RT3_ERR_INVALID, "unknown compute shader '" + shader_ + "' (known: postprocess, spherical_harmonic_conversion, interpolate_probes)");
+            throw Error(RT3_ERR_INVALID, "unknown compute shader '" + shader_ + "' (known: postprocess, structured_importance_sampling, spherical_harmonic_conversion, interpolate_probes)");
         return name_;
     }
 

@@ -510,6 +510,10 @@ struct SceneView {
      * indexed by the global triangle id — replaces the binary search + geometry + index fetches in front of the vertex fetch by
      * one 16-byte load; the values fetched afterwards, and so the results, are the same */
     const uint32_t* shade_rec;
+    /* optional 64-byte shading records (rt3_accel_build, when the table fits the L2: <= 96 MB): the three vertex normals, the three
+     * texture coordinates and the segment of a triangle, COPIED next to each other — one gather of two sectors in place of the 16-byte
+     * record above followed by three dependent 32-byte vertex fetches.  Same floats, same results. */
+    const float* shade64;
 };
 
 RT3_HD uint32_t find_segment(const SceneView& s, uint32_t prim) {
@@ -587,8 +591,24 @@ RT3_HD vec3 sample_environment(const SceneView& s, vec3 dir) {
  * The per-vertex colour the old shader reads (hit_logic.slang:27) does not exist in the 32-byte
  * Vertex (assets/mod.rs:127-133) and is taken as (1,1,1). */
 RT3_HD GbufferData hit_info(const SceneView& s, uint32_t prim, float bu, float bv, uint32_t* out_geometry = nullptr) {
-    uint32_t seg, i0, i1, i2;
-    if (s.shade_rec != nullptr) {
+    uint32_t seg, i0 = 0, i1 = 0, i2 = 0;
+    float an[3], bn[3], cn[3], at[2], bt[2], ct[2];                /* normals and texture coordinates of the three vertices */
+    bool have_attributes = false;
+#ifndef RT3_SHADE64
+#define RT3_SHADE64 1          /* compile-time A/B switch of the 64-byte shading records (0: the gather chain of round 1) */
+#endif
+    if (RT3_SHADE64 && s.shade64 != nullptr) {
+        const float* r = s.shade64 + 16u * (size_t)prim;
+#ifdef __CUDA_ARCH__
+        const float4 q0 = __ldg((const float4*)r), q1 = __ldg((const float4*)r + 1), q2 = __ldg((const float4*)r + 2), q3 = __ldg((const float4*)r + 3);
+        an[0] = q0.x; an[1] = q0.y; an[2] = q0.z; bn[0] = q0.w; bn[1] = q1.x; bn[2] = q1.y; cn[0] = q1.z; cn[1] = q1.w; cn[2] = q2.x;
+        at[0] = q2.y; at[1] = q2.z; bt[0] = q2.w; bt[1] = q3.x; ct[0] = q3.y; ct[1] = q3.z; seg = as_uint(q3.w);
+#else
+        an[0] = r[0]; an[1] = r[1]; an[2] = r[2]; bn[0] = r[3]; bn[1] = r[4]; bn[2] = r[5]; cn[0] = r[6]; cn[1] = r[7]; cn[2] = r[8];
+        at[0] = r[9]; at[1] = r[10]; bt[0] = r[11]; bt[1] = r[12]; ct[0] = r[13]; ct[1] = r[14]; seg = as_uint(r[15]);
+#endif
+        have_attributes = true;
+    } else if (s.shade_rec != nullptr) {
         const uint32_t* r = s.shade_rec + 4u * (size_t)prim;
 #ifdef __CUDA_ARCH__
         const uint4 q = __ldg((const uint4*)r);
@@ -605,18 +625,22 @@ RT3_HD GbufferData hit_info(const SceneView& s, uint32_t prim, float bu, float b
     uint32_t gi = s.seg_geometry[seg];
     if (out_geometry) *out_geometry = gi;
     const rt3_geometry_info& g = s.geometries[gi];
-    const rt3_vertex& a = s.vertices[i0];
-    const rt3_vertex& b = s.vertices[i1];
-    const rt3_vertex& c = s.vertices[i2];
+    if (!have_attributes) {
+        const rt3_vertex& a = s.vertices[i0];
+        const rt3_vertex& b = s.vertices[i1];
+        const rt3_vertex& c = s.vertices[i2];
+        for (int k = 0; k < 3; ++k) { an[k] = a.n[k]; bn[k] = b.n[k]; cn[k] = c.n[k]; }
+        at[0] = a.t[0]; at[1] = a.t[1]; bt[0] = b.t[0]; bt[1] = b.t[1]; ct[0] = c.t[0]; ct[1] = c.t[1];
+    }
     float w0 = 1.0f - bu - bv, w1 = bu, w2 = bv;
-    vec3 n = v3(fma_(c.n[0], w2, fma_(b.n[0], w1, a.n[0] * w0)), fma_(c.n[1], w2, fma_(b.n[1], w1, a.n[1] * w0)),
-                fma_(c.n[2], w2, fma_(b.n[2], w1, a.n[2] * w0)));
+    vec3 n = v3(fma_(cn[0], w2, fma_(bn[0], w1, an[0] * w0)), fma_(cn[1], w2, fma_(bn[1], w1, an[1] * w0)),
+                fma_(cn[2], w2, fma_(bn[2], w1, an[2] * w0)));
     n = normalize(n);
     n = normalize(xform_dir(g.xform, n));
     const float* ix = s.inst_xform + 12u * s.seg_instance[seg];
     if (!xform_is_identity(ix)) n = normalize(xform_dir(ix, n));
-    float tu = fma_(c.t[0], w2, fma_(b.t[0], w1, a.t[0] * w0));
-    float tv = fma_(c.t[1], w2, fma_(b.t[1], w1, a.t[1] * w0));
+    float tu = fma_(ct[0], w2, fma_(bt[0], w1, at[0] * w0));
+    float tv = fma_(ct[1], w2, fma_(bt[1], w1, at[1] * w0));
     vec3 color = v3(g.base_color[0], g.base_color[1], g.base_color[2]);
     if (g.base_color_tex > -1) color = color * sample_texture(s, g.base_color_tex, tu, tv);
     GbufferData o;

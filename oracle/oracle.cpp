@@ -77,7 +77,7 @@ struct orc_scene {
         s.env_func = env_func.empty() ? nullptr : env_func.data(); s.env_marginal = env_marginal.data(); s.env_conditional = env_conditional.data();
         s.env_total = env_total;
         s.bn = bn.empty() ? nullptr : bn.data(); s.bn_w = bn_w; s.bn_h = bn_h;
-        s.shade_rec = nullptr;          /* the oracle keeps the reference's own fetch chain (hit_logic.slang:10-19) */
+        s.shade_rec = nullptr; s.shade64 = nullptr;   /* the oracle keeps the reference's own fetch chain (hit_logic.slang:10-19) */
         return s;
     }
 };

@@ -75,6 +75,7 @@ def load():
         "rt3_host_free": (i32, [vp, vp]),
         "rt3_trace_closest_host": (i32, [vp, vp, u64, vp]),
         "rt3_trace_any_host": (i32, [vp, vp, u64, vp]),
+        "rt3_set_option": (i32, [vp, i32, i32]),
         "rt3_counters_read": (i32, [vp, P(Counters), i32]),
         "rt3_kernel_launches": (u64, [vp]),
         "rt3_measure_l2_bandwidth": (i32, [vp, C.c_size_t, i32, P(C.c_double)]),

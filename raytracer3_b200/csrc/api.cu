@@ -256,7 +256,7 @@ void rt3_destroy(rt3_context* c) {
     if (c->d_srgb_lut) cudaFree(c->d_srgb_lut);
     if (c->d_counters) cudaFree(c->d_counters);
     Scratch* all[] = {&c->d_geometries, &c->d_seg_first, &c->d_seg_geo, &c->d_seg_inst, &c->d_inst_xform, &c->d_tex_ptr, &c->d_tex_dim, &c->bvh_nodes,
-                      &c->bvh_tris, &c->d_insts, &c->d_shade_rec, &c->px_radiance, &c->px_path, &c->px_failed, &c->d_counts, &c->d_rects, &c->d_untile_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
+                      &c->bvh_tris, &c->d_insts, &c->d_shade_rec, &c->d_shade64, &c->px_radiance, &c->px_path, &c->px_failed, &c->d_counts, &c->d_rects, &c->d_untile_rects, &c->d_params, &c->f_gbuffer, &c->f_depth, &c->f_light, &c->f_prev, &c->f_rays, &c->f_hits,
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();
     for (RefLane& ln : c->lanes) {
@@ -647,6 +647,15 @@ rt3_status rt3_trace_any_host(rt3_context* c, const rt3_ray* rays_host, uint64_t
         rt3_launch_trace_any(c, r, nullptr, n, b, nullptr, 0);
         RT3_CUDA(c, cudaMemcpyAsync(out_bits_host, b, words * 4, cudaMemcpyDeviceToHost, 0));
         RT3_CUDA(c, cudaStreamSynchronize(0));
+    });
+}
+
+rt3_status rt3_set_option(rt3_context* c, int option, int value) {
+    return guarded(c, [&]() {
+        if (option == RT3_OPT_STRIPS) {
+            if (value < 0 || value > RT3_MAX_LANES) RT3_FAIL(c, RT3_ERR_INVALID, "RT3_OPT_STRIPS: 0 (default) .. 4");
+            c->opt_strips = value;
+        } else RT3_FAIL(c, RT3_ERR_INVALID, "unknown option");
     });
 }
 

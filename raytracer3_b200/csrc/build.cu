@@ -81,6 +81,18 @@ __global__ void __launch_bounds__(256) k_shade_records(rt3m::SceneView s, uint32
     rec[i] = make_uint4(g.vertex_offset + s.indices[io], g.vertex_offset + s.indices[io + 1], g.vertex_offset + s.indices[io + 2], seg);
 }
 
+/* 64-byte shading records (SceneView::shade64): normals x 3, texture coordinates x 3, segment — copies of what hit_info would gather. */
+__global__ void __launch_bounds__(256) k_shade_records64(rt3m::SceneView s, uint32_t n, const uint4* rec, float4* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 r = rec[i];
+    const rt3_vertex a = s.vertices[r.x], b = s.vertices[r.y], c = s.vertices[r.z];
+    out[4 * (size_t)i + 0] = make_float4(a.n[0], a.n[1], a.n[2], b.n[0]);
+    out[4 * (size_t)i + 1] = make_float4(b.n[1], b.n[2], c.n[0], c.n[1]);
+    out[4 * (size_t)i + 2] = make_float4(c.n[2], a.t[0], a.t[1], b.t[0]);
+    out[4 * (size_t)i + 3] = make_float4(b.t[1], c.t[0], c.t[1], __uint_as_float(r.w));
+}
+
 /* Bottom level of the two-level build: the triangles of one mesh (segments [seg0, ...) of its first instance, global ids
  * [prim0, prim0 + n)) in OBJECT space — geometry transform applied, instance transform not — stored as VERTICES with the
  * mesh-local id (REC_TRI_VERTS).  The vertex arithmetic is that of rt3m::world_triangle up to the instance transform. */
@@ -530,7 +542,7 @@ static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats&
         for (int k = 0; k < 3; ++k) { bs.scene_lo[k] = lo[k]; bs.scene_hi[k] = hi[k]; }
         WideBuild io;
         io.optimal_collapse = optimal; io.treelet = treelet;
-        io.recs = &s_tris; io.n = n; io.kind = REC_TRI_EDGES; io.pad = max_extent(lo, hi) * (1.0f / 65536.0f);
+        io.recs = &s_tris; io.n = n; io.kind = REC_TRI_EDGES; io.pad = max_extent(lo, hi) * RT3_PAD_FRACTION;
         memcpy(io.lo, lo, sizeof(lo)); memcpy(io.hi, hi, sizeof(hi));
         io.wide = ensure<WideNode>(c, c->bvh_nodes, n); io.root_index = 0; io.first_free_node = 1;
         io.out_recs = out_tris; io.first_free_rec = 0;
@@ -626,9 +638,9 @@ static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs
             WideBuild io;
             io.optimal_collapse = optimal; io.treelet = treelet;
             io.recs = &mesh_tris[m]; io.n = mi.n; io.kind = REC_TRI_VERTS;
-            /* padding covers the intersection slop and node quantisation (object extent / 65536, as in the single-level build) AND the
+            /* padding covers the intersection slop and node quantisation (object extent x RT3_PAD_FRACTION, as in the single-level build) AND the
              * rounding of the world -> object ray transform, which grows with the distance of the ray origin in object units */
-            io.pad = (max_extent(mi.lo, mi.hi) + world_ext * mesh_inv_scale[m]) * (1.0f / 65536.0f);
+            io.pad = (max_extent(mi.lo, mi.hi) + world_ext * mesh_inv_scale[m]) * RT3_PAD_FRACTION;
             memcpy(io.lo, mi.lo, sizeof(mi.lo)); memcpy(io.hi, mi.hi, sizeof(mi.hi));
             io.wide = wide; io.root_index = mi.root; io.first_free_node = mi.root + 1;
             io.out_recs = out_recs; io.first_free_rec = next_rec;
@@ -637,10 +649,10 @@ static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs
         }
         /* pass 3: top level over the instance boxes */
         std::vector<Tri48> boxes(ni);
-        const float top_pad = world_ext * (1.0f / 65536.0f);
+        const float top_pad = world_ext * RT3_PAD_FRACTION;
         for (uint32_t i = 0; i < ni; ++i) {
             recs[i].root = meshes[inst_mesh[i]].root;
-            const float bpad = meshes[inst_mesh[i]].n ? (max_extent(meshes[inst_mesh[i]].lo, meshes[inst_mesh[i]].hi) + world_ext * mesh_inv_scale[inst_mesh[i]]) * (1.0f / 65536.0f) : 0.f;
+            const float bpad = meshes[inst_mesh[i]].n ? (max_extent(meshes[inst_mesh[i]].lo, meshes[inst_mesh[i]].hi) + world_ext * mesh_inv_scale[inst_mesh[i]]) * RT3_PAD_FRACTION : 0.f;
             float rs = 0.f;   /* object-space padding seen in world space */
             for (int row = 0; row < 3; ++row) rs = fmaxf(rs, fabsf(recs[i].xform[4 * row]) + fabsf(recs[i].xform[4 * row + 1]) + fabsf(recs[i].xform[4 * row + 2]));
             Tri48& b = boxes[i];
@@ -688,11 +700,17 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
         RT3_CUDA(c, cudaStreamSynchronize(st));
         c->n_wide_nodes = 1; c->n_leaf_records = 0; c->two_level = false; bs.wide_nodes = 1; bs.node_bytes = sizeof(WideNode);
     }
-    c->view.shade_rec = nullptr;
+    c->view.shade_rec = nullptr; c->view.shade64 = nullptr;
     if (n && !getenv("RT3_NO_SHADE_REC")) {
         uint4* rec = ensure<uint4>(c, c->d_shade_rec, n);
         RT3_LAUNCH(c, k_shade_records, div_up(n, 256), 256, 0, st, c->view, n, rec);
         c->view.shade_rec = (const uint32_t*)rec;
+        c->view.shade64 = nullptr;
+        if ((size_t)n * 64 <= ((size_t)96 << 20) && !getenv("RT3_NO_SHADE64")) {       /* only while the table stays L2-resident */
+            float4* r64 = ensure<float4>(c, c->d_shade64, 4 * (size_t)n);
+            RT3_LAUNCH(c, k_shade_records64, div_up(n, 256), 256, 0, st, c->view, n, rec, r64);
+            c->view.shade64 = (const float*)r64;
+        }
     }
     /* children of the wide nodes: cost-optimal (dynamic programme over the BVH2, computed in the refit) unless the caller asks for
      * the fastest build, then greedy by surface area.  Measured: 36 % fewer nodes, +2 % path-tracing and +2..6 % incoherent-ray

@@ -40,7 +40,21 @@ struct Tri48 {               /* 48 B: three float4 */
 struct WideNode { uint32_t w[20]; };   /* 80 B: see encode_wide_node() */
 
 static const uint32_t LEAF_FLAG = 0x80000000u;
+/* Traversal stack.  A node step pushes at most ONE entry (the rest of the node group it leaves behind) and then descends one level, so
+ * the stack never holds more than one entry per level of the path from the root: sp <= levels of the wide tree.  Two levels: entering an
+ * instance pushes up to three entries (pending node group, pending record group, sentinel) on top of the top-level path, then the
+ * bottom-level path: sp <= levels_top + 3 + levels_bottom.  rt3_build_accel refuses trees for which these bounds reach RT3_MAX_STACK
+ * (build.cu: "deeper than the traversal stack"), so the `sp < RT3_MAX_STACK` tests at the push sites can never fail on a structure the
+ * builder handed out; they only keep a corrupted structure from writing out of bounds. */
 #define RT3_MAX_STACK 64
+/* Padding of every triangle box, as a fraction of the scene extent E.  It has to cover (a) the acceptance slop of the ray/triangle test,
+ * (b) the rounding of the quantised plane distances: b = fma(-32768, s, (p - o) * idir) carries up to 2^-24 * (|p - o| + 257 * node extent)
+ * in units of distance, i.e. 2^-24 * (|p - o| + 257 E) at the root.  With E / 32768 = 512 * 2^-24 E the culling stays conservative for ray
+ * origins within ~250 E of the scene (round 1 used E / 65536, which left no headroom at the root).  Rays that start farther
+ * away than that should be clipped to the scene box by the caller. */
+#ifndef RT3_PAD_FRACTION
+#define RT3_PAD_FRACTION (1.0f / 32768.0f)
+#endif
 
 struct u32x4 { uint32_t x, y, z, w; };
 
@@ -671,7 +685,7 @@ RT3_HD uint32_t slab_child(uint32_t nx, uint32_t fx, uint32_t ny, uint32_t fy, u
  * children in near-to-far priority order for this ray's octant, bits 0..23 = triangles of hit leaves.
  * Plane distance = (p + q 2^e - o) / d = (32768 + q) * s + (b - 32768 s) with s = 2^e / d, b = (p - o) / d: one PRMT and
  * one FFMA per plane.  The rounding of (b - 32768 s) costs at most 1/512 of a quantisation step, which the
- * builder's triangle-box padding (scene extent / 65536) covers. */
+ * builder's triangle-box padding (scene extent x RT3_PAD_FRACTION) covers. */
 RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n0, const u32x4& n1, const u32x4& n2,
                                     const u32x4& n3, const u32x4& n4) {
     const uint32_t e = n0.w;

@@ -91,7 +91,7 @@ struct rt3_context {
     rt3m::SceneView view;           /* device pointers */
 
     /* acceleration structure */
-    Scratch bvh_nodes, bvh_tris, d_insts, d_shade_rec;   /* d_insts: rt3b::InstRec table of the two-level structure */
+    Scratch bvh_nodes, bvh_tris, d_insts, d_shade_rec, d_shade64;   /* d_insts: rt3b::InstRec table of the two-level structure */
     uint32_t n_wide_nodes = 0, n_leaf_records = 0;
     bool two_level = false;
     bool accel_valid = false;
@@ -99,6 +99,7 @@ struct rt3_context {
 
     /* pass scratch */
     RefLane lanes[RT3_MAX_LANES];
+    int opt_strips = 0;              /* 0 = default ($RT3_STRIPS or 2); rt3_set_option(RT3_OPT_STRIPS) */
     Scratch px_radiance, px_path, px_failed, d_counts, d_rects, d_untile_rects, d_params;   /* d_untile_rects: un-tiling may run on another stream than the passes */
     cudaEvent_t ev_fork = nullptr;
     /* Stream ordering between calls: all pass / trace calls of one context share the scratch above, so a call on another stream than

@@ -20,7 +20,7 @@ __device__ __forceinline__ void flush_counter(unsigned long long v, unsigned lon
 }
 
 /* ---- pass 1 -------------------------------------------------------------------------------- */
-__global__ void __launch_bounds__(128) k_gbuffer(SceneView s, const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris, rt3_params p, PixelMap m,
+__global__ void __launch_bounds__(128, 8) k_gbuffer(SceneView s, const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris, rt3_params p, PixelMap m,
                                                  uint32_t* __restrict__ gbuffer, float* __restrict__ depth, uint32_t* __restrict__ ids,
                                                  float* __restrict__ bary, DeviceCounters* counters, const InstRec* __restrict__ insts) {
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;

@@ -93,7 +93,7 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
                           float* light, cudaStream_t st) {
     if (!m.work) return;
     static const int env_strips = env_int_passes("RT3_STRIPS", 2);
-    uint32_t S = (uint32_t)std::max(1, std::min(env_strips, RT3_MAX_LANES));
+    uint32_t S = (uint32_t)std::max(1, std::min(c->opt_strips > 0 ? c->opt_strips : env_strips, RT3_MAX_LANES));
     while (S > 1 && (m.work + STRIP_UNIT - 1) / STRIP_UNIT < 16u * S) --S;        /* small frames: one wavefront */
     float4* px_radiance = ensure<float4>(c, c->px_radiance, m.work);
     uint2* px_path = ensure<uint2>(c, c->px_path, m.work);

@@ -63,6 +63,10 @@ class RenderContext:
         torch = _torch()
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
+    def set_strips(self, n):
+        """RT3_OPT_STRIPS: concurrent wavefronts per reference-pass call (0 = default)."""
+        self.check(self.L.rt3_set_option(self.h, 1, int(n)))
+
     def kernel_launches(self):
         return int(self.L.rt3_kernel_launches(self.h))
 

@@ -49,7 +49,7 @@ static EmuBvh* build_lbvh(const float* tris9, uint32_t n, bool use_dp, float spl
         t.prim = i; t.pad0 = t.pad1 = 0;
     }
     float ext = n ? std::max(b->hi[0] - b->lo[0], std::max(b->hi[1] - b->lo[1], b->hi[2] - b->lo[2])) : 0.f;
-    b->pad = ext * (1.0f / 65536.0f);
+    b->pad = ext * RT3_PAD_FRACTION;
     if (n == 0) {
         b->nodes.resize(1);
         memset(&b->nodes[0], 0, sizeof(WideNode));
@@ -321,7 +321,7 @@ extern "C" EmuBvh* emu_build_sah(const float* tris9, uint32_t n) {
         t.prim = i; t.pad0 = t.pad1 = 0;
     }
     float ext = std::max(b->hi[0] - b->lo[0], std::max(b->hi[1] - b->lo[1], b->hi[2] - b->lo[2]));
-    b->pad = ext * (1.0f / 65536.0f);
+    b->pad = ext * RT3_PAD_FRACTION;
     std::vector<Bvh2Node> n2(2 * (size_t)n - 1); std::vector<uint32_t> counts(n, 0);
     SahBuilder sb(n2, counts, b->tris_in, b->pad);
     uint32_t root = sb.build(0, n);

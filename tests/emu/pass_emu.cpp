@@ -30,6 +30,7 @@ int launch(unsigned grid, unsigned block, std::function<void()> f) {
 unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
 const int SM_COUNT = 148;
+int g_shade64 = 0; uint32_t g_n_prims = 0;   /* pemu_set_shade64: also build and use the 64-byte shading records */
 int g_strips = 1;                         /* pemu_set_strips: how many strips rt3_launch_reference would use */
 uint64_t* g_round_lengths = nullptr;      /* pemu_set_round_lengths: queue length at the start of every round (regeneration statistics) */
 
@@ -82,6 +83,18 @@ int pemu_frame(const void* scene_view, const uint32_t* shade_rec, const uint32_t
     wemu::g_error = nullptr; wemu::g_collectives = 0;
     SceneView view = *(const SceneView*)scene_view;
     view.shade_rec = shade_rec;
+    std::vector<float> shade64;
+    if (g_shade64 && shade_rec) {                       /* k_shade_records64 (build.cu): normals x 3, texture coordinates x 3, segment */
+        shade64.resize(16 * (size_t)g_n_prims);
+        for (uint32_t i = 0; i < g_n_prims; ++i) {
+            const rt3_vertex &a = view.vertices[shade_rec[4 * i]], &b = view.vertices[shade_rec[4 * i + 1]], &c = view.vertices[shade_rec[4 * i + 2]];
+            float* o = shade64.data() + 16 * (size_t)i;
+            o[0] = a.n[0]; o[1] = a.n[1]; o[2] = a.n[2]; o[3] = b.n[0]; o[4] = b.n[1]; o[5] = b.n[2]; o[6] = c.n[0]; o[7] = c.n[1]; o[8] = c.n[2];
+            o[9] = a.t[0]; o[10] = a.t[1]; o[11] = b.t[0]; o[12] = b.t[1]; o[13] = c.t[0]; o[14] = c.t[1];
+            memcpy(o + 15, &shade_rec[4 * i + 3], 4);
+        }
+        view.shade64 = shade64.data();
+    }
     const rt3_params p = *pp;
     const WideNode* nodes = (const WideNode*)nodes20;
     const Tri48* tris = (const Tri48*)tris12;
@@ -147,6 +160,7 @@ int pemu_frame(const void* scene_view, const uint32_t* shade_rec, const uint32_t
     return 0;
 }
 void pemu_set_strips(int n) { g_strips = n; }
+void pemu_set_shade64(int on, uint32_t n_prims) { g_shade64 = on; g_n_prims = n_prims; }
 void pemu_set_round_lengths(uint64_t* out4096) { g_round_lengths = out4096; }
 const char* pemu_last_error() { return wemu::g_error ? wemu::g_error : ""; }
 

@@ -116,12 +116,14 @@ class PassEmu:
         self.shade_rec = np.zeros((max(len(edges), 1), 4), np.uint32)
         self.P.pemu_shade_records(ptr(self.view), len(edges), ptr(self.shade_rec))
 
-    def frame(self, params, prev_light=None, postprocess=False, strips=1, round_lengths=None):
+    def frame(self, params, prev_light=None, postprocess=False, strips=1, round_lengths=None, shade64=True):
         """strips: the number of concurrent wavefronts rt3_launch_reference would split the frame into (pass_types.h); round_lengths: a
         uint64[4096] array that receives the queue length at the start of every round, summed over the strips (regeneration statistics)"""
         w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])
         self.P.pemu_set_strips.argtypes = [C.c_int]
         self.P.pemu_set_round_lengths.argtypes = [C.c_void_p]
+        self.P.pemu_set_shade64.argtypes = [C.c_int, C.c_uint32]
+        self.P.pemu_set_shade64(1 if shade64 else 0, len(self.shade_rec) if self.orc.num_triangles else 0)
         self.P.pemu_set_strips(int(strips))
         self.P.pemu_set_round_lengths(None if round_lengths is None else ptr(round_lengths))
         out = dict(gbuffer=np.zeros((h, w, 4), np.uint32), depth=np.zeros((h, w), np.float32), ids=np.zeros((h, w, 2), np.uint32),

@@ -315,3 +315,48 @@ def test_failed_rebuild_invalidates_the_acceleration_structure(gpu_ctx):
     assert e.value.status == _lib.ERR_STATE
     w.create_acceleration_structure()                                            # and a good build makes it usable again
     assert len(w.trace_closest_host(rays)) == 100
+
+
+def test_far_origins_and_tiny_objects_are_not_culled(gpu_ctx):
+    """Conservative culling (bvh_logic.h RT3_PAD_FRACTION): rays that start tens of scene extents away, and a tiny object inside a huge
+    scene, against BRUTE FORCE over every triangle on the CPU — no true hit may be lost to the quantised slab test."""
+    from oracle.oracle_py import OracleScene
+    from raytracer3_b200.host import RenderWorld
+    from raytracer3_b200.types import RAY
+    rng = np.random.default_rng(77)
+    # (a) far origins aimed at the scene
+    sc = scenes.synthetic_atrium(0.02, environment=False)
+    orc = OracleScene(sc)
+    lo, hi = orc.bounds()
+    ext = float((hi - lo).max())
+    n = 60000
+    tgt = rng.uniform(lo, hi, (n, 3))
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    dist = rng.choice([3.0, 30.0, 100.0], n) * ext
+    rays = np.zeros(n, RAY)
+    rays["o"] = tgt - d * dist[:, None]
+    rays["d"] = d
+    rays["tmin"], rays["tmax"] = 0.0, 1e9
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc); w.create_acceleration_structure()
+    got, want = w.trace_closest_host(rays), orc.trace_closest(rays, brute=True)
+    assert (want["prim"] != MISS).mean() > 0.5
+    assert (got["prim"] == want["prim"]).all(), int((got["prim"] != want["prim"]).sum())
+    assert (_bits(got["t"]) == _bits(want["t"])).all()
+    # (b) a 1 cm triangle pair inside a 10 km quad: the scene extent sets the padding, the small object must still be found
+    mb = scenes.MeshBuilder()
+    mb.add(*scenes.quad((-5000, 0, -5000), (0, 0, 10000), (10000, 0, 0)), base_color=(0.5, 0.5, 0.5))
+    mb.add(*scenes.quad((0.3, 0.5, 0.2), (0.01, 0, 0), (0, 0.01, 0)), base_color=(0.9, 0.1, 0.1))
+    sc2 = scenes._scene(mb, {"cam0": dict(position=(0, 1, -2), direction=(0, 0, 1), fov_deg=60.0)}, name="tiny_in_huge")
+    orc2 = OracleScene(sc2)
+    m = 20000
+    rays2 = np.zeros(m, RAY)
+    rays2["o"] = rng.uniform((-3, 0.2, -3), (3, 3, 3), (m, 3))
+    aim = np.array([0.305, 0.505, 0.2]) + rng.uniform(-0.008, 0.008, (m, 3)) * np.array([1, 1, 0])
+    dd = aim - rays2["o"]; dd /= np.linalg.norm(dd, axis=1, keepdims=True)
+    rays2["d"] = dd
+    rays2["tmin"], rays2["tmax"] = 0.0, 1e9
+    w.clear(); w.load_scene(sc2); w.create_acceleration_structure()
+    got2, want2 = w.trace_closest_host(rays2), orc2.trace_closest(rays2, brute=True)
+    assert (want2["prim"] >= 2).mean() > 0.2                                   # the tiny quad is actually hit
+    assert (got2["prim"] == want2["prim"]).all(), int((got2["prim"] != want2["prim"]).sum())

@@ -36,7 +36,7 @@ def timed(fn, reps):
 
 def atrium():
     sc = scenes.synthetic_atrium(scenes.SPONZA_DETAIL)
-    sc["bluenoise"] = scenes.blue_noise_tile()
+    sc["bluenoise"], _ = scenes.reference_blue_noise()
     return sc
 
 
@@ -122,6 +122,37 @@ def cfg4(ctx, log2n=25):
     ts_ = w.trace_stats(dc[: 1 << 20])
     out.update({"hit_fraction": hit_frac, "occluded_fraction": occ, "nodes_per_ray": ts_.nodes_per_ray, "tris_per_ray": ts_.tris_per_ray,
                 "l2_bytes_per_ray": ts_.node_bytes_per_ray + ts_.tri_bytes_per_ray})
+    return out
+
+
+def cfg3_regen(ctx):
+    """The 64 samples of configs[2] inside ONE reference-pass call (gconst.samples = 64, refrence_mode.slang:28): the wavefront with ray
+    regeneration keeps one long queue (terminated paths are replaced in place by the pixel's next sample) instead of 64 x 3 shrinking ones,
+    and the G-buffer pass runs once.  3840x2160 and 1920x1080; RT3_OPT_STRIPS = 1 and the default."""
+    sc = atrium()
+    w = RenderWorld(ctx); w.clear(); w.load_scene(sc); w.create_acceleration_structure()
+    out = {"config": "64 spp in one frame call (regeneration), 1 GPU (synthetic_atrium)"}
+    for W, H in ((1920, 1080), (3840, 2160)):
+        r = Renderer(ctx, w, W, H)
+        cam = camera_for(sc, "cam0", W, H)
+        for strips in (1, 0):
+            ctx.set_strips(strips)
+            p = make_params(cam, W, H, frame=0, bounces=4, samples=64, flags=FLAGS)
+            r.frame(make_params(cam, W, H, frame=0, bounces=4, samples=2, flags=FLAGS))
+            ctx.counters(reset=True)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r.frame(p)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            c = ctx.counters(reset=True)
+            rays = c.rays_primary + c.rays_secondary
+            out[f"{W}x{H}_strips{strips or 'default'}"] = {"total_ms": ms, "rays": int(rays), "mrays_s": rays / ms / 1e3, "spp_s": c.paths_started / (ms * 1e-3),
+                                                        "secondary_mrays_s": c.rays_secondary / ms / 1e3}
+        ctx.set_strips(0)
+        del r
     return out
 
 

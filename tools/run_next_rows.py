@@ -87,6 +87,10 @@ def main():
     for k, fn in passes.items():
         out[k + "_ms"] = timed(fn)
     out["frame_ms"] = timed(lambda i: r.probe_frame(p))
+    r.probe_frame(p, sis=True)
+    out["structured_importance_sampling_ms"] = timed(lambda i: ComputePass.new(rg, "sis").shader("structured_importance_sampling").constants(p).read("gbuffer", "gbuffer")
+                                                     .write("out", "probe_directions").dispatch(WorkSize2D.FractionalFullScreen(2, 2)))
+    out["frame_with_sis_ms"] = timed(lambda i: r.probe_frame(p, sis=True))
     print(json.dumps(out), flush=True)
 
 
