@@ -217,6 +217,18 @@ def cfg3_step(R, params, slot):
     return R.exchange(light, slot)
 
 
+def inframe_params(sc, flags):
+    """The 64 samples of configs[2] inside ONE frame call (gconst.samples = 64, the loop of refrence_mode.slang:28): the G-buffer pass runs once
+    and the reference pass is one wavefront with ray regeneration."""
+    from raytracer3_b200.camera import camera_for, make_params
+    return make_params(camera_for(sc, CAMERA, CFG3_W, CFG3_H), CFG3_W, CFG3_H, frame=0, bounces=BOUNCES, samples=CFG3_SPP, blendfactor=1.0, flags=flags)
+
+
+def inframe_step(R, p, slot):
+    R.cur = 0
+    return R.exchange(R.frame(p), slot)
+
+
 def setup_cuda(args):
     import torch
     import torch.distributed as dist
@@ -435,6 +447,16 @@ def run_single(args, S):
         line["strong_base"] = {"workload": f"{CFG3_W}x{CFG3_H}, {CFG3_SPP} spp progressive (BASELINE configs[2]), one step on this GPU through the tile path",
                                "value": (c3.rays_primary + c3.rays_secondary) / (ms3 * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms3,
                                "note": "what bench.py --gpus N > 1 reports as `value` is this workload sharded over N GPUs"}
+        pin = inframe_params(sc, flags)
+        e0.record()
+        inframe_step(Rt, pin, 0)
+        e1.record()
+        barrier()
+        ci = ctx.counters(reset=True)
+        msi = e0.elapsed_time(e1)
+        line["strong_base"]["inframe_64spp"] = {"value": (ci.rays_primary + ci.rays_secondary) / (msi * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": msi,
+                                                "spp_per_s": float(ci.paths_started) / (msi * 1e-3),
+                                                "workload": "the same 64 samples per pixel in ONE frame call (samples = 64): one G-buffer pass, one wavefront with ray regeneration"}
         del Rt
         keep = {}
         line["cpu_baseline"] = cpu_baseline(sc, flags, frame=e2e_last, keep=keep)
@@ -561,9 +583,20 @@ def run_multi(args, S):
     wms = e0.elapsed_time(e1)
     wcnt = ctx.counters(reset=True)
 
+    # ---- the same 64 samples per pixel inside ONE frame call (samples = 64): one G-buffer pass + one wavefront with ray regeneration per image
+    pin = inframe_params(sc, flags)
+    isteps = max(2, min(args.steps, 5))
+    inframe_step(R, pin, 0)
+    barrier()
+    ctx.counters(reset=True)
+    ims = measure_steps(lambda k: inframe_step(R, pin, k % 2), isteps, barrier, torch)
+    icnt = ctx.counters(reset=True)
+    iband = inframe_step(R, pin, 0).clone()
+    ctx.counters(reset=True)
+
     # ---- verification, outside every timed region: rank 0 renders the whole 64-sample image ALONE, un-tiled, and compares it bit for bit
     # with the image the ranks assembled in host memory; the same run is the single-GPU point of the strong-scaling curve
-    verified, single = None, None
+    verified, single, inframe_verified = None, None, None
     if rank == 0:
         r1 = Renderer(ctx, world, W, H)
         torch.cuda.synchronize()
@@ -576,6 +609,9 @@ def run_multi(args, S):
         single_ms = e0.elapsed_time(e1)
         c1 = ctx.counters(reset=True)
         verified = bool(torch.equal(shared[last_slot].view(torch.int32), alone.cpu().view(torch.int32)))
+        alone_in = r1.frame(pin)
+        inframe_verified = bool(torch.equal(iband.view(torch.int32), alone_in[R.row0:R.row1].view(torch.int32)))
+        ctx.counters(reset=True)
         single = {"value": (c1.rays_primary + c1.rays_secondary) / (single_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": single_ms,
                   "note": "the same 64-sample image rendered by rank 0 alone (full-frame passes, first run: includes its allocations) while the other ranks wait"}
     barrier()
@@ -586,7 +622,8 @@ def run_multi(args, S):
 
     rays_local = float(cnt.rays_primary + cnt.rays_secondary)
     stats = torch.tensor([ms, rays_local, float(cnt.paths_started), e2e_s, float(e2e_cnt.rays_primary + e2e_cnt.rays_secondary), float(launches),
-                          float(prof_cnt.rays_secondary), float(trace_ms), float(trace_launches), wms, float(wcnt.rays_primary + wcnt.rays_secondary)],
+                          float(prof_cnt.rays_secondary), float(trace_ms), float(trace_launches), wms, float(wcnt.rays_primary + wcnt.rays_secondary),
+                          ims, float(icnt.rays_primary + icnt.rays_secondary), float(icnt.paths_started)],
                          dtype=torch.float64, device=dev)
     mx = stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
     sm = stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
@@ -612,6 +649,10 @@ def run_multi(args, S):
             "gpu_launches": int(launches_all),
             "gathered_equals_single_gpu_image": verified,
             "single_gpu_same_workload": single,
+            "inframe_64spp": {"value": float(sm[12]) / (float(mx[11]) * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": float(mx[11]) / isteps, "steps": isteps,
+                              "spp_per_s": float(sm[13]) / (float(mx[11]) * 1e-3), "band_equals_single_gpu_image": inframe_verified,
+                              "workload": "the same 64 samples per pixel in ONE frame call per image (samples = 64): one G-buffer pass, one wavefront with ray "
+                                          "regeneration per rank, one delivery"},
             "weak": {"value": wrays / (wms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": wms / wsteps, "steps": wsteps,
                      "workload": f"{Ww}x{Hw} (N x 1920x1080 pixels), 1 spp, one delivery per frame overlapped with the next frame (round 1's --gpus N workload)"},
         }

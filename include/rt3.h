@@ -117,10 +117,11 @@ typedef struct { float t, u, v; uint32_t prim; } rt3_hit;           /* 16 B; pri
 /* Quality levels of the binary tree under the 8-wide collapse (hits are bit-identical in all of them):
  *   RT3_BUILD_FAST_TRACE (default, also flags == 0; the reference's PREFER_FAST_TRACE, raytracing.rs:121): treelet restructuring (Karras &
  *     Aila 2013: the best topology of every 7-subtree treelet by dynamic programming, two bottom-up passes) and the children of each wide
- *     node chosen by the SAH dynamic programme of Ylitie et al. 2017.  Measured on B200, 263 k triangles: 10.8 ms build.
+ *     node chosen by the SAH dynamic programme of Ylitie et al. 2017.  Measured on B200, 263 k triangles: 10.3 ms build.  Trees of more than
+ *     4 M records (a flattened 16.8 M-triangle scene would take 379 ms) get the rotations below instead, unless RT3_BUILD_TREELET is set.
  *   RT3_BUILD_ROTATIONS: three bottom-up passes of SAH tree rotations instead of the treelets (1.9 ms build, traversal 4 % slower).
  *   RT3_BUILD_FAST_BUILD: plain LBVH, children chosen greedily by surface area (1.4 ms build, traversal 11 % slower).
- * RT3_BUILD_TREELET is the explicit name of the default and is accepted for compatibility. */
+ * RT3_BUILD_TREELET: treelet restructuring whatever the size. */
 enum { RT3_BUILD_FAST_TRACE = 1u, RT3_BUILD_FAST_BUILD = 2u, RT3_BUILD_TWO_LEVEL = 4u, RT3_BUILD_TREELET = 8u, RT3_BUILD_ROTATIONS = 16u };
 
 typedef struct {
@@ -178,6 +179,11 @@ RT3_API rt3_status rt3_pass_reference(rt3_context*, const rt3_params*, rt3_rect,
 /* shaders/old/postprocess.slang:90-112 (AgX tonemap + sky background). */
 RT3_API rt3_status rt3_pass_postprocess(rt3_context*, const rt3_params*, rt3_rect, const float* depth_r32f,
                                         const float* in_rgba32f, float* out_rgba32f, void* cuda_stream);
+
+/* postprocess.slang:90-112 fused with the conversion to the reference's swapchain format (B8G8R8A8_UNORM, swapchain.rs:27-48): one 32-bit
+ * word per pixel (A << 24 | R << 16 | G << 8 | B), a quarter of the bytes of the RGBA32F image for a host that reads the presented frame back. */
+RT3_API rt3_status rt3_pass_present_bgra8(rt3_context*, const rt3_params*, rt3_rect, const float* depth_r32f, const float* in_rgba32f,
+                                          uint32_t* out_b8g8r8a8, void* cuda_stream);
 
 /* Screen-space probe GI: shaders/old/trace_probes.slang, spherical_harmonic_conversion.slang,
  * interpolate_probes.slang.  One probe per 16x16 pixels, 8x8 octahedral directions per probe.

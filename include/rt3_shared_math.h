@@ -1294,6 +1294,12 @@ RT3_HD vec3 postprocess_pixel(const SceneView& s, const rt3_params& p, uint32_t 
     return agx_eotf(agx_look(agx(color)));
 }
 
+/* The presented pixel: postprocess.slang's output stored in the reference's swapchain format, B8G8R8A8_UNORM (swapchain.rs:27-48).  The
+ * float -> UNORM8 conversion is Vulkan's (spec "Conversion from Normalized Fixed-Point..."): clamp to [0, 1], times 255, round to nearest
+ * (half up here; the spec allows either neighbour).  Memory order B, G, R, A = one little-endian word A << 24 | R << 16 | G << 8 | B. */
+RT3_HD uint32_t unorm8(float x) { return (uint32_t)(clamp_(x, 0.0f, 1.0f) * 255.0f + 0.5f); }
+RT3_HD uint32_t pack_bgra8(vec3 c) { return 0xFF000000u | (unorm8(c.x) << 16) | (unorm8(c.y) << 8) | unorm8(c.z); }
+
 /* Host-side table: sRGB byte -> linear float (IEC 61966-2-1), evaluated in double and rounded once. */
 inline void build_srgb_lut(float* lut256) {
     for (int i = 0; i < 256; ++i) {

@@ -500,6 +500,19 @@ void orc_pass_postprocess(const orc_scene* s, const rt3_params* p, rt3_rect rc, 
     });
 }
 
+/* postprocess.slang:90-112 + the conversion to B8G8R8A8_UNORM of the swapchain blit (swapchain.rs:27-48) */
+void orc_pass_present_bgra8(const orc_scene* s, const rt3_params* p, rt3_rect rc, const float* depth, const float* in, uint32_t* out, int threads) {
+    SceneView sv = s->view();
+    uint32_t pitch = (uint32_t)p->window_size[0];
+    parallel_for(rc.h, threads, 8, [&](uint64_t y0, uint64_t y1) {
+        for (uint32_t y = rc.y0 + (uint32_t)y0; y < rc.y0 + (uint32_t)y1; ++y)
+            for (uint32_t x = rc.x0; x < rc.x0 + rc.w; ++x) {
+                size_t px = (size_t)y * pitch + x;
+                out[px] = pack_bgra8(postprocess_pixel(sv, *p, x, y, depth[px], v3(in[4 * px], in[4 * px + 1], in[4 * px + 2])));
+            }
+    });
+}
+
 /* ---- screen-space probes (row F4) ----------------------------------------------------------------
  * shaders/old/trace_probes.slang: one ray per atlas texel; directions == NULL selects the uniform assignment. */
 void orc_pass_probe_trace(const orc_scene* s, const rt3_params* p, const uint32_t* gbuffer, const float* depth, const uint16_t* directions,

@@ -54,6 +54,7 @@ void orc_pass_postprocess(const orc_scene*, const rt3_params*, rt3_rect, const f
  * atlas: (W/16*8) x (H/16*8) RGBA32F; sh: orc_probe_sh_capacity() records of 9 floats, Z-curve indexed; directions may be NULL. */
 void orc_pass_probe_trace(const orc_scene*, const rt3_params*, const uint32_t* gbuffer, const float* depth, const uint16_t* directions,
                           const float* prev_atlas, float* atlas, int threads);
+void orc_pass_present_bgra8(const orc_scene*, const rt3_params*, rt3_rect, const float* depth, const float* in, uint32_t* out_b8g8r8a8, int threads);
 void orc_pass_probe_sis(const rt3_params*, const uint32_t* gbuffer, uint16_t* directions_out, int threads);   /* structured_importance_sampling.slang */
 void orc_pass_probe_sh(const rt3_params*, const float* atlas, float* sh, int threads);
 void orc_pass_probe_interpolate(const rt3_params*, const uint32_t* gbuffer, const float* depth, const float* sh, float* light, int threads);

@@ -56,6 +56,7 @@ def lib():
         L.orc_set_ray_capture.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]
         L.orc_pass_reference.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_pass_postprocess.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_pass_present_bgra8.argtypes = [C.c_void_p, C.c_void_p, Rect, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_probe_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_probe_sh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_pass_probe_sis.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
@@ -207,6 +208,13 @@ class OracleScene:
         w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])
         out = np.zeros((h, w, 4), np.float32) if light is None else np.array(light, np.float32, copy=True)
         self.L.orc_pass_probe_interpolate(ptr(params), ptr(gbuffer), ptr(depth), ptr(sh), ptr(out), self.threads)
+        return out
+
+    def pass_present_bgra8(self, params, depth, inp, rect=None):
+        w, h = int(params["window_size"][0][0]), int(params["window_size"][0][1])
+        rect = rect or (0, 0, w, h)
+        out = np.zeros((h, w), np.uint32)
+        self.L.orc_pass_present_bgra8(self.h, ptr(params), Rect(*rect), ptr(depth), ptr(inp), ptr(out), self.threads)
         return out
 
     def pass_postprocess(self, params, depth, inp, rect=None):

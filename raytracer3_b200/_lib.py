@@ -57,6 +57,7 @@ def load():
         "rt3_pass_gbuffer": (i32, [vp, vp, Rect, vp, vp, vp, vp, vp]),
         "rt3_pass_reference": (i32, [vp, vp, Rect, vp, vp, vp, vp, vp]),
         "rt3_pass_postprocess": (i32, [vp, vp, Rect, vp, vp, vp, vp]),
+        "rt3_pass_present_bgra8": (i32, [vp, vp, Rect, vp, vp, vp, vp]),
         "rt3_probe_layout": (i32, [vp, P(u32), P(u32), P(u32)]),
         "rt3_pass_probe_trace": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
         "rt3_pass_probe_sis": (i32, [vp, vp, vp, vp, vp]),

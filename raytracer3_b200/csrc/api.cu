@@ -260,7 +260,7 @@ void rt3_destroy(rt3_context* c) {
                       &c->f_bits, &c->l2_buf};
     for (Scratch* s : all) s->release();
     for (RefLane& ln : c->lanes) {
-        Scratch* q[] = {&ln.q_rays[0], &ln.q_rays[1], &ln.q_hits, &ln.q_thr[0], &ln.q_thr[1], &ln.q_pdf[0], &ln.q_pdf[1], &ln.q_srays, &ln.q_scontrib, &ln.q_sbits, &ln.counts};
+        Scratch* q[] = {&ln.q_rays[0], &ln.q_rays[1], &ln.q_hits, &ln.q_thr[0], &ln.q_thr[1], &ln.q_pdf[0], &ln.q_pdf[1], &ln.q_srays, &ln.q_scontrib, &ln.q_sbits, &ln.q_regen, &ln.counts};
         for (Scratch* s : q) s->release();
         if (ln.stream) cudaStreamDestroy(ln.stream);
         if (ln.done) cudaEventDestroy(ln.done);
@@ -414,6 +414,14 @@ rt3_status rt3_pass_postprocess(rt3_context* c, const rt3_params* p, rt3_rect r,
         if (c->scene_dirty) refresh_scene_tables(c);
         CallOrder order(c, (cudaStream_t)st);
         rt3_launch_postprocess(c, *p, single_rect_map(c, p, r), depth, in, out, (cudaStream_t)st);
+    });
+}
+rt3_status rt3_pass_present_bgra8(rt3_context* c, const rt3_params* p, rt3_rect r, const float* depth, const float* in, uint32_t* out, void* st) {
+    return guarded(c, [&]() {
+        if (!p || !depth || !in || !out) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        if (c->scene_dirty) refresh_scene_tables(c);
+        CallOrder order(c, (cudaStream_t)st);
+        rt3_launch_present(c, *p, single_rect_map(c, p, r), depth, in, out, (cudaStream_t)st);
     });
 }
 /* ---- screen-space probes (row F4) ---- */

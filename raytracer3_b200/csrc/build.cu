@@ -366,7 +366,7 @@ struct WideBuild {
     WideNode* wide; uint32_t root_index, first_free_node;
     Tri48* out_recs; uint32_t first_free_rec;
     bool optimal_collapse = false;   /* choose the children of every wide node by the cost dynamic programme instead of greedily */
-    bool treelet = false;            /* with optimal_collapse: treelet restructuring instead of rotations (RT3_BUILD_TREELET) */
+    int treelet = 0;                 /* with optimal_collapse: treelet restructuring instead of rotations; 1 = up to RT3_TREELET_AUTO_MAX records, 2 = always */
     uint32_t nodes_end = 0, recs_end = 0, levels = 0; float sah_nodes = 0.f, sah_recs = 0.f;   /* results */
 };
 
@@ -444,7 +444,9 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
         dbg_mark("hierarchy");
         tm.begin();
         DpNode* dp = io.optimal_collapse ? (DpNode*)(base + o_dp) : nullptr;
-        const bool treelet = io.optimal_collapse && io.treelet;
+        /* the treelet pass costs ~34 us per thousand triangles (8.9 ms at 263 k, 364 ms at 16.8 M; tree rotations: 0.5 / 19.7 ms): by default only
+         * trees of up to RT3_TREELET_AUTO_MAX records get it, larger ones the rotations; RT3_BUILD_TREELET asks for it regardless of size */
+        const bool treelet = io.optimal_collapse && (io.treelet == 2 || (io.treelet == 1 && n <= RT3_TREELET_AUTO_MAX));
         const int passes = treelet ? RT3_TREELET_PASSES : (io.optimal_collapse ? RT3_REFIT_PASSES : 1);
         for (int pass = 0; pass < passes; ++pass) {
             if (pass) {
@@ -522,7 +524,7 @@ static bool invert_affine(const float m[12], float out[12]) {
 }
 
 /* ---- single level: every instance flattened to world space (the default) -------------------------------------------- */
-static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal, bool treelet) {
+static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal, int treelet) {
     const uint32_t n = c->n_triangles;
     StageTimer tm(c, st);
     dbg_mark("enter single");
@@ -560,7 +562,7 @@ static void build_single_level(rt3_context* c, cudaStream_t st, rt3_build_stats&
 }
 
 /* ---- two levels (RT3_BUILD_TWO_LEVEL): one bottom-level tree per distinct mesh, one top-level tree over the instances ---- */
-static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal, bool treelet) {
+static void build_two_level(rt3_context* c, cudaStream_t st, rt3_build_stats& bs, bool optimal, int treelet) {
     StageTimer tm(c, st);
     const std::vector<InstanceRec>& inst = c->h_instances;
     const uint32_t ni = (uint32_t)inst.size();
@@ -719,7 +721,7 @@ void rt3_build_accel(rt3_context* c, uint32_t flags, cudaStream_t st, rt3_build_
     /* FAST_TRACE (the default, the reference's PREFER_FAST_TRACE) = treelet restructuring; RT3_BUILD_ROTATIONS keeps round 1's cheaper
      * optimisation (tree rotations).  Measured on B200, bench scene (profiles/r2a_ab_experiments.log): traversal launch 0.497 -> 0.477 ms,
      * incoherent closest 5.37 -> 5.68 Grays/s, frame 3011 -> 3063 Mrays/s, for a 1.9 -> 10.8 ms build. */
-    const bool treelet = optimal && !(flags & RT3_BUILD_ROTATIONS);
+    const int treelet = (!optimal || (flags & RT3_BUILD_ROTATIONS)) ? 0 : ((flags & RT3_BUILD_TREELET) ? 2 : 1);
     if (n == 0) {
     } else if ((flags & RT3_BUILD_TWO_LEVEL) && !c->h_instances.empty()) {
         build_two_level(c, st, bs, optimal, treelet);

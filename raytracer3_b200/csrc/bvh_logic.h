@@ -356,6 +356,7 @@ RT3_HD void refit_visit(Mem& mem, uint32_t n, uint32_t cur, bool rotate, bool wi
 #ifndef RT3_TREELET_LEAVES
 #define RT3_TREELET_LEAVES 7      /* 5 / 7 / 9 leaves: 8.82 / 8.53 / 8.54 work units per incoherent ray on the bench scene (rotations: 9.12) */
 #endif
+#define RT3_TREELET_AUTO_MAX (1u << 22)   /* FAST_TRACE restructures treelets in trees of up to 4 M records by default (build.cu) */
 #define RT3_TREELET_PASSES 2       /* 1 / 2 / 3 / 5 passes: 8.92 / 8.55 / 8.53 / 8.52 */
 template <class Mem>
 RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {

@@ -61,7 +61,7 @@ struct TextureRec { uint8_t* data = nullptr; uint32_t w = 0, h = 0; };
  * runs one strip of the frame per lane (passes.cu). */
 constexpr int RT3_MAX_LANES = 4;
 struct RefLane {
-    Scratch q_rays[2], q_hits, q_thr[2], q_pdf[2], q_srays, q_scontrib, q_sbits, counts;
+    Scratch q_rays[2], q_hits, q_thr[2], q_pdf[2], q_srays, q_scontrib, q_sbits, q_regen, counts;
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
 };
@@ -160,6 +160,7 @@ void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, 
 void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m, const uint32_t* gbuffer, const float* depth, const float* prev,
                           float* light, cudaStream_t st);
 void rt3_launch_postprocess(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, float* out, cudaStream_t st);
+void rt3_launch_present(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, uint32_t* out, cudaStream_t st);
 void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles, uint32_t tile_w, uint32_t tile_h, const float* slab, float* frame,
                        uint32_t frame_w, uint32_t frame_h, cudaStream_t st);
 void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,

@@ -73,9 +73,10 @@ __device__ __forceinline__ void store_ray(rt3_ray* q, uint32_t pos, vec3 o, vec3
 
 /* ---- the reference-mode loop as ONE wavefront per frame call, with ray REGENERATION ---------------------------------------------------
  * refrence_mode.slang:28-57 is `for i < samples { for b < bounces { ... } }` per pixel.  Here all live paths advance one bounce per round
- * (k_trace_dyn, then k_ref_shade); a path that ends — miss, last bounce, invalid lobe — is REPLACED in the same thread by the first bounce of
- * its pixel's next sample (the surface comes from the G-buffer again, :23,:30-34), and the survivors and the regenerated paths are compacted
- * together into the next queue with one ballot + one atomic per warp.  The queue therefore stays as long as the number of unfinished pixels
+ * (k_trace_dyn, then k_ref_shade); a path that ends — miss, last bounce, invalid lobe — while its pixel has samples left is REPLACED before the
+ * next round by the first bounce of the pixel's next sample (the surface comes from the G-buffer again, :23,:30-34): k_ref_shade compacts the
+ * survivors into the next queue and the pixels to regenerate into a second list (one ballot + one atomic per warp each), k_ref_regen starts
+ * their next samples with all lanes busy and appends them to the same queue.  The queue therefore stays as long as the number of unfinished pixels
  * instead of shrinking bounce by bounce and restarting per sample.  Every pixel still has exactly one path in flight and runs its samples in
  * order, so its RNG stream and the order of its radiance additions are those of the per-pixel loop: bit-identical to the oracle.
  * Per-pixel state: px_radiance (sum, w = 1 for non-background pixels) and px_path = {RNG counter (random.slang:62: never reset between
@@ -175,20 +176,21 @@ __global__ void __launch_bounds__(PASS_THREADS) k_ref_init(SceneView s, rt3_para
 #else
 #define RT3_SHADE_BOUNDS __launch_bounds__(PASS_THREADS)
 #endif
-/* REGEN = the frame call has more than one sample per pixel: only then is the regeneration code compiled in (64 against 80 registers) */
+/* REGEN = the frame call has more than one sample per pixel: paths that end are handed to k_ref_regen through regen_idx / regen_count */
 template <bool LAYERED, bool REGEN>
-__global__ void RT3_SHADE_BOUNDS k_ref_shade(SceneView s, rt3_params p, PixelMap m, RegenInputs gin, const rt3_ray* __restrict__ rays_in,
+__global__ void RT3_SHADE_BOUNDS k_ref_shade(SceneView s, rt3_params p, PixelMap m, uint32_t* __restrict__ regen_idx, uint32_t* regen_count,
+                                                            const rt3_ray* __restrict__ rays_in,
                                                             const rt3_hit* __restrict__ hits, const float4* __restrict__ thr_in,
                                                             const uint32_t* __restrict__ count_in, rt3_ray* __restrict__ rays_out,
                                                             float4* __restrict__ thr_out, uint32_t* count_out, float4* __restrict__ px_radiance,
                                                             uint2* __restrict__ px_path, NeeQueues nq, DeviceCounters* counters) {
     const uint32_t n = *count_in;
-    unsigned long long traced = 0, escaped = 0, shadows = 0, started = 0;
+    unsigned long long traced = 0, escaped = 0, shadows = 0;
     const bool nee = nee_enabled(p.flags);
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {
         const uint32_t i = base + threadIdx.x;
-        bool alive = false, shadow = false;
+        bool alive = false, shadow = false, regen = false;
         float pdf_brdf = 0.f;
         vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0), sdir = v3(0, 0, 0), scon = v3(0, 0, 0);
         uint32_t idx = 0;
@@ -246,27 +248,75 @@ __global__ void RT3_SHADE_BOUNDS k_ref_shade(SceneView s, rt3_params p, PixelMap
                 rng_index = rng.index;
                 b_next = (path.y & 0xFFu) + 1u;
             }
-            if (REGEN && !alive && sample + 1u < p.samples) {                          /* regeneration: the pixel's next sample starts here (:28) */
-                uint32_t x, y; size_t px;
-                pixel_of(m, idx, x, y, px);
-                const float gdepth = gin.depth[px];
-                uint4 g4 = ((const uint4*)gin.gbuffer)[px];
-                uint4_ packed = {g4.x, g4.y, g4.z, g4.w};
-                const GbufferData gsurface = gbuffer_unpack(packed);                   /* :23 */
-                RandomSamplerState rng = rng_init(x, y, p.frame);
-                rng.index = rng_index;
-                RT3_NEED_RADIANCE();
-                do {
-                    ++sample;
-                    started++;
-                    alive = start_sample<LAYERED>(s, p, nee, x, y, gsurface, gdepth, rng, radiance, o, d, thr, pdf_brdf, shadow, sdir, scon);
-                } while (!alive && sample + 1u < p.samples);
-                rng_index = rng.index;
-                b_next = 1u;
-            }
+            regen = REGEN && !alive && sample + 1u < p.samples;                        /* the pixel has samples left: k_ref_regen starts the next one (:28) */
+            if (regen) px_path[idx] = make_uint2(rng_index, sample << 8);
 #undef RT3_NEED_RADIANCE
             if (have_radiance) px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
             if (alive) px_path[idx] = make_uint2(rng_index, (sample << 8) | b_next);
+        }
+        const uint32_t pos = warp_enqueue(alive, count_out);
+        if (alive) {
+            store_ray(rays_out, pos, o, d, 0.001f, RT3_BACKGROUND_DEPTH);
+            thr_out[pos] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(idx));
+            if (nee) nq.pdf_out[pos] = pdf_brdf;
+        }
+        if (REGEN) {
+            const uint32_t rp = warp_enqueue(regen, regen_count);
+            if (regen) regen_idx[rp] = idx;
+        }
+        if (nee) {
+            const uint32_t sp = warp_enqueue(shadow, nq.scount);
+            if (shadow) {
+                shadows++;
+                store_ray(nq.srays, sp, o, sdir, 0.001f, RT3_BACKGROUND_DEPTH);
+                nq.scontrib[sp] = make_float4(scon.x, scon.y, scon.z, __uint_as_float(idx));
+            }
+        }
+    }
+    if (nee) flush_counter(shadows, &counters->rays_shadow);
+    flush_counter(traced, &counters->rays_secondary);
+    flush_counter(escaped, &counters->paths_escaped);
+}
+
+/* Ray regeneration, second half: every pixel on the regeneration queue starts its next sample (loop index 0 from the G-buffer, as in
+ * k_ref_init) and the new paths are appended to the queue the survivors of this round were compacted into.  A kernel of its own so that the
+ * work runs with all lanes busy: inside k_ref_shade the ~30 % of lanes whose path ended would execute it at a third of the warp width. */
+template <bool LAYERED>
+__global__ void __launch_bounds__(PASS_THREADS) k_ref_regen(SceneView s, rt3_params p, PixelMap m, RegenInputs gin, const uint32_t* __restrict__ regen_idx,
+                                                            const uint32_t* __restrict__ regen_count, rt3_ray* __restrict__ rays_out,
+                                                            float4* __restrict__ thr_out, uint32_t* count_out, float4* __restrict__ px_radiance,
+                                                            uint2* __restrict__ px_path, NeeQueues nq, DeviceCounters* counters) {
+    const uint32_t n = *regen_count;
+    unsigned long long started = 0, shadows = 0;
+    const bool nee = nee_enabled(p.flags);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {
+        const uint32_t i = base + threadIdx.x;
+        bool alive = false, shadow = false;
+        float pdf_brdf = 0.f;
+        vec3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0), sdir = v3(0, 0, 0), scon = v3(0, 0, 0);
+        uint32_t idx = 0;
+        if (i < n) {
+            idx = regen_idx[i];
+            uint32_t x, y; size_t px;
+            pixel_of(m, idx, x, y, px);
+            const uint2 path = px_path[idx];
+            uint32_t sample = path.y >> 8;
+            const float gdepth = gin.depth[px];
+            uint4 g4 = ((const uint4*)gin.gbuffer)[px];
+            uint4_ packed = {g4.x, g4.y, g4.z, g4.w};
+            const GbufferData surface = gbuffer_unpack(packed);                    /* :23 */
+            RandomSamplerState rng = rng_init(x, y, p.frame);
+            rng.index = path.x;
+            const float4 rad4 = px_radiance[idx];
+            vec3 radiance = v3(rad4.x, rad4.y, rad4.z);
+            do {
+                ++sample;
+                started++;
+                alive = start_sample<LAYERED>(s, p, nee, x, y, surface, gdepth, rng, radiance, o, d, thr, pdf_brdf, shadow, sdir, scon);
+            } while (!alive && sample + 1u < p.samples);
+            px_radiance[idx] = make_float4(radiance.x, radiance.y, radiance.z, 1.0f);
+            if (alive) px_path[idx] = make_uint2(rng.index, (sample << 8) | 1u);
         }
         const uint32_t pos = warp_enqueue(alive, count_out);
         if (alive) {
@@ -283,10 +333,8 @@ __global__ void RT3_SHADE_BOUNDS k_ref_shade(SceneView s, rt3_params p, PixelMap
             }
         }
     }
+    flush_counter(started, &counters->paths_started);
     if (nee) flush_counter(shadows, &counters->rays_shadow);
-    flush_counter(traced, &counters->rays_secondary);
-    flush_counter(escaped, &counters->paths_escaped);
-    if (REGEN) flush_counter(started, &counters->paths_started);
 }
 
 /* RT3_FLAG_NEE: add the light-sample contribution of every unoccluded shadow ray (one per pixel and bounce at most, so
@@ -332,6 +380,17 @@ __global__ void __launch_bounds__(PASS_THREADS) k_postprocess(SceneView s, rt3_p
     float4 c = ((const float4*)in)[px];
     vec3 r = postprocess_pixel(s, p, x, y, depth[px], v3(c.x, c.y, c.z));
     ((float4*)out)[px] = make_float4(r.x, r.y, r.z, 1.0f);
+}
+
+/* postprocess.slang:90-112 fused with the conversion to the swapchain format (B8G8R8A8_UNORM, swapchain.rs:27-48): 4 bytes per pixel out
+ * instead of 16 — what a host without CUDA-Vulkan interop reads back per presented frame */
+__global__ void __launch_bounds__(PASS_THREADS) k_present_bgra8(SceneView s, rt3_params p, PixelMap m, const float* __restrict__ depth,
+                                                                const float* __restrict__ in, uint32_t* __restrict__ out) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x, y; size_t px;
+    if (idx >= m.work || !pixel_of(m, idx, x, y, px)) return;
+    float4 c = ((const float4*)in)[px];
+    out[px] = pack_bgra8(postprocess_pixel(s, p, x, y, depth[px], v3(c.x, c.y, c.z)));
 }
 
 /* ---- screen-space probes ------------------------------------------------------------------------

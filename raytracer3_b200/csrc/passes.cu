@@ -41,8 +41,10 @@ static void run_reference_strip(rt3_context* c, RefLane& ln, const rt3_params& p
     rt3_ray* q_rays[2] = {ensure<rt3_ray>(c, ln.q_rays[0], W), ensure<rt3_ray>(c, ln.q_rays[1], W)};
     float4* q_thr[2] = {ensure<float4>(c, ln.q_thr[0], W), ensure<float4>(c, ln.q_thr[1], W)};
     rt3_hit* q_hits = ensure<rt3_hit>(c, ln.q_hits, W);
+    const bool regen = p.samples > 1;
+    uint32_t* q_regen = regen ? ensure<uint32_t>(c, ln.q_regen, W) : nullptr;
     unsigned long long* cnt64 = ensure<unsigned long long>(c, ln.counts, 64);
-    uint32_t* counts = (uint32_t*)cnt64;                  /* [0],[1] path queues, [2] shadow queue; cnt64[32..] the traversal kernel's work counter */
+    uint32_t* counts = (uint32_t*)cnt64;                  /* [0],[1] path queues, [2] shadow queue, [3] regeneration list; cnt64[32..] the traversal kernel's work counter */
     float* q_pdf[2] = {nullptr, nullptr};
     NeeQueues nq = {nullptr, nullptr, nullptr, nullptr, nullptr};
     uint32_t* sbits = nullptr;
@@ -53,7 +55,6 @@ static void run_reference_strip(rt3_context* c, RefLane& ln, const rt3_params& p
     }
     const unsigned grid = std::min<unsigned>(div_up(W, PASS_THREADS), (unsigned)c->sm_count * 8u);
     const RegenInputs gin = {gbuffer, depth};
-    const bool regen = p.samples > 1;
     auto resolve_shadows = [&]() {                      /* any-hit pass over the shadow queue, then add the unoccluded contributions */
         rt3_launch_trace_any(c, nq.srays, nq.scount, W, sbits, cnt64 + 32, st);
         RT3_LAUNCH(c, k_ref_shadow, grid, PASS_THREADS, 0, st, nq.scontrib, sbits, nq.scount, px_radiance);
@@ -72,13 +73,16 @@ static void run_reference_strip(rt3_context* c, RefLane& ln, const rt3_params& p
     for (uint64_t r = 0; r < rounds; ++r) {
         rt3_launch_trace_closest(c, q_rays[cur], counts + cur, W, q_hits, cnt64 + 32, st);
         RT3_CUDA(c, cudaMemsetAsync(counts + (1 - cur), 0, 4, st));
-        if (nee) RT3_CUDA(c, cudaMemsetAsync(counts + 2, 0, 4, st));
+        if (nee || regen) RT3_CUDA(c, cudaMemsetAsync(counts + 2, 0, 8, st));
         nq.pdf_in = q_pdf[cur]; nq.pdf_out = q_pdf[1 - cur];
-#define RT3_SHADE(L, R) RT3_LAUNCH(c, (k_ref_shade<L, R>), grid, PASS_THREADS, 0, st, c->view, p, m, gin, q_rays[cur], q_hits, q_thr[cur], counts + cur, q_rays[1 - cur], \
-                                   q_thr[1 - cur], counts + (1 - cur), px_radiance, px_path, nq, c->d_counters)
-        if (layered) { if (regen) RT3_SHADE(true, true); else RT3_SHADE(true, false); }
-        else { if (regen) RT3_SHADE(false, true); else RT3_SHADE(false, false); }
+#define RT3_SHADE(L, R) RT3_LAUNCH(c, (k_ref_shade<L, R>), grid, PASS_THREADS, 0, st, c->view, p, m, q_regen, counts + 3, q_rays[cur], q_hits, q_thr[cur], counts + cur, \
+                                   q_rays[1 - cur], q_thr[1 - cur], counts + (1 - cur), px_radiance, px_path, nq, c->d_counters)
+#define RT3_REGEN(L) RT3_LAUNCH(c, (k_ref_regen<L>), grid, PASS_THREADS, 0, st, c->view, p, m, gin, q_regen, counts + 3, q_rays[1 - cur], q_thr[1 - cur], counts + (1 - cur), \
+                                px_radiance, px_path, nq, c->d_counters)
+        if (layered) { if (regen) { RT3_SHADE(true, true); RT3_REGEN(true); } else RT3_SHADE(true, false); }
+        else { if (regen) { RT3_SHADE(false, true); RT3_REGEN(false); } else RT3_SHADE(false, false); }
 #undef RT3_SHADE
+#undef RT3_REGEN
         if (nee && r + 1 != rounds) resolve_shadows();
         cur = 1 - cur;
     }
@@ -119,6 +123,11 @@ void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m
 void rt3_launch_postprocess(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, float* out, cudaStream_t st) {
     if (!m.work) return;
     RT3_LAUNCH(c, k_postprocess, div_up(m.work, PASS_THREADS), PASS_THREADS, 0, st, c->view, p, m, depth, in, out);
+}
+
+void rt3_launch_present(rt3_context* c, const rt3_params& p, const PixelMap& m, const float* depth, const float* in, uint32_t* out, cudaStream_t st) {
+    if (!m.work) return;
+    RT3_LAUNCH(c, k_present_bgra8, div_up(m.work, PASS_THREADS), PASS_THREADS, 0, st, c->view, p, m, depth, in, out);
 }
 
 void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,

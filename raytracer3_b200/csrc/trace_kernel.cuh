@@ -48,6 +48,9 @@ __device__ __forceinline__ rt3_ray load_ray(const rt3_ray* rays, uint64_t i) {
 #ifndef RT3_TRI_BALANCE
 #define RT3_TRI_BALANCE 0
 #endif
+#ifndef RT3_NODE_COOP
+#define RT3_NODE_COOP 0
+#endif
 #ifndef RT3_TRI_WAIT
 #define RT3_TRI_WAIT 0
 #endif
@@ -121,6 +124,44 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
          * per-lane loop (ncu source page of the per-lane-loop version: profiles/r1b_*). */
         do {
             RT3_EMU_PHASE(0, active && tg_hits == 0u && ng_hits > 0x00FFFFFFu);
+#if RT3_NODE_COOP
+            /* EXPERIMENT (-DRT3_NODE_COOP=1; north_star: "vectorised node loads staged in shared memory"): the warp fetches the nodes of all its
+             * lanes cooperatively — the 32 x 5 sixteen-byte words are dealt to the lanes in address order (lane L of round r loads word
+             * (32 r + L) % 5 of the node of lane (32 r + L) / 5), so five neighbouring lanes read one node's 80 contiguous bytes (3 sectors)
+             * instead of every lane issuing five 16-byte loads to its own node (5 sectors) — through 2.5 KB of shared memory per warp. */
+            {
+                __shared__ u32x4 s_node[TRACE_THREADS / 32][32 * 5];
+                const uint32_t wid = threadIdx.x >> 5;
+                const bool step = active && tg_hits == 0u && ng_hits > 0x00FFFFFFu;
+                uint32_t node_index = 0xFFFFFFFFu;
+                int bit = 0;
+                if (step) {
+                    bit = bfind32(ng_hits);
+                    const uint32_t imask = ng_hits & 0xFFu;
+                    const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xFFu)) & 7u;
+                    node_index = ng_base + (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
+                }
+                if (__ballot_sync(0xFFFFFFFFu, step)) {
+#pragma unroll
+                    for (uint32_t rr = 0; rr < 5u; ++rr) {
+                        const uint32_t c = rr * 32u + lane, owner = c / 5u, part = c - owner * 5u;
+                        const uint32_t oi = __shfl_sync(0xFFFFFFFFu, node_index, owner);
+                        if (oi != 0xFFFFFFFFu) s_node[wid][c] = ld_u32x4(nodes[oi].w + 4u * part);
+                    }
+                    __syncwarp();
+                    if (step) {
+                        ng_hits &= ~(1u << bit);
+                        if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) RT3_PUSH(ng_base, ng_hits);
+                        const u32x4 n0 = s_node[wid][lane * 5u], n1 = s_node[wid][lane * 5u + 1u], n2 = s_node[wid][lane * 5u + 2u], n3 = s_node[wid][lane * 5u + 3u],
+                                    n4 = s_node[wid][lane * 5u + 4u];
+                        const uint32_t hm = intersect_wide_node(r, h.t, n0, n1, n2, n3, n4);
+                        ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
+                        tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
+                    }
+                    __syncwarp();
+                }
+            }
+#else
             if (active && tg_hits == 0u && ng_hits > 0x00FFFFFFu) {
                 const int bit = bfind32(ng_hits);
                 const uint32_t imask = ng_hits & 0xFFu;
@@ -135,6 +176,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                 ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
                 tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
             }
+#endif
             bool found_any = false;
 #if RT3_TRI_BALANCE
             if (!TWO) {

@@ -246,7 +246,7 @@ class WorkSize2D:
         return self.x, self.y
 
 
-_FORMATS = {"RGBA32UI": ("int32", 4), "R32F": ("float32", 1), "RGBA32F": ("float32", 4), "RG32UI": ("int32", 2), "RG32F": ("float32", 2), "R16UI": ("int16", 1)}
+_FORMATS = {"B8G8R8A8": ("int32", 1), "RGBA32UI": ("int32", 4), "R32F": ("float32", 1), "RGBA32F": ("float32", 4), "RG32UI": ("int32", 2), "RG32F": ("float32", 2), "R16UI": ("int16", 1)}
 
 
 class RenderGraph:
@@ -354,6 +354,8 @@ class ComputePass(_PassBuilder):
         p = ptr(self._constants)
         if self._shader == "postprocess":
             ctx.check(ctx.L.rt3_pass_postprocess(ctx.h, p, Rect(0, 0, x, y), self._ptr("Depth"), self._ptr("In"), self._ptr("Out"), ctx.stream()))
+        elif self._shader == "present":                            # postprocess + the swapchain blit's conversion to B8G8R8A8_UNORM (swapchain.rs:27-48)
+            ctx.check(ctx.L.rt3_pass_present_bgra8(ctx.h, p, Rect(0, 0, x, y), self._ptr("Depth"), self._ptr("In"), self._ptr("Out"), ctx.stream()))
         elif self._shader == "structured_importance_sampling":     # shaders/old/structured_importance_sampling.slang, 8x8 threads per probe
             ctx.check(ctx.L.rt3_pass_probe_sis(ctx.h, p, self._ptr("gbuffer"), self._ptr("out"), ctx.stream()))
         elif self._shader == "spherical_harmonic_conversion":
@@ -362,7 +364,7 @@ class ComputePass(_PassBuilder):
             ctx.check(ctx.L.rt3_pass_probe_interpolate(ctx.h, p, self._ptr("gbuffer"), self._ptr("gbuffer_depth"), self._ptr("sh_coeficents"),
                                                        self._ptr("Light"), ctx.stream()))
         else:
-            raise ValueError(f"unknown compute shader '{self._shader}' (known: postprocess, structured_importance_sampling, "
+            raise ValueError(f"unknown compute shader '{self._shader}' (known: postprocess, present, structured_importance_sampling, "
                              "spherical_harmonic_conversion, interpolate_probes)")
         return self.name
 

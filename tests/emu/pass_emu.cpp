@@ -116,7 +116,7 @@ int pemu_frame(const void* scene_view, const uint32_t* shade_rec, const uint32_t
         std::vector<rt3_ray> q_rays[2] = {std::vector<rt3_ray>(W), std::vector<rt3_ray>(W)}, srays(nee ? W : 1);
         std::vector<float4> q_thr[2] = {std::vector<float4>(W), std::vector<float4>(W)}, scontrib(nee ? W : 1);
         std::vector<rt3_hit> q_hits(W);
-        std::vector<uint32_t> sbits((W + 31) / 32 + 1);
+        std::vector<uint32_t> sbits((W + 31) / 32 + 1), q_regen(W);
         std::vector<float> q_pdf[2] = {std::vector<float>(nee ? W : 1), std::vector<float>(nee ? W : 1)};
         uint32_t counts[4] = {0, 0, 0, 0};
         NeeQueues nq = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -139,14 +139,20 @@ int pemu_frame(const void* scene_view, const uint32_t* shade_rec, const uint32_t
             if (g_round_lengths && r < 4096) g_round_lengths[r] += counts[cur];
             if (trace_closest(nodes, tris, q_rays[cur].data(), counts + cur, W, q_hits.data())) return -1;
             counts[1 - cur] = 0;
-            if (nee) counts[2] = 0;
+            counts[2] = 0; counts[3] = 0;
             nq.pdf_in = nee ? q_pdf[cur].data() : nullptr; nq.pdf_out = nee ? q_pdf[1 - cur].data() : nullptr;
             if (launch(grid, PASS_THREADS, [&]() {
-#define PEMU_SHADE(L, R) k_ref_shade<L, R>(view, p, m, gin, q_rays[cur].data(), q_hits.data(), q_thr[cur].data(), counts + cur, q_rays[1 - cur].data(), \
+#define PEMU_SHADE(L, R) k_ref_shade<L, R>(view, p, m, q_regen.data(), counts + 3, q_rays[cur].data(), q_hits.data(), q_thr[cur].data(), counts + cur, q_rays[1 - cur].data(), \
                                            q_thr[1 - cur].data(), counts + (1 - cur), px_radiance.data(), px_path.data(), nq, &dc)
                     if (layered) { if (p.samples > 1) PEMU_SHADE(true, true); else PEMU_SHADE(true, false); }
                     else { if (p.samples > 1) PEMU_SHADE(false, true); else PEMU_SHADE(false, false); }
 #undef PEMU_SHADE
+                })) return -1;
+            if (p.samples > 1 && launch(grid, PASS_THREADS, [&]() {                  /* regeneration: the next samples of the pixels whose path ended */
+                    if (layered) k_ref_regen<true>(view, p, m, gin, q_regen.data(), counts + 3, q_rays[1 - cur].data(), q_thr[1 - cur].data(), counts + (1 - cur),
+                                                   px_radiance.data(), px_path.data(), nq, &dc);
+                    else k_ref_regen<false>(view, p, m, gin, q_regen.data(), counts + 3, q_rays[1 - cur].data(), q_thr[1 - cur].data(), counts + (1 - cur),
+                                            px_radiance.data(), px_path.data(), nq, &dc);
                 })) return -1;
             if (nee && r + 1 != rounds && resolve_shadows()) return -1;
             cur = 1 - cur;

@@ -16,7 +16,8 @@ CASES = {
     "atrium": lambda: scenes.synthetic_atrium(0.03, environment=False),
 }
 # compile-time experiments of trace_kernel.cuh (none is in the product build): they must not change a single hit either
-VARIANTS = [((), False), (("RT3_TRI_REPS=1",), False), (("RT3_TRI_WAIT=8",), False), ((), True), (("RT3_TRI_WAIT=16",), True), (("RT3_SMEM_STACK=4",), False)]
+VARIANTS = [((), False), (("RT3_TRI_REPS=1",), False), (("RT3_TRI_WAIT=8",), False), ((), True), (("RT3_TRI_WAIT=16",), True), (("RT3_SMEM_STACK=4",), False),
+            (("RT3_NODE_COOP=1",), False)]
 
 
 def _scene(name, n=1500):

@@ -360,3 +360,30 @@ def test_far_origins_and_tiny_objects_are_not_culled(gpu_ctx):
     got2, want2 = w.trace_closest_host(rays2), orc2.trace_closest(rays2, brute=True)
     assert (want2["prim"] >= 2).mean() > 0.2                                   # the tiny quad is actually hit
     assert (got2["prim"] == want2["prim"]).all(), int((got2["prim"] != want2["prim"]).sum())
+
+
+def test_present_bgra8_matches_oracle(gpu_ctx, cornell):
+    """rt3_pass_present_bgra8 = postprocess.slang + the swapchain format (B8G8R8A8_UNORM, swapchain.rs:27-48): one word per pixel, bit-identical
+    to the oracle and consistent with the RGBA32F post-process output (|float * 255 - byte| <= 0.5)."""
+    import torch
+    from raytracer3_b200.host import ComputePass, Renderer, WorkSize2D
+    sc, orc = cornell
+    w = _world(gpu_ctx, sc)
+    W, H = 200, 120
+    p = make_params(camera_for(sc, "cam0", W, H), W, H, frame=2, bounces=4, samples=4, flags=FLAG_ENV)
+    r = Renderer(gpu_ctx, w, W, H)
+    light = r.frame(p, postprocess=True)
+    rg = r.rg
+    rg.image("B8G8R8A8", "present")
+    (ComputePass.new(rg, "present").shader("present").constants(p).read("Depth", "gbuffer_depth").read("In", f"light{1 - r.cur}").write("Out", "present")
+     .dispatch(WorkSize2D.FullScreen()))
+    got = rg.tensor("present").cpu().numpy().view(np.uint32)
+    gb, dp, _, _ = orc.pass_gbuffer(p)
+    lt, _ = orc.pass_reference(p, gb, dp)
+    want = orc.pass_present_bgra8(p, dp, lt)
+    assert (got == want).all()
+    out = rg.tensor("out").cpu().numpy()
+    for shift, ch in ((16, 0), (8, 1), (0, 2)):
+        byte = ((got >> shift) & 0xFF).astype(np.float64)
+        assert np.abs(np.clip(out[..., ch], 0, 1).astype(np.float64) * 255.0 - byte).max() <= 0.5 + 1e-4
+    assert ((got >> 24) == 255).all() and len(np.unique(got)) > 500
