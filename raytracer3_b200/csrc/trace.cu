@@ -95,7 +95,7 @@ int env_int(const char* name, int dflt) { const char* v = getenv(name); return v
 template <bool ANY>
 void launch_dyn(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, rt3_hit* hits, uint32_t* bits, unsigned long long* wc, cudaStream_t st) {
     static const int keep = env_int("RT3_TRACE_KEEP", 28);
-    static const int waves = env_int("RT3_TRACE_BLOCKS_PER_SM", 8);
+    static const int waves = env_int("RT3_TRACE_BLOCKS_PER_SM", 8 * 128 / TRACE_THREADS);
     static const int legacy = env_int("RT3_TRACE_STATIC", 0);
     unsigned long long* w = work_counter(c, wc, st);
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * waves, (n_max + TRACE_THREADS - 1) / TRACE_THREADS);

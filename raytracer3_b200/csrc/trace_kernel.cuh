@@ -16,7 +16,11 @@
 
 namespace {
 
-constexpr int TRACE_THREADS = 128;
+/* threads per CTA of the traversal kernels (experiments: -DRT3_TRACE_THREADS=64 with RT3_TRACE_BLOCKS_PER_SM=16 retires CTAs in smaller units) */
+#ifndef RT3_TRACE_THREADS
+#define RT3_TRACE_THREADS 128
+#endif
+constexpr int TRACE_THREADS = RT3_TRACE_THREADS;
 
 __device__ __forceinline__ rt3_ray load_ray(const rt3_ray* rays, uint64_t i) {
     const float4* p = (const float4*)(rays + i);
