@@ -262,6 +262,12 @@ RT3_API rt3_status rt3_measure_l2_bandwidth(rt3_context*, size_t bytes, int iter
 typedef struct { double nodes_per_ray, tris_per_ray, node_bytes_per_ray, tri_bytes_per_ray; } rt3_trace_stats;
 RT3_API rt3_status rt3_trace_closest_stats(rt3_context*, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out);
 
+/* The ramp-up and tail of a persistent traversal launch, measured by an instrumented instantiation of the kernel (three timer reads per warp):
+ * kernel_us = first warp in to last warp out; mean_warp_busy_us = a warp's time in the kernel; mean_warp_tail_us = its time after it first
+ * found the queue exhausted (it finishes the rays it still holds, with fewer and fewer lanes busy); tail_fraction = their ratio over all warps. */
+typedef struct { double kernel_us, mean_warp_busy_us, mean_warp_tail_us, tail_fraction; uint32_t warps, _pad; } rt3_tail_stats;
+RT3_API rt3_status rt3_trace_closest_tail_stats(rt3_context*, const rt3_ray* rays, uint64_t n, rt3_tail_stats* out);
+
 /* Per-kernel timing of the closest-hit traversal launches made by the passes: while enabled, every launch is bracketed by
  * CUDA events on its own stream; rt3_profile_read synchronises, returns the summed duration and launch count, and resets. */
 RT3_API rt3_status rt3_profile_enable(rt3_context*, int enable);

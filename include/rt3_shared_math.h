@@ -536,6 +536,17 @@ RT3_HD void world_triangle(const SceneView& s, uint32_t seg, uint32_t prim_in_ge
     if (!xform_is_identity(ix)) { a = xform_point(ix, a); b = xform_point(ix, b); c = xform_point(ix, c); }
 }
 
+/* Repeat addressing of the two texel columns (rows) of a bilinear footprint: x0 = floor(frac(u) * n - 0.5) lies in [-1, n - 1] and
+ * x1 = x0 + 1, so (x mod n + n) mod n is a conditional wrap; the general formula — four integer divisions per footprint axis pair, two
+ * thirds of the instructions of the whole lookup — is kept for coordinates outside that range (non-finite uv).  Same result for every input. */
+RT3_HD void wrap_texel_pair(int& x0, int& x1, int n) {
+    if (x0 >= -1 && x0 < n) {
+        x0 = x0 < 0 ? n - 1 : x0;
+        x1 = x1 >= n ? 0 : x1;
+    } else {
+        x0 = (x0 % n + n) % n; x1 = (x1 % n + n) % n;
+    }
+}
 /* Textures[i].SampleLevel(uv, 0) as DEFINED for the missing bindless_descriptor.slang: RGBA8 sRGB,
  * bilinear, repeat addressing, texel centres at (i + 0.5) / size. */
 RT3_HD vec3 sample_texture(const SceneView& s, int slot, float u, float v) {
@@ -547,8 +558,7 @@ RT3_HD vec3 sample_texture(const SceneView& s, int slot, float u, float v) {
     float ax = fx - flx, ay = fy - fly;
     int x0 = (int)flx, y0 = (int)fly;
     int x1 = x0 + 1, y1 = y0 + 1;
-    x0 = (x0 % (int)w + (int)w) % (int)w; x1 = (x1 % (int)w + (int)w) % (int)w;
-    y0 = (y0 % (int)h + (int)h) % (int)h; y1 = (y1 % (int)h + (int)h) % (int)h;
+    wrap_texel_pair(x0, x1, (int)w); wrap_texel_pair(y0, y1, (int)h);
     const uint8_t* p00 = t + 4u * ((uint32_t)y0 * w + (uint32_t)x0);
     const uint8_t* p10 = t + 4u * ((uint32_t)y0 * w + (uint32_t)x1);
     const uint8_t* p01 = t + 4u * ((uint32_t)y1 * w + (uint32_t)x0);
@@ -571,7 +581,7 @@ RT3_HD vec3 sample_environment(const SceneView& s, vec3 dir) {
     float ax = fx - flx, ay = fy - fly;
     int x0 = (int)flx, y0 = (int)fly, x1 = x0 + 1, y1 = y0 + 1;
     int w = (int)s.env_w, h = (int)s.env_h;
-    x0 = (x0 % w + w) % w; x1 = (x1 % w + w) % w;
+    wrap_texel_pair(x0, x1, w);
     y0 = y0 < 0 ? 0 : (y0 > h - 1 ? h - 1 : y0);
     y1 = y1 < 0 ? 0 : (y1 > h - 1 ? h - 1 : y1);
     const float* p00 = s.env + 3u * ((uint32_t)y0 * s.env_w + (uint32_t)x0);

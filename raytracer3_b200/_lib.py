@@ -4,7 +4,7 @@ import ctypes as C
 import os
 import re
 
-from .types import BuildStats, Counters, Rect, TraceStats
+from .types import BuildStats, Counters, Rect, TailStats, TraceStats
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "librt3.so")
@@ -81,6 +81,7 @@ def load():
         "rt3_kernel_launches": (u64, [vp]),
         "rt3_measure_l2_bandwidth": (i32, [vp, C.c_size_t, i32, P(C.c_double)]),
         "rt3_trace_closest_stats": (i32, [vp, vp, u64, P(TraceStats)]),
+        "rt3_trace_closest_tail_stats": (i32, [vp, vp, u64, P(TailStats)]),
         "rt3_profile_enable": (i32, [vp, i32]),
         "rt3_profile_read": (i32, [vp, P(C.c_double), P(u64)]),
         "rt3_accel_download": (i32, [vp, vp, C.c_size_t, vp, C.c_size_t]),

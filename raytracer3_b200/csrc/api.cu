@@ -695,6 +695,15 @@ rt3_status rt3_trace_closest_stats(rt3_context* c, const rt3_ray* rays, uint64_t
     });
 }
 
+rt3_status rt3_trace_closest_tail_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_tail_stats* out) {
+    return guarded(c, [&]() {
+        require_accel(c);
+        if (!out || (n && !rays)) RT3_FAIL(c, RT3_ERR_INVALID, "NULL argument");
+        CallOrder order(c, 0);
+        rt3_launch_trace_tail_stats(c, rays, n, out);
+    });
+}
+
 rt3_status rt3_profile_enable(rt3_context* c, int enable) {
     return guarded(c, [&]() {
         RT3_CUDA(c, cudaDeviceSynchronize());

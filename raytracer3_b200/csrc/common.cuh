@@ -155,6 +155,7 @@ void rt3_launch_trace_closest(rt3_context* c, const rt3_ray* rays, const uint32_
 void rt3_launch_trace_any(rt3_context* c, const rt3_ray* rays, const uint32_t* d_count, uint64_t n_max, uint32_t* bits, unsigned long long* work_counter,
                           cudaStream_t st);
 void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_trace_stats* out);
+void rt3_launch_trace_tail_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_tail_stats* out);
 void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary,
                         cudaStream_t st);
 void rt3_launch_reference(rt3_context* c, const rt3_params& p, const PixelMap& m, const uint32_t* gbuffer, const float* depth, const float* prev,

@@ -149,6 +149,35 @@ void rt3_launch_trace_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3
     out->tri_bytes_per_ray = out->tris_per_ray * sizeof(Tri48);
 }
 
+/* The fixed cost of a persistent traversal launch, measured directly: the instrumented instantiation of k_trace_dyn (same loop, three
+ * timer reads per warp) over `n` rays. */
+void rt3_launch_trace_tail_stats(rt3_context* c, const rt3_ray* rays, uint64_t n, rt3_tail_stats* out) {
+    memset(out, 0, sizeof(*out));
+    if (n == 0) return;
+    cudaStream_t st = 0;
+    unsigned long long* w = work_counter(c, nullptr, st);
+    unsigned long long* ts = (unsigned long long*)c->d_counts.ptr + 40;
+    const unsigned long long init[5] = {0ull, 0ull, ~0ull, 0ull, 0ull};
+    RT3_CUDA(c, cudaMemcpyAsync(ts, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    rt3_hit* hits = ensure<rt3_hit>(c, c->f_hits, n);
+    static const int waves = env_int("RT3_TRACE_BLOCKS_PER_SM", 8 * 128 / TRACE_THREADS);
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)c->sm_count * waves, (n + TRACE_THREADS - 1) / TRACE_THREADS);
+    if (c->two_level)
+        RT3_LAUNCH(c, (k_trace_dyn<false, 28, true, true>), grid, TRACE_THREADS, 0, st, c->bvh_nodes.as<WideNode>(), c->bvh_tris.as<Tri48>(), rays, (const uint32_t*)nullptr, n, hits,
+                   (uint32_t*)nullptr, w, 0x47000000u, c->d_insts.as<InstRec>(), ts);
+    else
+        RT3_LAUNCH(c, (k_trace_dyn<false, 28, false, true>), grid, TRACE_THREADS, 0, st, c->bvh_nodes.as<WideNode>(), c->bvh_tris.as<Tri48>(), rays, (const uint32_t*)nullptr, n, hits,
+                   (uint32_t*)nullptr, w, 0x47000000u, (const InstRec*)nullptr, ts);
+    unsigned long long h[5];
+    RT3_CUDA(c, cudaMemcpy(h, ts, sizeof(h), cudaMemcpyDeviceToHost));
+    const double warps = (double)h[4];
+    out->warps = (uint32_t)h[4];
+    out->kernel_us = (double)(h[3] - h[2]) * 1e-3;
+    out->mean_warp_busy_us = warps ? (double)h[0] / warps * 1e-3 : 0.0;
+    out->mean_warp_tail_us = warps ? (double)h[1] / warps * 1e-3 : 0.0;
+    out->tail_fraction = h[0] ? (double)h[1] / (double)h[0] : 0.0;
+}
+
 double rt3_run_l2_sweep(rt3_context* c, size_t bytes, int iters) {
     size_t n_vec = bytes / 16;
     uint4* buf = ensure<uint4>(c, c->l2_buf, n_vec + 1);

@@ -67,12 +67,25 @@ __device__ __forceinline__ rt3_ray load_ray(const rt3_ray* rays, uint64_t i) {
 /* TWO = two-level structure (RT3_BUILD_TWO_LEVEL): top-level leaf records are instances; see traverse_wide in bvh_logic.h for the
  * stack protocol (node group, record group, sentinel).  The world-space ray stays in registers for the triangle test, which
  * rebuilds the world-space triangle from the stored object-space vertices (bit-identical to the flattened build). */
-template <bool ANY, int KEEP, bool TWO>
+/* TAIL (instrumented instantiation only, rt3_trace_tail_stats): every warp records when it entered, when it first found the queue
+ * exhausted and when it left (%globaltimer, ns) into tail_stats = {sum busy, sum tail, min start, max end, warps}. */
+__device__ __forceinline__ unsigned long long global_ns() {
+#ifdef __CUDA_ARCH__
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+#else
+    return 0ull;
+#endif
+}
+template <bool ANY, int KEEP, bool TWO, bool TAIL = false>
 __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris,
                                                              const rt3_ray* __restrict__ rays, const uint32_t* __restrict__ d_count, uint64_t n_static,
                                                              rt3_hit* __restrict__ hits, uint32_t* __restrict__ bits, unsigned long long* work_counter, uint32_t magic,
-                                                             const InstRec* __restrict__ insts) {
+                                                             const InstRec* __restrict__ insts, unsigned long long* tail_stats = nullptr) {
     const uint64_t n = d_count ? (uint64_t)*d_count : n_static;
+    unsigned long long t_start = 0, t_exhausted = 0;
+    if (TAIL) t_start = global_ns();
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     RayPrep r;
@@ -118,7 +131,10 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                     active = true;
                 }
             }
-            if (base + want >= n) exhausted = true;
+            if (base + want >= n) {
+                if (TAIL && !exhausted) t_exhausted = global_ns();
+                exhausted = true;
+            }
         }
         if (__ballot_sync(0xFFFFFFFFu, active) == 0u) break;
         const int keep = exhausted ? 1 : KEEP;
@@ -327,6 +343,16 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
             }
         } while (__popc(__ballot_sync(0xFFFFFFFFu, active)) >= keep);
     }
+#ifdef __CUDA_ARCH__      /* the warp emulation has no timer and never instantiates TAIL */
+    if (TAIL && (threadIdx.x & 31u) == 0u) {
+        const unsigned long long t_end = global_ns();
+        atomicAdd(tail_stats + 0, t_end - t_start);
+        atomicAdd(tail_stats + 1, t_end - (t_exhausted ? t_exhausted : t_end));
+        atomicMin(tail_stats + 2, t_start);
+        atomicMax(tail_stats + 3, t_end);
+        atomicAdd(tail_stats + 4, 1ull);
+    }
+#endif
 #undef RT3_PUSH
 #undef RT3_POP
 }

@@ -23,7 +23,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import _lib
-from .types import PARAMS, BuildStats, Counters, Rect, TraceStats, ptr
+from .types import PARAMS, BuildStats, Counters, Rect, TailStats, TraceStats, ptr
 
 
 def _torch():
@@ -207,6 +207,12 @@ class RenderWorld:
         out = np.empty((len(rays) + 31) // 32, np.uint32) if out is None else out
         self.ctx.check(self.ctx.L.rt3_trace_any_host(self.ctx.h, ptr(rays), len(rays), ptr(out)))
         return out
+
+    def trace_tail_stats(self, rays_dev):
+        """Ramp-up / tail of one persistent traversal launch over `rays_dev` (instrumented kernel, rt3.h rt3_tail_stats)."""
+        ts = TailStats()
+        self.ctx.check(self.ctx.L.rt3_trace_closest_tail_stats(self.ctx.h, rays_dev.data_ptr(), rays_dev.shape[0], C.byref(ts)))
+        return ts
 
     def trace_stats(self, rays_dev):
         ts = TraceStats()

@@ -113,6 +113,14 @@ class TraceStats(C.Structure):
     ]
 
 
+class TailStats(C.Structure):
+    _fields_ = [("kernel_us", C.c_double), ("mean_warp_busy_us", C.c_double), ("mean_warp_tail_us", C.c_double), ("tail_fraction", C.c_double),
+                ("warps", C.c_uint32), ("_pad", C.c_uint32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_ if k != "_pad"}
+
+
 def ptr(a, ctype=C.c_void_p):
     """ctypes pointer to a contiguous numpy array (or None)."""
     if a is None:
