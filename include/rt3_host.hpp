@@ -261,6 +261,9 @@ class ComputePass : public PassBuilder<ComputePass> {
                       "rt3_pass_postprocess");
         else if (shader_ == "spherical_harmonic_conversion")
             ctx.check(rt3_pass_probe_sh(ctx.handle(), params(), (const float*)ptr("probe_atlas"), (float*)ptr("out"), ctx.stream()), "rt3_pass_probe_sh");
+        else if (shader_ == "present")                              /* postprocess + the swapchain blit's conversion to B8G8R8A8_UNORM */
+            ctx.check(rt3_pass_present_bgra8(ctx.handle(), params(), rect, (const float*)ptr("Depth"), (const float*)ptr("In"), (uint32_t*)ptr("Out"),
+                                             ctx.stream()), "rt3_pass_present_bgra8");
         else if (shader_ == "structured_importance_sampling")       /* shaders/old/structured_importance_sampling.slang, 8x8 threads per probe */
             ctx.check(rt3_pass_probe_sis(ctx.handle(), params(), (const uint32_t*)ptr("gbuffer"), (uint16_t*)ptr("out"), ctx.stream()), "rt3_pass_probe_sis");
         else if (shader_ == "interpolate_probes")
