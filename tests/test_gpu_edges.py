@@ -387,3 +387,48 @@ def test_present_bgra8_matches_oracle(gpu_ctx, cornell):
         byte = ((got >> shift) & 0xFF).astype(np.float64)
         assert np.abs(np.clip(out[..., ch], 0, 1).astype(np.float64) * 255.0 - byte).max() <= 0.5 + 1e-4
     assert ((got >> 24) == 255).all() and len(np.unique(got)) > 500
+
+
+def test_strip_count_does_not_change_the_image_and_options_are_checked(gpu_ctx):
+    """RT3_OPT_STRIPS = 1 .. 4 concurrent wavefronts per reference-pass call (regeneration and NEE included): bit-identical images."""
+    import torch
+    from raytracer3_b200 import _lib
+    from raytracer3_b200.host import Renderer, RenderWorld
+    sc = scenes.synthetic_atrium(0.03)
+    sc["bluenoise"] = scenes.blue_noise_tile(64, iters=4)
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc); w.create_acceleration_structure()
+    W, H = 640, 360
+    r = Renderer(gpu_ctx, w, W, H)
+    cam = camera_for(sc, "cam0", W, H)
+    try:
+        for flags, samples in ((FLAG_ENV | FLAG_BLUENOISE, 1), (FLAG_ENV | FLAG_NEE, 3)):
+            p = make_params(cam, W, H, frame=7, bounces=4, samples=samples, flags=flags)
+            images = []
+            for strips in (1, 2, 3, 4):
+                gpu_ctx.set_strips(strips)
+                images.append(r.frame(p).clone())
+            for k in range(1, 4):
+                assert torch.equal(images[0].view(torch.int32), images[k].view(torch.int32)), (flags, k + 1)
+            assert float(images[0][..., :3].sum()) > 0
+        with pytest.raises(_lib.Rt3Error):
+            gpu_ctx.set_strips(5)
+        with pytest.raises(_lib.Rt3Error):
+            gpu_ctx.check(gpu_ctx.L.rt3_set_option(gpu_ctx.h, 99, 1))
+    finally:
+        gpu_ctx.set_strips(0)
+
+
+def test_tail_statistics_of_a_traversal_launch(gpu_ctx):
+    """rt3_trace_closest_tail_stats: the instrumented instantiation gives the same hits' worth of work and sane timings."""
+    import torch
+    from raytracer3_b200.host import RenderWorld
+    sc = scenes.synthetic_atrium(0.03, environment=False)
+    w = RenderWorld(gpu_ctx)
+    w.clear(); w.load_scene(sc); w.create_acceleration_structure()
+    closest, _ = scenes.incoherent_rays(sc, 400000, seed=5)
+    rays = torch.from_numpy(closest.view(np.float32).reshape(-1, 8)).cuda()
+    ts = w.trace_tail_stats(rays)
+    assert ts.warps > 0 and ts.kernel_us > 1.0
+    assert 0.0 < ts.mean_warp_tail_us <= ts.mean_warp_busy_us <= ts.kernel_us * 1.01
+    assert 0.0 < ts.tail_fraction < 1.0
