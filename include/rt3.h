@@ -199,6 +199,18 @@ RT3_API rt3_status rt3_probe_layout(const rt3_params*, uint32_t* atlas_w, uint32
 RT3_API rt3_status rt3_pass_probe_sis(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, uint16_t* directions_r16ui, void* cuda_stream);
 RT3_API rt3_status rt3_pass_probe_trace(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, const float* depth_r32f,
                                         const uint16_t* opt_directions_r16ui, const float* prev_atlas_rgba32f, float* atlas_rgba32f, void* cuda_stream);
+/* rt3_pass_probe_trace that ALLOCATES NOTHING.  No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same results as
+ * rt3_pass_probe_trace; the per-texel scratch (probe ray, hit, staged value + target) and the traversal kernel's ray-fetch counter live in
+ * one file-scope `static __device__` array of 34 MiB that every GPU which loads the library holds until exit.
+ *   - limit: atlas_w * atlas_h <= RT3_STATIC_PROBE_MAX_TEXELS (a 1920x1088 window); larger frames return RT3_ERR_INVALID with a message;
+ *   - the scene tables must be current (RT3_ERR_STATE otherwise: this call never refreshes them) and rt3_profile_enable must be off;
+ *   - every call on a device shares the array: it keeps the previous call's contents, each call overwrites all it reads and zeroes its
+ *     counter itself; calls that OVERLAP on the GPU (other streams or contexts, no ordering between them) race — serialise them. */
+#define RT3_STATIC_PROBE_MAX_TEXELS 524288u
+RT3_API rt3_status rt3_pass_probe_trace_static(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, const float* depth_r32f,
+                                               const uint16_t* opt_directions_r16ui, const float* prev_atlas_rgba32f, float* atlas_rgba32f,
+                                               void* cuda_stream);
 RT3_API rt3_status rt3_pass_probe_sh(rt3_context*, const rt3_params*, const float* atlas_rgba32f, float* sh, void* cuda_stream);
 RT3_API rt3_status rt3_pass_probe_interpolate(rt3_context*, const rt3_params*, const uint32_t* gbuffer_rgba32ui, const float* depth_r32f,
                                               const float* sh, float* light_rgba32f, void* cuda_stream);

@@ -60,6 +60,7 @@ def load():
         "rt3_pass_present_bgra8": (i32, [vp, vp, Rect, vp, vp, vp, vp]),
         "rt3_probe_layout": (i32, [vp, P(u32), P(u32), P(u32)]),
         "rt3_pass_probe_trace": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
+        "rt3_pass_probe_trace_static": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
         "rt3_pass_probe_sis": (i32, [vp, vp, vp, vp, vp]),
         "rt3_pass_probe_sh": (i32, [vp, vp, vp, vp, vp]),
         "rt3_pass_probe_interpolate": (i32, [vp, vp, vp, vp, vp, vp, vp]),

@@ -225,6 +225,7 @@ rt3_status rt3_create(int cuda_device, rt3_context** out) {
         for (int i = 0; i < 8; ++i) RT3_CUDA(c, cudaEventCreate(&c->ev[i]));
         RT3_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
         RT3_CUDA(c, cudaEventCreateWithFlags(&c->ev_last, cudaEventDisableTiming));
+        (void)rt3_static_scratch_setup(cuda_device);     /* address of the static scratch of rt3_pass_probe_trace_static; a failure is reported by that call */
         RT3_CUDA(c, cudaMalloc(&c->d_counters, sizeof(DeviceCounters)));
         RT3_CUDA(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
         float lut[256];
@@ -442,6 +443,20 @@ rt3_status rt3_pass_probe_trace(rt3_context* c, const rt3_params* p, const uint3
         if (c->scene_dirty) refresh_scene_tables(c);
         CallOrder order(c, (cudaStream_t)st);
         rt3_launch_probe_trace(c, *p, depth, directions, prev_atlas, atlas, (cudaStream_t)st);
+    });
+}
+/* No allocation on this path: no cudaMalloc / cudaFree, no ensure(), no table refresh (a changed scene is an error here, not a rebuild). */
+rt3_status rt3_pass_probe_trace_static(rt3_context* c, const rt3_params* p, const uint32_t* gbuffer, const float* depth, const uint16_t* directions,
+                                       const float* prev_atlas, float* atlas, void* st) {
+    return guarded(c, [&]() {
+        check_params(c, p); require_accel(c);
+        (void)gbuffer;
+        if (!depth || !atlas) RT3_FAIL(c, RT3_ERR_INVALID, "depth/atlas is NULL");
+        if (p->blendfactor < 1.0f && !prev_atlas) RT3_FAIL(c, RT3_ERR_INVALID, "prev_atlas is NULL with blendfactor < 1");
+        if (c->scene_dirty) RT3_FAIL(c, RT3_ERR_STATE, "scene tables changed since the last pass call: call an allocating pass (or rt3_accel_build) first");
+        if (c->prof_on) RT3_FAIL(c, RT3_ERR_STATE, "rt3_profile_enable creates events per launch: disable it for the allocation-free entry point");
+        CallOrder order(c, (cudaStream_t)st);
+        rt3_launch_probe_trace_static(c, *p, depth, directions, prev_atlas, atlas, (cudaStream_t)st);
     });
 }
 rt3_status rt3_pass_probe_sis(rt3_context* c, const rt3_params* p, const uint32_t* gbuffer, uint16_t* directions, void* st) {

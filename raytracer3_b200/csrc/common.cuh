@@ -166,6 +166,9 @@ void rt3_launch_untile(rt3_context* c, const rt3_rect* d_rects, uint32_t n_tiles
                        uint32_t frame_w, uint32_t frame_h, cudaStream_t st);
 void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,
                             cudaStream_t st);
+cudaError_t rt3_static_scratch_setup(int device);
+void rt3_launch_probe_trace_static(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,
+                                   cudaStream_t st);
 void rt3_launch_probe_sis(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, uint16_t* directions, cudaStream_t st);
 void rt3_launch_probe_sh(rt3_context* c, const rt3_params& p, const float* atlas, float* sh, cudaStream_t st);
 void rt3_launch_probe_interpolate(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, const float* depth, const float* sh, float* light,

@@ -22,7 +22,9 @@ using namespace rt3m;
 
 #include "pass_kernels.cuh"
 
+#include <cstdio>
 #include <cstdlib>
+#include <mutex>
 static int env_int_passes(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
 
 void rt3_launch_gbuffer(rt3_context* c, const rt3_params& p, const PixelMap& m, uint32_t* gbuffer, float* depth, uint32_t* ids, float* bary,
@@ -148,6 +150,67 @@ void rt3_launch_probe_trace(rt3_context* c, const rt3_params& p, const float* de
                (float4*)atlas, staged, staged_target, c->d_counters);
     if (directions) RT3_LAUNCH(c, k_probe_resolve, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, aw, ah, staged, staged_target, (float4*)atlas);
 }
+/* ---- rt3_pass_probe_trace_static: the probe-trace pass with NO allocation anywhere on its path ----------------------------------------
+ * (no counterpart in the reference; added for callers that cannot call cudaMalloc: code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  The pass needs scratch per atlas texel — the probe ray (32 B), its hit
+ * (16 B) and, when a direction image is bound, the staged texel value (16 B) and its target (4 B) — plus the persistent traversal kernel's
+ * ray-fetch counter.  Here that scratch is ONE file-scope device array sized for RT3_STATIC_PROBE_MAX_TEXELS texels (a 1920x1088 window:
+ * 960x544 = 522,240): 68 B x 524,288 + 256 B = 34 MiB that every GPU which loads librt3.so holds until the process exits.
+ * In host code `g_static_probe_scratch` is only a stand-in for the symbol, not a device address: its address per device comes from
+ * cudaGetSymbolAddress, asked once per device with that device current (rt3_static_scratch_setup, called from rt3_create), and that
+ * pointer is what the kernels get.  All calls on a device share the array: it keeps the last call's contents, every call overwrites what it
+ * reads (rays, hits, staged values and targets of all n texels) and zeroes the ray-fetch counter itself; two calls that overlap on the GPU
+ * (different streams or contexts without ordering) race. */
+constexpr size_t STATIC_PROBE_N = RT3_STATIC_PROBE_MAX_TEXELS;
+constexpr size_t STATIC_OFF_RAYS = 0;
+constexpr size_t STATIC_OFF_HITS = STATIC_OFF_RAYS + STATIC_PROBE_N * sizeof(rt3_ray);
+constexpr size_t STATIC_OFF_STAGED = STATIC_OFF_HITS + STATIC_PROBE_N * sizeof(rt3_hit);
+constexpr size_t STATIC_OFF_TARGET = STATIC_OFF_STAGED + STATIC_PROBE_N * sizeof(float4);
+constexpr size_t STATIC_OFF_WORK = STATIC_OFF_TARGET + STATIC_PROBE_N * sizeof(uint32_t);
+constexpr size_t STATIC_BYTES = STATIC_OFF_WORK + 256;
+static __device__ __align__(256) unsigned char g_static_probe_scratch[STATIC_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static unsigned char* g_static_probe_ptr[STATIC_MAX_DEVICES];         /* device address of the array on each device, 0 = not asked yet */
+static std::mutex g_static_probe_mutex;
+
+/* Once per device, with that device current (the caller, rt3_create, has set it).  Returns cudaSuccess or the error of the query. */
+cudaError_t rt3_static_scratch_setup(int device) {
+    if (device < 0 || device >= STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_probe_mutex);
+    if (g_static_probe_ptr[device]) return cudaSuccess;
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_probe_scratch);
+    if (e != cudaSuccess) return e;
+    g_static_probe_ptr[device] = (unsigned char*)ptr;
+    return cudaSuccess;
+}
+
+void rt3_launch_probe_trace_static(rt3_context* c, const rt3_params& p, const float* depth, const uint16_t* directions, const float* prev_atlas, float* atlas,
+                                   cudaStream_t st) {
+    const uint32_t aw = probe_count_x(p) * 8u, ah = probe_count_y(p) * 8u;
+    const size_t n = (size_t)aw * ah;
+    if (n > STATIC_PROBE_N) {
+        char msg[200];
+        snprintf(msg, sizeof(msg), "probe atlas %u x %u = %zu texels exceeds the static scratch of RT3_STATIC_PROBE_MAX_TEXELS = %zu (use rt3_pass_probe_trace)",
+                 aw, ah, n, STATIC_PROBE_N);
+        RT3_FAIL(c, RT3_ERR_INVALID, msg);
+    }
+    unsigned char* base = (c->device >= 0 && c->device < STATIC_MAX_DEVICES) ? g_static_probe_ptr[c->device] : nullptr;
+    if (!base) RT3_FAIL(c, RT3_ERR_STATE, "static scratch address unknown on this device (cudaGetSymbolAddress failed at rt3_create)");
+    if (!n) return;
+    rt3_ray* rays = (rt3_ray*)(base + STATIC_OFF_RAYS);
+    rt3_hit* hits = (rt3_hit*)(base + STATIC_OFF_HITS);
+    float4* staged = directions ? (float4*)(base + STATIC_OFF_STAGED) : nullptr;
+    uint32_t* staged_target = directions ? (uint32_t*)(base + STATIC_OFF_TARGET) : nullptr;
+    unsigned long long* work = (unsigned long long*)(base + STATIC_OFF_WORK);      /* zeroed by the traversal launcher (cudaMemsetAsync) */
+    RT3_LAUNCH(c, k_probe_raygen, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, p, aw, ah, depth, directions, rays);
+    rt3_launch_trace_closest(c, rays, nullptr, n, hits, work, st);
+    RT3_LAUNCH(c, k_probe_texel, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, c->view, p, aw, ah, depth, directions, rays, hits, (const float4*)prev_atlas,
+               (float4*)atlas, staged, staged_target, c->d_counters);
+    if (directions) RT3_LAUNCH(c, k_probe_resolve, div_up(n, PASS_THREADS), PASS_THREADS, 0, st, aw, ah, staged, staged_target, (float4*)atlas);
+}
+
 void rt3_launch_probe_sis(rt3_context* c, const rt3_params& p, const uint32_t* gbuffer, uint16_t* directions, cudaStream_t st) {
     const uint32_t probes = probe_count_x(p) * probe_count_y(p);
     if (!probes) return;
