@@ -117,8 +117,8 @@ typedef struct { float t, u, v; uint32_t prim; } rt3_hit;           /* 16 B; pri
 /* Quality levels of the binary tree under the 8-wide collapse (hits are bit-identical in all of them):
  *   RT3_BUILD_FAST_TRACE (default, also flags == 0; the reference's PREFER_FAST_TRACE, raytracing.rs:121): treelet restructuring (Karras &
  *     Aila 2013: the best topology of every 7-subtree treelet by dynamic programming, two bottom-up passes) and the children of each wide
- *     node chosen by the SAH dynamic programme of Ylitie et al. 2017.  Measured on B200, 263 k triangles: 10.3 ms build.  Trees of more than
- *     4 M records (a flattened 16.8 M-triangle scene would take 379 ms) get the rotations below instead, unless RT3_BUILD_TREELET is set.
+ *     node chosen by the SAH dynamic programme of Ylitie et al. 2017.  Measured on B200, 263 k triangles: 4.9 ms build.  Trees of more than
+ *     4 M records (a flattened 16.8 M-triangle scene would take 146 ms) get the rotations below instead, unless RT3_BUILD_TREELET is set.
  *   RT3_BUILD_ROTATIONS: three bottom-up passes of SAH tree rotations instead of the treelets (1.9 ms build, traversal 4 % slower).
  *   RT3_BUILD_FAST_BUILD: plain LBVH, children chosen greedily by surface area (1.4 ms build, traversal 11 % slower).
  * RT3_BUILD_TREELET: treelet restructuring whatever the size. */

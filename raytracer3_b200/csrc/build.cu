@@ -293,26 +293,142 @@ __global__ void __launch_bounds__(256) k_refit(const Tri48* tris_sorted, uint32_
     }
 }
 
-/* RT3_BUILD_TREELET: the same walk with treelet_visit (bvh_logic.h) in place of the rotations */
-template <bool WITH_DP>
-__global__ void __launch_bounds__(128) k_refit_treelet(const Tri48* tris_sorted, uint32_t n, int kind, float pad, Bvh2Node* nodes, const uint32_t* parent,
-                                                       uint32_t* flags, uint32_t* counts, DpNode* dp, int first_pass) {
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    DevMem mem{nodes, counts, dp, n};
-    if (first_pass) {
-        Bvh2Node leaf;
-        tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi, kind);
-        leaf.left = leaf.right = 0;
-        mem.store_node(n - 1 + k, leaf);
+/* ---- treelet restructuring, one WARP per treelet --------------------------------------------------------------------------------------
+ * The bottom-up walk is serialised by the depth of the tree: near the root a single thread owns the only node that is ready, and with one
+ * thread per treelet (round 2's first version) it ground through the 17 k-instruction dynamic programme of bvh_logic.h alone — 8.9 of the
+ * 10.3 ms of a 263 k-triangle build, whatever number of treelets a leaf-count threshold removed (measured: profiles/r2q_*).  Here the lanes
+ * of a warp walk up in lock step; a lane that owns a small subtree visits it alone (all such lanes at once), and the treelets of the other
+ * owners are taken one after the other by the WHOLE warp:
+ *   formation and application (treelet_visit_t) run on all 32 lanes with the same arguments — same loads, broadcast — and only the owner
+ *   lane stores (CoopMem), so nothing has to be handed from lane to lane;
+ *   the 127 subset areas and the programme over the subsets (CoopTreeletDp) are spread over the lanes through 1.25 KB of shared memory per
+ *   warp: subsets of 2 .. 5 leaves one subset per lane (the serial loop, so ties fall as in the definition), subsets of 6 and 7 leaves one
+ *   PARTITION per lane followed by a warp reduction on (cost, position in the serial enumeration) — the serial solver's first-minimum rule.
+ * The result is the tree of the serial definition, bit for bit (GPU test against the CPU emulation: node count and visit statistics). */
+struct CoopMem {
+    DevMem m; bool writer;
+    __device__ uint32_t slot(uint32_t ref) const { return m.slot(ref); }
+    __device__ Bvh2Node node(uint32_t i) const { return m.node(i); }
+    __device__ uint32_t count(uint32_t ref) const { return m.count(ref); }
+    __device__ void dp_costs(uint32_t ref, float out[7]) const { m.dp_costs(ref, out); }
+    __device__ void store_node(uint32_t i, const Bvh2Node& v) { if (writer) m.store_node(i, v); }
+    __device__ void store_count(uint32_t i, uint32_t c) { if (writer) m.store_count(i, c); }
+    __device__ void store_dp(uint32_t i, const DpNode& d) { if (writer) m.store_dp(i, d); }
+};
+
+struct CoopTreeletDp {
+    float* area; float* copt; uint16_t* part;          /* this warp's tables in shared memory, 1 << RT3_TREELET_LEAVES entries each */
+    uint32_t lane;
+    /* the i-th proper submask of `rest` in the serial enumeration (rest-1)&rest, ((rest-1)&rest - 1)&rest, ..., 0: decreasing numeric
+     * order, i.e. the submask of rank 2^m - 2 - i, its bits deposited at the places of rest's bits */
+    static __device__ __forceinline__ uint32_t submask_at(uint32_t rest, uint32_t i) {
+        uint32_t r = (1u << __popc(rest)) - 2u - i, sub = 0u, m = rest;
+        while (m) { const uint32_t low = m & (0u - m); if (r & 1u) sub |= low; r >>= 1; m ^= low; }
+        return sub;
     }
-    uint32_t cur = parent[n - 1 + k];
-    while (cur != 0xFFFFFFFFu) {
-        __threadfence();
-        if (atomicAdd(flags + cur, 1u) == 0u) return;
-        __threadfence();
-        treelet_visit(mem, n, cur, WITH_DP);
-        cur = parent[cur];
+    __device__ void solve(const Bvh2Node* leaf_box, int nl) {
+        const uint32_t full = (1u << nl) - 1u;
+        for (uint32_t sset = lane; sset <= full; sset += 32u) {                      /* areas: min / max are exact, any order of the unions */
+            if (!sset) continue;
+            float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+#pragma unroll
+            for (int k = 0; k < RT3_TREELET_LEAVES; ++k)
+                if (sset & (1u << k))
+                    for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(lo[q], leaf_box[k].lo[q]); hi[q] = rt3m::max_(hi[q], leaf_box[k].hi[q]); }
+            area[sset] = box_area(lo, hi);
+            copt[sset] = 0.0f; part[sset] = 0;
+        }
+        __syncwarp();
+        for (int k = 2; k <= nl; ++k) {                                              /* subsets of k leaves need only smaller subsets: one round per size */
+            if (k <= 5) {
+                for (uint32_t sset = lane; sset <= full; sset += 32u) {
+                    if (__popc(sset) != k) continue;
+                    float bc = 3.4e38f; uint32_t bp = 0;
+                    const uint32_t low = sset & (0u - sset), rest = sset ^ low;
+                    for (uint32_t sub = (rest - 1u) & rest;; sub = (sub - 1u) & rest) {
+                        const uint32_t pp = low | sub;
+                        const float c = copt[pp] + copt[sset ^ pp];
+                        if (c < bc) { bc = c; bp = pp; }
+                        if (sub == 0u) break;
+                    }
+                    copt[sset] = (sset == full ? 0.0f : area[sset]) + bc;
+                    part[sset] = (uint16_t)bp;
+                }
+            } else {
+                for (uint32_t sset = 3u; sset <= full; ++sset) {                     /* warp-uniform scan: at most 7 + 1 subsets of 6 / 7 leaves */
+                    if (__popc(sset) != k) continue;
+                    const uint32_t low = sset & (0u - sset), rest = sset ^ low;
+                    const uint32_t count = (1u << (k - 1)) - 1u;                     /* proper submasks of rest, the empty one included */
+                    float bc = 3.4e38f; uint32_t bi = 0xFFFFFFFFu, bp = 0;
+                    for (uint32_t i = lane; i < count; i += 32u) {
+                        const uint32_t pp = low | submask_at(rest, i);
+                        const float c = copt[pp] + copt[sset ^ pp];
+                        if (c < bc) { bc = c; bi = i; bp = pp; }                     /* i increases: the first minimum of this lane's share */
+                    }
+#pragma unroll
+                    for (int off = 16; off; off >>= 1) {
+                        const float c2 = __shfl_xor_sync(0xFFFFFFFFu, bc, off);
+                        const uint32_t i2 = __shfl_xor_sync(0xFFFFFFFFu, bi, off), p2 = __shfl_xor_sync(0xFFFFFFFFu, bp, off);
+                        if (c2 < bc || (c2 == bc && i2 < bi)) { bc = c2; bi = i2; bp = p2; }
+                    }
+                    if (lane == 0u) {
+                        copt[sset] = (sset == full ? 0.0f : area[sset]) + bc;
+                        part[sset] = (uint16_t)(bi == 0xFFFFFFFFu ? 0u : bp);        /* no cost below 3.4e38: the serial loop leaves 0 */
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    __device__ float cost_of(uint32_t sset) const { return copt[sset]; }
+    __device__ uint32_t part_of(uint32_t sset) const { return part[sset]; }
+};
+
+constexpr int TREELET_THREADS = 128;
+template <bool WITH_DP>
+__global__ void __launch_bounds__(TREELET_THREADS) k_refit_treelet(const Tri48* tris_sorted, uint32_t n, int kind, float pad, Bvh2Node* nodes, const uint32_t* parent,
+                                                                   uint32_t* flags, uint32_t* counts, DpNode* dp, int first_pass) {
+    __shared__ float s_area[TREELET_THREADS / 32][1 << RT3_TREELET_LEAVES], s_copt[TREELET_THREADS / 32][1 << RT3_TREELET_LEAVES];
+    __shared__ uint16_t s_part[TREELET_THREADS / 32][1 << RT3_TREELET_LEAVES];
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t NONE = 0xFFFFFFFFu;
+    DevMem mem{nodes, counts, dp, n};
+    uint32_t cur = NONE;                                       /* the node this lane is arriving at; lanes past the last leaf only help */
+    if (k < n) {
+        if (first_pass) {
+            Bvh2Node leaf;
+            tri_bounds(tris_sorted[k], pad, leaf.lo, leaf.hi, kind);
+            leaf.left = leaf.right = 0;
+            mem.store_node(n - 1 + k, leaf);
+        }
+        cur = parent[n - 1 + k];
+    }
+    CoopTreeletDp cdp{s_area[wid], s_copt[wid], s_part[wid], lane};
+    for (;;) {
+        if (cur != NONE) {                                     /* one atomic flag per node: the second arrival owns two finished subtrees */
+            __threadfence();
+            if (atomicAdd(flags + cur, 1u) == 0u) cur = NONE;
+            else __threadfence();
+        }
+        __syncwarp();
+        if (__ballot_sync(0xFFFFFFFFu, cur != NONE) == 0u) break;
+        bool small = false;
+        if (cur != NONE && RT3_TREELET_MIN_LEAVES > 0) {
+            const Bvh2Node p0 = mem.node(cur);
+            small = mem.count(p0.left) + mem.count(p0.right) < (uint32_t)RT3_TREELET_MIN_LEAVES;
+            if (small) refit_visit(mem, n, cur, RT3_TREELET_SMALL_ROTATE != 0, WITH_DP);    /* these lanes all at once, each its own node */
+        }
+        __syncwarp();
+        uint32_t big = __ballot_sync(0xFFFFFFFFu, cur != NONE && !small);
+        while (big) {                                          /* the others one after the other, by the whole warp */
+            const int src = __ffs(big) - 1;
+            big &= big - 1u;
+            const uint32_t c = __shfl_sync(0xFFFFFFFFu, cur, src);
+            CoopMem cm{mem, lane == (uint32_t)src};
+            treelet_visit_t(cm, n, c, WITH_DP, cdp);
+            __syncwarp();
+        }
+        if (cur != NONE) cur = parent[cur];                    /* the root's parent is 0xFFFFFFFF */
     }
 }
 
@@ -454,8 +570,8 @@ static void build_wide(rt3_context* c, cudaStream_t st, WideBuild& io, rt3_build
                 if (n > 1) RT3_LAUNCH(c, k_parents, div_up(n - 1, 256), 256, 0, st, nodes2, n, parent);
             }
             if (treelet) {
-                if (pass < passes - 1) RT3_LAUNCH(c, (k_refit_treelet<false>), div_up(n, 128), 128, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
-                else RT3_LAUNCH(c, (k_refit_treelet<true>), div_up(n, 128), 128, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
+                if (pass < passes - 1) RT3_LAUNCH(c, (k_refit_treelet<false>), div_up(n, TREELET_THREADS), TREELET_THREADS, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
+                else RT3_LAUNCH(c, (k_refit_treelet<true>), div_up(n, TREELET_THREADS), TREELET_THREADS, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
             } else if (!io.optimal_collapse) RT3_LAUNCH(c, (k_refit<false, false>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, 1);
             else if (pass < passes - 1) RT3_LAUNCH(c, (k_refit<true, false>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);
             else RT3_LAUNCH(c, (k_refit<true, true>), div_up(n, 256), 256, 0, st, sorted, n, io.kind, io.pad, nodes2, parent, nflags, counts, dp, pass == 0);

@@ -356,11 +356,80 @@ RT3_HD void refit_visit(Mem& mem, uint32_t n, uint32_t cur, bool rotate, bool wi
 #ifndef RT3_TREELET_LEAVES
 #define RT3_TREELET_LEAVES 7      /* 5 / 7 / 9 leaves: 8.82 / 8.53 / 8.54 work units per incoherent ray on the bench scene (rotations: 9.12) */
 #endif
+#ifndef RT3_TREELET_AUTO_MAX
 #define RT3_TREELET_AUTO_MAX (1u << 22)   /* FAST_TRACE restructures treelets in trees of up to 4 M records by default (build.cu) */
+#endif
 #define RT3_TREELET_PASSES 2       /* 1 / 2 / 3 / 5 passes: 8.92 / 8.55 / 8.53 / 8.52 */
-template <class Mem>
-RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
+/* Subtrees of fewer than RT3_TREELET_MIN_LEAVES triangles are not restructured on their own (Karras & Aila 2013 section 3.4, gamma): they are
+ * covered by the treelets of their ancestors, and most internal nodes of a binary tree are that small, so the threshold removes most of the
+ * dynamic-programming runs.  Such nodes get the cheap visit (RT3_TREELET_SMALL_ROTATE: with the tree rotations, else bounds only). */
+#ifndef RT3_TREELET_MIN_LEAVES
+#define RT3_TREELET_MIN_LEAVES 7      /* 0 / 7 / 16 / 32: 8.558 / 8.558 / 8.602 / 8.646 work units per incoherent ray on the bench scene */
+#endif
+#ifndef RT3_TREELET_SMALL_ROTATE
+#define RT3_TREELET_SMALL_ROTATE 1
+#endif
+/* The dynamic programme over the subsets of a treelet's leaves, serial form (the DEFINITION: the CPU emulation runs it, and the device's
+ * warp-cooperative solver in build.cu must return the same copt / part tables, ties included).  copt[S] = least summed area of the internal
+ * nodes of a binary tree over the leaves in S (the treelet root's own area excluded), part[S] = the child set of that tree's root which
+ * holds S's lowest member. */
+struct SerialTreeletDp {
+    float area[1 << RT3_TREELET_LEAVES], copt[1 << RT3_TREELET_LEAVES];
+    uint16_t part[1 << RT3_TREELET_LEAVES];
+    RT3_HD void solve(const Bvh2Node* leaf_box, int nl) {
+        const int K = RT3_TREELET_LEAVES;
+        const uint32_t full = (1u << nl) - 1u;
+        /* box of a subset = union of the boxes of its members in the low three and in the remaining places: 8 + 2^(K-3) partial unions,
+         * then one union per subset (min / max are exact, so the order of the unions does not matter) */
+        {
+            const int KH = K > 3 ? K - 3 : 0;
+            float plo[8][3], phi[8][3], qlo[1 << KH][3], qhi[1 << KH][3];
+            for (int g = 0; g < 2; ++g) {
+                const int first = g ? 3 : 0, cnt = g ? KH : 3;
+                for (uint32_t sub = 0; sub < (1u << cnt); ++sub) {
+                    float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+                    for (int k = 0; k < cnt; ++k)
+                        if ((sub & (1u << k)) && first + k < nl)
+                            for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(lo[q], leaf_box[first + k].lo[q]); hi[q] = rt3m::max_(hi[q], leaf_box[first + k].hi[q]); }
+                    for (int q = 0; q < 3; ++q) { if (g) { qlo[sub][q] = lo[q]; qhi[sub][q] = hi[q]; } else { plo[sub][q] = lo[q]; phi[sub][q] = hi[q]; } }
+                }
+            }
+            for (uint32_t sset = 1; sset <= full; ++sset) {
+                float lo[3], hi[3];
+                for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(plo[sset & 7u][q], qlo[sset >> 3][q]); hi[q] = rt3m::max_(phi[sset & 7u][q], qhi[sset >> 3][q]); }
+                area[sset] = box_area(lo, hi);
+                copt[sset] = 0.0f; part[sset] = 0;
+            }
+        }
+        /* subsets in increasing numeric order: every proper subset of S is smaller than S, so its copt is final when S is reached */
+        for (uint32_t sset = 3; sset <= full; ++sset) {
+            if ((sset & (sset - 1u)) == 0u) continue;                                  /* singleton */
+            float bc = 3.4e38f; uint32_t bp = 0;
+            const uint32_t low = sset & (0u - sset);                                    /* the partition holding the lowest member is P: halves the search */
+            const uint32_t rest = sset ^ low;
+            for (uint32_t sub = (rest - 1u) & rest;; sub = (sub - 1u) & rest) {        /* P = low | sub for every proper subset sub of rest (incl. empty) */
+                const uint32_t pp = low | sub;
+                const float c = copt[pp] + copt[sset ^ pp];
+                if (c < bc) { bc = c; bp = pp; }
+                if (sub == 0u) break;
+            }
+            copt[sset] = (sset == full ? 0.0f : area[sset]) + bc;                       /* the root's own area is the same for every topology */
+            part[sset] = (uint16_t)bp;
+        }
+    }
+    RT3_HD float cost_of(uint32_t sset) const { return copt[sset]; }
+    RT3_HD uint32_t part_of(uint32_t sset) const { return part[sset]; }
+};
+
+/* Dp: SerialTreeletDp, or the device's warp-cooperative solver (then every lane of the warp runs this function with the same arguments and
+ * only the treelet's owner lane stores: Mem's store_* are predicated, build.cu). */
+template <class Mem, class Dp>
+RT3_HD void treelet_visit_t(Mem& mem, uint32_t n, uint32_t cur, bool with_dp, Dp& dp) {
     const int K = RT3_TREELET_LEAVES;
+    if (RT3_TREELET_MIN_LEAVES > 0) {
+        const Bvh2Node P0 = mem.node(cur);
+        if (mem.count(P0.left) + mem.count(P0.right) < (uint32_t)RT3_TREELET_MIN_LEAVES) { refit_visit(mem, n, cur, RT3_TREELET_SMALL_ROTATE != 0, with_dp); return; }
+    }
     uint32_t leaf_ref[K], inner_id[K];
     Bvh2Node leaf_box[K];
     float leaf_area[K];
@@ -385,46 +454,8 @@ RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
         nl++;
     }
     const uint32_t full = (1u << nl) - 1u;
-    float area[1 << K], copt[1 << K];
-    uint16_t part[1 << K];
-    /* box of a subset = union of the boxes of its members in the low three and in the remaining places: 8 + 2^(K-3) partial unions,
-     * then one union per subset (min / max are exact, so the order of the unions does not matter) */
-    {
-        const int KH = K > 3 ? K - 3 : 0;
-        float plo[8][3], phi[8][3], qlo[1 << KH][3], qhi[1 << KH][3];
-        for (int g = 0; g < 2; ++g) {
-            const int first = g ? 3 : 0, cnt = g ? KH : 3;
-            for (uint32_t sub = 0; sub < (1u << cnt); ++sub) {
-                float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
-                for (int k = 0; k < cnt; ++k)
-                    if ((sub & (1u << k)) && first + k < nl)
-                        for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(lo[q], leaf_box[first + k].lo[q]); hi[q] = rt3m::max_(hi[q], leaf_box[first + k].hi[q]); }
-                for (int q = 0; q < 3; ++q) { if (g) { qlo[sub][q] = lo[q]; qhi[sub][q] = hi[q]; } else { plo[sub][q] = lo[q]; phi[sub][q] = hi[q]; } }
-            }
-        }
-        for (uint32_t sset = 1; sset <= full; ++sset) {
-            float lo[3], hi[3];
-            for (int q = 0; q < 3; ++q) { lo[q] = rt3m::min_(plo[sset & 7u][q], qlo[sset >> 3][q]); hi[q] = rt3m::max_(phi[sset & 7u][q], qhi[sset >> 3][q]); }
-            area[sset] = box_area(lo, hi);
-            copt[sset] = 0.0f; part[sset] = 0;
-        }
-    }
-    /* subsets in increasing numeric order: every proper subset of S is smaller than S, so its copt is final when S is reached */
-    for (uint32_t sset = 3; sset <= full; ++sset) {
-        if ((sset & (sset - 1u)) == 0u) continue;                                  /* singleton */
-        float bc = 3.4e38f; uint32_t bp = 0;
-        const uint32_t low = sset & (0u - sset);                                    /* the partition holding the lowest member is P: halves the search */
-        const uint32_t rest = sset ^ low;
-        for (uint32_t sub = (rest - 1u) & rest;; sub = (sub - 1u) & rest) {        /* P = low | sub for every proper subset sub of rest (incl. empty) */
-            const uint32_t pp = low | sub;
-            const float c = copt[pp] + copt[sset ^ pp];
-            if (c < bc) { bc = c; bp = pp; }
-            if (sub == 0u) break;
-        }
-        copt[sset] = (sset == full ? 0.0f : area[sset]) + bc;                       /* the root's own area is the same for every topology */
-        part[sset] = (uint16_t)bp;
-    }
-    const bool restructure = nl > 2 && copt[full] < found_cost * 0.99999f;
+    dp.solve(leaf_box, nl);
+    const bool restructure = nl > 2 && dp.cost_of(full) < found_cost * 0.99999f;
     /* the topology to write: node list in pre-order (set, id), children resolved after; written in reverse (children first) */
     uint32_t t_set[K], t_id[K]; int t_n = 0;
     uint16_t t_l[K], t_r[K];                                                        /* child sets */
@@ -439,7 +470,7 @@ RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
             t_set[me] = sset;
             if (me > 0) t_id[me] = inner_id[next_inner++];
             idx_of_set[sset] = (uint8_t)me;
-            const uint32_t pl = part[sset], pr = sset ^ pl;
+            const uint32_t pl = dp.part_of(sset), pr = sset ^ pl;
             t_l[me] = (uint16_t)pl; t_r[me] = (uint16_t)pr;
             if (pr & (pr - 1u)) st[sp++] = pr;
             if (pl & (pl - 1u)) st[sp++] = pl;
@@ -476,6 +507,11 @@ RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
     } else {
         refit_visit(mem, n, cur, false, with_dp);                                   /* topology kept: bounds, count and programme row of cur */
     }
+}
+template <class Mem>
+RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
+    SerialTreeletDp dp;
+    treelet_visit_t(mem, n, cur, with_dp, dp);
 }
 
 /*

@@ -258,7 +258,15 @@ def test_treelet_build_gives_identical_hits_and_the_emulators_tree(gpu_ctx):
             assert EmuBvh(nodes=nodes, tri_records=tris).check_triangles() == 0
     for name in ("treelet", "treelet_explicit", "treelet2"):
         assert (res[name][1] == res["rot"][1]).all() and (res[name][2] == res["rot"][2]).all(), name
-    assert res["treelet"][0] == res["treelet_explicit"][0] == EmuBvh(tris=T, treelet_passes=2).info()["nodes"]   # the device build is the emulator's build
+    emu = EmuBvh(tris=T, treelet_passes=2)
+    assert res["treelet"][0] == res["treelet_explicit"][0] == emu.info()["nodes"]                                # the device build is the emulator's build
+    # ... down to the visit statistics: the device restructures treelets with a warp-cooperative solver (build.cu CoopTreeletDp) that must
+    # return the tables of the serial definition the emulator runs, ties included; one different choice anywhere changes these averages
+    sub = np.ascontiguousarray(np.concatenate([closest, scenes.random_rays(sc, 20000, seed=10)])[:30000])
+    w.create_acceleration_structure(BUILD_FAST_TRACE)
+    st_gpu = w.trace_stats(torch.from_numpy(sub.view(np.float32).reshape(-1, 8)).cuda())
+    _, st_emu = emu.trace_closest(sub)
+    assert abs(st_gpu.nodes_per_ray - st_emu[0]) <= 1e-9 * st_emu[0] and abs(st_gpu.tris_per_ray - st_emu[1]) <= 1e-9 * st_emu[1], (st_gpu.nodes_per_ray, st_emu)
     assert res["rot"][0] == EmuBvh(tris=T).info()["nodes"]
     assert res["treelet"][3] < res["rot"][3]                               # fewer node visits + 0.4 x triangle tests per ray
     assert (res["rot"][1][:, 3] != MISS).mean() > 0.5
