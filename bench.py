@@ -492,13 +492,19 @@ def run_multi(args, S):
     rank, N, local_rank = S["rank"], S["world_size"], S["local_rank"]
     dev = f"cuda:{local_rank}"
     flags = FLAG_ENV | FLAG_BLUENOISE
-    W, H = CFG3_W, CFG3_H
+    # --workload cfg5 = BASELINE configs[4] as written: the 8x8 instanced grid, ONE 1920x1080 frame of 4 bounces, 1 spp per step, its tiles
+    # sharded over the N GPUs (strong scaling of a small frame), one delivery per frame
+    cfg5 = args.workload == "cfg5"
+    W, H = (1920, 1080) if cfg5 else (CFG3_W, CFG3_H)
     R = TiledRenderer(ctx, world, W, H, rank, N, tile=args.tile)
     mode = R.setup_exchange(args.exchange, slots=2)
-    p3 = cfg3_params(sc, flags)
+    p3 = None if cfg5 else cfg3_params(sc, flags)
+
+    def frames_of(k):
+        return [params_for(sc, W, H, k, flags)] if cfg5 else p3
 
     def step(k):
-        return cfg3_step(R, p3, k % 2)
+        return cfg3_step(R, frames_of(k), k % 2)
 
     for k in range(args.warmup):
         step(k)
@@ -560,39 +566,43 @@ def run_multi(args, S):
     # ---- weak scaling (round 1's --gpus N workload), kept as an extra key: N x 1080p pixels, 1 spp, one delivery per frame overlapped with
     # the next frame's tracing
     Ww, Hw = frame_dims(N)
-    Rw = TiledRenderer(ctx, world, Ww, Hw, rank, N, tile=args.tile)
-    Rw.setup_exchange(mode, slots=2)
-    wsteps = max(3, min(args.steps * 4, 40))
-    wparams = [params_for(sc, Ww, Hw, i, flags) for i in range(wsteps + 3)]
-
-    def wstep(k):
-        Rw.frame_exchange_overlapped(wparams[k % len(wparams)], k % 2)
-    for k in range(3):
-        wstep(k)
-    Rw.drain()
-    barrier()
-    ctx.counters(reset=True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    for k in range(wsteps):
-        wstep(k)
-    Rw.drain()
-    e1.record()
-    barrier()
-    wms = e0.elapsed_time(e1)
-    wcnt = ctx.counters(reset=True)
+    wsteps, wms, wcnt = 1, 1.0, ctx.counters(reset=True)
+    if not cfg5:
+        Rw = TiledRenderer(ctx, world, Ww, Hw, rank, N, tile=args.tile)
+        Rw.setup_exchange(mode, slots=2)
+        wsteps = max(3, min(args.steps * 4, 40))
+        wparams = [params_for(sc, Ww, Hw, i, flags) for i in range(wsteps + 3)]
+
+        def wstep(k):
+            Rw.frame_exchange_overlapped(wparams[k % len(wparams)], k % 2)
+        for k in range(3):
+            wstep(k)
+        Rw.drain()
+        barrier()
+        ctx.counters(reset=True)
+        barrier()
+        e0.record()
+        for k in range(wsteps):
+            wstep(k)
+        Rw.drain()
+        e1.record()
+        barrier()
+        wms = e0.elapsed_time(e1)
+        wcnt = ctx.counters(reset=True)
 
     # ---- the same 64 samples per pixel inside ONE frame call (samples = 64): one G-buffer pass + one wavefront with ray regeneration per image
     pin = inframe_params(sc, flags)
-    isteps = max(2, min(args.steps, 5))
-    inframe_step(R, pin, 0)
-    barrier()
-    ctx.counters(reset=True)
-    ims = measure_steps(lambda k: inframe_step(R, pin, k % 2), isteps, barrier, torch)
-    icnt = ctx.counters(reset=True)
-    iband = inframe_step(R, pin, 0).clone()
-    ctx.counters(reset=True)
+    isteps, ims, icnt, iband = 1, 1.0, ctx.counters(reset=True), None
+    if not cfg5:
+        isteps = max(2, min(args.steps, 5))
+        inframe_step(R, pin, 0)
+        barrier()
+        ctx.counters(reset=True)
+        ims = measure_steps(lambda k: inframe_step(R, pin, k % 2), isteps, barrier, torch)
+        icnt = ctx.counters(reset=True)
+        iband = inframe_step(R, pin, 0).clone()
+        ctx.counters(reset=True)
 
     # ---- verification, outside every timed region: rank 0 renders the whole 64-sample image ALONE, un-tiled, and compares it bit for bit
     # with the image the ranks assembled in host memory; the same run is the single-GPU point of the strong-scaling curve
@@ -602,18 +612,19 @@ def run_multi(args, S):
         torch.cuda.synchronize()
         e0.record()
         alone = None
-        for p in p3:
+        for p in frames_of(e2e_steps - 1):
             alone = r1.frame(p)
         e1.record()
         torch.cuda.synchronize()
         single_ms = e0.elapsed_time(e1)
         c1 = ctx.counters(reset=True)
         verified = bool(torch.equal(shared[last_slot].view(torch.int32), alone.cpu().view(torch.int32)))
-        alone_in = r1.frame(pin)
-        inframe_verified = bool(torch.equal(iband.view(torch.int32), alone_in[R.row0:R.row1].view(torch.int32)))
+        if iband is not None:
+            alone_in = r1.frame(pin)
+            inframe_verified = bool(torch.equal(iband.view(torch.int32), alone_in[R.row0:R.row1].view(torch.int32)))
         ctx.counters(reset=True)
         single = {"value": (c1.rays_primary + c1.rays_secondary) / (single_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": single_ms,
-                  "note": "the same 64-sample image rendered by rank 0 alone (full-frame passes, first run: includes its allocations) while the other ranks wait"}
+                  "note": "the same step rendered by rank 0 alone (full-frame passes, first run: includes its allocations) while the other ranks wait"}
     barrier()
     torch.cuda.cudart().cudaHostUnregister(shared.data_ptr())
     barrier()
@@ -631,9 +642,12 @@ def run_multi(args, S):
         ms, e2e_s, wms = float(mx[0]), float(mx[3]), float(mx[9])
         rays, paths, e2e_rays, launches_all, wrays = float(sm[1]), float(sm[2]), float(sm[4]), float(sm[5]), float(sm[10])
         cfg = scene_config(S, args)
-        cfg.update({"workload": f"{S['base_name']} {W}x{H} path tracing, bounces={BOUNCES}, {CFG3_SPP} spp progressive accumulation (64 frames x 1 spp, "
-                                f"blendfactor 1/(n+1)), env light + blue noise, {args.tile}x{args.tile} screen tiles sharded over {N} GPUs, one delivery of "
-                                "the finished tiles per image (BASELINE configs[2])",
+        cfg.update({"workload": (f"8x8 instanced {S['base_name']} (" + ("two-level BLAS/TLAS" if args.two_level else "flattened") + f") {W}x{H} path tracing, "
+                                 f"bounces={BOUNCES}, 1 spp, env light + blue noise, one frame per step, its {args.tile}x{args.tile} screen tiles sharded over "
+                                 f"{N} GPUs, one delivery per frame (BASELINE configs[4])") if cfg5 else
+                                (f"{S['base_name']} {W}x{H} path tracing, bounces={BOUNCES}, {CFG3_SPP} spp progressive accumulation (64 frames x 1 spp, "
+                                 f"blendfactor 1/(n+1)), env light + blue noise, {args.tile}x{args.tile} screen tiles sharded over {N} GPUs, one delivery of "
+                                 "the finished tiles per image (BASELINE configs[2])"),
                     "parallelism": f"tiles{N}", "tile": args.tile, "delivery": mode, "delivery_note": R.exchange_note,
                     "tiles_per_rank": int(R.n_real), "rays_max_over_mean": float(mx[1]) / (float(sm[1]) / N),
                     "l2_policy": "per-frame buffers of a rank (slabs, queues) exceed the 126 MB L2 between steps at N <= 4; scene + BVH L2-resident by design"})
@@ -641,19 +655,19 @@ def run_multi(args, S):
             "metric": "Mrays/s", "value": rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "spp_per_s": paths / (ms * 1e-3), "rays_per_step": rays / args.steps, "config": cfg, "clocks": clocks.summary(),
-            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 304 * CFG3_SPP * N, "d2h_bytes_per_step": W * H * 16,
+            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 304 * (1 if cfg5 else CFG3_SPP) * N, "d2h_bytes_per_step": W * H * 16,
                     "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
-                    "path": "rt3_pass_*_tiles x 64 frames + one delivery (" + mode + ") per image; every rank reads its band of rows back into one page-locked "
+                    "path": "rt3_pass_*_tiles x " + ("1 frame" if cfg5 else "64 frames") + " + one delivery (" + mode + ") per image; every rank reads its band of rows back into one page-locked "
                             "host frame shared by the ranks (POSIX shm); every image in host memory before the clock stops",
                     "host_frame_verified": verified, "host_numa_node_rank0": S["numa_node"]},
             "gpu_launches": int(launches_all),
             "gathered_equals_single_gpu_image": verified,
             "single_gpu_same_workload": single,
-            "inframe_64spp": {"value": float(sm[12]) / (float(mx[11]) * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": float(mx[11]) / isteps, "steps": isteps,
+            "inframe_64spp": None if cfg5 else {"value": float(sm[12]) / (float(mx[11]) * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": float(mx[11]) / isteps, "steps": isteps,
                               "spp_per_s": float(sm[13]) / (float(mx[11]) * 1e-3), "band_equals_single_gpu_image": inframe_verified,
                               "workload": "the same 64 samples per pixel in ONE frame call per image (samples = 64): one G-buffer pass, one wavefront with ray "
                                           "regeneration per rank, one delivery"},
-            "weak": {"value": wrays / (wms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": wms / wsteps, "steps": wsteps,
+            "weak": None if cfg5 else {"value": wrays / (wms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": wms / wsteps, "steps": wsteps,
                      "workload": f"{Ww}x{Hw} (N x 1920x1080 pixels), 1 spp, one delivery per frame overlapped with the next frame (round 1's --gpus N workload)"},
         }
         line.update(roofline_objects(float(stats[6]), float(stats[7]), float(stats[8]), ms / args.steps, 1, line["clocks"]))
