@@ -10,18 +10,22 @@
  *       orc_pass_postprocess<- shaders/old/postprocess.slang:90-112
  *     with the shader math taken from include/rt3_shared_math.h (each function there cites its source);
  *   - trace() (the missing bindless_descriptor.slang wrapper over TraceRay) is a closest-hit query
- *     over world-space triangles, implemented twice: brute force over every triangle (the definition)
- *     and a binned-SAH BVH2 written for this oracle (the fast path; proven equal to brute force in tests).
+ *     over world-space triangles, implemented three times: brute force over every triangle (the definition),
+ *     a binned-SAH BVH2 written for this oracle, and that BVH collapsed to 4 children per node with SSE slab /
+ *     triangle tests (the default and the timed CPU arm); all proven equal bit for bit in tests.
  *   - deliberately single-ray, one-pixel-at-a-time recursion-free loops: nothing here is shared with
  *     the CUDA implementation except the math header.
  */
 #include "oracle.h"
 #include "rt3_shared_math.h"
 
+#include <immintrin.h>
+
 #include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdlib>
+#include <limits>
 #include <thread>
 #include <vector>
 
@@ -41,6 +45,13 @@ struct Box {
     float area() const { vec3 e = hi - lo; return 2.0f * (e.x * e.y + e.y * e.z + e.z * e.x); }
 };
 struct Node2 { Box box; uint32_t left, count; /* count>0: leaf, tris [left,left+count); else children left,left+1 */ };
+/* The TIMED CPU arm's structure (bench.py cpu_baseline / --impl reference; also the default of the passes): the BVH2 above collapsed to four
+ * children per node, boxes in SoA for one SSE slab test per node, and every leaf's <= 4 triangles in SoA for one SSE Moeller-Trumbore test
+ * whose operations mirror rt3m::ray_triangle one for one (same t, u, v bits).  Results do not depend on the structure (closer_hit is order
+ * independent); the BVH2 and brute force remain as cross-checks (tests/test_oracle_kats.py). */
+constexpr uint32_t REF_LEAF = 0x80000000u, REF_NONE = 0xFFFFFFFFu;
+struct alignas(16) Node4 { float lo[3][4], hi[3][4]; uint32_t child[4]; uint32_t valid, pad_[3]; };   /* child: REF_NONE, REF_LEAF | leaf block, or node index; valid: bit k = slot k is used */
+struct alignas(16) Leaf4 { float v0[3][4], e1[3][4], e2[3][4]; uint32_t id[4]; };    /* unused lanes: e1 = e2 = 0 (det = 0: rejected), id = RT3_MISS */
 
 }  // namespace
 
@@ -64,6 +75,9 @@ struct orc_scene {
     std::vector<WorldTri> tris;      /* global id order */
     std::vector<uint32_t> order;     /* BVH leaf order -> global id */
     std::vector<Node2> nodes;
+    std::vector<Node4> nodes4;
+    std::vector<Leaf4> leaves4;
+    uint32_t root4 = REF_NONE;
     Box bounds;
     float pad = 0.f;
     SceneView view() const {
@@ -205,7 +219,7 @@ rt3_hit closest_brute(const orc_scene& s, const rt3_ray& r) {
     if (h.prim == RT3_MISS) h.t = r.tmax;
     return h;
 }
-rt3_hit closest_bvh(const orc_scene& s, const rt3_ray& r) {
+rt3_hit closest_bvh2(const orc_scene& s, const rt3_ray& r) {
     rt3_hit h; h.t = r.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
     if (s.nodes.empty()) return h;
     vec3 o = v3(r.o), d = v3(r.d);
@@ -247,7 +261,7 @@ bool any_brute(const orc_scene& s, const rt3_ray& r) {
     }
     return false;
 }
-bool any_bvh(const orc_scene& s, const rt3_ray& r) {
+bool any_bvh2(const orc_scene& s, const rt3_ray& r) {
     if (s.nodes.empty()) return false;
     vec3 o = v3(r.o), d = v3(r.d);
     vec3 id = v3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
@@ -265,6 +279,177 @@ bool any_bvh(const orc_scene& s, const rt3_ray& r) {
     }
     return false;
 }
+
+/* ---- BVH4 + SSE (the timed CPU arm) ------------------------------------------------------------------------------------------------ */
+void build_bvh4(orc_scene& s) {
+    s.nodes4.clear(); s.leaves4.clear(); s.root4 = REF_NONE;
+    if (s.nodes.empty()) return;
+    const float inf = std::numeric_limits<float>::infinity();
+    auto make_leaf = [&](const Node2& nd) -> uint32_t {
+        Leaf4 lf;
+        for (int k = 0; k < 4; ++k) {
+            for (int a = 0; a < 3; ++a) { lf.v0[a][k] = 0.f; lf.e1[a][k] = 0.f; lf.e2[a][k] = 0.f; }
+            lf.id[k] = RT3_MISS;
+        }
+        for (uint32_t k = 0; k < nd.count && k < 4u; ++k) {
+            const uint32_t i = s.order[nd.left + k];
+            const WorldTri& t = s.tris[i];
+            lf.v0[0][k] = t.v0.x; lf.v0[1][k] = t.v0.y; lf.v0[2][k] = t.v0.z;
+            lf.e1[0][k] = t.e1.x; lf.e1[1][k] = t.e1.y; lf.e1[2][k] = t.e1.z;
+            lf.e2[0][k] = t.e2.x; lf.e2[1][k] = t.e2.y; lf.e2[2][k] = t.e2.z;
+            lf.id[k] = i;
+        }
+        s.leaves4.push_back(lf);
+        return REF_LEAF | (uint32_t)(s.leaves4.size() - 1);
+    };
+    if (s.nodes[0].count) {                                  /* the whole scene is one leaf: a node with one child */
+        if (s.nodes[0].count > 4) return;                     /* cannot happen (the builder splits above 4); the BVH2 stays in charge */
+        Node4 n4;
+        for (int k = 0; k < 4; ++k) { for (int a = 0; a < 3; ++a) { n4.lo[a][k] = inf; n4.hi[a][k] = inf; } n4.child[k] = REF_NONE; }
+        n4.valid = 1u; n4.pad_[0] = n4.pad_[1] = n4.pad_[2] = 0u;
+        const Box& b = s.nodes[0].box;
+        n4.lo[0][0] = b.lo.x; n4.lo[1][0] = b.lo.y; n4.lo[2][0] = b.lo.z; n4.hi[0][0] = b.hi.x; n4.hi[1][0] = b.hi.y; n4.hi[2][0] = b.hi.z;
+        n4.child[0] = make_leaf(s.nodes[0]);
+        s.nodes4.push_back(n4); s.root4 = 0;
+        return;
+    }
+    struct Job { uint32_t node2, node4; };
+    std::vector<Job> stack;
+    s.nodes4.push_back(Node4()); s.root4 = 0;
+    stack.push_back({0u, 0u});
+    while (!stack.empty()) {
+        const Job j = stack.back(); stack.pop_back();
+        uint32_t cand[4]; int nc = 0;
+        cand[nc++] = s.nodes[j.node2].left; cand[nc++] = s.nodes[j.node2].left + 1;
+        while (nc < 4) {                                      /* open the inner candidate of largest surface area */
+            int best = -1; float ba = -1.f;
+            for (int k = 0; k < nc; ++k) if (!s.nodes[cand[k]].count && s.nodes[cand[k]].box.area() > ba) { ba = s.nodes[cand[k]].box.area(); best = k; }
+            if (best < 0) break;
+            const uint32_t l = s.nodes[cand[best]].left;
+            cand[best] = l; cand[nc++] = l + 1;
+        }
+        Node4 n4;
+        for (int k = 0; k < 4; ++k) { for (int a = 0; a < 3; ++a) { n4.lo[a][k] = inf; n4.hi[a][k] = inf; } n4.child[k] = REF_NONE; }
+        n4.valid = (1u << nc) - 1u; n4.pad_[0] = n4.pad_[1] = n4.pad_[2] = 0u;
+        for (int k = 0; k < nc; ++k) {
+            const Node2& c = s.nodes[cand[k]];
+            n4.lo[0][k] = c.box.lo.x; n4.lo[1][k] = c.box.lo.y; n4.lo[2][k] = c.box.lo.z;
+            n4.hi[0][k] = c.box.hi.x; n4.hi[1][k] = c.box.hi.y; n4.hi[2][k] = c.box.hi.z;
+            if (c.count) {
+                if (c.count > 4) { s.nodes4.clear(); s.leaves4.clear(); s.root4 = REF_NONE; return; }
+                n4.child[k] = make_leaf(c);
+            } else {
+                n4.child[k] = (uint32_t)s.nodes4.size();
+                s.nodes4.push_back(Node4());
+                stack.push_back({cand[k], n4.child[k]});
+            }
+        }
+        s.nodes4[j.node4] = n4;
+    }
+}
+
+struct Ray4 { __m128 ox, oy, oz, dx, dy, dz, idx, idy, idz; };
+inline Ray4 splat_ray(vec3 o, vec3 d, vec3 id) {
+    Ray4 r;
+    r.ox = _mm_set1_ps(o.x); r.oy = _mm_set1_ps(o.y); r.oz = _mm_set1_ps(o.z);
+    r.dx = _mm_set1_ps(d.x); r.dy = _mm_set1_ps(d.y); r.dz = _mm_set1_ps(d.z);
+    r.idx = _mm_set1_ps(id.x); r.idy = _mm_set1_ps(id.y); r.idz = _mm_set1_ps(id.z);
+    return r;
+}
+/* slab() for the four children of a node: the same expression per lane (_mm_min_ps(a, b) = a < b ? a : b = rt3m::min_, likewise max);
+ * returns the hit mask, tn4 = entry distances */
+inline int slab4(const Node4& n, const Ray4& r, float tmin, float tmax, __m128& tn4) {
+    const __m128 x1 = _mm_mul_ps(_mm_sub_ps(_mm_load_ps(n.lo[0]), r.ox), r.idx), x2 = _mm_mul_ps(_mm_sub_ps(_mm_load_ps(n.hi[0]), r.ox), r.idx);
+    const __m128 y1 = _mm_mul_ps(_mm_sub_ps(_mm_load_ps(n.lo[1]), r.oy), r.idy), y2 = _mm_mul_ps(_mm_sub_ps(_mm_load_ps(n.hi[1]), r.oy), r.idy);
+    const __m128 z1 = _mm_mul_ps(_mm_sub_ps(_mm_load_ps(n.lo[2]), r.oz), r.idz), z2 = _mm_mul_ps(_mm_sub_ps(_mm_load_ps(n.hi[2]), r.oz), r.idz);
+    const __m128 tn = _mm_max_ps(_mm_max_ps(_mm_min_ps(x1, x2), _mm_min_ps(y1, y2)), _mm_max_ps(_mm_min_ps(z1, z2), _mm_set1_ps(tmin)));
+    const __m128 tf = _mm_min_ps(_mm_min_ps(_mm_max_ps(x1, x2), _mm_max_ps(y1, y2)), _mm_min_ps(_mm_max_ps(z1, z2), _mm_set1_ps(tmax)));
+    tn4 = tn;
+    return _mm_movemask_ps(_mm_cmple_ps(tn, _mm_mul_ps(tf, _mm_set1_ps(1.0000005f)))) & (int)n.valid;        /* unused slots never hit */
+}
+/* rt3m::ray_triangle for the four triangles of a leaf block, operation for operation:
+ *   cross(a, b) = (fma(a.y, b.z, -(a.z b.y)), fma(a.z, b.x, -(a.x b.z)), fma(a.x, b.y, -(a.y b.x))),  dot(a, b) = fma(a.z, b.z, fma(a.y, b.y, a.x b.x)) */
+inline __m128 neg4(__m128 a) { return _mm_xor_ps(a, _mm_set1_ps(-0.0f)); }
+inline __m128 dot4(__m128 ax, __m128 ay, __m128 az, __m128 bx, __m128 by, __m128 bz) { return _mm_fmadd_ps(az, bz, _mm_fmadd_ps(ay, by, _mm_mul_ps(ax, bx))); }
+inline int ray_triangle4(const Leaf4& lf, const Ray4& r, float t[4], float u[4], float v[4]) {
+    const __m128 e1x = _mm_load_ps(lf.e1[0]), e1y = _mm_load_ps(lf.e1[1]), e1z = _mm_load_ps(lf.e1[2]);
+    const __m128 e2x = _mm_load_ps(lf.e2[0]), e2y = _mm_load_ps(lf.e2[1]), e2z = _mm_load_ps(lf.e2[2]);
+    const __m128 px = _mm_fmadd_ps(r.dy, e2z, neg4(_mm_mul_ps(r.dz, e2y))), py = _mm_fmadd_ps(r.dz, e2x, neg4(_mm_mul_ps(r.dx, e2z))),
+                 pz = _mm_fmadd_ps(r.dx, e2y, neg4(_mm_mul_ps(r.dy, e2x)));                                   /* pvec = cross(d, e2) */
+    const __m128 det = dot4(e1x, e1y, e1z, px, py, pz);
+    const __m128 nonzero = _mm_cmpneq_ps(det, _mm_setzero_ps());
+    const __m128 inv = _mm_div_ps(_mm_set1_ps(1.0f), det);
+    const __m128 tx = _mm_sub_ps(r.ox, _mm_load_ps(lf.v0[0])), ty = _mm_sub_ps(r.oy, _mm_load_ps(lf.v0[1])), tz = _mm_sub_ps(r.oz, _mm_load_ps(lf.v0[2]));
+    const __m128 uu = _mm_mul_ps(dot4(tx, ty, tz, px, py, pz), inv);
+    const __m128 qx = _mm_fmadd_ps(ty, e1z, neg4(_mm_mul_ps(tz, e1y))), qy = _mm_fmadd_ps(tz, e1x, neg4(_mm_mul_ps(tx, e1z))),
+                 qz = _mm_fmadd_ps(tx, e1y, neg4(_mm_mul_ps(ty, e1x)));                                       /* qvec = cross(tvec, e1) */
+    const __m128 vv = _mm_mul_ps(dot4(r.dx, r.dy, r.dz, qx, qy, qz), inv);
+    const __m128 tt = _mm_mul_ps(dot4(e2x, e2y, e2z, qx, qy, qz), inv);
+    const __m128 zero = _mm_setzero_ps();
+    const __m128 ok = _mm_and_ps(_mm_and_ps(nonzero, _mm_cmpge_ps(uu, zero)), _mm_and_ps(_mm_cmpge_ps(vv, zero), _mm_cmple_ps(_mm_add_ps(uu, vv), _mm_set1_ps(1.0f))));
+    _mm_storeu_ps(t, tt); _mm_storeu_ps(u, uu); _mm_storeu_ps(v, vv);
+    return _mm_movemask_ps(ok);
+}
+
+rt3_hit closest_bvh4(const orc_scene& s, const rt3_ray& r) {
+    rt3_hit h; h.t = r.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
+    const vec3 o = v3(r.o), d = v3(r.d);
+    const Ray4 r4 = splat_ray(o, d, v3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z)));
+    struct Entry { uint32_t ref; float tn; };
+    Entry stack[192]; int sp = 0; stack[sp++] = {s.root4, 0.0f};
+    while (sp) {
+        const Entry e = stack[--sp];
+        if (e.tn > h.t) continue;                             /* ties are kept: tn <= t */
+        if (e.ref & REF_LEAF) {
+            const Leaf4& lf = s.leaves4[e.ref & ~REF_LEAF];
+            float t[4], u[4], v[4];
+            int m = ray_triangle4(lf, r4, t, u, v);
+            while (m) {
+                const int k = __builtin_ctz(m); m &= m - 1;
+                if (t[k] > r.tmin && t[k] < r.tmax && closer_hit(t[k], lf.id[k], h.t, h.prim)) { h.t = t[k]; h.u = u[k]; h.v = v[k]; h.prim = lf.id[k]; }
+            }
+            continue;
+        }
+        const Node4& n = s.nodes4[e.ref];
+        __m128 tn4;
+        int m = slab4(n, r4, r.tmin, h.t, tn4);
+        if (!m) continue;
+        float tn[4]; _mm_storeu_ps(tn, tn4);
+        if (sp + 4 > 192) abort();
+        const int base = sp;
+        while (m) { const int k = __builtin_ctz(m); m &= m - 1; stack[sp++] = {n.child[k], tn[k]}; }
+        for (int i = base + 1; i < sp; ++i) {                 /* farthest first on the stack: the nearest child is popped next */
+            const Entry x = stack[i]; int j = i;
+            while (j > base && stack[j - 1].tn < x.tn) { stack[j] = stack[j - 1]; --j; }
+            stack[j] = x;
+        }
+    }
+    return h;
+}
+bool any_bvh4(const orc_scene& s, const rt3_ray& r) {
+    const vec3 o = v3(r.o), d = v3(r.d);
+    const Ray4 r4 = splat_ray(o, d, v3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z)));
+    uint32_t stack[192]; int sp = 0; stack[sp++] = s.root4;
+    while (sp) {
+        const uint32_t ref = stack[--sp];
+        if (ref & REF_LEAF) {
+            const Leaf4& lf = s.leaves4[ref & ~REF_LEAF];
+            float t[4], u[4], v[4];
+            int m = ray_triangle4(lf, r4, t, u, v);
+            while (m) { const int k = __builtin_ctz(m); m &= m - 1; if (t[k] > r.tmin && t[k] < r.tmax) return true; }
+            continue;
+        }
+        const Node4& n = s.nodes4[ref];
+        __m128 tn4;
+        int m = slab4(n, r4, r.tmin, r.tmax, tn4);
+        if (sp + 4 > 192) abort();
+        while (m) { const int k = __builtin_ctz(m); m &= m - 1; stack[sp++] = n.child[k]; }
+    }
+    return false;
+}
+/* the passes and the default query mode: BVH4 + SSE when it was built, else the scalar BVH2 */
+rt3_hit closest_bvh(const orc_scene& s, const rt3_ray& r) { return s.root4 != REF_NONE ? closest_bvh4(s, r) : closest_bvh2(s, r); }
+bool any_bvh(const orc_scene& s, const rt3_ray& r) { return s.root4 != REF_NONE ? any_bvh4(s, r) : any_bvh2(s, r); }
 
 inline rt3_ray make_ray(vec3 o, vec3 d, float tmin, float tmax) {
     rt3_ray r; r.o[0] = o.x; r.o[1] = o.y; r.o[2] = o.z; r.d[0] = d.x; r.d[1] = d.y; r.d[2] = d.z; r.tmin = tmin; r.tmax = tmax; return r;
@@ -329,6 +514,7 @@ double orc_scene_build(orc_scene* s) {
     vec3 e = s->bounds.hi - s->bounds.lo;
     s->pad = total ? max_(e.x, max_(e.y, e.z)) * (1.0f / 65536.0f) : 0.f;
     Builder b(*s); b.build();
+    if (!getenv("RT3_ORACLE_BVH2")) build_bvh4(*s);       /* RT3_ORACLE_BVH2=1: A/B of the timed CPU arm against the scalar BVH2 */
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 uint32_t orc_num_triangles(const orc_scene* s) { return (uint32_t)s->tris.size(); }
@@ -366,7 +552,7 @@ void orc_world_triangles(const orc_scene* s, float* out9) {
 
 void orc_trace_closest(const orc_scene* s, const rt3_ray* rays, uint64_t n, rt3_hit* out, int mode, int threads) {
     parallel_for(n, threads, mode ? 4096 : 64, [&](uint64_t b, uint64_t e) {
-        for (uint64_t i = b; i < e; ++i) out[i] = mode ? closest_bvh(*s, rays[i]) : closest_brute(*s, rays[i]);
+        for (uint64_t i = b; i < e; ++i) out[i] = mode == 2 ? closest_bvh2(*s, rays[i]) : (mode ? closest_bvh(*s, rays[i]) : closest_brute(*s, rays[i]));
     });
 }
 void orc_trace_any(const orc_scene* s, const rt3_ray* rays, uint64_t n, uint32_t* out_bits, int mode, int threads) {
@@ -375,7 +561,7 @@ void orc_trace_any(const orc_scene* s, const rt3_ray* rays, uint64_t n, uint32_t
         for (uint64_t w = b; w < e; ++w) {
             uint32_t bits = 0;
             for (uint64_t i = w * 32; i < std::min(n, w * 32 + 32); ++i)
-                if (mode ? any_bvh(*s, rays[i]) : any_brute(*s, rays[i])) bits |= 1u << (i & 31);
+                if (mode == 2 ? any_bvh2(*s, rays[i]) : (mode ? any_bvh(*s, rays[i]) : any_brute(*s, rays[i]))) bits |= 1u << (i & 31);
             out_bits[w] = bits;
         }
     });

@@ -13,6 +13,10 @@
  * is not in the tree).  The oracle is pinned instead by: published known answers for the integer
  * hashes (MurmurHash3 x86_32, Jenkins), IEEE half/RGB9E5 conversions checked against numpy,
  * brute-force == BVH closest-hit equivalence, and an analytic furnace test (tests/).
+ *
+ * Query structures (orc_trace_* `mode`): 0 = every triangle (the definition), 2 = a scalar binned-SAH BVH2, 1 = the default of the passes and
+ * of the TIMED CPU arm: that BVH collapsed to four children per node with SSE 4-wide slab and Moeller-Trumbore tests which mirror the scalar
+ * arithmetic operation for operation.  All three return the same bits (tests/test_oracle_kats.py).
  */
 #ifndef RT3_ORACLE_H
 #define RT3_ORACLE_H
@@ -40,6 +44,7 @@ void orc_world_edges(const orc_scene*, float* out9);                       /* (v
 uint64_t orc_scene_view(const orc_scene*, void* out, uint64_t capacity);   /* rt3m::SceneView of host pointers; returns its size */
 
 /* mode 0 = brute force over all triangles, 1 = BVH2 */
+/* mode: 0 brute force, 1 BVH4 + SSE (default), 2 scalar BVH2 */
 void orc_trace_closest(const orc_scene*, const rt3_ray* rays, uint64_t n, rt3_hit* out, int mode, int threads);
 void orc_trace_any(const orc_scene*, const rt3_ray* rays, uint64_t n, uint32_t* out_bits, int mode, int threads);
 

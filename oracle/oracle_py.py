@@ -150,17 +150,18 @@ class OracleScene:
         self.L.orc_world_edges(self.h, ptr(out))
         return out
 
-    def trace_closest(self, rays, brute=False):
+    def trace_closest(self, rays, brute=False, bvh2=False):
+        """Default: the BVH4 + SSE structure (the timed CPU arm); bvh2=True: the scalar BVH2; brute=True: every triangle (the definition)."""
         rays = np.ascontiguousarray(rays)
         assert rays.dtype == RAY
         out = np.zeros(len(rays), HIT)
-        self.L.orc_trace_closest(self.h, ptr(rays), len(rays), ptr(out), 0 if brute else 1, self.threads)
+        self.L.orc_trace_closest(self.h, ptr(rays), len(rays), ptr(out), 0 if brute else (2 if bvh2 else 1), self.threads)
         return out
 
-    def trace_any(self, rays, brute=False):
+    def trace_any(self, rays, brute=False, bvh2=False):
         rays = np.ascontiguousarray(rays)
         out = np.zeros((len(rays) + 31) // 32, np.uint32)
-        self.L.orc_trace_any(self.h, ptr(rays), len(rays), ptr(out), 0 if brute else 1, self.threads)
+        self.L.orc_trace_any(self.h, ptr(rays), len(rays), ptr(out), 0 if brute else (2 if bvh2 else 1), self.threads)
         return out
 
     def pass_gbuffer(self, params, rect=None, gbuffer=None, depth=None):

@@ -428,3 +428,23 @@ def test_env_sampling_tables():
         d = np.array(d, np.float32) / np.linalg.norm(d)
         L.orc_equirect_uv(ptr(f3(d)), ptr(o2))
         assert 0 <= o2[0] <= 1 and 0 <= o2[1] <= 1
+
+
+@pytest.mark.parametrize("scene_fn", [lambda: scenes.cornell_box(), lambda: scenes.random_soup(3000, seed=9), lambda: scenes.synthetic_atrium(0.03, environment=False),
+                                      lambda: scenes.random_soup(1, n_geometries=1), lambda: scenes.random_soup(3, n_geometries=1)])
+def test_bvh4_sse_equals_scalar_bvh2_equals_brute_force(scene_fn):
+    """The three query structures of the oracle give the same bits: every triangle (the definition), the scalar BVH2, and the BVH4 with
+    4-wide SSE slab and Moeller-Trumbore tests that the passes and the timed CPU arm use.  The SSE triangle test mirrors rt3m::ray_triangle
+    operation for operation, so t, u, v are bit-identical, not merely close."""
+    sc = scene_fn()
+    orc = OracleScene(sc)
+    c, a = scenes.incoherent_rays(sc, 6000, seed=17)
+    rays = np.concatenate([c, scenes.random_rays(sc, 6000, seed=18)])
+    want = orc.trace_closest(rays, brute=True)
+    for kw in (dict(), dict(bvh2=True)):
+        got = orc.trace_closest(rays, **kw)
+        assert (got["prim"] == want["prim"]).all(), kw
+        for f in ("t", "u", "v"):
+            assert (got[f].view(np.uint32) == want[f].view(np.uint32)).all(), (kw, f)
+    wa = orc.trace_any(a, brute=True)
+    assert (orc.trace_any(a) == wa).all() and (orc.trace_any(a, bvh2=True) == wa).all()
