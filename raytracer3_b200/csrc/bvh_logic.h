@@ -56,6 +56,14 @@ static const uint32_t LEAF_FLAG = 0x80000000u;
 #define RT3_PAD_FRACTION (1.0f / 32768.0f)
 #endif
 
+/* RT3_NODE_V2 (default): the node test forms the HIT BYTE of the eight children first and derives both halves of the hit mask from it —
+ * one predicated add of an immediate per child (7 << 3 slot | 1 << 24 + slot), the record bits by one AND with the node's valid24, the inner
+ * bits in this ray's near-to-far order by one shared-memory table look-up (perm[7 - octant][byte]: bit s of the byte moves to bit
+ * s ^ (7 - octant)) — 22 instructions where the per-child (count << offset) assembly of round 1's format took about 60 (SASS counts in
+ * DESIGN.md section 4.3).  0 keeps round 1's node format and test. */
+#ifndef RT3_NODE_V2
+#define RT3_NODE_V2 1
+#endif
 struct u32x4 { uint32_t x, y, z, w; };
 
 #ifdef __CUDA_ARCH__
@@ -518,7 +526,10 @@ RT3_HD void treelet_visit(Mem& mem, uint32_t n, uint32_t cur, bool with_dp) {
  * Node layout (20 words):
  *   w0..w2  p = node box min (float)            w3  ex | ey<<8 | ez<<16 | imask<<24   (e biased by 127)
  *   w4      child_base (first inner child)      w5  tri_base
- *   w6,w7   meta[8]: 0 = empty; inner: 0x20 | (24 + slot); leaf: unary(count 1..3) << 5 | tri offset (0..23)
+ *   w6      valid24: leaf child in slot s with c records (1..3) owns bits 3 s .. 3 s + c - 1; inner and empty slots own none.  The records
+ *           of a node lie consecutively from tri_base in slot order, so record bit b has index tri_base + popc(valid24 & ((1 << b) - 1)).
+ *   w7      0 (reserved)
+ *           (RT3_NODE_V2 = 0, round 1's format: w6,w7 = meta[8]: 0 = empty; inner: 0x20 | (24 + slot); leaf: unary(count) << 5 | tri offset)
  *   w8,w9   qlo.x[8]   w10,w11 qlo.y[8]   w12,w13 qlo.z[8]
  *   w14,w15 qhi.x[8]   w16,w17 qhi.y[8]   w18,w19 qhi.z[8]
  * child box = p + q * 2^e, conservative (floor / ceil).
@@ -635,8 +646,16 @@ RT3_HD void collapse_one(const CollapseCtx& c, uint32_t ref, uint32_t wide_index
             tri_term += box_area(nd.lo, nd.hi) * (float)cnt;
         }
     }
+#if RT3_NODE_V2
+    uint32_t valid24 = 0;
+    for (int s = 0; s < 8; ++s)
+        if (meta[s] != 0u && (meta[s] & 0x1Fu) < 24u) valid24 |= (meta[s] >> 5) << (3 * s);       /* leaf: unary(count) at 3 s */
+    out.w[6] = valid24;
+    out.w[7] = 0u;
+#else
     out.w[6] = meta[0] | (meta[1] << 8) | (meta[2] << 16) | (meta[3] << 24);
     out.w[7] = meta[4] | (meta[5] << 8) | (meta[6] << 16) | (meta[7] << 24);
+#endif
     for (int a = 0; a < 3; ++a) {
         out.w[8 + 2 * a] = qlo[a][0] | (qlo[a][1] << 8) | (qlo[a][2] << 16) | (qlo[a][3] << 24);
         out.w[9 + 2 * a] = qlo[a][4] | (qlo[a][5] << 8) | (qlo[a][6] << 16) | (qlo[a][7] << 24);
@@ -651,10 +670,52 @@ RT3_HD void collapse_one(const CollapseCtx& c, uint32_t ref, uint32_t wide_index
 }
 
 /* ---------------------------------------------------------------- traversal -------------------- */
+struct PermLut { uint8_t v[2048]; };
+constexpr PermLut make_perm_lut() {
+    PermLut t{};
+    for (int o = 0; o < 8; ++o)
+        for (int b = 0; b < 256; ++b) {
+            unsigned r = 0;
+            for (int s = 0; s < 8; ++s) if ((b >> s) & 1) r |= 1u << (s ^ o);
+            t.v[o * 256 + b] = (uint8_t)r;
+        }
+    return t;
+}
+#if RT3_NODE_V2
+#ifdef __CUDACC__
+static __device__ const PermLut g_perm_lut = make_perm_lut();
+#endif
+#ifdef __CUDA_ARCH__
+/* every kernel that traverses copies the table into shared memory once per CTA (2 KB: one 16-byte word per thread of a 128-thread CTA;
+ * NT = the kernel's CTA size, a compile-time constant) */
+#define RT3_PERM_LUT_SETUP(base, NT)                                                                                               \
+    __shared__ __align__(2048) uint8_t s_perm_lut_[2048];                                                                          \
+    _Pragma("unroll") for (uint32_t i_ = 0; i_ < 128u; i_ += (NT))                                                                 \
+        if ((NT) >= 128 ? threadIdx.x < 128u : true) ((uint4*)s_perm_lut_)[i_ + threadIdx.x] = __ldg((const uint4*)g_perm_lut.v + i_ + threadIdx.x); \
+    __syncthreads();                                                                                                               \
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(s_perm_lut_)
+RT3_HD uint32_t perm_lookup(uint32_t addr) {
+    uint32_t v;
+    asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+#else
+#define RT3_PERM_LUT_SETUP(base, NT) const uint32_t base = 0u
+inline uint32_t perm_lookup(uint32_t addr) {
+    static const PermLut lut = make_perm_lut();
+    return lut.v[addr & 2047u];
+}
+#endif
+#else
+#define RT3_PERM_LUT_SETUP(base, NT) const uint32_t base = 0u
+#endif
 struct RayPrep {
     float ox, oy, oz, dx, dy, dz;     /* origin, direction                        */
     float idx, idy, idz;               /* safe reciprocal direction                */
     uint32_t octinv4;                  /* (7 - octant) replicated in 4 bytes       */
+#if RT3_NODE_V2
+    uint32_t lutrow;                   /* address of row (7 - octant) of the permutation table (shared memory; host: index) */
+#endif
     float tmin;
     uint32_t magic;                    /* 0x47000000 held in a REGISTER: ptxas then encodes the PRMT selector as the immediate
                                           (with both constant it materialises each selector with an extra move per plane) */
@@ -664,7 +725,7 @@ RT3_HD float safe_rcp_dir(float d) {
     if (rt3m::abs_(d) < tiny) d = (rt3m::as_uint(d) >> 31) ? -tiny : tiny;
     return 1.0f / d;
 }
-RT3_HD RayPrep prepare_ray(const rt3_ray& r, uint32_t magic = 0x47000000u) {
+RT3_HD RayPrep prepare_ray(const rt3_ray& r, uint32_t magic = 0x47000000u, uint32_t lut_base = 0u) {
     RayPrep p;
     p.magic = magic;
     p.ox = r.o[0]; p.oy = r.o[1]; p.oz = r.o[2];
@@ -672,6 +733,11 @@ RT3_HD RayPrep prepare_ray(const rt3_ray& r, uint32_t magic = 0x47000000u) {
     p.idx = safe_rcp_dir(p.dx); p.idy = safe_rcp_dir(p.dy); p.idz = safe_rcp_dir(p.dz);
     uint32_t oct = (p.idx < 0.0f ? 1u : 0u) | (p.idy < 0.0f ? 2u : 0u) | (p.idz < 0.0f ? 4u : 0u);
     p.octinv4 = (7u - oct) * 0x01010101u;
+#if RT3_NODE_V2
+    p.lutrow = lut_base + ((7u - oct) << 8);
+#else
+    (void)lut_base;
+#endif
     p.tmin = r.tmin;
     return p;
 }
@@ -718,6 +784,38 @@ RT3_HD uint32_t slab_child(uint32_t nx, uint32_t fx, uint32_t ny, uint32_t fy, u
     return (tn <= tf) ? (((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu)) : 0u;
 }
 
+template <int J>
+RT3_HD bool slab_hit(uint32_t nx, uint32_t fx, uint32_t ny, uint32_t fy, uint32_t nz, uint32_t fz, float sx, float sy, float sz, float bx,
+                     float by, float bz, float tmin, float tmax, uint32_t mg) {
+    const float t0x = rt3m::fma_(byte_as_biased_float<J>(nx, mg), sx, bx), t1x = rt3m::fma_(byte_as_biased_float<J>(fx, mg), sx, bx);
+    const float t0y = rt3m::fma_(byte_as_biased_float<J>(ny, mg), sy, by), t1y = rt3m::fma_(byte_as_biased_float<J>(fy, mg), sy, by);
+    const float t0z = rt3m::fma_(byte_as_biased_float<J>(nz, mg), sz, bz), t1z = rt3m::fma_(byte_as_biased_float<J>(fz, mg), sz, bz);
+    const float tn = bmax(bmax(t0x, t0y), bmax(t0z, tmin));
+    const float tf = bmin(bmin(t1x, t1y), bmin(t1z, tmax));
+    return tn <= tf;
+}
+/* index of record bit `bit` of a node: the records lie consecutively in bit order, valid = the node's valid24 (all ones for a group that
+ * was made dense, see dense_records) */
+RT3_HD uint32_t record_index(uint32_t valid, int bit) {
+#if RT3_NODE_V2
+    return (uint32_t)popc32(valid & ~(0xFFFFFFFFu << bit));
+#else
+    (void)valid;
+    return (uint32_t)bit;
+#endif
+}
+/* a pending record group in self-contained form (two-level mode parks groups on the stack, which has no room for valid24): bit k of the
+ * result stands for record tri_base + k */
+RT3_HD uint32_t dense_records(uint32_t hits, uint32_t valid) {
+#if RT3_NODE_V2
+    uint32_t d = 0;
+    while (hits) { const int b = bfind32(hits); hits &= ~(1u << b); d |= 1u << record_index(valid, b); }
+    return d;
+#else
+    (void)valid;
+    return hits;
+#endif
+}
 /* Intersect the 8 quantised child boxes of one node.  Returns the hit mask: bits 24..31 = inner
  * children in near-to-far priority order for this ray's octant, bits 0..23 = triangles of hit leaves.
  * Plane distance = (p + q 2^e - o) / d = (32768 + q) * s + (b - 32768 s) with s = 2^e / d, b = (p - o) / d: one PRMT and
@@ -732,6 +830,26 @@ RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n
     const float bx = rt3m::fma_(-32768.0f, sx, (rt3m::as_float(n0.x) - r.ox) * r.idx);
     const float by = rt3m::fma_(-32768.0f, sy, (rt3m::as_float(n0.y) - r.oy) * r.idy);
     const float bz = rt3m::fma_(-32768.0f, sz, (rt3m::as_float(n0.z) - r.oz) * r.idz);
+#if RT3_NODE_V2
+    uint32_t acc = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        const uint32_t qlx = half ? n2.y : n2.x, qly = half ? n2.w : n2.z, qlz = half ? n3.y : n3.x;
+        const uint32_t qhx = half ? n3.w : n3.z, qhy = half ? n4.y : n4.x, qhz = half ? n4.w : n4.z;
+        const uint32_t nx = r.idx < 0.0f ? qhx : qlx, fx = r.idx < 0.0f ? qlx : qhx;
+        const uint32_t ny = r.idy < 0.0f ? qhy : qly, fy = r.idy < 0.0f ? qly : qhy;
+        const uint32_t nz = r.idz < 0.0f ? qhz : qlz, fz = r.idz < 0.0f ? qlz : qhz;
+        /* the constants are disjoint, so the compiler turns every line into one predicated add of an immediate */
+        if (slab_hit<0>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, r.magic)) acc |= (7u << (12 * half + 0)) | (1u << (24 + 4 * half));
+        if (slab_hit<1>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, r.magic)) acc |= (7u << (12 * half + 3)) | (2u << (24 + 4 * half));
+        if (slab_hit<2>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, r.magic)) acc |= (7u << (12 * half + 6)) | (4u << (24 + 4 * half));
+        if (slab_hit<3>(nx, fx, ny, fy, nz, fz, sx, sy, sz, bx, by, bz, r.tmin, tmax, r.magic)) acc |= (7u << (12 * half + 9)) | (8u << (24 + 4 * half));
+    }
+    /* empty slots never hit (their planes are lo = 255 > hi = 0) and own no bit of imask / valid24 anyway */
+    const uint32_t inner = perm_lookup(((acc >> 24) & (n0.w >> 24)) | r.lutrow);
+    return (inner << 24) | (acc & n1.z & 0x00FFFFFFu);
+}
+#else
     uint32_t hitmask = 0;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
@@ -752,6 +870,7 @@ RT3_HD uint32_t intersect_wide_node(const RayPrep& r, float tmax, const u32x4& n
     }
     return hitmask;
 }
+#endif
 
 struct TraverseStats { uint32_t nodes, tris; };
 
@@ -780,13 +899,14 @@ RT3_HD void instance_triangle(const InstRec& in, const u32x4& a, const u32x4& b,
  * object-space ray and restarts at the instance's root; popping the sentinel restores the world-space ray. */
 template <bool ANY>
 RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ray& ray, rt3_hit& hit, TraverseStats* stats, bool active = true,
-                          const InstRec* insts = nullptr) {
-    RayPrep r = prepare_ray(ray);
+                          const InstRec* insts = nullptr, uint32_t lut_base = 0u) {
+    RayPrep r = prepare_ray(ray, 0x47000000u, lut_base);
     const vec3 o = rt3m::v3(ray.o), d = rt3m::v3(ray.d);
     uint32_t stack_base[RT3_MAX_STACK], stack_hits[RT3_MAX_STACK];
     int sp = 0;
     uint32_t ng_base = 0, ng_hits = 0x80000000u;   /* node group: root */
     uint32_t tg_base = 0, tg_hits = 0;             /* record group     */
+    uint32_t tg_valid = 0x00FFFFFFu;               /* ... and its node's valid24 (record_index) */
     uint32_t cur_inst = RT3_STACK_SENTINEL;        /* two-level: instance being traversed, or none (top level) */
     /* Two-phase iteration (same shape as k_trace_dyn): a node step for rays with no record pending, then ONE record
      * per ray that has one pending.  On the device the loop is warp-synchronous (every lane of the warp must call this
@@ -815,7 +935,7 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
             if (stats) stats->nodes++;
             const uint32_t hm = intersect_wide_node(r, hit.t, n0, n1, n2, n3, n4);
             ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
-            tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
+            tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu; tg_valid = n1.z;
         }
         bool found_any = false;
         for (int rep = 0; rep < 2; ++rep) {   /* up to two record steps per node step, as in k_trace_dyn */
@@ -824,15 +944,15 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
         if (active && tg_hits && !found_any) {
             const int bit = bfind32(tg_hits);
             tg_hits &= ~(1u << bit);
-            const Tri48* tp = tris + (tg_base + (uint32_t)bit);
+            const Tri48* tp = tris + (tg_base + record_index(tg_valid, bit));
             const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
             if (insts != nullptr && cur_inst == RT3_STACK_SENTINEL) {
                 /* top-level record = instance: save what is pending here, dive into its bottom-level tree */
                 if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) { stack_base[sp] = ng_base; stack_hits[sp] = ng_hits; sp++; }
-                if (tg_hits && sp < RT3_MAX_STACK) { stack_base[sp] = tg_base; stack_hits[sp] = tg_hits; sp++; }
+                if (tg_hits && sp < RT3_MAX_STACK) { stack_base[sp] = tg_base; stack_hits[sp] = dense_records(tg_hits, tg_valid); sp++; }
                 if (sp < RT3_MAX_STACK) { stack_base[sp] = RT3_STACK_SENTINEL; stack_hits[sp] = 0u; sp++; }
                 cur_inst = a.w;
-                r = prepare_ray(object_ray(insts[cur_inst], ray));
+                r = prepare_ray(object_ray(insts[cur_inst], ray), 0x47000000u, lut_base);
                 ng_base = insts[cur_inst].root; ng_hits = 0x80000000u; tg_hits = 0u;
             } else {
                 if (stats) stats->tris++;
@@ -857,8 +977,8 @@ RT3_HD bool traverse_wide(const WideNode* nodes, const Tri48* tris, const rt3_ra
             if (sp == 0) { active = false; break; }
             sp--;
             const uint32_t eb = stack_base[sp], eh = stack_hits[sp];
-            if (eb == RT3_STACK_SENTINEL && eh == 0u) { cur_inst = RT3_STACK_SENTINEL; r = prepare_ray(ray); continue; }
-            if (eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; ng_hits = 0u; }
+            if (eb == RT3_STACK_SENTINEL && eh == 0u) { cur_inst = RT3_STACK_SENTINEL; r = prepare_ray(ray, 0x47000000u, lut_base); continue; }
+            if (eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; tg_valid = 0x00FFFFFFu; ng_hits = 0u; }
         }
     }
 #undef RT3_WARP_ANY

@@ -23,6 +23,7 @@ __device__ __forceinline__ void flush_counter(unsigned long long v, unsigned lon
 __global__ void __launch_bounds__(128, 8) k_gbuffer(SceneView s, const WideNode* __restrict__ nodes, const Tri48* __restrict__ tris, rt3_params p, PixelMap m,
                                                  uint32_t* __restrict__ gbuffer, float* __restrict__ depth, uint32_t* __restrict__ ids,
                                                  float* __restrict__ bary, DeviceCounters* counters, const InstRec* __restrict__ insts) {
+    RT3_PERM_LUT_SETUP(lut_base, 128);                                           /* octant permutation table of the node test (bvh_logic.h) */
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t x, y; size_t px;
     const bool valid = idx < m.work && pixel_of(m, idx, x, y, px);
@@ -30,7 +31,7 @@ __global__ void __launch_bounds__(128, 8) k_gbuffer(SceneView s, const WideNode*
     if (valid) ray = setup_primary_ray(x, y, p);                            /* gbuffer.slang:10 */
     else { ray.o[0] = ray.o[1] = ray.o[2] = 0.f; ray.d[0] = ray.d[1] = 0.f; ray.d[2] = 1.f; ray.tmin = 0.f; ray.tmax = 0.f; }
     rt3_hit h; h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
-    traverse_wide<false>(nodes, tris, ray, h, nullptr, valid, insts);            /* gbuffer.slang:12 (warp-synchronous: all lanes call) */
+    traverse_wide<false>(nodes, tris, ray, h, nullptr, valid, insts, lut_base);  /* gbuffer.slang:12 (warp-synchronous: all lanes call) */
     if (valid) {
         if (h.prim == RT3_MISS) {                                           /* gbuffer.slang:14-16 */
             depth[px] = RT3_BACKGROUND_DEPTH;

@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
     const uint64_t n = d_count ? (uint64_t)*d_count : n_static;
     const uint32_t lane = threadIdx.x & 31u;
     unsigned long long st_nodes = 0, st_tris = 0;
+    RT3_PERM_LUT_SETUP(lut_base, TRACE_THREADS);
     for (;;) {
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(work_counter, 32ull);
@@ -43,7 +44,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const WideNode* __restr
         else { r.o[0] = r.o[1] = r.o[2] = 0.f; r.d[0] = r.d[1] = 0.f; r.d[2] = 1.f; r.tmin = 0.f; r.tmax = 0.f; }
         h.t = r.tmax;
         TraverseStats ts = {0, 0};
-        any = traverse_wide<ANY>(nodes, tris, r, h, STATS ? &ts : nullptr, valid, insts);   /* warp-synchronous: every lane calls */
+        any = traverse_wide<ANY>(nodes, tris, r, h, STATS ? &ts : nullptr, valid, insts, lut_base);   /* warp-synchronous: every lane calls */
         if (STATS) { st_nodes += ts.nodes; st_tris += ts.tris; }
         if (ANY) {
             uint32_t word = __ballot_sync(0xFFFFFFFFu, any);

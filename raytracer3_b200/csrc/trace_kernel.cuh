@@ -95,6 +95,8 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
     uint64_t my_index = 0;
     rt3_hit h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
     uint32_t ng_base = 0, ng_hits = 0, tg_base = 0, tg_hits = 0;
+    uint32_t tg_valid = 0x00FFFFFFu;       /* valid24 of the node the pending records belong to (record_index, bvh_logic.h) */
+    RT3_PERM_LUT_SETUP(lut_base, TRACE_THREADS);          /* RT3_NODE_V2: the octant permutation table in shared memory */
 #if RT3_SMEM_STACK > 0
     __shared__ uint2 s_stack[RT3_SMEM_STACK][TRACE_THREADS];
     uint32_t stack_base[RT3_MAX_STACK - RT3_SMEM_STACK], stack_hits[RT3_MAX_STACK - RT3_SMEM_STACK];
@@ -108,6 +110,9 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
     int sp = 0;
     bool active = false, exhausted = false;
     r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.idx = r.idy = r.idz = r.tmin = 0.f; r.octinv4 = 0; r.magic = magic;
+#if RT3_NODE_V2
+    r.lutrow = lut_base;
+#endif
     for (;;) {
         /* ---- refill idle lanes */
         const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
@@ -122,7 +127,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                 const uint64_t i = base + __popc(idle & lt_mask);
                 if (i < n) {
                     const rt3_ray ray = load_ray(rays, i);
-                    r = prepare_ray(ray, magic);
+                    r = prepare_ray(ray, magic, lut_base);
                     if (TWO) { wox = ray.o[0]; woy = ray.o[1]; woz = ray.o[2]; wdx = ray.d[0]; wdy = ray.d[1]; wdz = ray.d[2]; cur_inst = RT3_STACK_SENTINEL; }
                     ray_tmax = ray.tmax;
                     h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
@@ -176,7 +181,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                                     n4 = s_node[wid][lane * 5u + 4u];
                         const uint32_t hm = intersect_wide_node(r, h.t, n0, n1, n2, n3, n4);
                         ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
-                        tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
+                        tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu; tg_valid = n1.z;
                     }
                     __syncwarp();
                 }
@@ -194,7 +199,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                             n4 = ld_u32x4(nd->w + 16);
                 const uint32_t hm = intersect_wide_node(r, h.t, n0, n1, n2, n3, n4);
                 ng_base = n1.x; ng_hits = (hm & 0xFF000000u) | (n0.w >> 24);
-                tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu;
+                tg_base = n1.y; tg_hits = hm & 0x00FFFFFFu; tg_valid = n1.z;
             }
 #endif
             bool found_any = false;
@@ -230,7 +235,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                         if (j < mine) {
                             const int bit = bfind32(rest);
                             rest &= ~(1u << bit);
-                            s_src[wid][first + j] = (uint16_t)(lane | ((uint32_t)bit << 8));
+                            s_src[wid][first + j] = (uint16_t)(lane | (record_index(tg_valid, bit) << 8));   /* owner lane, record offset */
                         }
                     if (active) tg_hits = rest;                                   /* what did not fit into this step stays pending */
                     __syncwarp();
@@ -284,15 +289,15 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
             if (active && tg_hits && !found_any) {
                 const int bit = bfind32(tg_hits);
                 tg_hits &= ~(1u << bit);
-                const Tri48* tp = tris + (tg_base + (uint32_t)bit);
+                const Tri48* tp = tris + (tg_base + record_index(tg_valid, bit));
                 const u32x4 a = ld_u32x4(tp), b = ld_u32x4((const uint32_t*)tp + 4), c = ld_u32x4((const uint32_t*)tp + 8);
                 if (TWO && cur_inst == RT3_STACK_SENTINEL) {
                     if (ng_hits > 0x00FFFFFFu && sp < RT3_MAX_STACK) RT3_PUSH(ng_base, ng_hits);
-                    if (tg_hits && sp < RT3_MAX_STACK) RT3_PUSH(tg_base, tg_hits);
+                    if (tg_hits && sp < RT3_MAX_STACK) RT3_PUSH(tg_base, dense_records(tg_hits, tg_valid));
                     if (sp < RT3_MAX_STACK) RT3_PUSH(RT3_STACK_SENTINEL, 0u);
                     cur_inst = a.w;
                     rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
-                    r = prepare_ray(object_ray(insts[cur_inst], wr), magic);
+                    r = prepare_ray(object_ray(insts[cur_inst], wr), magic, lut_base);
                     ng_base = insts[cur_inst].root; ng_hits = 0x80000000u; tg_hits = 0u;
                 } else {
                     float t, u, v;
@@ -329,10 +334,10 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                         if (eb == RT3_STACK_SENTINEL && eh == 0u) {
                             cur_inst = RT3_STACK_SENTINEL;
                             rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
-                            r = prepare_ray(wr, magic);
+                            r = prepare_ray(wr, magic, lut_base);
                             continue;
                         }
-                        if (eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; ng_hits = 0u; }
+                        if (eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; tg_valid = 0x00FFFFFFu; ng_hits = 0u; }
                     }
                 }
                 if (done) {
