@@ -73,7 +73,7 @@ RT3_HD u32x4 ld_u32x4(const void* p) { uint4 v = __ldg((const uint4*)p); u32x4 r
 RT3_HD int clz32(uint32_t x) { return __clz((int)x); }
 RT3_HD int clz64(uint64_t x) { return __clzll((long long)x); }
 RT3_HD int popc32(uint32_t x) { return __popc(x); }
-RT3_HD int bfind32(uint32_t x) { return 31 - __clz((int)x); }
+RT3_HD int bfind32(uint32_t x) { int r; asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(x)); return r; }   /* one FLO; -1 for x = 0, like 31 - clz */
 /* per-byte sign fill: 0x80 -> 0xFF, else 0x00 */
 /* prmt generic mode: a selector nibble with its msb set replicates the sign bit of the selected byte
  * (the __byte_perm intrinsic only honours 3 selector bits, so the PTX form is used directly). */
