@@ -46,6 +46,10 @@ __device__ __forceinline__ rt3_ray load_ray(const rt3_ray* rays, uint64_t i) {
 #endif
 /* record steps per node step of the two-phase loop: a second one drains lanes that hold two triangles before the warp returns to the
  * node phase (measured: traversal launch 0.507 -> 0.497 ms, incoherent closest / any +2.6 % / +4 %; a third one costs more than it saves) */
+/* reciprocal ray direction by MUFU.RCP + one Newton step instead of three IEEE divisions per fetched ray (bvh_logic.h: safe_rcp_dir_t) */
+#ifndef RT3_FAST_RCP
+#define RT3_FAST_RCP 1
+#endif
 #ifndef RT3_TRI_REPS
 #define RT3_TRI_REPS 2
 #endif
@@ -127,7 +131,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                 const uint64_t i = base + __popc(idle & lt_mask);
                 if (i < n) {
                     const rt3_ray ray = load_ray(rays, i);
-                    r = prepare_ray(ray, magic, lut_base);
+                    r = prepare_ray<RT3_FAST_RCP>(ray, magic, lut_base);
                     if (TWO) { wox = ray.o[0]; woy = ray.o[1]; woz = ray.o[2]; wdx = ray.d[0]; wdy = ray.d[1]; wdz = ray.d[2]; cur_inst = RT3_STACK_SENTINEL; }
                     ray_tmax = ray.tmax;
                     h.t = ray.tmax; h.u = 0.f; h.v = 0.f; h.prim = RT3_MISS;
@@ -297,7 +301,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                     if (sp < RT3_MAX_STACK) RT3_PUSH(RT3_STACK_SENTINEL, 0u);
                     cur_inst = a.w;
                     rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
-                    r = prepare_ray(object_ray(insts[cur_inst], wr), magic, lut_base);
+                    r = prepare_ray<RT3_FAST_RCP>(object_ray(insts[cur_inst], wr), magic, lut_base);
                     ng_base = insts[cur_inst].root; ng_hits = 0x80000000u; tg_hits = 0u;
                 } else {
                     float t, u, v;
@@ -334,7 +338,7 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
                         if (eb == RT3_STACK_SENTINEL && eh == 0u) {
                             cur_inst = RT3_STACK_SENTINEL;
                             rt3_ray wr; wr.o[0] = wox; wr.o[1] = woy; wr.o[2] = woz; wr.d[0] = wdx; wr.d[1] = wdy; wr.d[2] = wdz; wr.tmin = r.tmin; wr.tmax = ray_tmax;
-                            r = prepare_ray(wr, magic, lut_base);
+                            r = prepare_ray<RT3_FAST_RCP>(wr, magic, lut_base);
                             continue;
                         }
                         if (eh > 0x00FFFFFFu) { ng_base = eb; ng_hits = eh; } else { tg_base = eb; tg_hits = eh; tg_valid = 0x00FFFFFFu; ng_hits = 0u; }
