@@ -198,6 +198,59 @@ void emu_info(const EmuBvh* b, uint32_t* out4, float* sah2) {
     sah2[0] = b->sah[0]; sah2[1] = b->sah[1];
 }
 /* order-independent check that the collapse kept every triangle exactly once: returns number of mismatches */
+/* Self-check of the hit-byte-first node format (bvh_logic.h, RT3_NODE_V2): the octant permutation table, record_index / dense_records on
+ * random masks, and every node of a built tree: valid24 and the inner mask own disjoint slots, the record counts add up.  Returns the
+ * number of violations. */
+uint32_t emu_check_node_v2(const EmuBvh* b) {
+    uint32_t bad = 0;
+#if RT3_NODE_V2
+    const PermLut lut = make_perm_lut();
+    for (uint32_t o = 0; o < 8; ++o)
+        for (uint32_t x = 0; x < 256; ++x) {
+            const uint32_t y = lut.v[o * 256 + x];
+            if (__builtin_popcount(y) != __builtin_popcount(x)) bad++;
+            if (lut.v[o * 256 + y] != x) bad++;                                   /* XOR permutations are involutions */
+            for (uint32_t s = 0; s < 8; ++s) if (((x >> s) & 1u) != ((y >> (s ^ o)) & 1u)) bad++;
+            if (perm_lookup((o << 8) | x) != y) bad++;
+        }
+    uint32_t rng = 12345u;
+    for (int it = 0; it < 20000; ++it) {
+        uint32_t valid = 0;
+        for (int s = 0; s < 8; ++s) { rng = rng * 1664525u + 1013904223u; const uint32_t c = (rng >> 24) & 3u; valid |= ((1u << c) - 1u) << (3 * s); }
+        rng = rng * 1664525u + 1013904223u;
+        const uint32_t hits = valid & (rng >> 8);
+        const uint32_t dense = dense_records(hits, valid);
+        if (__builtin_popcount(dense) != __builtin_popcount(hits)) bad++;
+        uint32_t k = 0;
+        for (int bit = 0; bit < 24; ++bit)
+            if ((valid >> bit) & 1u) {
+                if (record_index(valid, bit) != k) bad++;
+                if ((((hits >> bit) & 1u) != ((dense >> k) & 1u))) bad++;
+                if (((dense >> k) & 1u) && record_index(0x00FFFFFFu, (int)k) != k) bad++;   /* a dense group addresses itself */
+                k++;
+            }
+    }
+    if (b) {
+        uint64_t records = 0;
+        for (uint32_t ni = 0; ni < b->n_nodes; ++ni) {
+            const WideNode& n = b->nodes[ni];
+            const uint32_t imask = n.w[3] >> 24, valid = n.w[6];
+            if (valid >> 24) bad++;
+            if (n.w[7] != 0u) bad++;
+            for (int s = 0; s < 8; ++s) {
+                const uint32_t f = (valid >> (3 * s)) & 7u;
+                if (f != 0u && f != 1u && f != 3u && f != 7u) bad++;             /* unary count */
+                if (f != 0u && ((imask >> s) & 1u)) bad++;                       /* a slot is a leaf or an inner child, never both */
+            }
+            records += (uint64_t)__builtin_popcount(valid);
+        }
+        if (records != b->n_tris) bad++;
+    }
+#else
+    (void)b;
+#endif
+    return bad;
+}
 uint32_t emu_check_triangles(const EmuBvh* b) {
     std::vector<uint32_t> seen(b->tris_in.size(), 0);
     uint32_t bad = 0;

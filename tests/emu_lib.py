@@ -46,6 +46,8 @@ def lib():
         L.emu_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.emu_check_triangles.restype = C.c_uint32
         L.emu_check_triangles.argtypes = [C.c_void_p]
+        L.emu_check_node_v2.restype = C.c_uint32
+        L.emu_check_node_v2.argtypes = [C.c_void_p]
         L.emu_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int, C.c_void_p]
         L.emu_trace_any.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]
         _lib = L
@@ -198,6 +200,10 @@ class EmuBvh:
 
     def check_triangles(self):
         return self.L.emu_check_triangles(self.h)
+
+    def check_node_format(self):
+        """hit-byte-first node format (bvh_logic.h): permutation table, record_index / dense_records, valid24 of every node"""
+        return self.L.emu_check_node_v2(self.h)
 
     def trace_closest(self, rays, brute=False):
         rays = np.ascontiguousarray(rays)

@@ -24,6 +24,7 @@ def test_wide_bvh_equals_brute_force(name, optimal):
     b = EmuBvh(tris=T, optimal_collapse=optimal)
     info = b.info()
     assert info["tris"] == len(T) and b.check_triangles() == 0          # order-independent: every triangle kept exactly once, unmodified
+    assert b.check_node_format() == 0                                   # valid24 / inner mask of every node, permutation table, record indexing
     assert info["levels"] < 64
     c, a = scenes.incoherent_rays(sc, 3000, seed=31, tris=T.astype(np.float64))
     rays = np.concatenate([c, scenes.random_rays(sc, 3000, seed=32)])

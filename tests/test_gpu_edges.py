@@ -224,7 +224,8 @@ def test_collapse_policies_give_identical_hits(gpu_ctx):
         results[name] = (bs.wide_nodes, w.trace_closest(rays).cpu().numpy().view(np.uint32), w.trace_any(arays).cpu().numpy())
         if not flags & BUILD_TWO_LEVEL:
             nodes, tris = w.download_accel()
-            assert EmuBvh(nodes=nodes, tri_records=tris).check_triangles() == 0
+            wrapped = EmuBvh(nodes=nodes, tri_records=tris)
+            assert wrapped.check_triangles() == 0 and wrapped.check_node_format() == 0
     for name in ("build", "trace2", "build2"):
         assert (results[name][1] == results["trace"][1]).all() and (results[name][2] == results["trace"][2]).all(), name
     assert results["trace"][0] < 0.85 * results["build"][0] and results["trace2"][0] < 0.85 * results["build2"][0]
@@ -255,7 +256,8 @@ def test_treelet_build_gives_identical_hits_and_the_emulators_tree(gpu_ctx):
         res[name] = (bs.wide_nodes, w.trace_closest(rays).cpu().numpy().view(np.uint32), w.trace_any(arays).cpu().numpy(), st.nodes_per_ray + 0.4 * st.tris_per_ray)
         if not flags & BUILD_TWO_LEVEL:
             nodes, tris = w.download_accel()
-            assert EmuBvh(nodes=nodes, tri_records=tris).check_triangles() == 0
+            wrapped = EmuBvh(nodes=nodes, tri_records=tris)
+            assert wrapped.check_triangles() == 0 and wrapped.check_node_format() == 0
     for name in ("treelet", "treelet_explicit", "treelet2"):
         assert (res[name][1] == res["rot"][1]).all() and (res[name][2] == res["rot"][2]).all(), name
     emu = EmuBvh(tris=T, treelet_passes=2)
