@@ -56,6 +56,9 @@ __device__ __forceinline__ rt3_ray load_ray(const rt3_ray* rays, uint64_t i) {
 #ifndef RT3_TRI_BALANCE
 #define RT3_TRI_BALANCE 0
 #endif
+#ifndef RT3_TRI_REP2_MIN
+#define RT3_TRI_REP2_MIN 1
+#endif
 #ifndef RT3_NODE_COOP
 #define RT3_NODE_COOP 0
 #endif
@@ -287,7 +290,12 @@ __global__ void RT3_TRACE_BOUNDS k_trace_dyn(const WideNode* __restrict__ nodes,
 #endif
 #if RT3_TRI_REPS > 1
             for (int rep_ = 0; rep_ < RT3_TRI_REPS; ++rep_) {
+#if RT3_TRI_REP2_MIN > 1
+            /* EXPERIMENT (-DRT3_TRI_REP2_MIN=T): the second record step only when at least T lanes still hold a record */
+            if (rep_ && __popc(__ballot_sync(0xFFFFFFFFu, active && tg_hits != 0u && !found_any)) < RT3_TRI_REP2_MIN) break;
+#else
             if (rep_ && __ballot_sync(0xFFFFFFFFu, active && tg_hits != 0u && !found_any) == 0u) break;
+#endif
 #endif
             RT3_EMU_PHASE(1, active && tg_hits && !found_any);
             if (active && tg_hits && !found_any) {
