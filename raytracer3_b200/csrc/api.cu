@@ -130,6 +130,7 @@ PixelMap single_rect_map(rt3_context* c, const rt3_params* p, rt3_rect r) {
     uint64_t work = (uint64_t)m.bw * m.bh * 32u;
     if (work >= 0x7FFFFFFFull) RT3_FAIL(c, RT3_ERR_INVALID, "rect too large");
     m.work = (r.w && r.h) ? (uint32_t)work : 0u;
+    finish_pixel_map(m);
     return m;
 }
 
@@ -157,6 +158,7 @@ PixelMap tiles_map(rt3_context* c, const rt3_params* p, const rt3_rect* tiles, u
     uint64_t work = (uint64_t)n * m.bw * m.bh * 32u;
     if (work >= 0x7FFFFFFFull) RT3_FAIL(c, RT3_ERR_INVALID, "tile list too large");
     m.work = (uint32_t)work;
+    finish_pixel_map(m);
     return m;
 }
 

@@ -57,12 +57,36 @@ PixelMap full_frame(const rt3_params& p) {
     m.rects = nullptr; m.n_tiles = 1; m.tile_w = W; m.tile_h = H;
     m.bw = (W + 7) / 8; m.bh = (H + 3) / 4; m.pitch = W; m.slab = 0;
     m.work = m.bw * m.bh * 32u;
+    finish_pixel_map(m);
     return m;
 }
 
 }  // namespace
 
 extern "C" {
+
+/* fastdiv (pass_types.h) against the integer division on random and edge operands; returns the number of mismatches */
+uint32_t pemu_check_fastdiv(uint32_t tries) {
+    uint32_t bad = 0, rng = 2463534242u;
+    auto next = [&]() { rng ^= rng << 13; rng ^= rng >> 17; rng ^= rng << 5; return rng; };
+    const uint32_t edge_d[] = {1u, 2u, 3u, 5u, 7u, 8u, 240u, 255u, 256u, 257u, 65535u, 65536u, 0x7FFFFFFEu, 0x7FFFFFFFu};
+    const uint32_t edge_n[] = {0u, 1u, 2u, 0x7FFFFFFEu, 0x7FFFFFFFu - 1u, 0x40000000u, 0x3FFFFFFFu};
+    for (uint32_t d : edge_d) {
+        const FastDiv f = make_fastdiv(d);
+        for (uint32_t n : edge_n) if (fastdiv(n, f) != n / d) bad++;
+        for (uint32_t q = 0; q < 64; ++q) {                                    /* around multiples of d */
+            const unsigned long long base = (unsigned long long)(next() % (0x7FFFFFFFu / d + 1u)) * d;
+            for (long long off = -2; off <= 2; ++off) { const long long n = (long long)base + off; if (n >= 0 && n < 0x7FFFFFFFll && fastdiv((uint32_t)n, f) != (uint32_t)n / d) bad++; }
+        }
+    }
+    for (uint32_t i = 0; i < tries; ++i) {
+        uint32_t d = next() >> (next() % 31u); if (d == 0) d = 1; if (d > 0x7FFFFFFFu) d >>= 1;
+        const uint32_t n = next() & 0x7FFFFFFFu;
+        if (n == 0x7FFFFFFFu) continue;
+        if (fastdiv(n, make_fastdiv(d)) != n / d) bad++;
+    }
+    return bad;
+}
 
 /* SceneView with the per-triangle shading records the device build adds (k_shade_records, build.cu) */
 void pemu_shade_records(const void* scene_view, uint32_t n_prims, uint32_t* rec4) {

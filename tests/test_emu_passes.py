@@ -90,3 +90,11 @@ def test_strips_do_not_change_the_image(strips):
     sc = scenes.synthetic_atrium(0.02)
     sc["bluenoise"] = scenes.blue_noise_tile(64)
     _check(sc, 200, 120, types.FLAG_ENV | types.FLAG_BLUENOISE | types.FLAG_NEE, samples=2, bounces=3, strips=strips)
+
+
+def test_work_index_division_by_multiply_high_is_exact():
+    """pass_types.h fastdiv: the work-index -> pixel map of every pass kernel divides by launch constants with a multiply-high"""
+    from emu_lib import pass_lib
+    P = pass_lib()
+    P.pemu_check_fastdiv.restype = __import__("ctypes").c_uint32
+    assert P.pemu_check_fastdiv(2000000) == 0
