@@ -1,3 +1,4 @@
+# NOTE: the -DRT3_NODE96 code was removed after this measurement; it is profiles/r2ai_node96_experiment.patch
 # single-GPU A/B: 96-byte nodes fetched with three 256-bit loads (-DRT3_NODE96=1) against 80-byte nodes with five 128-bit loads
 line() { python -c "
 import sys,json

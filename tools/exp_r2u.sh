@@ -1,3 +1,4 @@
+# NOTE: the -DRT3_HALF_CVT code was removed after this measurement; it is profiles/r2u_half_cvt_experiment.patch
 # single-GPU A/Bs (round 2, session 13): resident traversal CTAs x strips (room for the shade kernels of the other strip beside a
 # persistent traversal grid), and -DRT3_HALF_CVT=1 (byte -> float conversions of the node test on the FMA pipe through FHFMA)
 line() { python -c "
